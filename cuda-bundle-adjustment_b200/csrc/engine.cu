@@ -1,0 +1,1022 @@
+// engine.cu -- host side of the B200 bundle-adjustment engine and its C ABI
+// (include/cugo_b200.h).  One Solver = one device, one stream.  The product path
+// has no CPU fallback: every numeric stage is a CUDA kernel in kernels_*.cuh.
+#include "../../include/cugo_b200.h"
+
+#include <cub/cub.cuh>
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "engine.h"
+#include "kernels_chol.cuh"
+#include "kernels_edge.cuh"
+#include "kernels_lm.cuh"
+#include "kernels_schur.cuh"
+#include "kernels_struct.cuh"
+#include "symbolic.h"
+
+namespace cugo_b200 {
+
+struct CudaError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+struct ArgError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+struct StateError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+struct UnsupportedError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            throw ::cugo_b200::CudaError(std::string(#call) + ": " + cudaGetErrorString(e_) + " (" + __FILE__ + \
+                            ":" + std::to_string(__LINE__) + ")");                                 \
+    } while (0)
+
+static inline int divUp(long long a, int b) { return (int)((a + b - 1) / b); }
+
+// grow-only device buffer
+template <typename T>
+struct DBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    ~DBuf() { if (p) cudaFree(p); }
+    T* alloc(size_t n) {
+        if (n > cap) {
+            if (p) cudaFree(p);
+            p = nullptr;
+            CK(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
+            cap = std::max<size_t>(n, 1);
+        }
+        return p;
+    }
+    operator T*() const { return p; }
+};
+
+struct HostSet {
+    int dim = 0, n = 0, nomega = 0, ncam = 0, rk = 0;
+    double delta = 1.0;
+    std::vector<int> iP, iL, out;
+    std::vector<double> meas, omega, cam;
+};
+
+struct Solver {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    // host copies of the problem
+    int nP_all = 0, nP = 0, nL_all = 0, nL = 0;
+    bool haveVertices = false;
+    std::vector<HostSet> sets;
+    bool structDirty = true, systemBuilt = false, solved = false;
+    // device state
+    Dev d{};
+    Chol c{};
+    SetParams sp{};
+    long E = 0;
+    int nmulRef = 0, nnzSymm = 0, maxRt = 0;
+    SymCounts counts{};
+    std::vector<int> h_levelPtr, h_trsmPtr, h_updPtr;
+    // buffers
+    DBuf<double> pose0, pose1, poseBak, lm0, lm1, lmBak;
+    DBuf<int> r_iP, r_iL, r_cam;
+    DBuf<double> r_m0, r_m1, r_m2, r_w, cams;
+    DBuf<uint8_t> r_set, r_out;
+    DBuf<int> s_iP, s_iL, s_cam, s_gid, s_hplPre, lmEdgePtr, chunkLm, flag, wgt, wexcl;
+    DBuf<double2> s_uv, p_uv;
+    DBuf<double> s_r, s_w, p_r, p_w;
+    DBuf<uint8_t> s_set, s_out, p_set, p_out;
+    DBuf<int> posePtr, p_iL, p_cam, p_src, pkeyIn, pkeyOut, pvalIn;
+    DBuf<int> colPtr, rowInd, hplLm, edge2Hpl;
+    DBuf<unsigned long long> keyA, keyB, valA, valB;
+    DBuf<int> ivalA, prodCnt, prodOff, head, blkOf, bRowPtr, bColInd, bRowOf, prodPtr;
+    DBuf<int2> prodIJ;
+    DBuf<double> Hpp, Hll, Hpl, b, x, invHll, bsc, Hsc, chiPartial, scalePartial, maxDiagL, maxDiagP, chiEdge;
+    DBuf<double> scalars;          // small device scratch for reductions
+    DBuf<LMState> state;
+    DBuf<uint8_t> cubTmp;
+    // symbolic
+    DBuf<int> y_adjPtr, y_adj, y_verts, y_iperm, y_mark, y_level, y_queue, y_tmp, y_stack, y_snStart, y_snParent,
+        y_colToSn, y_snRowPtr, y_snLevel, y_childHead, y_childNext, y_snRows;
+    DBuf<int> z_levelPtr, z_levelSn, z_childPtr, z_childIdx, z_invPtr, z_inv, z_snBlkPtr, z_asmBlk, z_asmRow,
+        z_asmCol, z_trsmPtr, z_updPtr;
+    DBuf<long long> z_Lptr, z_Uptr;
+    DBuf<SymCounts> y_counts;
+    DBuf<double> cL, cU, cX;
+    // graph of one trial slot
+    cudaGraph_t slotGraph = nullptr;
+    cudaGraphExec_t slotExec = nullptr;
+    int kernelsPerSlot = 0;
+    LMState* h_state = nullptr;    // pinned
+    double* h_scalars = nullptr;   // pinned
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    double lastOptimizeMs = 0.0;
+    long lastKernels = 0;
+
+    ~Solver() {
+        cudaSetDevice(device);
+        if (slotExec) cudaGraphExecDestroy(slotExec);
+        if (slotGraph) cudaGraphDestroy(slotGraph);
+        if (h_state) cudaFreeHost(h_state);
+        if (h_scalars) cudaFreeHost(h_scalars);
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+        if (stream) cudaStreamDestroy(stream);
+    }
+
+    void use() { CK(cudaSetDevice(device)); }
+    void uploadPoses(const double* poses7);
+    void setVertices(int nPa, int nPact, const double* poses7, int nLa, int nLact, const double* lms);
+    void setEstimates(const double* poses7, const double* lms);
+    int addEdgeSet(int dim, int n, const int* iP, const int* iL, const double* meas, const double* omega,
+                   int nomega, const double* cam, int ncam, int rk, double delta);
+    void refreshSetParams();
+    void buildStructure();
+    void ensureStructure() { if (structDirty) buildStructure(); }
+    void captureSlot();
+    void enqueueBuild();
+    void enqueueSolve();
+    void enqueueSlot();
+    double computeErrors();
+    void buildSystem();
+    double maxDiagonal();
+    bool solve();
+    void update();
+    double computeScale(double lambda);
+    int optimize(int niter, int cap, double* chi2, double* lambda, int* trials);
+    void getEstimates(double* poses7, double* lms);
+    long getStructure(int which, int* out, long cap);
+    long getValues(int which, double* out, long cap);
+    double stagedLambda = 0.0;
+};
+
+void Solver::uploadPoses(const double* poses7) {
+    std::vector<double> p8((size_t)nP_all * POSE_STRIDE, 0.0);
+    for (int i = 0; i < nP_all; i++)
+        for (int k = 0; k < 7; k++) p8[(size_t)i * POSE_STRIDE + k] = poses7[(size_t)i * 7 + k];
+    CK(cudaMemcpyAsync(pose0.p, p8.data(), p8.size() * sizeof(double), cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpyAsync(pose1.p, p8.data(), p8.size() * sizeof(double), cudaMemcpyHostToDevice, stream));
+    CK(cudaStreamSynchronize(stream));
+}
+
+void Solver::setVertices(int nPa, int nPact, const double* poses7, int nLa, int nLact, const double* lms) {
+    if (nPa < 0 || nLa < 0 || nPact < 0 || nLact < 0 || nPact > nPa || nLact > nLa || !poses7 || (!lms && nLa > 0))
+        throw ArgError("set_vertices: bad sizes or null pointers");
+    use();
+    if (nPa != nP_all || nPact != nP || nLa != nL_all || nLact != nL) structDirty = true;
+    nP_all = nPa; nP = nPact; nL_all = nLa; nL = nLact;
+    pose0.alloc((size_t)nP_all * POSE_STRIDE); pose1.alloc((size_t)nP_all * POSE_STRIDE);
+    poseBak.alloc((size_t)nP_all * POSE_STRIDE);
+    lm0.alloc((size_t)nL_all * 3); lm1.alloc((size_t)nL_all * 3); lmBak.alloc((size_t)nL_all * 3);
+    haveVertices = true;
+    setEstimates(poses7, lms);
+}
+
+void Solver::setEstimates(const double* poses7, const double* lms) {
+    if (!haveVertices) throw StateError("set_estimates before set_vertices");
+    use();
+    uploadPoses(poses7);
+    if (nL_all > 0) {
+        CK(cudaMemcpyAsync(lm0.p, lms, (size_t)nL_all * 3 * sizeof(double), cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(lm1.p, lms, (size_t)nL_all * 3 * sizeof(double), cudaMemcpyHostToDevice, stream));
+    }
+    state.alloc(1);
+    // estimates live in buffer 0 again
+    LMState zero{};
+    zero.nu = 2.0; zero.needBuild = 1;
+    CK(cudaMemcpyAsync(state.p, &zero, sizeof(LMState), cudaMemcpyHostToDevice, stream));
+    CK(cudaStreamSynchronize(stream));
+    d.pose[0] = pose0; d.pose[1] = pose1; d.lm[0] = lm0; d.lm[1] = lm1; d.st = state;
+    systemBuilt = false; solved = false;
+}
+
+int Solver::addEdgeSet(int dim, int n, const int* iP, const int* iL, const double* meas, const double* omega,
+                       int nomega, const double* cam, int ncam, int rk, double delta) {
+    if (!haveVertices) throw StateError("add_edge_set before set_vertices");
+    if ((dim != 2 && dim != 3) || n < 0) throw ArgError("add_edge_set: dim must be 2 or 3, n >= 0");
+    if (n > 0 && (!iP || !iL || !meas || !omega || !cam)) throw ArgError("add_edge_set: null pointer");
+    if ((nomega != 1 && nomega != n) || (ncam != 1 && ncam != n)) throw ArgError("add_edge_set: nomega/ncam must be 1 or n");
+    if (rk < 0 || rk > 3) throw ArgError("add_edge_set: unknown robust kernel");
+    if ((int)sets.size() >= MAX_SETS) throw ArgError("add_edge_set: too many edge sets");
+    for (int i = 0; i < n; i++) {
+        if (iP[i] < 0 || iP[i] >= nP_all || iL[i] < 0 || iL[i] >= nL_all) throw ArgError("add_edge_set: vertex index out of range");
+        if (iP[i] >= nP && iL[i] >= nL) throw ArgError("add_edge_set: edge with both vertices fixed is not active");
+    }
+    HostSet s;
+    s.dim = dim; s.n = n; s.nomega = nomega; s.ncam = ncam; s.rk = rk; s.delta = delta;
+    s.iP.assign(iP, iP + n); s.iL.assign(iL, iL + n);
+    s.meas.assign(meas, meas + (size_t)n * dim);
+    if (n > 0) {
+        s.omega.assign(omega, omega + nomega);
+        s.cam.assign(cam, cam + (size_t)ncam * 5);
+    } else {
+        s.omega.assign(1, 1.0);
+        s.cam.assign(5, 0.0);
+        s.nomega = s.ncam = 1;
+    }
+    sets.push_back(std::move(s));
+    structDirty = true;
+    return (int)sets.size() - 1;
+}
+
+void Solver::refreshSetParams() {
+    memset(&sp, 0, sizeof(sp));
+    for (size_t i = 0; i < sets.size(); i++) {
+        sp.dim[i] = sets[i].dim; sp.rkType[i] = sets[i].rk; sp.rkDelta[i] = sets[i].delta;
+        for (int k = 0; k < 5; k++) sp.cam[i][k] = sets[i].cam[k];
+    }
+}
+
+// ---------------------------------------------------------------------------
+// structure build: everything below is device work except size read-backs
+// ---------------------------------------------------------------------------
+template <typename K, typename V>
+static void sortPairs(Solver& S, const K* kin, K* kout, const V* vin, V* vout, int n, int endBit) {
+    size_t bytes = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, kin, kout, vin, vout, n, 0, endBit, S.stream));
+    S.cubTmp.alloc(bytes);
+    CK(cub::DeviceRadixSort::SortPairs(S.cubTmp.p, bytes, kin, kout, vin, vout, n, 0, endBit, S.stream));
+}
+static void exclusiveScan(Solver& S, const int* in, int* out, int n) {
+    size_t bytes = 0;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, bytes, in, out, n, S.stream));
+    S.cubTmp.alloc(bytes);
+    CK(cub::DeviceScan::ExclusiveSum(S.cubTmp.p, bytes, in, out, n, S.stream));
+}
+static int bitsFor(unsigned long long maxv) {
+    int b = 1;
+    while (b < 64 && (maxv >> b)) b++;
+    return b;
+}
+static int readInt(Solver& S, const int* dptr) {
+    int v = 0;
+    CK(cudaMemcpyAsync(&v, dptr, sizeof(int), cudaMemcpyDeviceToHost, S.stream));
+    CK(cudaStreamSynchronize(S.stream));
+    return v;
+}
+
+void Solver::buildStructure() {
+    if (!haveVertices) throw StateError("build_structure before set_vertices");
+    use();
+    if (nL_all == 0 || nL == 0) throw UnsupportedError("graph has no free landmarks: pose-only problems use the reference's dense LU path, outside this engine");
+    if (nP == 0) throw UnsupportedError("graph has no free poses");
+    E = 0;
+    bool perEdgeCam = false, anyOut = false;
+    for (auto& s : sets) {
+        E += s.n;
+        if (s.ncam > 1) perEdgeCam = true;
+        if (!s.out.empty()) anyOut = true;
+    }
+    if (E == 0) throw StateError("build_structure: no edges");
+    if (E > 0x7fffffff / 18) throw UnsupportedError("edge count exceeds 32-bit block indexing");
+    refreshSetParams();
+    if (slotExec) { cudaGraphExecDestroy(slotExec); slotExec = nullptr; }
+    if (slotGraph) { cudaGraphDestroy(slotGraph); slotGraph = nullptr; }
+
+    // ---- raw edge arrays (input order) -> device
+    {
+        std::vector<int> iP(E), iL(E), cam;
+        std::vector<double> m0(E), m1(E), m2(E), w(E), camTab;
+        std::vector<uint8_t> set(E), out;
+        if (perEdgeCam) { cam.resize(E); camTab.resize(sets.size() * 5); }
+        if (anyOut) out.assign(E, 0);
+        size_t o = 0;
+        for (size_t si = 0; si < sets.size(); si++) {
+            const HostSet& s = sets[si];
+            if (perEdgeCam) for (int k = 0; k < 5; k++) camTab[si * 5 + k] = s.cam[k];
+            for (int i = 0; i < s.n; i++, o++) {
+                iP[o] = s.iP[i]; iL[o] = s.iL[i];
+                m0[o] = s.meas[(size_t)i * s.dim]; m1[o] = s.meas[(size_t)i * s.dim + 1];
+                m2[o] = s.dim == 3 ? s.meas[(size_t)i * 3 + 2] : 0.0;
+                w[o] = s.nomega > 1 ? s.omega[i] : s.omega[0];
+                set[o] = (uint8_t)si;
+                if (perEdgeCam) {
+                    if (s.ncam > 1) {
+                        cam[o] = (int)(camTab.size() / 5);
+                        camTab.insert(camTab.end(), s.cam.begin() + (size_t)i * 5, s.cam.begin() + (size_t)i * 5 + 5);
+                    } else {
+                        cam[o] = (int)si;
+                    }
+                }
+                if (anyOut && !s.out.empty()) out[o] = s.out[i] ? 1 : 0;
+            }
+        }
+        auto up = [&](auto& buf, const auto& h) {
+            buf.alloc(h.size());
+            CK(cudaMemcpyAsync(buf.p, h.data(), h.size() * sizeof(h[0]), cudaMemcpyHostToDevice, stream));
+        };
+        up(r_iP, iP); up(r_iL, iL); up(r_m0, m0); up(r_m1, m1); up(r_m2, m2); up(r_w, w); up(r_set, set);
+        if (perEdgeCam) { up(r_cam, cam); up(cams, camTab); }
+        if (anyOut) up(r_out, out);
+        CK(cudaStreamSynchronize(stream));   // host vectors die here
+    }
+    RawEdges raw{(int)E, r_iP, r_iL, r_m0, r_m1, r_m2, r_w, r_set, perEdgeCam ? r_cam.p : nullptr,
+                 anyOut ? r_out.p : nullptr};
+    const int TB = 256;
+    const int gE = divUp(E, TB), gE1 = divUp(E + 1, TB);
+
+    // ---- landmark-major order
+    keyA.alloc(E); keyB.alloc(E); ivalA.alloc(E); s_gid.alloc(E);
+    k_make_lm_keys<<<gE, TB, 0, stream>>>(raw, nP_all, keyA, ivalA);
+    sortPairs(*this, keyA.p, keyB.p, ivalA.p, s_gid.p, (int)E,
+              bitsFor((unsigned long long)nL_all * (unsigned long long)nP_all));
+    s_iP.alloc(E); s_iL.alloc(E); s_uv.alloc(E); s_r.alloc(E); s_w.alloc(E); s_set.alloc(E);
+    if (perEdgeCam) s_cam.alloc(E);
+    if (anyOut) s_out.alloc(E);
+    flag.alloc(E + 1); s_hplPre.alloc(E + 1);
+    k_gather_lm<<<gE1, TB, 0, stream>>>(raw, s_gid, nP, nL, s_iP, s_iL, s_uv, s_r, s_w, s_set,
+                                        perEdgeCam ? s_cam.p : nullptr, anyOut ? s_out.p : nullptr, flag);
+    exclusiveScan(*this, flag.p, s_hplPre.p, (int)E + 1);
+    lmEdgePtr.alloc(nL_all + 1);
+    k_lower_bounds<<<divUp(nL_all + 1, TB), TB, 0, stream>>>(s_iL, (int)E, nL_all, lmEdgePtr);
+    const int nHpl = readInt(*this, s_hplPre.p + E);
+    colPtr.alloc(nL + 1); rowInd.alloc(nHpl); hplLm.alloc(nHpl); edge2Hpl.alloc(E);
+    k_fill_hpl<<<std::max(gE, divUp(nL + 1, TB)), TB, 0, stream>>>((int)E, s_iP, s_iL, s_gid, flag, s_hplPre,
+                                                                     lmEdgePtr, nL, colPtr, rowInd, hplLm, edge2Hpl);
+    // ---- CTA chunks of the landmark-major kernels
+    wgt.alloc(nL_all + 1); wexcl.alloc(nL_all + 1);
+    k_lm_weights<<<divUp(nL_all + 1, TB), TB, 0, stream>>>(lmEdgePtr, nL_all, wgt);
+    exclusiveScan(*this, wgt.p, wexcl.p, nL_all + 1);
+    const int lastW = readInt(*this, wexcl.p + nL_all - 1);
+    const int nChunks = lastW / LM_CHUNK + 1;
+    chunkLm.alloc(nChunks + 1);
+    k_chunk_bounds<<<divUp(nL_all + 1, TB), TB, 0, stream>>>(wexcl, nL_all, nChunks, chunkLm);
+
+    // ---- pose-major copy
+    pkeyIn.alloc(E); pkeyOut.alloc(E); pvalIn.alloc(E); p_src.alloc(E);
+    k_make_pose_keys<<<gE, TB, 0, stream>>>(s_iP, (int)E, pkeyIn, pvalIn);
+    sortPairs(*this, pkeyIn.p, pkeyOut.p, pvalIn.p, p_src.p, (int)E, bitsFor((unsigned long long)nP_all));
+    p_iL.alloc(E); p_uv.alloc(E); p_r.alloc(E); p_w.alloc(E); p_set.alloc(E);
+    if (perEdgeCam) p_cam.alloc(E);
+    if (anyOut) p_out.alloc(E);
+    k_gather_pose<<<gE, TB, 0, stream>>>((int)E, p_src, s_iL, s_uv, s_r, s_w, s_set, perEdgeCam ? s_cam.p : nullptr,
+                                         anyOut ? s_out.p : nullptr, p_iL, p_uv, p_r, p_w, p_set,
+                                         perEdgeCam ? p_cam.p : nullptr, anyOut ? p_out.p : nullptr);
+    posePtr.alloc(nP_all + 1);
+    k_lower_bounds<<<divUp(nP_all + 1, TB), TB, 0, stream>>>(pkeyOut, (int)E, nP_all, posePtr);
+
+    // ---- Hsc block pattern + product lists
+    prodCnt.alloc(nL + 1); prodOff.alloc(nL + 1);
+    k_prod_counts<<<divUp(nL + 1, TB), TB, 0, stream>>>(colPtr, nL, prodCnt);
+    exclusiveScan(*this, prodCnt.p, prodOff.p, nL + 1);
+    const int nmul = readInt(*this, prodOff.p + nL);
+    nmulRef = nmul;
+    const long long nmulAllLL = (long long)nmul + nP;
+    if (nmulAllLL > 0x7fffffff) throw UnsupportedError("product list exceeds 32-bit indexing");
+    const int nmulAll = (int)nmulAllLL;
+    keyA.alloc(nmulAll); keyB.alloc(nmulAll); valA.alloc(nmulAll); valB.alloc(nmulAll);
+    k_gen_products<<<divUp(std::max(nL, nP), TB), TB, 0, stream>>>(colPtr, rowInd, prodOff, nL, nP, nmul, keyA, valA);
+    sortPairs(*this, keyA.p, keyB.p, valA.p, valB.p, nmulAll, bitsFor((unsigned long long)nP * (unsigned long long)nP));
+    head.alloc(nmulAll + 1); blkOf.alloc(nmulAll + 1);
+    k_prod_heads<<<divUp(nmulAll + 1, TB), TB, 0, stream>>>(keyB, nmulAll, head);
+    exclusiveScan(*this, head.p, blkOf.p, nmulAll + 1);
+    const int nblk = readInt(*this, blkOf.p + nmulAll);
+    bRowOf.alloc(nblk); bColInd.alloc(nblk); prodPtr.alloc(nblk + 1); prodIJ.alloc(nmulAll); bRowPtr.alloc(nP + 1);
+    k_fill_blocks<<<divUp(nmulAll, TB), TB, 0, stream>>>(keyB, valB, head, blkOf, nmulAll, nP, nblk, bRowOf, bColInd,
+                                                         prodPtr, prodIJ);
+    k_lower_bounds<<<divUp(nP + 1, TB), TB, 0, stream>>>(bRowOf, nblk, nP, bRowPtr);
+    nnzSymm = (2 * nblk - nP) * 36;
+
+    // ---- symbolic factorisation (one device thread runs symbolic.h)
+    const int P = nP;
+    y_adjPtr.alloc(P + 1); y_adj.alloc(2 * (size_t)nblk + 1); y_verts.alloc(P); y_iperm.alloc(P); y_mark.alloc(P);
+    y_level.alloc(P); y_queue.alloc(P); y_tmp.alloc(P + 1); y_stack.alloc(4 * (size_t)P + 8); y_snStart.alloc(P + 1);
+    y_snParent.alloc(P); y_colToSn.alloc(P); y_snRowPtr.alloc(P + 1); y_snLevel.alloc(P); y_childHead.alloc(P);
+    y_childNext.alloc(P);
+    const long long rowsCap = sym_rows_cap(P);
+    y_snRows.alloc((size_t)rowsCap); y_counts.alloc(1);
+    SymWork w{};
+    w.P = P; w.bRowPtr = bRowPtr; w.bColInd = bColInd; w.leaf = CHOL_MAXW; w.maxw = CHOL_MAXW;
+    w.adjPtr = y_adjPtr; w.adj = y_adj; w.verts = y_verts; w.iperm = y_iperm; w.mark = y_mark; w.level = y_level;
+    w.queue = y_queue; w.tmp = y_tmp; w.stack = y_stack; w.snStart = y_snStart; w.snParent = y_snParent;
+    w.colToSn = y_colToSn; w.snRowPtr = y_snRowPtr; w.snLevel = y_snLevel; w.childHead = y_childHead;
+    w.childNext = y_childNext; w.snRows = y_snRows; w.rowsCap = rowsCap;
+    k_sym_analyze<<<1, 1, 0, stream>>>(w, y_counts);
+    CK(cudaMemcpyAsync(&counts, y_counts.p, sizeof(SymCounts), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    if (counts.err) throw CudaError("symbolic analysis overflowed its row-structure workspace");
+    const int nsn = counts.nsn;
+    z_levelPtr.alloc(counts.nlev + 1); z_levelSn.alloc(nsn); z_Lptr.alloc(nsn + 1); z_Uptr.alloc(nsn + 1);
+    z_childPtr.alloc(nsn + 1); z_childIdx.alloc(nsn + 1); z_invPtr.alloc(nsn); z_inv.alloc((size_t)counts.ninv + 1);
+    z_snBlkPtr.alloc(nsn + 1); z_asmBlk.alloc(nblk); z_asmRow.alloc(nblk); z_asmCol.alloc(nblk);
+    z_trsmPtr.alloc(nsn + 1); z_updPtr.alloc(nsn + 1);
+    SymMaps m{};
+    m.levelPtr = z_levelPtr; m.levelSn = z_levelSn; m.Lptr = z_Lptr; m.Uptr = z_Uptr; m.childPtr = z_childPtr;
+    m.childIdx = z_childIdx; m.invPtr = z_invPtr; m.inv = z_inv; m.snBlkPtr = z_snBlkPtr; m.asmBlk = z_asmBlk;
+    m.asmRow = z_asmRow; m.asmCol = z_asmCol;
+    k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, CHOL_RS, CHOL_TS);
+    h_levelPtr.resize(counts.nlev + 1); h_trsmPtr.resize(nsn + 1); h_updPtr.resize(nsn + 1);
+    CK(cudaMemcpyAsync(h_levelPtr.data(), z_levelPtr.p, sizeof(int) * (counts.nlev + 1), cudaMemcpyDeviceToHost, stream));
+    CK(cudaMemcpyAsync(h_trsmPtr.data(), z_trsmPtr.p, sizeof(int) * (nsn + 1), cudaMemcpyDeviceToHost, stream));
+    CK(cudaMemcpyAsync(h_updPtr.data(), z_updPtr.p, sizeof(int) * (nsn + 1), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    if (counts.maxCols > CHOL_MAXW) throw CudaError("internal: supernode wider than CHOL_MAXW");
+    maxRt = counts.maxFront;   // upper bound of r_t
+    cL.alloc((size_t)counts.lsize); cU.alloc((size_t)counts.usize); cX.alloc((size_t)P * 6);
+
+    // ---- system buffers
+    Hpp.alloc((size_t)nP * 36); Hll.alloc((size_t)nL * 9); Hpl.alloc((size_t)nHpl * 18);
+    b.alloc((size_t)nP * 6 + (size_t)nL * 3); x.alloc((size_t)nP * 6 + (size_t)nL * 3);
+    invHll.alloc((size_t)nL * 9); bsc.alloc((size_t)nP * 6); Hsc.alloc((size_t)nblk * 36);
+    const int errGrid = std::min(divUp(E, 256), 148 * 8);
+    chiPartial.alloc(errGrid); scalePartial.alloc(nChunks); maxDiagL.alloc(nChunks); maxDiagP.alloc(nP);
+    scalars.alloc(8);
+    CK(cudaMemsetAsync(x.p, 0, ((size_t)nP * 6 + (size_t)nL * 3) * sizeof(double), stream));
+
+    d.nP_all = nP_all; d.nP = nP; d.nL_all = nL_all; d.nL = nL; d.E = (int)E; d.nHpl = nHpl; d.nblk = nblk;
+    d.nmul = nmulAll; d.nChunks = nChunks;
+    d.s_iP = s_iP; d.s_iL = s_iL; d.s_uv = s_uv; d.s_r = s_r; d.s_w = s_w; d.s_set = s_set;
+    d.s_cam = perEdgeCam ? s_cam.p : nullptr; d.s_out = anyOut ? s_out.p : nullptr; d.s_gid = s_gid;
+    d.s_hplPre = s_hplPre; d.lmEdgePtr = lmEdgePtr; d.chunkLm = chunkLm;
+    d.posePtr = posePtr; d.p_iL = p_iL; d.p_uv = p_uv; d.p_r = p_r; d.p_w = p_w; d.p_set = p_set;
+    d.p_cam = perEdgeCam ? p_cam.p : nullptr; d.p_out = anyOut ? p_out.p : nullptr;
+    d.cams = perEdgeCam ? cams.p : nullptr;
+    d.colPtr = colPtr; d.rowInd = rowInd; d.hplLm = hplLm;
+    d.bRowPtr = bRowPtr; d.bColInd = bColInd; d.bRowOf = bRowOf; d.prodPtr = prodPtr; d.prodIJ = prodIJ;
+    d.Hpp = Hpp; d.Hll = Hll; d.Hpl = Hpl; d.b = b; d.x = x; d.invHll = invHll; d.bsc = bsc; d.Hsc = Hsc;
+    d.chiPartial = chiPartial; d.scalePartial = scalePartial; d.maxDiagL = maxDiagL; d.maxDiagP = maxDiagP;
+    d.chiEdge = nullptr; d.errGrid = errGrid;
+    d.pose[0] = pose0; d.pose[1] = pose1; d.lm[0] = lm0; d.lm[1] = lm1; d.st = state;
+
+    c.P = P; c.nsn = nsn; c.nlev = counts.nlev;
+    c.perm = y_verts; c.snStart = y_snStart; c.snRowPtr = y_snRowPtr; c.snRows = y_snRows;
+    c.levelPtr = z_levelPtr; c.levelSn = z_levelSn; c.Lptr = z_Lptr; c.Uptr = z_Uptr; c.childPtr = z_childPtr;
+    c.childIdx = z_childIdx; c.invPtr = z_invPtr; c.inv = z_inv; c.snBlkPtr = z_snBlkPtr; c.asmBlk = z_asmBlk;
+    c.asmRow = z_asmRow; c.asmCol = z_asmCol; c.trsmPtr = z_trsmPtr; c.updPtr = z_updPtr;
+    c.L = cL; c.U = cU; c.xperm = cX;
+
+    // dynamic shared memory opt-in for the factorisation kernels
+    const int ncMax = 6 * CHOL_MAXW;
+    CK(cudaFuncSetAttribute(k_chol_diag<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, ncMax * ncMax * 8));
+    CK(cudaFuncSetAttribute(k_chol_trsm<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            (ncMax * ncMax + CHOL_RS * ncMax) * 8));
+    const size_t bwdBytes = ((size_t)ncMax * ncMax + ncMax + 6 * (size_t)maxRt) * 8;
+    if (bwdBytes > 227 * 1024) throw UnsupportedError("front too large for the shared-memory backward solve of this version");
+    CK(cudaFuncSetAttribute(k_chol_bwd<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwdBytes));
+    CK(cudaStreamSynchronize(stream));
+    structDirty = false; systemBuilt = false; solved = false;
+    captureSlot();
+}
+
+// ---------------------------------------------------------------------------
+// kernel sequences
+// ---------------------------------------------------------------------------
+void Solver::enqueueBuild() {
+    k_build_lm<LM_CHUNK><<<d.nChunks, LM_CHUNK, 0, stream>>>(d, sp);
+    k_build_pose<128><<<d.nP, 128, 0, stream>>>(d, sp);
+    kernelsPerSlot += 2;
+}
+
+// Schur complement -> multifrontal Cholesky (levels up) -> backward solve (levels
+// down) -> back-substitution (+ landmark part of the update)
+void Solver::enqueueSolve() {
+    k_schur_inv<256><<<divUp(d.nL, 256), 256, 0, stream>>>(d);
+    k_schur_blocks<4><<<divUp(d.nblk, 4), 128, 0, stream>>>(d);
+    kernelsPerSlot += 2;
+    for (int lev = 0; lev < c.nlev; lev++) {
+        const int q0 = h_levelPtr[lev], q1 = h_levelPtr[lev + 1];
+        const int nsnLev = q1 - q0;
+        int ncMax = 6 * CHOL_MAXW;
+        k_chol_diag<256><<<nsnLev, 256, ncMax * ncMax * 8, stream>>>(d, c, lev);
+        const int nTrsm = h_trsmPtr[q1] - h_trsmPtr[q0];
+        k_chol_trsm<256><<<nTrsm, 256, (ncMax * ncMax + CHOL_RS * ncMax) * 8, stream>>>(d, c, lev);
+        kernelsPerSlot += 2;
+        const int nUpd = h_updPtr[q1] - h_updPtr[q0];
+        if (nUpd > 0) { k_chol_update<<<nUpd, 128, 0, stream>>>(d, c, lev); kernelsPerSlot++; }
+    }
+    const int ncMax = 6 * CHOL_MAXW;
+    const size_t bwdBytes = ((size_t)ncMax * ncMax + ncMax + 6 * (size_t)maxRt) * 8;
+    for (int lev = c.nlev - 1; lev >= 0; lev--) {
+        k_chol_bwd<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bwdBytes, stream>>>(d, c, lev);
+        kernelsPerSlot++;
+    }
+    k_backsub<LM_CHUNK><<<d.nChunks, LM_CHUNK, 0, stream>>>(d);
+    kernelsPerSlot++;
+}
+
+// one LM trial: [build] prepare solve update errors decide
+void Solver::enqueueSlot() {
+    kernelsPerSlot = 0;
+    enqueueBuild();
+    k_lm_prepare<256><<<1, 256, 0, stream>>>(d);
+    enqueueSolve();
+    k_update_poses<128><<<divUp(d.nP, 128), 128, 0, stream>>>(d);
+    k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 1, 1);
+    k_lm_decide<256><<<1, 256, 0, stream>>>(d);
+    kernelsPerSlot += 4;
+}
+
+void Solver::captureSlot() {
+    use();
+    if (!h_state) CK(cudaMallocHost(&h_state, sizeof(LMState)));
+    if (!h_scalars) CK(cudaMallocHost(&h_scalars, 8 * sizeof(double)));
+    if (!ev0) { CK(cudaEventCreate(&ev0)); CK(cudaEventCreate(&ev1)); }
+    CK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+    enqueueSlot();
+    CK(cudaStreamEndCapture(stream, &slotGraph));
+    CK(cudaGetLastError());
+    CK(cudaGraphInstantiate(&slotExec, slotGraph, 0));
+}
+
+// ---------------------------------------------------------------------------
+// staged (host-driven) API: same kernels, one BlockSolver method per call
+// ---------------------------------------------------------------------------
+static double readScalar(Solver& S, int slot) {
+    CK(cudaMemcpyAsync(S.h_scalars + slot, S.scalars.p + slot, sizeof(double), cudaMemcpyDeviceToHost, S.stream));
+    CK(cudaStreamSynchronize(S.stream));
+    CK(cudaGetLastError());
+    return S.h_scalars[slot];
+}
+
+double Solver::computeErrors() {
+    ensureStructure();
+    use();
+    k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
+    k_reduce<256><<<1, 256, 0, stream>>>(d.chiPartial, d.errGrid, nullptr, 0, 0, scalars.p);
+    return readScalar(*this, 0);
+}
+
+void Solver::buildSystem() {
+    ensureStructure();
+    use();
+    k_state_set<<<1, 1, 0, stream>>>(d.st, stagedLambda, 1);
+    enqueueBuild();
+    CK(cudaStreamSynchronize(stream));
+    CK(cudaGetLastError());
+    systemBuilt = true; solved = false;
+}
+
+double Solver::maxDiagonal() {
+    if (!systemBuilt) throw StateError("max_diagonal before build_system");
+    use();
+    k_reduce<256><<<1, 256, 0, stream>>>(d.maxDiagL, d.nChunks, d.maxDiagP, d.nP, 1, scalars.p + 1);
+    return readScalar(*this, 1);
+}
+
+bool Solver::solve() {
+    if (!systemBuilt) throw StateError("solve before build_system");
+    use();
+    k_state_set<<<1, 1, 0, stream>>>(d.st, stagedLambda, 0);
+    enqueueSolve();
+    CK(cudaMemcpyAsync(h_state, d.st, sizeof(LMState), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    CK(cudaGetLastError());
+    solved = true;
+    return h_state->fail == 0;
+}
+
+void Solver::update() {
+    if (!solved) throw StateError("update before solve");
+    use();
+    // k_backsub already wrote the trial landmarks; poses follow, then the trial buffer becomes current
+    k_update_poses<128><<<divUp(d.nP, 128), 128, 0, stream>>>(d);
+    k_state_flip<<<1, 1, 0, stream>>>(d.st);
+    CK(cudaStreamSynchronize(stream));
+    CK(cudaGetLastError());
+    solved = false;
+}
+
+double Solver::computeScale(double lambda) {
+    if (!systemBuilt) throw StateError("compute_scale before build_system");
+    use();
+    (void)lambda;   // the landmark partials were formed with the lambda of the last solve()
+    k_scale_poses<256><<<1, 256, 0, stream>>>(d, stagedLambda, scalars.p + 2);
+    return readScalar(*this, 2);
+}
+
+// ---------------------------------------------------------------------------
+// device-resident LM
+// ---------------------------------------------------------------------------
+int Solver::optimize(int niter, int cap, double* chi2, double* lambda, int* trials) {
+    ensureStructure();
+    use();
+    if (niter > MAX_STATS) throw ArgError("optimize: niterations exceeds MAX_STATS");
+    CK(cudaEventRecord(ev0, stream));
+    long launched = 0;
+    k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
+    k_lm_begin<256><<<1, 256, 0, stream>>>(d, niter);
+    launched += 2;
+    int slots = 0;
+    const int maxSlots = niter * 10 + 1;
+    int batch = niter;
+    while (niter > 0) {
+        for (int i = 0; i < batch; i++) CK(cudaGraphLaunch(slotExec, stream));
+        slots += batch;
+        launched += (long)batch * kernelsPerSlot;
+        CK(cudaMemcpyAsync(h_state, d.st, sizeof(LMState), cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        if (h_state->done || slots >= maxSlots) break;
+        batch = std::max(1, std::min(2, maxSlots - slots));   // rejected trials: top up
+    }
+    if (niter <= 0) {
+        CK(cudaMemcpyAsync(h_state, d.st, sizeof(LMState), cudaMemcpyDeviceToHost, stream));
+    }
+    CK(cudaEventRecord(ev1, stream));
+    CK(cudaStreamSynchronize(stream));
+    CK(cudaGetLastError());
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, ev0, ev1));
+    lastOptimizeMs = ms; lastKernels = launched;
+    const int n = std::min(h_state->nstats, MAX_STATS);
+    for (int i = 0; i < n && i < cap; i++) {
+        if (chi2) chi2[i] = h_state->statChi2[i];
+        if (lambda) lambda[i] = h_state->statLambda[i];
+        if (trials) trials[i] = h_state->statTrials[i];
+    }
+    systemBuilt = false; solved = false;
+    return n;
+}
+
+void Solver::getEstimates(double* poses7, double* lms) {
+    if (!haveVertices) throw StateError("get_estimates before set_vertices");
+    use();
+    LMState st;
+    CK(cudaMemcpyAsync(&st, d.st, sizeof(LMState), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    const int cur = st.cur;
+    std::vector<double> p8((size_t)nP_all * POSE_STRIDE);
+    CK(cudaMemcpyAsync(p8.data(), d.pose[cur], p8.size() * sizeof(double), cudaMemcpyDeviceToHost, stream));
+    if (lms && nL_all > 0)
+        CK(cudaMemcpyAsync(lms, d.lm[cur], (size_t)nL_all * 3 * sizeof(double), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    if (poses7)
+        for (int i = 0; i < nP_all; i++)
+            for (int k = 0; k < 7; k++) poses7[(size_t)i * 7 + k] = p8[(size_t)i * POSE_STRIDE + k];
+}
+
+static int readCur(Solver& S) {
+    LMState st;
+    CK(cudaMemcpyAsync(&st, S.d.st, sizeof(LMState), cudaMemcpyDeviceToHost, S.stream));
+    CK(cudaStreamSynchronize(S.stream));
+    return st.cur;
+}
+
+// ---------------------------------------------------------------------------
+// parity-only structure outputs in the reference's formats (built on demand)
+// ---------------------------------------------------------------------------
+// scalar CSR of the full symmetric Hsc + BSR2CSR gather map, restating
+// HschurSparseBlockMatrix::convertBSRToCSR (src/sparse_block_matrix.cpp:158-262):
+// scalar row 6R+dr = [transposes of blocks (R',R), R'<R ascending] then [row blocks
+// ascending]; BSR2CSR = 36*blk + 6*dc + dr for an entry and its mirror.
+__global__ void k_csr_counts(const int* bRowPtr, const int* bColInd, int nP, int* upCnt) {
+    // upCnt[C] = number of blocks (R, C) with R < C
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= bRowPtr[nP]) return;
+    int lo = 0, hi = nP;       // row of block k
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (bRowPtr[mid] <= k) lo = mid; else hi = mid; }
+    if (bColInd[k] != lo) atomicAdd(&upCnt[bColInd[k]], 1);
+}
+__global__ void k_csr_rowptr(const int* bRowPtr, const int* upCnt, int nP, int* blkRowCnt) {
+    const int R = blockIdx.x * blockDim.x + threadIdx.x;
+    if (R > nP) return;
+    blkRowCnt[R] = (R < nP) ? (bRowPtr[R + 1] - bRowPtr[R] + upCnt[R]) : 0;
+}
+__global__ void k_csr_fill(const int* bRowPtr, const int* bColInd, const int* bRowOf, const int* blkRowOff,
+                           const int* upCnt, int nP, int nblk, int* rowPtr, int* colInd, int* bsr2csr) {
+    // one thread per (block k, dc, dr)
+    const long long id = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (id <= 6LL * nP) {
+        const int r = (int)id;
+        if (r < 6 * nP) rowPtr[r] = 36 * blkRowOff[r / 6] + (r % 6) * 6 * (blkRowOff[r / 6 + 1] - blkRowOff[r / 6]);
+        else rowPtr[r] = 36 * blkRowOff[nP];
+    }
+    if (id >= 36LL * nblk) return;
+    const int k = (int)(id / 36), e = (int)(id % 36), dc = e / 6, dr = e % 6;
+    const int R = bRowOf[k], C = bColInd[k];
+    const int src = 36 * k + 6 * dc + dr;
+    {   // entry (6R+dr, 6C+dc): position among row R's own blocks, after its upCnt[R] mirrored blocks
+        const int nb = blkRowOff[R + 1] - blkRowOff[R];
+        const int base = 36 * blkRowOff[R] + dr * 6 * nb;
+        const int pos = upCnt[R] + (k - bRowPtr[R]);
+        colInd[base + 6 * pos + dc] = 6 * C + dc;
+        bsr2csr[base + 6 * pos + dc] = src;
+    }
+    if (R != C) {   // mirror (6C+dc, 6R+dr): rank of R among the blocks (R', C), R' < C
+        int rank = 0;
+        for (int Rp = 0; Rp < R; Rp++) {   // count rows R' < R that hold a block in column C
+            int lo = bRowPtr[Rp], hi = bRowPtr[Rp + 1];
+            while (lo < hi) { const int mid = (lo + hi) >> 1; if (bColInd[mid] < C) lo = mid + 1; else hi = mid; }
+            if (lo < bRowPtr[Rp + 1] && bColInd[lo] == C) rank++;
+        }
+        const int nb = blkRowOff[C + 1] - blkRowOff[C];
+        const int base = 36 * blkRowOff[C] + dc * 6 * nb;
+        colInd[base + 6 * rank + dr] = 6 * R + dr;
+        bsr2csr[base + 6 * rank + dr] = src;
+    }
+}
+// product list in the reference's order: (i, j, k) sorted by (i, j)
+__global__ void k_mul_keys(const int2* prodIJ, const int* blkOf, int n, unsigned long long nHpl,
+                           unsigned long long* keys, int* vals) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const int2 ij = prodIJ[p];
+    keys[p] = ij.x < 0 ? 0xffffffffffffffffULL : (unsigned long long)ij.x * nHpl + (unsigned long long)ij.y;
+    vals[p] = blkOf[p];
+}
+__global__ void k_mul_out(const unsigned long long* keys, const int* vals, int nmul, unsigned long long nHpl, int* out) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= nmul) return;
+    out[3 * p] = (int)(keys[p] / nHpl);
+    out[3 * p + 1] = (int)(keys[p] % nHpl);
+    out[3 * p + 2] = vals[p];
+}
+
+long Solver::getStructure(int which, int* out, long cap) {
+    ensureStructure();
+    use();
+    auto copyOut = [&](const int* dptr, long n) {
+        if (out && cap >= n && n > 0) {
+            CK(cudaMemcpyAsync(out, dptr, n * sizeof(int), cudaMemcpyDeviceToHost, stream));
+            CK(cudaStreamSynchronize(stream));
+        }
+        return n;
+    };
+    switch (which) {
+    case CUGO_B200_HPL_COLPTR: return copyOut(colPtr, nL + 1);
+    case CUGO_B200_HPL_ROWIND: return copyOut(rowInd, d.nHpl);
+    case CUGO_B200_HSC_ROWPTR: return copyOut(bRowPtr, nP + 1);
+    case CUGO_B200_HSC_COLIND: return copyOut(bColInd, d.nblk);
+    case CUGO_B200_EDGE2HPL: return copyOut(edge2Hpl, E);
+    case CUGO_B200_PERM: return copyOut(y_verts, nP);
+    case CUGO_B200_CSR_ROWPTR:
+    case CUGO_B200_CSR_COLIND:
+    case CUGO_B200_BSR2CSR: {
+        const long n = (which == CUGO_B200_CSR_ROWPTR) ? 6L * nP + 1 : nnzSymm;
+        if (!out || cap < n) return n;
+        DBuf<int> upCnt, rowCnt, rowOff, rp, ci, map;
+        upCnt.alloc(nP + 1); rowCnt.alloc(nP + 1); rowOff.alloc(nP + 1);
+        rp.alloc(6 * (size_t)nP + 1); ci.alloc(nnzSymm); map.alloc(nnzSymm);
+        CK(cudaMemsetAsync(upCnt.p, 0, (nP + 1) * sizeof(int), stream));
+        k_csr_counts<<<divUp(d.nblk, 256), 256, 0, stream>>>(bRowPtr, bColInd, nP, upCnt);
+        k_csr_rowptr<<<divUp(nP + 1, 256), 256, 0, stream>>>(bRowPtr, upCnt, nP, rowCnt);
+        exclusiveScan(*this, rowCnt.p, rowOff.p, nP + 1);
+        const long long work = std::max(36LL * d.nblk, 6LL * nP + 1);
+        k_csr_fill<<<divUp(work, 256), 256, 0, stream>>>(bRowPtr, bColInd, bRowOf, rowOff, upCnt, nP, d.nblk, rp, ci, map);
+        const int* src = which == CUGO_B200_CSR_ROWPTR ? rp.p : (which == CUGO_B200_CSR_COLIND ? ci.p : map.p);
+        CK(cudaMemcpyAsync(out, src, n * sizeof(int), cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        CK(cudaGetLastError());
+        return n;
+    }
+    case CUGO_B200_MULIDS: {
+        const long n = 3L * nmulRef;
+        if (!out || cap < n) return n;
+        DBuf<unsigned long long> k1, k2;
+        DBuf<int> v1, v2, o;
+        k1.alloc(d.nmul); k2.alloc(d.nmul); v1.alloc(d.nmul); v2.alloc(d.nmul); o.alloc(std::max<long>(n, 1));
+        k_mul_keys<<<divUp(d.nmul, 256), 256, 0, stream>>>(prodIJ, blkOf, d.nmul, (unsigned long long)d.nHpl, k1, v1);
+        sortPairs(*this, k1.p, k2.p, v1.p, v2.p, d.nmul, 64);
+        k_mul_out<<<divUp(std::max(nmulRef, 1), 256), 256, 0, stream>>>(k2, v2, nmulRef, (unsigned long long)d.nHpl, o);
+        CK(cudaMemcpyAsync(out, o.p, n * sizeof(int), cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        CK(cudaGetLastError());
+        return n;
+    }
+    default: throw ArgError("get_structure: unknown array id");
+    }
+}
+
+long Solver::getValues(int which, double* out, long cap) {
+    ensureStructure();
+    use();
+    const double* src = nullptr;
+    long n = 0;
+    switch (which) {
+    case CUGO_B200_HPP: src = Hpp; n = 36L * nP; break;
+    case CUGO_B200_HLL: src = Hll; n = 9L * nL; break;
+    case CUGO_B200_HPL: src = Hpl; n = 18L * d.nHpl; break;
+    case CUGO_B200_B: src = b; n = 6L * nP + 3L * nL; break;
+    case CUGO_B200_X: src = x; n = 6L * nP + 3L * nL; break;
+    case CUGO_B200_BSC: src = bsc; n = 6L * nP; break;
+    case CUGO_B200_HSC: src = Hsc; n = 36L * d.nblk; break;
+    case CUGO_B200_INVHLL: src = invHll; n = 9L * nL; break;
+    case CUGO_B200_CHI_PER_EDGE: {
+        n = E;
+        if (!out || cap < n) return n;
+        chiEdge.alloc(E);
+        CK(cudaMemsetAsync(chiEdge.p, 0, E * sizeof(double), stream));
+        Dev dd = d;
+        dd.chiEdge = chiEdge;
+        k_errors<256><<<d.errGrid, 256, 0, stream>>>(dd, sp, 0, 0);
+        src = chiEdge;
+        break;
+    }
+    default: throw ArgError("get_values: unknown array id");
+    }
+    if (out && cap >= n && n > 0) {
+        CK(cudaMemcpyAsync(out, src, n * sizeof(double), cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        CK(cudaGetLastError());
+    }
+    return n;
+}
+
+}  // namespace cugo_b200
+
+// ===========================================================================
+// C ABI (include/cugo_b200.h)
+// ===========================================================================
+using cugo_b200::Solver;
+struct cugo_b200_solver {
+    Solver impl;
+};
+
+template <typename F>
+static int guarded(cugo_b200_solver* s, F&& f) {
+    if (!s) return CUGO_B200_EINVAL;
+    try {
+        f(s->impl);
+        return CUGO_B200_OK;
+    } catch (const cugo_b200::ArgError& e) {
+        s->impl.err = e.what(); return CUGO_B200_EINVAL;
+    } catch (const cugo_b200::StateError& e) {
+        s->impl.err = e.what(); return CUGO_B200_ESTATE;
+    } catch (const cugo_b200::UnsupportedError& e) {
+        s->impl.err = e.what(); return CUGO_B200_EUNSUPPORTED;
+    } catch (const cugo_b200::CudaError& e) {
+        s->impl.err = e.what(); return CUGO_B200_ECUDA;
+    } catch (const std::exception& e) {
+        s->impl.err = e.what(); return CUGO_B200_ECUDA;
+    } catch (...) {
+        s->impl.err = "unknown error"; return CUGO_B200_ECUDA;
+    }
+}
+
+extern "C" {
+
+int cugo_b200_create(int device, int use_float32, cugo_b200_solver** out) {
+    if (!out) return CUGO_B200_EINVAL;
+    *out = nullptr;
+    if (use_float32) return CUGO_B200_EUNSUPPORTED;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return CUGO_B200_ENODEVICE; }
+    if (device < 0 || device >= ndev) return CUGO_B200_EINVAL;
+    cugo_b200_solver* s = nullptr;
+    try {
+        s = new cugo_b200_solver();
+    } catch (...) {
+        return CUGO_B200_ECUDA;
+    }
+    s->impl.device = device;
+    if (cudaSetDevice(device) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&s->impl.stream, cudaStreamNonBlocking) != cudaSuccess) {
+        cudaGetLastError();
+        delete s;
+        return CUGO_B200_ECUDA;
+    }
+    *out = s;
+    return CUGO_B200_OK;
+}
+
+int cugo_b200_destroy(cugo_b200_solver* s) {
+    if (!s) return CUGO_B200_EINVAL;
+    delete s;
+    return CUGO_B200_OK;
+}
+
+const char* cugo_b200_last_error(const cugo_b200_solver* s) { return s ? s->impl.err.c_str() : "null solver"; }
+
+int cugo_b200_set_vertices(cugo_b200_solver* s, int nP_all, int nP_active, const double* poses7, int nL_all,
+                           int nL_active, const double* landmarks3) {
+    return guarded(s, [&](Solver& S) { S.setVertices(nP_all, nP_active, poses7, nL_all, nL_active, landmarks3); });
+}
+
+int cugo_b200_clear_edge_sets(cugo_b200_solver* s) {
+    return guarded(s, [&](Solver& S) { S.sets.clear(); S.structDirty = true; });
+}
+
+int cugo_b200_add_edge_set(cugo_b200_solver* s, int dim, int n, const int* iP, const int* iL,
+                           const double* measurements, const double* omegas, int nomega, const double* cameras5,
+                           int ncam, int robust_type, double robust_delta, int* set_id) {
+    return guarded(s, [&](Solver& S) {
+        const int id = S.addEdgeSet(dim, n, iP, iL, measurements, omegas, nomega, cameras5, ncam, robust_type, robust_delta);
+        if (set_id) *set_id = id;
+    });
+}
+
+int cugo_b200_set_robust_kernel(cugo_b200_solver* s, int set_id, int robust_type, double robust_delta) {
+    return guarded(s, [&](Solver& S) {
+        if (set_id < 0 || set_id >= (int)S.sets.size()) throw cugo_b200::ArgError("set_robust_kernel: bad set id");
+        if (robust_type < 0 || robust_type > 3) throw cugo_b200::ArgError("set_robust_kernel: unknown kernel");
+        S.sets[set_id].rk = robust_type; S.sets[set_id].delta = robust_delta;
+        // kernel parameters are launch arguments: refresh them and re-capture the trial graph
+        if (!S.structDirty) {
+            S.refreshSetParams();
+            if (S.slotExec) { cudaGraphExecDestroy(S.slotExec); S.slotExec = nullptr; }
+            if (S.slotGraph) { cudaGraphDestroy(S.slotGraph); S.slotGraph = nullptr; }
+            S.captureSlot();
+        }
+    });
+}
+
+int cugo_b200_set_outliers(cugo_b200_solver* s, int set_id, const int* mask) {
+    return guarded(s, [&](Solver& S) {
+        if (set_id < 0 || set_id >= (int)S.sets.size()) throw cugo_b200::ArgError("set_outliers: bad set id");
+        auto& hs = S.sets[set_id];
+        if (mask) hs.out.assign(mask, mask + hs.n); else hs.out.clear();
+        S.structDirty = true;
+    });
+}
+
+int cugo_b200_set_estimates(cugo_b200_solver* s, const double* poses7, const double* landmarks3) {
+    return guarded(s, [&](Solver& S) {
+        if (!poses7) throw cugo_b200::ArgError("set_estimates: null poses");
+        S.setEstimates(poses7, landmarks3);
+    });
+}
+
+int cugo_b200_build_structure(cugo_b200_solver* s) {
+    return guarded(s, [&](Solver& S) { S.buildStructure(); });
+}
+
+int cugo_b200_compute_errors(cugo_b200_solver* s, double* chi2) {
+    return guarded(s, [&](Solver& S) { const double v = S.computeErrors(); if (chi2) *chi2 = v; });
+}
+int cugo_b200_build_system(cugo_b200_solver* s) {
+    return guarded(s, [&](Solver& S) { S.stagedLambda = 0.0; S.buildSystem(); });
+}
+int cugo_b200_max_diagonal(cugo_b200_solver* s, double* max_diag) {
+    return guarded(s, [&](Solver& S) { const double v = S.maxDiagonal(); if (max_diag) *max_diag = v; });
+}
+int cugo_b200_set_lambda(cugo_b200_solver* s, double lambda) {
+    return guarded(s, [&](Solver& S) { S.stagedLambda = lambda; });
+}
+int cugo_b200_restore_diagonal(cugo_b200_solver* s) {
+    return guarded(s, [&](Solver& S) { S.stagedLambda = 0.0; });
+}
+int cugo_b200_solve(cugo_b200_solver* s, int* ok) {
+    return guarded(s, [&](Solver& S) { const bool r = S.solve(); if (ok) *ok = r ? 1 : 0; });
+}
+int cugo_b200_update(cugo_b200_solver* s) {
+    return guarded(s, [&](Solver& S) { S.update(); });
+}
+int cugo_b200_compute_scale(cugo_b200_solver* s, double lambda, double* scale) {
+    return guarded(s, [&](Solver& S) { const double v = S.computeScale(lambda); if (scale) *scale = v; });
+}
+int cugo_b200_push(cugo_b200_solver* s) {
+    return guarded(s, [&](Solver& S) {
+        S.use();
+        const int cur = cugo_b200::readCur(S);
+        CK(cudaMemcpyAsync(S.poseBak.p, S.d.pose[cur], (size_t)S.nP_all * cugo_b200::POSE_STRIDE * sizeof(double),
+                           cudaMemcpyDeviceToDevice, S.stream));
+        CK(cudaMemcpyAsync(S.lmBak.p, S.d.lm[cur], (size_t)S.nL_all * 3 * sizeof(double), cudaMemcpyDeviceToDevice, S.stream));
+        CK(cudaStreamSynchronize(S.stream));
+    });
+}
+int cugo_b200_pop(cugo_b200_solver* s) {
+    return guarded(s, [&](Solver& S) {
+        S.use();
+        const int cur = cugo_b200::readCur(S);
+        CK(cudaMemcpyAsync(S.d.pose[cur], S.poseBak.p, (size_t)S.nP_all * cugo_b200::POSE_STRIDE * sizeof(double),
+                           cudaMemcpyDeviceToDevice, S.stream));
+        CK(cudaMemcpyAsync(S.d.lm[cur], S.lmBak.p, (size_t)S.nL_all * 3 * sizeof(double), cudaMemcpyDeviceToDevice, S.stream));
+        CK(cudaStreamSynchronize(S.stream));
+    });
+}
+
+int cugo_b200_optimize(cugo_b200_solver* s, int niterations, int capacity, double* chi2, double* lambda, int* trials,
+                       int* nstats) {
+    return guarded(s, [&](Solver& S) {
+        const int n = S.optimize(niterations, capacity, chi2, lambda, trials);
+        if (nstats) *nstats = n;
+    });
+}
+
+int cugo_b200_get_estimates(cugo_b200_solver* s, double* poses7, double* landmarks3) {
+    return guarded(s, [&](Solver& S) { S.getEstimates(poses7, landmarks3); });
+}
+
+int cugo_b200_get_structure(cugo_b200_solver* s, int which, int* out, long capacity, long* n) {
+    return guarded(s, [&](Solver& S) { const long r = S.getStructure(which, out, capacity); if (n) *n = r; });
+}
+int cugo_b200_get_values(cugo_b200_solver* s, int which, double* out, long capacity, long* n) {
+    return guarded(s, [&](Solver& S) { const long r = S.getValues(which, out, capacity); if (n) *n = r; });
+}
+int cugo_b200_get_sizes(cugo_b200_solver* s, long sizes[10]) {
+    return guarded(s, [&](Solver& S) {
+        S.ensureStructure();
+        sizes[0] = S.nP; sizes[1] = S.nL; sizes[2] = S.E; sizes[3] = S.d.nHpl; sizes[4] = S.d.nblk;
+        sizes[5] = S.nmulRef; sizes[6] = S.nnzSymm; sizes[7] = S.counts.nsn; sizes[8] = S.counts.nlev;
+        sizes[9] = S.kernelsPerSlot;
+    });
+}
+int cugo_b200_get_last_timing(cugo_b200_solver* s, double* optimize_ms, long* kernels_launched) {
+    return guarded(s, [&](Solver& S) {
+        if (optimize_ms) *optimize_ms = S.lastOptimizeMs;
+        if (kernels_launched) *kernels_launched = S.lastKernels;
+    });
+}
+void* cugo_b200_stream(cugo_b200_solver* s) { return s ? (void*)s->impl.stream : nullptr; }
+
+}  // extern "C"

@@ -1,0 +1,126 @@
+// engine.h -- device-side data layout of the B200 bundle-adjustment engine.
+// All arrays live in HBM for the lifetime of a structure; kernels take one
+// `Dev` struct of raw pointers by value.  See DESIGN.md section 3 for the layout.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cugo_b200 {
+
+constexpr int MAX_SETS = 8;
+constexpr int MAX_STATS = 256;     // outer LM iterations recorded per optimize()
+constexpr int LM_CHUNK = 128;      // landmark-major kernels: edges per CTA (nominal)
+constexpr int POSE_STRIDE = 8;     // poses are padded 7 -> 8 doubles (16 B vector loads)
+
+// per edge set parameters (reference: one EdgeSet object each, include/ba_types.h)
+struct SetParams {
+    int dim[MAX_SETS];        // 2 mono / 3 stereo
+    int rkType[MAX_SETS];
+    double rkDelta[MAX_SETS];
+    double cam[MAX_SETS][5];  // shared camera of the set (used when the set has no per-edge cameras)
+};
+
+// Device-resident Levenberg-Marquardt state (reference keeps these on the host:
+// src/cuda_graph_optimisation.cpp:48-154)
+struct LMState {
+    double lambda, nu, F, Fhat, rho, scale, maxDiag;
+    int iter;        // outer iteration index
+    int q;           // trial index inside the outer iteration
+    int cur;         // which estimate buffer holds the accepted estimates
+    int done;        // optimisation finished
+    int needBuild;   // linear system must be rebuilt from est[cur]
+    int fail;        // factorisation hit a non-positive pivot in this trial
+    int niter;       // requested outer iterations
+    int nstats;
+    int slots;       // trial slots executed (diagnostics)
+    int pad;
+    double statChi2[MAX_STATS];
+    double statLambda[MAX_STATS];
+    int statTrials[MAX_STATS];
+};
+
+struct Dev {
+    // sizes
+    int nP_all, nP, nL_all, nL, E, nHpl, nblk, nmul, nChunks;
+    // estimates, double buffered: pose [nP_all*8], landmark [nL_all*3]
+    double* pose[2];
+    double* lm[2];
+    // edges in landmark-major order (sorted by (iL, iP)): SoA
+    const int* s_iP;
+    const int* s_iL;
+    const double2* s_uv;
+    const double* s_r;          // stereo third measurement (0 for mono)
+    const double* s_w;          // information (omega) per edge
+    const uint8_t* s_set;       // edge set id
+    const int* s_cam;           // per-edge camera index or nullptr
+    const uint8_t* s_out;       // outlier mask or nullptr
+    const int* s_gid;           // global edge id (set-major input order)
+    const int* s_hplPre;        // [E+1] exclusive prefix of "has Hpl block" flags
+    const int* lmEdgePtr;       // [nL_all+1]
+    const int* chunkLm;         // [nChunks+1] landmark ranges of the landmark-major CTAs
+    // the same edges in pose-major order (sorted by iP, then landmark)
+    const int* posePtr;         // [nP_all+1]
+    const int* p_iL;
+    const double2* p_uv;
+    const double* p_r;
+    const double* p_w;
+    const uint8_t* p_set;
+    const int* p_cam;
+    const uint8_t* p_out;
+    const double* cams;         // [ncams][5] per-edge camera table (or nullptr)
+    // Hpl CSC (reference: gpu::buildHplStructure)
+    const int* colPtr;          // [nL+1]
+    const int* rowInd;          // [nHpl]
+    const int* hplLm;           // [nHpl] landmark of each block
+    // Hsc upper BSR + product lists grouped by destination block
+    const int* bRowPtr;         // [nP+1]
+    const int* bColInd;         // [nblk]
+    const int* bRowOf;          // [nblk]
+    const int* prodPtr;         // [nblk+1]
+    const int2* prodIJ;         // [nmul] (Hpl slot of row pose, Hpl slot of col pose); x<0 = none
+    // linear system
+    double* Hpp;                // [36 nP]
+    double* Hll;                // [9 nL]
+    double* Hpl;                // [18 nHpl]
+    double* b;                  // [6 nP + 3 nL]
+    double* x;                  // [6 nP + 3 nL]
+    double* invHll;             // [9 nL]
+    double* bsc;                // [6 nP]
+    double* Hsc;                // [36 nblk]
+    // reductions
+    double* chiPartial;         // [errGrid]
+    double* scalePartial;       // [nChunks]
+    double* maxDiagL;           // [nChunks]
+    double* maxDiagP;           // [nP]
+    double* chiEdge;            // [E] per-edge rho(chi2) in global edge order, or nullptr
+    int errGrid;
+    LMState* st;
+};
+
+// multifrontal factorisation data (see symbolic.h)
+struct Chol {
+    int P, nsn, nlev;
+    const int* perm;       // new -> old
+    const int* snStart;
+    const int* snRowPtr;
+    const int* snRows;
+    const int* levelPtr;
+    const int* levelSn;
+    const long long* Lptr;
+    const long long* Uptr;
+    const int* childPtr;
+    const int* childIdx;
+    const int* invPtr;
+    const int* inv;
+    const int* snBlkPtr;
+    const int* asmBlk;
+    const int* asmRow;
+    const int* asmCol;
+    const int* trsmPtr;    // [nsn+1] prefix of row-slab tasks in levelSn order
+    const int* updPtr;     // [nsn+1] prefix of update-tile tasks in levelSn order
+    double* L;
+    double* U;
+    double* xperm;         // [6P] solution in permuted order
+};
+
+}  // namespace cugo_b200

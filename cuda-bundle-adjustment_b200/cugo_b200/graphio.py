@@ -1,5 +1,5 @@
 """Binary graph file ("BAG1") shared by the Python harness and the C++ programs
-(oracle/ref_driver.cpp, the facade sample).  It carries exactly the fields of the
+(the reference driver used by the parity tests, the facade sample).  It carries exactly the fields of the
 reference's JSON schema (samples/sample_ba_from_file/main.cpp:88-160) as raw
 little-endian arrays:
 

@@ -27,7 +27,7 @@ SHAPES = {
     "small": (40, 600, 2600, 1600, 7101, 0),
     "loop": (300, 4000, 18000, 6000, 7102, 150),
     "kitti07": (248, 26127, 95037, 0, 7001, 0),
-    "kitti00": (1332, 133383, 561116, 336672, 7000, 400),
+    "kitti00": (1332, 133383, 561116, 336672, 7000, 900),
     "venice": (1778, 993923, 5001946, 0, 7003, 0),
 }
 

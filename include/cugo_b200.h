@@ -1,0 +1,130 @@
+/*
+ * cugo_b200.h -- C ABI of the B200-native bundle-adjustment engine.
+ *
+ * This is the drop-in boundary for the reference's hot path: the seam between
+ * cugo::BlockSolver (src/block_solver.h:46-173) and the free functions of
+ * namespace cugo::gpu (src/cuda/cuda_block_solver.h:55-256).  Every entry point
+ * names the reference interface it replaces.  Plain pointers and sizes only; all
+ * pointers are HOST pointers unless stated; every function returns 0 on success
+ * or a negative CUGO_B200_E* code (cugo_b200_last_error() gives the text).  The
+ * library never throws across this boundary and has no CPU fallback: without a
+ * CUDA device cugo_b200_create() fails with CUGO_B200_ENODEVICE.
+ *
+ * Data contract (same as the reference):
+ *   pose      7 doubles  qx qy qz qw tx ty tz   (world -> camera, Se3D src/fixed_vector.h:393-471)
+ *   landmark  3 doubles
+ *   vertices are passed in INDEX order: non-fixed first (0..active-1), then fixed
+ *             (VertexSet::generateEstimateData, src/optimisable_graph.hpp:84-126)
+ *   edge      (iP, iL) vertex indices, measurement (2 mono / 3 stereo doubles),
+ *             information omega (per edge or one per set), camera fx fy cx cy bf
+ *             (per edge or one per set)  -- EdgeSet::init, src/optimisable_graph.hpp:474-572
+ *   blocks    column-major, full: Hpp 6x6, Hll 3x3, Hpl 6x3; x = [xp (6P) | xl (3L)]
+ */
+#ifndef CUGO_B200_H
+#define CUGO_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cugo_b200_solver cugo_b200_solver;
+
+enum {
+    CUGO_B200_OK = 0,
+    CUGO_B200_EINVAL = -1,      /* bad argument */
+    CUGO_B200_ENODEVICE = -2,   /* no usable CUDA device (there is no CPU path) */
+    CUGO_B200_ECUDA = -3,       /* CUDA runtime error */
+    CUGO_B200_ESTATE = -4,      /* call order violated (e.g. solve before build_system) */
+    CUGO_B200_EUNSUPPORTED = -5 /* outside the hot path (e.g. pose-only graph: reference DenseLinearSolver) */
+};
+
+/* robust kernels: reference RobustKernelType {None, Cauchy, Tukey} (src/robust_kernel.h:12-17);
+ * Huber (g2o RobustKernelHuber) is added because BASELINE.json's configs name it. */
+enum { CUGO_B200_RK_NONE = 0, CUGO_B200_RK_CAUCHY = 1, CUGO_B200_RK_TUKEY = 2, CUGO_B200_RK_HUBER = 3 };
+
+/* structure arrays readable through cugo_b200_get_structure (int32) */
+enum {
+    CUGO_B200_HPL_COLPTR = 0, /* [L+1]   d_Hpl_.outerIndices   gpu::buildHplStructure cuda_block_solver.cu:1571-1604 */
+    CUGO_B200_HPL_ROWIND = 1, /* [nHpl]  d_Hpl_.innerIndices */
+    CUGO_B200_HSC_ROWPTR = 2, /* [P+1]   Hsc_.outerIndices     sparse_block_matrix.cpp:63-156 */
+    CUGO_B200_HSC_COLIND = 3, /* [nblk]  Hsc_.innerIndices */
+    CUGO_B200_CSR_ROWPTR = 4, /* [6P+1]  Hsc_.rowPtr()         sparse_block_matrix.cpp:158-262 */
+    CUGO_B200_CSR_COLIND = 5, /* [nnzSymm] Hsc_.colInd() */
+    CUGO_B200_BSR2CSR = 6,    /* [nnzSymm] Hsc_.BSR2CSR() */
+    CUGO_B200_MULIDS = 7,     /* [3 nmul] d_HscMulBlockIds_, sorted by (i,j)  cuda_block_solver.cu:1606-1634 */
+    CUGO_B200_EDGE2HPL = 8,   /* [E] d_edge2Hpl_ in input edge order (-1: no block) */
+    CUGO_B200_PERM = 9        /* [P] fill-reducing block ordering, new -> old (ours; the reference's is METIS) */
+};
+
+/* value arrays readable through cugo_b200_get_values (double) */
+enum {
+    CUGO_B200_HPP = 0, CUGO_B200_HLL = 1, CUGO_B200_HPL = 2, CUGO_B200_B = 3, CUGO_B200_X = 4,
+    CUGO_B200_BSC = 5, CUGO_B200_HSC = 6, CUGO_B200_INVHLL = 7, CUGO_B200_CHI_PER_EDGE = 8
+};
+
+/* -- lifetime: replaces CudaDevice (src/cuda_device.cpp:15-42) + BlockSolver ctor. `device` is the
+ * CUDA ordinal chosen by the caller (one solver = one device + one stream). use_float32 must be 0
+ * in this version (the reference's USE_FLOAT32 build does not compile). */
+int cugo_b200_create(int device, int use_float32, cugo_b200_solver** out);
+int cugo_b200_destroy(cugo_b200_solver* s);
+const char* cugo_b200_last_error(const cugo_b200_solver* s);
+
+/* -- BlockSolver::initialize (src/block_solver.cpp:21-137): vertices ... */
+int cugo_b200_set_vertices(cugo_b200_solver* s, int nP_all, int nP_active, const double* poses7,
+                           int nL_all, int nL_active, const double* landmarks3);
+/* ... and edge sets (EdgeSet::init / mapDevice, src/optimisable_graph.hpp:474-601).  dim: 2 =
+ * MonoEdgeSet, 3 = StereoEdgeSet (include/ba_types.h:34-169).  nomega / ncam are 1 or n.  Only
+ * active edges (not both endpoints fixed) may be passed.  Returns the set id in *set_id. */
+int cugo_b200_clear_edge_sets(cugo_b200_solver* s);
+int cugo_b200_add_edge_set(cugo_b200_solver* s, int dim, int n, const int* iP, const int* iL,
+                           const double* measurements, const double* omegas, int nomega,
+                           const double* cameras5, int ncam, int robust_type, double robust_delta,
+                           int* set_id);
+/* EdgeSet::setRobustKernel (src/optimisable_graph.hpp:401-406); per set here, process-global there */
+int cugo_b200_set_robust_kernel(cugo_b200_solver* s, int set_id, int robust_type, double robust_delta);
+/* outlier mask of a set (reference d_outliers, computeOutliersKernel cuda_block_solver.cu:1135-1149);
+ * changing it invalidates the structure */
+int cugo_b200_set_outliers(cugo_b200_solver* s, int set_id, const int* mask);
+/* re-upload estimates only (a second initialize() on an unchanged graph keeps the structure,
+ * src/block_solver.cpp:161-170) */
+int cugo_b200_set_estimates(cugo_b200_solver* s, const double* poses7, const double* landmarks3);
+
+/* -- BlockSolver::buildStructure (src/block_solver.cpp:139-248) incl. symbolic analysis */
+int cugo_b200_build_structure(cugo_b200_solver* s);
+
+/* -- stage API, one call per BlockSolver method (src/block_solver.h:54-173) */
+int cugo_b200_compute_errors(cugo_b200_solver* s, double* chi2);              /* computeErrors   :250-272 */
+int cugo_b200_build_system(cugo_b200_solver* s);                              /* buildSystem     :274-307 */
+int cugo_b200_max_diagonal(cugo_b200_solver* s, double* max_diag);            /* maxDiagonal     :309-320 */
+int cugo_b200_set_lambda(cugo_b200_solver* s, double lambda);                 /* setLambda       :322-329 */
+int cugo_b200_restore_diagonal(cugo_b200_solver* s);                          /* restoreDiagonal :331-338 */
+int cugo_b200_solve(cugo_b200_solver* s, int* ok);                            /* solve           :340-388 */
+int cugo_b200_update(cugo_b200_solver* s);                                    /* update          :390-413 */
+int cugo_b200_compute_scale(cugo_b200_solver* s, double lambda, double* scale); /* computeScale  :415-421 */
+int cugo_b200_push(cugo_b200_solver* s);                                      /* push            :431-434 */
+int cugo_b200_pop(cugo_b200_solver* s);                                       /* pop             :436-439 */
+
+/* -- CudaGraphOptimisationImpl::optimize (src/cuda_graph_optimisation.cpp:48-154) with the LM
+ * control on the device.  chi2 / lambda / trials receive one entry per outer iteration
+ * (BatchStatistics semantics: chi2 after that iteration); capacity entries each (may be NULL). */
+int cugo_b200_optimize(cugo_b200_solver* s, int niterations, int capacity, double* chi2,
+                       double* lambda, int* trials, int* nstats);
+
+/* -- BlockSolver::finalize / VertexSet::finalise (src/optimisable_graph.hpp:137-154) */
+int cugo_b200_get_estimates(cugo_b200_solver* s, double* poses7, double* landmarks3);
+
+/* -- introspection for parity tests */
+int cugo_b200_get_structure(cugo_b200_solver* s, int which, int* out, long capacity, long* n);
+int cugo_b200_get_values(cugo_b200_solver* s, int which, double* out, long capacity, long* n);
+/* sizes: P_active L_active E nHpl nblk nmul nnzSymm nsupernodes nlevels kernels_per_trial */
+int cugo_b200_get_sizes(cugo_b200_solver* s, long sizes[10]);
+/* device time of the last optimize() in ms (CUDA events on the solver's stream) and the number of
+ * kernels it launched */
+int cugo_b200_get_last_timing(cugo_b200_solver* s, double* optimize_ms, long* kernels_launched);
+/* the solver's CUDA stream (cudaStream_t) for callers that time or chain work on it */
+void* cugo_b200_stream(cugo_b200_solver* s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CUGO_B200_H */
