@@ -716,13 +716,13 @@ __global__ void k_csr_fill(const int* bRowPtr, const int* bColInd, const int* bR
     }
 }
 // product list in the reference's order: (i, j, k) sorted by (i, j)
-__global__ void k_mul_keys(const int2* prodIJ, const int* blkOf, int n, unsigned long long nHpl,
+__global__ void k_mul_keys(const int2* prodIJ, const int* blkOf, const int* head, int n, unsigned long long nHpl,
                            unsigned long long* keys, int* vals) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     const int2 ij = prodIJ[p];
     keys[p] = ij.x < 0 ? 0xffffffffffffffffULL : (unsigned long long)ij.x * nHpl + (unsigned long long)ij.y;
-    vals[p] = blkOf[p];
+    vals[p] = blkOf[p] + head[p] - 1;   // blkOf is the exclusive scan of the head flags
 }
 __global__ void k_mul_out(const unsigned long long* keys, const int* vals, int nmul, unsigned long long nHpl, int* out) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -775,7 +775,7 @@ long Solver::getStructure(int which, int* out, long cap) {
         DBuf<unsigned long long> k1, k2;
         DBuf<int> v1, v2, o;
         k1.alloc(d.nmul); k2.alloc(d.nmul); v1.alloc(d.nmul); v2.alloc(d.nmul); o.alloc(std::max<long>(n, 1));
-        k_mul_keys<<<divUp(d.nmul, 256), 256, 0, stream>>>(prodIJ, blkOf, d.nmul, (unsigned long long)d.nHpl, k1, v1);
+        k_mul_keys<<<divUp(d.nmul, 256), 256, 0, stream>>>(prodIJ, blkOf, head, d.nmul, (unsigned long long)d.nHpl, k1, v1);
         sortPairs(*this, k1.p, k2.p, v1.p, v2.p, d.nmul, 64);
         k_mul_out<<<divUp(std::max(nmulRef, 1), 256), 256, 0, stream>>>(k2, v2, nmulRef, (unsigned long long)d.nHpl, o);
         CK(cudaMemcpyAsync(out, o.p, n * sizeof(int), cudaMemcpyDeviceToHost, stream));

@@ -1,0 +1,115 @@
+"""Comparison of a solver-like object (the oracle or the CUDA engine) with the reference goldens."""
+import hashlib
+import json
+import os
+
+import numpy as np
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+RK_NAMES = {0: "none", 1: "cauchy", 2: "tukey"}
+CASES = ["tiny", "small", "small_cauchy", "small_tukey", "small_fixedlm", "loop", "kitti07", "kitti00"]
+
+
+def load(case):
+    meta = json.load(open(os.path.join(GOLDEN_DIR, "ref_%s.json" % case)))
+    arrays = dict(np.load(os.path.join(GOLDEN_DIR, "ref_%s.npz" % case)))
+    return meta, arrays
+
+
+def problem_of(meta):
+    from cugo_b200 import pack, synth
+    g = synth.make_graph(meta["generator"]["name"], **meta["generator"]["kwargs"])
+    return g, pack.pack(g)
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def relerr(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+def check_int(meta, arrays, name, ours):
+    """bit-exact: against the full array when stored, else against its sha256."""
+    assert ours.size == meta["arrays"][name]["n"], name
+    if name in arrays:
+        np.testing.assert_array_equal(ours, arrays[name], err_msg=name)
+    assert sha(ours.astype(np.int32)) == meta["arrays"][name]["sha256"], name
+
+
+def check_f64(meta, arrays, name, ours, rtol):
+    assert ours.size == meta["arrays"][name]["n"], name
+    ref = arrays[name] if name in arrays else arrays[name + "_sub"]
+    mine = ours if name in arrays else ours[::97]
+    e = relerr(mine, ref)
+    assert e < rtol, "%s: relative error %.3e >= %.1e" % (name, e, rtol)
+    return e
+
+
+def check_edge2hpl(meta, arrays, prob, ours):
+    """The reference numbers its edges in unordered_set (pointer-hash) order, so edge2Hpl is
+    compared through the (pose, landmark) key."""
+    if "edge2hpl" not in arrays:
+        return
+    ref_pl = np.concatenate([arrays["mono_edge2pl"].reshape(-1, 2), arrays["stereo_edge2pl"].reshape(-1, 2)])
+    ref = {(int(p), int(l)): int(s) for (p, l), s in zip(ref_pl, arrays["edge2hpl"])}
+    k = 0
+    for s in prob.sets:
+        for i in range(s.n):
+            key = (int(s.iP[i]), int(s.iL[i]))
+            if ours[k] >= 0:
+                assert ref[key] == ours[k], key
+            k += 1
+    assert k == len(ref)
+
+
+def check_all(case, make_solver, value_rtol=1e-9, x_rtol=1e-7, chi_rtol=1e-9):
+    """make_solver(prob, robust, delta) -> object with the staged API + optimize + estimates."""
+    from cugo_b200 import pack
+    meta, arrays = load(case)
+    g, prob = problem_of(meta)
+    rk, delta = RK_NAMES[meta["rk_type"]], meta["rk_delta"]
+    s = make_solver(prob, rk, delta)
+    s.build_structure()
+    for name in ("hpl_colptr", "hpl_rowind", "hsc_rowptr", "hsc_colind", "csr_rowptr", "csr_colind", "bsr2csr",
+                 "mulids"):
+        check_int(meta, arrays, name, s.structure(name))
+    check_edge2hpl(meta, arrays, prob, s.structure("edge2hpl"))
+    st = meta["stage"]
+    F0 = s.compute_errors()
+    assert abs(F0 - st["F0"]) <= chi_rtol * st["F0"]
+    s.build_system()
+    report = {}
+    for name in ("Hpp", "Hll", "Hpl", "b"):
+        report[name] = check_f64(meta, arrays, name, s.values(name), value_rtol)
+    md = s.max_diagonal()
+    assert abs(md - st["maxDiag"]) <= 1e-12 * st["maxDiag"]
+    s.push()
+    s.set_lambda(st["lambda"])
+    assert s.solve() == bool(st["solve_ok"])
+    for name in ("bsc", "Hsc"):
+        report[name] = check_f64(meta, arrays, name, s.values(name), value_rtol)
+    report["x"] = check_f64(meta, arrays, "x", s.values("x"), x_rtol)
+    scale = s.compute_scale(st["lambda"])
+    assert abs(scale - st["scale"]) <= 1e-7 * abs(st["scale"])
+    s.update()
+    poses, lms = s.estimates()
+    report["updated_estimates"] = check_f64(meta, arrays, "updated_estimates",
+                                            np.concatenate([poses.reshape(-1), lms.reshape(-1)]), 1e-9)
+    F1 = s.compute_errors()
+    assert abs(F1 - st["F1"]) <= chi_rtol * st["F1"]
+    # full LM run from the original estimates
+    s2 = make_solver(prob, rk, delta)
+    chi2, lam, trials = s2.optimize(meta["niter"])
+    ref_chi2 = np.array(meta["chi2"])
+    assert len(chi2) == len(ref_chi2)
+    report["chi2"] = float(np.max(np.abs(chi2 - ref_chi2) / ref_chi2))
+    assert report["chi2"] <= chi_rtol, "chi2 trajectory relative error %.3e" % report["chi2"]
+    poses, lms = s2.estimates()
+    q, t, X = pack.unpack_estimates(prob, poses, lms)
+    fin = np.concatenate([np.concatenate([q, t], 1).reshape(-1), X.reshape(-1)])
+    ref = arrays["final_estimates"] if "final_estimates" in arrays else arrays["final_estimates_sub"]
+    mine = fin if "final_estimates" in arrays else fin[::97]
+    report["final_rmse"] = float(np.sqrt(np.mean((mine - ref) ** 2)))
+    return report

@@ -172,3 +172,19 @@ def test_full_size_properties(graphs, gpu):
     np.testing.assert_array_equal(chi_g, chi_2)
     chi_o, _, tr_o = o.optimize(10)
     np.testing.assert_allclose(chi_g, chi_o, rtol=CHI2_RTOL)
+
+
+@pytest.mark.parametrize("case", ["tiny", "small", "small_cauchy", "small_tukey", "small_fixedlm", "loop", "kitti07",
+                                  "kitti00"])
+def test_engine_matches_reference_goldens(case):
+    """The CUDA engine against the dumps of the unmodified reference library (tests/golden):
+    structure bit-exact, chi2 per iteration within 1e-9 relative, final estimates RMSE <= 1e-10."""
+    import golden_util
+    from cugo_b200 import solver
+
+    def make(prob, rk, delta):
+        s = solver.BlockSolver(0)
+        s.initialize(prob, robust=rk, delta=delta)
+        return s
+    rep = golden_util.check_all(case, make)
+    assert rep["final_rmse"] <= EST_ATOL, rep
