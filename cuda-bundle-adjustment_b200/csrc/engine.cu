@@ -118,6 +118,22 @@ struct Solver {
     cudaGraph_t slotGraph = nullptr;
     cudaGraphExec_t slotExec = nullptr;
     int kernelsPerSlot = 0;
+    // per-kernel profiling of one trial slot (events on the launching stream)
+    bool profiling = false;
+    std::vector<cudaEvent_t> profEvents;
+    std::vector<std::string> profNames;
+    void mark(const char* name) {
+        kernelsPerSlot++;
+        if (!profiling) return;
+        cudaEvent_t e;
+        CK(cudaEventCreate(&e));
+        CK(cudaEventRecord(e, stream));
+        profEvents.push_back(e);
+        profNames.push_back(name);
+    }
+    int profileSlot(int cap, char* names, int nameLen, double* ms);
+    void updateMeasurements(int setId, const double* meas, const double* omega, int nomega);
+    bool perEdgeCam_ = false, anyOut_ = false;
     LMState* h_state = nullptr;    // pinned
     double* h_scalars = nullptr;   // pinned
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -280,6 +296,7 @@ void Solver::buildStructure() {
     }
     if (E == 0) throw StateError("build_structure: no edges");
     if (E > 0x7fffffff / 18) throw UnsupportedError("edge count exceeds 32-bit block indexing");
+    perEdgeCam_ = perEdgeCam; anyOut_ = anyOut;
     refreshSetParams();
     if (slotExec) { cudaGraphExecDestroy(slotExec); slotExec = nullptr; }
     if (slotGraph) { cudaGraphDestroy(slotGraph); slotGraph = nullptr; }
@@ -473,48 +490,118 @@ void Solver::buildStructure() {
 // kernel sequences
 // ---------------------------------------------------------------------------
 void Solver::enqueueBuild() {
-    k_build_lm<LM_CHUNK><<<d.nChunks, LM_CHUNK, 0, stream>>>(d, sp);
-    k_build_pose<128><<<d.nP, 128, 0, stream>>>(d, sp);
-    kernelsPerSlot += 2;
+    k_build_lm<LM_CHUNK><<<d.nChunks, LM_CHUNK, 0, stream>>>(d, sp); mark("build_lm");
+    k_build_pose<128><<<d.nP, 128, 0, stream>>>(d, sp); mark("build_pose");
 }
 
 // Schur complement -> multifrontal Cholesky (levels up) -> backward solve (levels
 // down) -> back-substitution (+ landmark part of the update)
 void Solver::enqueueSolve() {
-    k_schur_inv<256><<<divUp(d.nL, 256), 256, 0, stream>>>(d);
-    k_schur_blocks<4><<<divUp(d.nblk, 4), 128, 0, stream>>>(d);
-    kernelsPerSlot += 2;
+    k_schur_inv<256><<<divUp(d.nL, 256), 256, 0, stream>>>(d); mark("schur_inv");
+    k_schur_blocks<4><<<divUp(d.nblk, 4), 128, 0, stream>>>(d); mark("schur_blocks");
+    const int ncMax = 6 * CHOL_MAXW;
     for (int lev = 0; lev < c.nlev; lev++) {
         const int q0 = h_levelPtr[lev], q1 = h_levelPtr[lev + 1];
-        const int nsnLev = q1 - q0;
-        int ncMax = 6 * CHOL_MAXW;
-        k_chol_diag<256><<<nsnLev, 256, ncMax * ncMax * 8, stream>>>(d, c, lev);
+        k_chol_diag<256><<<q1 - q0, 256, ncMax * ncMax * 8, stream>>>(d, c, lev); mark("chol_diag");
         const int nTrsm = h_trsmPtr[q1] - h_trsmPtr[q0];
-        k_chol_trsm<256><<<nTrsm, 256, (ncMax * ncMax + CHOL_RS * ncMax) * 8, stream>>>(d, c, lev);
-        kernelsPerSlot += 2;
+        k_chol_trsm<256><<<nTrsm, 256, (ncMax * ncMax + CHOL_RS * ncMax) * 8, stream>>>(d, c, lev); mark("chol_trsm");
         const int nUpd = h_updPtr[q1] - h_updPtr[q0];
-        if (nUpd > 0) { k_chol_update<<<nUpd, 128, 0, stream>>>(d, c, lev); kernelsPerSlot++; }
+        if (nUpd > 0) { k_chol_update<<<nUpd, 128, 0, stream>>>(d, c, lev); mark("chol_update"); }
     }
-    const int ncMax = 6 * CHOL_MAXW;
     const size_t bwdBytes = ((size_t)ncMax * ncMax + ncMax + 6 * (size_t)maxRt) * 8;
     for (int lev = c.nlev - 1; lev >= 0; lev--) {
-        k_chol_bwd<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bwdBytes, stream>>>(d, c, lev);
-        kernelsPerSlot++;
+        k_chol_bwd<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bwdBytes, stream>>>(d, c, lev); mark("chol_bwd");
     }
-    k_backsub<LM_CHUNK><<<d.nChunks, LM_CHUNK, 0, stream>>>(d);
-    kernelsPerSlot++;
+    k_backsub<LM_CHUNK><<<d.nChunks, LM_CHUNK, 0, stream>>>(d); mark("backsub");
 }
 
 // one LM trial: [build] prepare solve update errors decide
 void Solver::enqueueSlot() {
     kernelsPerSlot = 0;
     enqueueBuild();
-    k_lm_prepare<256><<<1, 256, 0, stream>>>(d);
+    k_lm_prepare<256><<<1, 256, 0, stream>>>(d); mark("lm_prepare");
     enqueueSolve();
-    k_update_poses<128><<<divUp(d.nP, 128), 128, 0, stream>>>(d);
-    k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 1, 1);
-    k_lm_decide<256><<<1, 256, 0, stream>>>(d);
-    kernelsPerSlot += 4;
+    k_update_poses<128><<<divUp(d.nP, 128), 128, 0, stream>>>(d); mark("update_poses");
+    k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 1, 1); mark("errors");
+    k_lm_decide<256><<<1, 256, 0, stream>>>(d); mark("lm_decide");
+}
+
+// Runs ONE trial slot outside the graph with an event after every kernel and returns
+// the per-kernel device times (ms).  The LM state must allow a trial (call after
+// set_estimates): it performs the first trial of a 1-iteration optimisation.
+int Solver::profileSlot(int cap, char* names, int nameLen, double* ms) {
+    ensureStructure();
+    use();
+    k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
+    k_lm_begin<256><<<1, 256, 0, stream>>>(d, 1);
+    const int saved = kernelsPerSlot;
+    profiling = true;
+    profEvents.clear(); profNames.clear();
+    cudaEvent_t e0;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventRecord(e0, stream));
+    enqueueSlot();
+    profiling = false;
+    kernelsPerSlot = saved;
+    CK(cudaStreamSynchronize(stream));
+    CK(cudaGetLastError());
+    int n = 0;
+    cudaEvent_t prev = e0;
+    for (size_t i = 0; i < profEvents.size(); i++) {
+        float t = 0;
+        CK(cudaEventElapsedTime(&t, prev, profEvents[i]));
+        if (n < cap) {
+            if (names) { strncpy(names + (size_t)n * nameLen, profNames[i].c_str(), nameLen - 1); names[(size_t)n * nameLen + nameLen - 1] = 0; }
+            if (ms) ms[n] = t;
+            n++;
+        }
+        prev = profEvents[i];
+    }
+    CK(cudaEventDestroy(e0));
+    for (auto e : profEvents) cudaEventDestroy(e);
+    profEvents.clear();
+    systemBuilt = false; solved = false;
+    return n;
+}
+
+// New measurements / information values for an unchanged graph (a second
+// initialize() of the reference re-uploads the whole edge arena but keeps the
+// structure: src/block_solver.cpp:161-170).  H2D into the raw arrays, then the two
+// gather kernels refresh the landmark-major and pose-major copies.
+void Solver::updateMeasurements(int setId, const double* meas, const double* omega, int nomega) {
+    if (setId < 0 || setId >= (int)sets.size()) throw ArgError("update_measurements: bad set id");
+    HostSet& hs = sets[setId];
+    if (!meas || !omega || (nomega != 1 && nomega != hs.n)) throw ArgError("update_measurements: bad arguments");
+    hs.meas.assign(meas, meas + (size_t)hs.n * hs.dim);
+    hs.omega.assign(omega, omega + nomega);
+    hs.nomega = nomega;
+    if (structDirty) return;      // picked up by the next build_structure
+    use();
+    size_t off = 0;
+    for (int i = 0; i < setId; i++) off += sets[i].n;
+    const int n = hs.n;
+    std::vector<double> m0(n), m1(n), m2(n), w(n);
+    for (int i = 0; i < n; i++) {
+        m0[i] = meas[(size_t)i * hs.dim]; m1[i] = meas[(size_t)i * hs.dim + 1];
+        m2[i] = hs.dim == 3 ? meas[(size_t)i * 3 + 2] : 0.0;
+        w[i] = nomega > 1 ? omega[i] : omega[0];
+    }
+    CK(cudaMemcpyAsync(r_m0.p + off, m0.data(), n * sizeof(double), cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpyAsync(r_m1.p + off, m1.data(), n * sizeof(double), cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpyAsync(r_m2.p + off, m2.data(), n * sizeof(double), cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpyAsync(r_w.p + off, w.data(), n * sizeof(double), cudaMemcpyHostToDevice, stream));
+    RawEdges raw{(int)E, r_iP, r_iL, r_m0, r_m1, r_m2, r_w, r_set, perEdgeCam_ ? r_cam.p : nullptr,
+                 anyOut_ ? r_out.p : nullptr};
+    const int TB = 256;
+    k_gather_lm<<<divUp(E + 1, TB), TB, 0, stream>>>(raw, s_gid, nP, nL, s_iP, s_iL, s_uv, s_r, s_w, s_set,
+                                                     perEdgeCam_ ? s_cam.p : nullptr, anyOut_ ? s_out.p : nullptr, flag);
+    k_gather_pose<<<divUp(E, TB), TB, 0, stream>>>((int)E, p_src, s_iL, s_uv, s_r, s_w, s_set,
+                                                   perEdgeCam_ ? s_cam.p : nullptr, anyOut_ ? s_out.p : nullptr, p_iL,
+                                                   p_uv, p_r, p_w, p_set, perEdgeCam_ ? p_cam.p : nullptr,
+                                                   anyOut_ ? p_out.p : nullptr);
+    CK(cudaStreamSynchronize(stream));
+    CK(cudaGetLastError());
+    systemBuilt = false; solved = false;
 }
 
 void Solver::captureSlot() {
@@ -1016,6 +1103,13 @@ int cugo_b200_get_last_timing(cugo_b200_solver* s, double* optimize_ms, long* ke
         if (optimize_ms) *optimize_ms = S.lastOptimizeMs;
         if (kernels_launched) *kernels_launched = S.lastKernels;
     });
+}
+int cugo_b200_profile_trial(cugo_b200_solver* s, int capacity, char* names, int name_len, double* ms, int* n) {
+    return guarded(s, [&](Solver& S) { const int r = S.profileSlot(capacity, names, name_len, ms); if (n) *n = r; });
+}
+int cugo_b200_update_measurements(cugo_b200_solver* s, int set_id, const double* measurements, const double* omegas,
+                                  int nomega) {
+    return guarded(s, [&](Solver& S) { S.updateMeasurements(set_id, measurements, omegas, nomega); });
 }
 void* cugo_b200_stream(cugo_b200_solver* s) { return s ? (void*)s->impl.stream : nullptr; }
 

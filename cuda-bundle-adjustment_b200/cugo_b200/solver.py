@@ -33,7 +33,7 @@ SYMBOLS = (
     "cugo_b200_set_lambda", "cugo_b200_restore_diagonal", "cugo_b200_solve", "cugo_b200_update",
     "cugo_b200_compute_scale", "cugo_b200_push", "cugo_b200_pop", "cugo_b200_optimize",
     "cugo_b200_get_estimates", "cugo_b200_get_structure", "cugo_b200_get_values", "cugo_b200_get_sizes",
-    "cugo_b200_get_last_timing", "cugo_b200_stream",
+    "cugo_b200_get_last_timing", "cugo_b200_stream", "cugo_b200_profile_trial", "cugo_b200_update_measurements",
 )
 
 _lib = None
@@ -210,6 +210,21 @@ class BlockSolver:
         ms, k = C.c_double(), C.c_long()
         self._ck(self.lib.cugo_b200_get_last_timing(self.h, C.byref(ms), C.byref(k)))
         return ms.value, k.value
+
+    def profile_trial(self):
+        """Per-kernel device times of one LM trial: list of (kernel name, ms)."""
+        cap, ln = 512, 32
+        names = C.create_string_buffer(cap * ln)
+        ms = np.zeros(cap, np.float64)
+        n = C.c_int()
+        self._ck(self.lib.cugo_b200_profile_trial(self.h, cap, names, ln, _p(ms, C.c_double), C.byref(n)))
+        raw = names.raw
+        return [(raw[i * ln:(i + 1) * ln].split(b"\0")[0].decode(), float(ms[i])) for i in range(n.value)]
+
+    def update_measurements(self, set_idx, meas, omega):
+        meas, omega = _f64(meas), _f64(omega)
+        self._ck(self.lib.cugo_b200_update_measurements(self.h, set_idx, _p(meas, C.c_double), _p(omega, C.c_double),
+                                                        int(omega.shape[0])))
 
     def stream(self):
         return self.lib.cugo_b200_stream(self.h)

@@ -121,6 +121,14 @@ int cugo_b200_get_sizes(cugo_b200_solver* s, long sizes[10]);
 /* device time of the last optimize() in ms (CUDA events on the solver's stream) and the number of
  * kernels it launched */
 int cugo_b200_get_last_timing(cugo_b200_solver* s, double* optimize_ms, long* kernels_launched);
+/* per-kernel device times (ms, CUDA events on the solver's stream) of ONE LM trial run outside the
+ * CUDA graph: names is a capacity x name_len char matrix.  Leaves the estimates advanced by that trial. */
+int cugo_b200_profile_trial(cugo_b200_solver* s, int capacity, char* names, int name_len, double* ms, int* n);
+/* new measurements / information for an unchanged graph: the reference's second initialize() re-uploads
+ * the edge arena but keeps the structure (src/block_solver.cpp:161-170, EdgeSet::mapDevice
+ * src/optimisable_graph.hpp:574-601) */
+int cugo_b200_update_measurements(cugo_b200_solver* s, int set_id, const double* measurements,
+                                  const double* omegas, int nomega);
 /* the solver's CUDA stream (cudaStream_t) for callers that time or chain work on it */
 void* cugo_b200_stream(cugo_b200_solver* s);
 

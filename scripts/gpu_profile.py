@@ -1,0 +1,38 @@
+"""Per-kernel device times of one LM trial (CUDA events, outside the graph) + optimize() timing."""
+import collections
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [os.path.join(ROOT, "cuda-bundle-adjustment_b200")]
+from cugo_b200 import pack, solver, synth  # noqa: E402
+
+name = sys.argv[1] if len(sys.argv) > 1 else "kitti00"
+prob = pack.pack(synth.make_graph(name))
+s = solver.BlockSolver(0)
+s.initialize(prob)
+s.build_structure()
+print(s.sizes())
+for rep in range(3):
+    s.set_estimates(prob.poses, prob.landmarks)
+    prof = s.profile_trial()
+agg = collections.OrderedDict()
+for k, ms in prof:
+    a = agg.setdefault(k, [0, 0.0, 0.0])
+    a[0] += 1; a[1] += ms; a[2] = max(a[2], ms)
+tot = sum(ms for _, ms in prof)
+print("one trial, per kernel (event-timed, launches serialised): total %.3f ms" % tot)
+for k, (n, t, mx) in agg.items():
+    print("  %-14s x%-3d %8.3f ms  (max %.3f)  %5.1f %%" % (k, n, t, mx, 100 * t / tot))
+print("chol per level (diag, trsm, update, bwd):")
+print("  diag", np.round([ms for k, ms in prof if k == "chol_diag"], 3).tolist())
+print("  trsm", np.round([ms for k, ms in prof if k == "chol_trsm"], 3).tolist())
+print("  upd ", np.round([ms for k, ms in prof if k == "chol_update"], 3).tolist())
+print("  bwd ", np.round([ms for k, ms in prof if k == "chol_bwd"], 3).tolist())
+for rep in range(5):
+    s.set_estimates(prob.poses, prob.landmarks)
+    chi, lam, tr = s.optimize(10)
+    ms, nk = s.last_timing()
+    print("optimize(10): %.3f ms device, %d kernels, %.3f ms/iter, %.2f M edges/s" % (ms, nk, ms / len(chi), prob.n_edges * len(chi) / ms / 1e3))

@@ -1,0 +1,17 @@
+#!/bin/bash
+# Round-end style GPU session: parity tests, both bench arms, ncu launch list + full capture.
+# Usage (on the GPU box, from the repo root): bash scripts/gpu_round.sh [tag]
+TAG=${1:-r01}
+OUT=gpurun_out/$TAG
+mkdir -p $OUT
+python -m pytest tests -q -m gpu -x > $OUT/pytest_gpu.log 2>&1; echo "pytest rc $?" >> $OUT/pytest_gpu.log
+tail -5 $OUT/pytest_gpu.log
+python bench.py --impl reference --steps 5 --warmup 2 > $OUT/bench_reference.json 2> $OUT/bench_reference.err
+python bench.py --steps 10 --warmup 3 > $OUT/bench.json 2> $OUT/bench.err
+cat $OUT/bench_reference.json | cut -c1-600; echo; cat $OUT/bench.json | cut -c1-1500; echo
+CMD="python bench.py --steps 1 --warmup 3 --cpu-iters 1"
+$CMD > $OUT/plain.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:k_ -c 900 --csv --log-file $OUT/launches.csv $CMD > $OUT/ncu_launches.log 2>&1
+$CMD > $OUT/plain2.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:"k_schur_blocks|k_build_lm|k_chol_diag|k_backsub" -c 8 -o $OUT/prof $CMD > $OUT/ncu_full.log 2>&1
+ls -la $OUT
