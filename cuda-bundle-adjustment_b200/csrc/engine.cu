@@ -15,6 +15,7 @@
 
 #include "engine.h"
 #include "kernels_chol.cuh"
+#include "kernels_chol2.cuh"
 #include "kernels_edge.cuh"
 #include "kernels_lm.cuh"
 #include "kernels_schur.cuh"
@@ -87,7 +88,8 @@ struct Solver {
     long E = 0;
     int nmulRef = 0, nnzSymm = 0, maxRt = 0;
     SymCounts counts{};
-    std::vector<int> h_levelPtr, h_trsmPtr, h_updPtr;
+    std::vector<int> h_levelPtr, h_trsmPtr, h_updPtr, h_levMaxNt;
+    bool cholV1 = false;           // CUGO_B200_CHOL_V1=1: first-generation factorisation kernels (A/B timing)
     // buffers
     DBuf<double> pose0, pose1, poseBak, lm0, lm1, lmBak;
     DBuf<int> r_iP, r_iL, r_cam;
@@ -113,7 +115,8 @@ struct Solver {
         z_asmCol, z_trsmPtr, z_updPtr;
     DBuf<long long> z_Lptr, z_Uptr;
     DBuf<SymCounts> y_counts;
-    DBuf<double> cL, cU, cX;
+    DBuf<double> cL, cU, cX, cW;
+    DBuf<int> z_levMaxNt;
     // graph of one trial slot
     cudaGraph_t slotGraph = nullptr;
     cudaGraphExec_t slotExec = nullptr;
@@ -432,15 +435,22 @@ void Solver::buildStructure() {
     m.levelPtr = z_levelPtr; m.levelSn = z_levelSn; m.Lptr = z_Lptr; m.Uptr = z_Uptr; m.childPtr = z_childPtr;
     m.childIdx = z_childIdx; m.invPtr = z_invPtr; m.inv = z_inv; m.snBlkPtr = z_snBlkPtr; m.asmBlk = z_asmBlk;
     m.asmRow = z_asmRow; m.asmCol = z_asmCol;
-    k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, CHOL_RS, CHOL_TS);
-    h_levelPtr.resize(counts.nlev + 1); h_trsmPtr.resize(nsn + 1); h_updPtr.resize(nsn + 1);
+    {
+        const char* v1 = getenv("CUGO_B200_CHOL_V1");
+        cholV1 = v1 && v1[0] == '1';
+    }
+    z_levMaxNt.alloc(counts.nlev + 1);
+    k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, CHOL_RS, CHOL_TS, cholV1 ? 0 : CHOL_RB, CHOL_TB,
+                                    z_levMaxNt);
+    h_levelPtr.resize(counts.nlev + 1); h_trsmPtr.resize(nsn + 1); h_updPtr.resize(nsn + 1); h_levMaxNt.resize(counts.nlev + 1);
+    CK(cudaMemcpyAsync(h_levMaxNt.data(), z_levMaxNt.p, sizeof(int) * counts.nlev, cudaMemcpyDeviceToHost, stream));
     CK(cudaMemcpyAsync(h_levelPtr.data(), z_levelPtr.p, sizeof(int) * (counts.nlev + 1), cudaMemcpyDeviceToHost, stream));
     CK(cudaMemcpyAsync(h_trsmPtr.data(), z_trsmPtr.p, sizeof(int) * (nsn + 1), cudaMemcpyDeviceToHost, stream));
     CK(cudaMemcpyAsync(h_updPtr.data(), z_updPtr.p, sizeof(int) * (nsn + 1), cudaMemcpyDeviceToHost, stream));
     CK(cudaStreamSynchronize(stream));
     if (counts.maxCols > CHOL_MAXW) throw CudaError("internal: supernode wider than CHOL_MAXW");
     maxRt = counts.maxFront;   // upper bound of r_t
-    cL.alloc((size_t)counts.lsize); cU.alloc((size_t)counts.usize); cX.alloc((size_t)P * 6);
+    cL.alloc((size_t)counts.lsize); cU.alloc((size_t)counts.usize); cX.alloc((size_t)P * 6); cW.alloc((size_t)P * 21);
 
     // ---- system buffers
     Hpp.alloc((size_t)nP * 36); Hll.alloc((size_t)nL * 9); Hpl.alloc((size_t)nHpl * 18);
@@ -471,7 +481,7 @@ void Solver::buildStructure() {
     c.levelPtr = z_levelPtr; c.levelSn = z_levelSn; c.Lptr = z_Lptr; c.Uptr = z_Uptr; c.childPtr = z_childPtr;
     c.childIdx = z_childIdx; c.invPtr = z_invPtr; c.inv = z_inv; c.snBlkPtr = z_snBlkPtr; c.asmBlk = z_asmBlk;
     c.asmRow = z_asmRow; c.asmCol = z_asmCol; c.trsmPtr = z_trsmPtr; c.updPtr = z_updPtr;
-    c.L = cL; c.U = cU; c.xperm = cX;
+    c.L = cL; c.U = cU; c.xperm = cX; c.Winv = cW;
 
     // dynamic shared memory opt-in for the factorisation kernels
     const int ncMax = 6 * CHOL_MAXW;
@@ -481,6 +491,12 @@ void Solver::buildStructure() {
     const size_t bwdBytes = ((size_t)ncMax * ncMax + ncMax + 6 * (size_t)maxRt) * 8;
     if (bwdBytes > 227 * 1024) throw UnsupportedError("front too large for the shared-memory backward solve of this version");
     CK(cudaFuncSetAttribute(k_chol_bwd<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwdBytes));
+    CK(cudaFuncSetAttribute(k_chol_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_LD * ncMax * 8));
+    CK(cudaFuncSetAttribute(k_chol_update2, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            (2 * ncMax * UPD_LD + 6 * CHOL_TB * UPD_CLD) * 8));
+    const size_t bwd2Bytes = ((size_t)ncMax * (ncMax + 1) + ncMax + 21 * CHOL_MAXW + 6 * (size_t)maxRt) * 8;
+    if (bwd2Bytes > 227 * 1024) throw UnsupportedError("front too large for the shared-memory backward solve of this version");
+    CK(cudaFuncSetAttribute(k_chol_bwd2<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd2Bytes));
     CK(cudaStreamSynchronize(stream));
     structDirty = false; systemBuilt = false; solved = false;
     captureSlot();
@@ -500,6 +516,26 @@ void Solver::enqueueSolve() {
     k_schur_inv<256><<<divUp(d.nL, 256), 256, 0, stream>>>(d); mark("schur_inv");
     k_schur_blocks<4><<<divUp(d.nblk, 4), 128, 0, stream>>>(d); mark("schur_blocks");
     const int ncMax = 6 * CHOL_MAXW;
+    if (!cholV1) {
+        for (int lev = 0; lev < c.nlev; lev++) {
+            const int q0 = h_levelPtr[lev], q1 = h_levelPtr[lev + 1];
+            const int ncLev = 6 * h_levMaxNt[lev], kpad = (ncLev + 7) & ~7;
+            k_chol_panel<<<h_trsmPtr[q1] - h_trsmPtr[q0], PANEL_TPB, PANEL_LD * ncLev * 8, stream>>>(d, c, lev);
+            mark("chol_panel");
+            const int nUpd = h_updPtr[q1] - h_updPtr[q0];
+            if (nUpd > 0) {
+                k_chol_update2<<<nUpd, 128, (2 * kpad * UPD_LD + 6 * CHOL_TB * UPD_CLD) * 8, stream>>>(d, c, lev, kpad);
+                mark("chol_update");
+            }
+        }
+        for (int lev = c.nlev - 1; lev >= 0; lev--) {
+            const int ncLev = 6 * h_levMaxNt[lev];
+            const size_t bytes = ((size_t)ncLev * (ncLev + 1) + ncLev + 21 * CHOL_MAXW + 6 * (size_t)maxRt) * 8;
+            k_chol_bwd2<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bytes, stream>>>(d, c, lev); mark("chol_bwd");
+        }
+        k_backsub<LM_CHUNK><<<d.nChunks, LM_CHUNK, 0, stream>>>(d); mark("backsub");
+        return;
+    }
     for (int lev = 0; lev < c.nlev; lev++) {
         const int q0 = h_levelPtr[lev], q1 = h_levelPtr[lev + 1];
         k_chol_diag<256><<<q1 - q0, 256, ncMax * ncMax * 8, stream>>>(d, c, lev); mark("chol_diag");

@@ -116,10 +116,11 @@ struct Chol {
     const int* asmBlk;
     const int* asmRow;
     const int* asmCol;
-    const int* trsmPtr;    // [nsn+1] prefix of row-slab tasks in levelSn order
+    const int* trsmPtr;    // [nsn+1] prefix of panel-slab tasks in levelSn order
     const int* updPtr;     // [nsn+1] prefix of update-tile tasks in levelSn order
     double* L;
     double* U;
+    double* Winv;          // [21 P] inverse of each 6x6 diagonal Cholesky block (packed lower), by permuted column block
     double* xperm;         // [6P] solution in permuted order
 };
 

@@ -168,17 +168,30 @@ __global__ void k_fill_blocks(const unsigned long long* keys, const unsigned lon
 __global__ void k_sym_analyze(SymWork w, SymCounts* out) {
     if (blockIdx.x == 0 && threadIdx.x == 0) sym_analyze(w, out);
 }
-__global__ void k_sym_fill(SymWork w, const SymCounts* c, SymMaps m, int* trsmPtr, int* updPtr, int rs, int ts) {
+// rb > 0: second-generation task tables (kernels_chol2.cuh): slabs of rb block rows, tiles of tb
+// block rows, and the widest supernode of every level (levMaxNt) for shared-memory sizing.
+// rb == 0: first-generation tables in scalar rows (rs rows per slab, ts x ts tiles).
+__global__ void k_sym_fill(SymWork w, const SymCounts* c, SymMaps m, int* trsmPtr, int* updPtr, int rs, int ts, int rb,
+                           int tb, int* levMaxNt) {
     if (blockIdx.x != 0 || threadIdx.x != 0) return;
     sym_fill(w, *c, m);
     // task tables of the numeric kernels, in levelSn order
     int a = 0, b = 0;
+    for (int l = 0; l < c->nlev; l++) levMaxNt[l] = 0;
     for (int q = 0; q < c->nsn; q++) {
         const int t = m.levelSn[q];
         const int rt = w.snRowPtr[t + 1] - w.snRowPtr[t];
+        const int nt = w.snStart[t + 1] - w.snStart[t];
+        if (nt > levMaxNt[w.snLevel[t]]) levMaxNt[w.snLevel[t]] = nt;
         trsmPtr[q] = a; updPtr[q] = b;
-        a += (6 * rt + 1 + rs - 1) / rs;
-        if (rt > 0) { const int nt = (6 * rt + 1 + ts - 1) / ts; b += nt * (nt + 1) / 2; }
+        if (rb > 0) {
+            const int ns = (rt + rb - 1) / rb;
+            a += ns > 0 ? ns : 1;
+            if (rt > 0) { const int n2 = (rt + tb) / tb; b += n2 * (n2 + 1) / 2; }
+        } else {
+            a += (6 * rt + 1 + rs - 1) / rs;
+            if (rt > 0) { const int n2 = (6 * rt + 1 + ts - 1) / ts; b += n2 * (n2 + 1) / 2; }
+        }
     }
     trsmPtr[c->nsn] = a; updPtr[c->nsn] = b;
 }
