@@ -482,6 +482,7 @@ void Solver::buildStructure() {
     c.childIdx = z_childIdx; c.invPtr = z_invPtr; c.inv = z_inv; c.snBlkPtr = z_snBlkPtr; c.asmBlk = z_asmBlk;
     c.asmRow = z_asmRow; c.asmCol = z_asmCol; c.trsmPtr = z_trsmPtr; c.updPtr = z_updPtr;
     c.L = cL; c.U = cU; c.xperm = cX; c.Winv = cW;
+    { const char* e = getenv("CUGO_B200_DEBUG"); c.dbg = (e && e[0] == '1') ? 1 : 0; }
 
     // dynamic shared memory opt-in for the factorisation kernels
     const int ncMax = 6 * CHOL_MAXW;
@@ -1146,6 +1147,10 @@ int cugo_b200_profile_trial(cugo_b200_solver* s, int capacity, char* names, int 
 int cugo_b200_update_measurements(cugo_b200_solver* s, int set_id, const double* measurements, const double* omegas,
                                   int nomega) {
     return guarded(s, [&](Solver& S) { S.updateMeasurements(set_id, measurements, omegas, nomega); });
+}
+int cugo_b200_debug_counters(long long* out, int n) {
+    if (!out || n < 0 || n > 64 * 24) return CUGO_B200_EINVAL;
+    return cudaMemcpyFromSymbol(out, cugo_b200::g_cholDbg, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
 }
 void* cugo_b200_stream(cugo_b200_solver* s) { return s ? (void*)s->impl.stream : nullptr; }
 

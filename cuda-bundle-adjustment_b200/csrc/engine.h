@@ -122,6 +122,7 @@ struct Chol {
     double* U;
     double* Winv;          // [21 P] inverse of each 6x6 diagonal Cholesky block (packed lower), by permuted column block
     double* xperm;         // [6P] solution in permuted order
+    int dbg;               // 1: kernels record phase timestamps (diagnostics)
 };
 
 }  // namespace cugo_b200

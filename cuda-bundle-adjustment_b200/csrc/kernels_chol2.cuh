@@ -53,6 +53,9 @@ __device__ __forceinline__ ChildRef load_child(const Chol& c, int q) {
     r.pad = 0;
     return r;
 }
+// phase timestamps of CTA 0 of each panel launch (diagnostics, enabled by Chol::dbg)
+__device__ long long g_cholDbg[64 * 24];
+#define CHOL_STAMP(ph) do { if (c.dbg && blockIdx.x == 0 && threadIdx.x == 0 && lev < 64) g_cholDbg[lev * 24 + (ph)] = clock64(); } while (0)
 __device__ __forceinline__ int tri(int i, int k) { return i * (i + 1) / 2 + k; }   // packed lower, k <= i
 
 // ---------------------------------------------------------------------------
@@ -73,9 +76,11 @@ __global__ void __launch_bounds__(PANEL_TPB) k_chol_panel(Dev d, Chol c, int lev
     const int R = nc + nS;
     const int ch0 = c.childPtr[n.t], nch = c.childPtr[n.t + 1] - ch0;
 
+    CHOL_STAMP(0);
     for (int i = tid; i < nc * PANEL_LD; i += PANEL_TPB) A[i] = 0.0;
     if (tid < nch && tid < CHOL_MAXCH) chs[tid] = load_child(c, ch0 + tid);
     __syncthreads();
+    CHOL_STAMP(1);
     // ---- original entries of Hsc
     if (tid < (PANEL_TPB / 36) * 36) {
         const int e = tid % 36, rr = e % 6, cc = e / 6;
@@ -95,6 +100,7 @@ __global__ void __launch_bounds__(PANEL_TPB) k_chol_panel(Dev d, Chol c, int lev
         for (int cc = tid; cc < nc; cc += PANEL_TPB)
             A[cc * PANEL_LD + R - 1] = d.bsc[(size_t)c.perm[n.s + cc / 6] * 6 + cc % 6];
     __syncthreads();
+    CHOL_STAMP(2);
     // ---- children: pull their update matrices block by block
     if (nch > 0) {
         const int nD = nt * nt, nSb = (rb1 - rb0) * nt;
@@ -146,6 +152,7 @@ __global__ void __launch_bounds__(PANEL_TPB) k_chol_panel(Dev d, Chol c, int lev
         }
     }
     __syncthreads();
+    CHOL_STAMP(3);
     // ---- factorisation, left-looking by 6-column blocks
     const int fr8 = lane >> 2, fk = lane & 3;
     for (int jb = 0; jb < nt; jb++) {
@@ -251,6 +258,7 @@ __global__ void __launch_bounds__(PANEL_TPB) k_chol_panel(Dev d, Chol c, int lev
         }
         __syncthreads();
     }
+    CHOL_STAMP(4);
     // ---- write the panel rows this CTA owns
     double* __restrict__ Pn = c.L + c.Lptr[n.t];
     if (slab == 0)
@@ -262,6 +270,7 @@ __global__ void __launch_bounds__(PANEL_TPB) k_chol_panel(Dev d, Chol c, int lev
         const int lr = i % nS, cc = i / nS;
         Pn[(size_t)cc * n.m + 6 * rb0 + lr] = A[cc * PANEL_LD + nc + lr];
     }
+    CHOL_STAMP(5);
 }
 
 // ---------------------------------------------------------------------------
@@ -288,6 +297,7 @@ __global__ void __launch_bounds__(128) k_chol_update2(Dev d, Chol c, int lev, in
     double* Cs = sm + 2 * kpadMax * UPD_LD;
     const double* __restrict__ Pn = c.L + c.Lptr[n.t];
     const int ch0 = c.childPtr[n.t], nch = c.childPtr[n.t + 1] - ch0;
+    CHOL_STAMP(8);
     if (tid < nch && tid < CHOL_MAXCH) chs[tid] = load_child(c, ch0 + tid);
     for (int i = tid; i < kp * TS; i += 128) {
         const int r = i % TS, k = i / TS;
@@ -296,6 +306,7 @@ __global__ void __launch_bounds__(128) k_chol_update2(Dev d, Chol c, int lev, in
         if (ti != tj) Bs[k * UPD_LD + r] = (kin && j0 + r < n.u) ? Pn[(size_t)k * n.m + nc + j0 + r] : 0.0;
     }
     __syncthreads();
+    CHOL_STAMP(9);
     const int wr = wid & 1, wc = wid >> 1;
     if (!(ti == tj && wc > wr)) {
         double acc[2][3][3][2];
@@ -336,6 +347,7 @@ __global__ void __launch_bounds__(128) k_chol_update2(Dev d, Chol c, int lev, in
                 }
     }
     __syncthreads();
+    CHOL_STAMP(10);
     // epilogue: add the children's blocks, store the lower triangle of U_t
     double* __restrict__ Ut = c.U + c.Uptr[n.t];
     const int rt = n.rt;
@@ -373,6 +385,7 @@ __global__ void __launch_bounds__(128) k_chol_update2(Dev d, Chol c, int lev, in
             dst[0] = v[0];
         }
     }
+    CHOL_STAMP(11);
 }
 
 // ---------------------------------------------------------------------------
@@ -390,6 +403,7 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd2(Dev d, Chol c, int lev) {
     double* xR = Wsm + 21 * nt;         // 6 rt
     const double* __restrict__ Pn = c.L + c.Lptr[n.t];
     const int* __restrict__ Rt = c.snRows + c.snRowPtr[n.t];
+    CHOL_STAMP(16);
     for (int i = tid; i < nr; i += TPB) xR[i] = c.xperm[(size_t)Rt[i / 6] * 6 + i % 6];
     for (int i = tid; i < nc * nc; i += TPB) {
         const int r = i % nc, cc = i / nc;
@@ -397,6 +411,7 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd2(Dev d, Chol c, int lev) {
     }
     for (int i = tid; i < 21 * nt; i += TPB) Wsm[i] = c.Winv[(size_t)n.s * 21 + i];
     __syncthreads();
+    CHOL_STAMP(17);
     constexpr int NW = TPB / 32;
     constexpr int CPW = (6 * CHOL_MAXW + NW - 1) / NW;      // columns per warp
     const int lane = tid & 31, wid = tid >> 5;
@@ -421,6 +436,7 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd2(Dev d, Chol c, int lev) {
         }
     }
     __syncthreads();
+    CHOL_STAMP(18);
     if (wid == 0) {
         for (int jb = nt - 1; jb >= 0; jb--) {
             const int j0 = 6 * jb;
@@ -444,6 +460,7 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd2(Dev d, Chol c, int lev) {
         }
     }
     __syncthreads();
+    CHOL_STAMP(19);
     for (int i = tid; i < nc; i += TPB) {
         const double v = w[i];
         c.xperm[(size_t)(n.s + i / 6) * 6 + i % 6] = v;

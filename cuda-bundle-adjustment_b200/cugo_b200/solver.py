@@ -34,6 +34,7 @@ SYMBOLS = (
     "cugo_b200_compute_scale", "cugo_b200_push", "cugo_b200_pop", "cugo_b200_optimize",
     "cugo_b200_get_estimates", "cugo_b200_get_structure", "cugo_b200_get_values", "cugo_b200_get_sizes",
     "cugo_b200_get_last_timing", "cugo_b200_stream", "cugo_b200_profile_trial", "cugo_b200_update_measurements",
+    "cugo_b200_debug_counters",
 )
 
 _lib = None
@@ -225,6 +226,11 @@ class BlockSolver:
         meas, omega = _f64(meas), _f64(omega)
         self._ck(self.lib.cugo_b200_update_measurements(self.h, set_idx, _p(meas, C.c_double), _p(omega, C.c_double),
                                                         int(omega.shape[0])))
+
+    def debug_counters(self, n=64 * 24):
+        a = (C.c_longlong * n)()
+        self._ck(self.lib.cugo_b200_debug_counters(a, n))
+        return np.array(a[:], dtype=np.int64).reshape(-1, 24)
 
     def stream(self):
         return self.lib.cugo_b200_stream(self.h)

@@ -129,6 +129,9 @@ int cugo_b200_profile_trial(cugo_b200_solver* s, int capacity, char* names, int 
  * src/optimisable_graph.hpp:574-601) */
 int cugo_b200_update_measurements(cugo_b200_solver* s, int set_id, const double* measurements,
                                   const double* omegas, int nomega);
+/* diagnostics: phase timestamps (SM clock) the factorisation kernels record per tree level when the
+ * environment has CUGO_B200_DEBUG=1: 8 slots per level, up to 64 levels */
+int cugo_b200_debug_counters(long long* out, int n);
 /* the solver's CUDA stream (cudaStream_t) for callers that time or chain work on it */
 void* cugo_b200_stream(cugo_b200_solver* s);
 

@@ -26,11 +26,17 @@ tot = sum(ms for _, ms in prof)
 print("one trial, per kernel (event-timed, launches serialised): total %.3f ms" % tot)
 for k, (n, t, mx) in agg.items():
     print("  %-14s x%-3d %8.3f ms  (max %.3f)  %5.1f %%" % (k, n, t, mx, 100 * t / tot))
-print("chol per level (diag, trsm, update, bwd):")
-print("  diag", np.round([ms for k, ms in prof if k == "chol_diag"], 3).tolist())
-print("  trsm", np.round([ms for k, ms in prof if k == "chol_trsm"], 3).tolist())
-print("  upd ", np.round([ms for k, ms in prof if k == "chol_update"], 3).tolist())
-print("  bwd ", np.round([ms for k, ms in prof if k == "chol_bwd"], 3).tolist())
+print("chol per level:")
+for nm in ("chol_diag", "chol_trsm", "chol_panel", "chol_update", "chol_bwd"):
+    v = np.round([ms for k, ms in prof if k == nm], 3).tolist()
+    if v:
+        print("  %-12s" % nm, v)
+if os.environ.get("CUGO_B200_DEBUG") == "1":
+    dc = s.debug_counters()
+    print("panel phases of CTA 0 per level (cycles): zero, hsc scatter, child pull, factor, store")
+    for lev in range(s.sizes()["nlevels"]):
+        print("  lev %2d panel" % lev, np.diff(dc[lev, :6]).tolist(), " update (stage, mma, pull+store)",
+              np.diff(dc[lev, 8:12]).tolist(), " bwd (load, gemv, trsv)", np.diff(dc[lev, 16:20]).tolist())
 for rep in range(5):
     s.set_estimates(prob.poses, prob.landmarks)
     chi, lam, tr = s.optimize(10)
