@@ -16,6 +16,7 @@
 #include "engine.h"
 #include "kernels_chol.cuh"
 #include "kernels_chol2.cuh"
+#include "kernels_chol3.cuh"
 #include "kernels_edge.cuh"
 #include "kernels_lm.cuh"
 #include "kernels_schur.cuh"
@@ -89,7 +90,7 @@ struct Solver {
     int nmulRef = 0, nnzSymm = 0, maxRt = 0;
     SymCounts counts{};
     std::vector<int> h_levelPtr, h_trsmPtr, h_updPtr, h_levMaxNt;
-    bool cholV1 = false;           // CUGO_B200_CHOL_V1=1: first-generation factorisation kernels (A/B timing)
+    int cholGen = 3;               // CUGO_B200_CHOL=1|2: earlier generations of the factorisation kernels (A/B timing)
     // buffers
     DBuf<double> pose0, pose1, poseBak, lm0, lm1, lmBak;
     DBuf<int> r_iP, r_iL, r_cam;
@@ -436,11 +437,11 @@ void Solver::buildStructure() {
     m.childIdx = z_childIdx; m.invPtr = z_invPtr; m.inv = z_inv; m.snBlkPtr = z_snBlkPtr; m.asmBlk = z_asmBlk;
     m.asmRow = z_asmRow; m.asmCol = z_asmCol;
     {
-        const char* v1 = getenv("CUGO_B200_CHOL_V1");
-        cholV1 = v1 && v1[0] == '1';
+        const char* g = getenv("CUGO_B200_CHOL");
+        cholGen = (g && (g[0] == '1' || g[0] == '2')) ? g[0] - '0' : 3;
     }
     z_levMaxNt.alloc(counts.nlev + 1);
-    k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, CHOL_RS, CHOL_TS, cholV1 ? 0 : CHOL_RB, CHOL_TB,
+    k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, CHOL_RS, CHOL_TS, cholGen == 1 ? 0 : CHOL_RB, CHOL_TB,
                                     z_levMaxNt);
     h_levelPtr.resize(counts.nlev + 1); h_trsmPtr.resize(nsn + 1); h_updPtr.resize(nsn + 1); h_levMaxNt.resize(counts.nlev + 1);
     CK(cudaMemcpyAsync(h_levMaxNt.data(), z_levMaxNt.p, sizeof(int) * counts.nlev, cudaMemcpyDeviceToHost, stream));
@@ -498,6 +499,10 @@ void Solver::buildStructure() {
     const size_t bwd2Bytes = ((size_t)ncMax * (ncMax + 1) + ncMax + 21 * CHOL_MAXW + 6 * (size_t)maxRt) * 8;
     if (bwd2Bytes > 227 * 1024) throw UnsupportedError("front too large for the shared-memory backward solve of this version");
     CK(cudaFuncSetAttribute(k_chol_bwd2<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd2Bytes));
+    CK(cudaFuncSetAttribute(k_chol_bwd3<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd2Bytes));
+    CK(cudaFuncSetAttribute(k_chol_panel3, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_LD * ncMax * 8));
+    CK(cudaFuncSetAttribute(k_chol_update3, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            (2 * ncMax * UPD_LD + 2 * 6 * CHOL_TB * UPD_CLD) * 8));
     CK(cudaStreamSynchronize(stream));
     structDirty = false; systemBuilt = false; solved = false;
     captureSlot();
@@ -517,22 +522,32 @@ void Solver::enqueueSolve() {
     k_schur_inv<256><<<divUp(d.nL, 256), 256, 0, stream>>>(d); mark("schur_inv");
     k_schur_blocks<4><<<divUp(d.nblk, 4), 128, 0, stream>>>(d); mark("schur_blocks");
     const int ncMax = 6 * CHOL_MAXW;
-    if (!cholV1) {
+    if (cholGen >= 2) {
+        const bool g3 = cholGen == 3;
         for (int lev = 0; lev < c.nlev; lev++) {
             const int q0 = h_levelPtr[lev], q1 = h_levelPtr[lev + 1];
-            const int ncLev = 6 * h_levMaxNt[lev], kpad = (ncLev + 7) & ~7;
-            k_chol_panel<<<h_trsmPtr[q1] - h_trsmPtr[q0], PANEL_TPB, PANEL_LD * ncLev * 8, stream>>>(d, c, lev);
+            const int ncLev = 6 * h_levMaxNt[lev];
+            if (g3) k_chol_panel3<<<h_trsmPtr[q1] - h_trsmPtr[q0], PANEL3_TPB, PANEL_LD * ncLev * 8, stream>>>(d, c, lev);
+            else k_chol_panel<<<h_trsmPtr[q1] - h_trsmPtr[q0], PANEL_TPB, PANEL_LD * ncLev * 8, stream>>>(d, c, lev);
             mark("chol_panel");
             const int nUpd = h_updPtr[q1] - h_updPtr[q0];
             if (nUpd > 0) {
-                k_chol_update2<<<nUpd, 128, (2 * kpad * UPD_LD + 6 * CHOL_TB * UPD_CLD) * 8, stream>>>(d, c, lev, kpad);
+                if (g3) {
+                    const int kpad = (ncLev + 15) & ~15;
+                    k_chol_update3<<<nUpd, UPD3_TPB, (2 * kpad * UPD_LD + 2 * 6 * CHOL_TB * UPD_CLD) * 8, stream>>>(d, c, lev, kpad);
+                } else {
+                    const int kpad = (ncLev + 7) & ~7;
+                    k_chol_update2<<<nUpd, 128, (2 * kpad * UPD_LD + 6 * CHOL_TB * UPD_CLD) * 8, stream>>>(d, c, lev, kpad);
+                }
                 mark("chol_update");
             }
         }
         for (int lev = c.nlev - 1; lev >= 0; lev--) {
             const int ncLev = 6 * h_levMaxNt[lev];
             const size_t bytes = ((size_t)ncLev * (ncLev + 1) + ncLev + 21 * CHOL_MAXW + 6 * (size_t)maxRt) * 8;
-            k_chol_bwd2<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bytes, stream>>>(d, c, lev); mark("chol_bwd");
+            if (g3) k_chol_bwd3<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bytes, stream>>>(d, c, lev);
+            else k_chol_bwd2<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bytes, stream>>>(d, c, lev);
+            mark("chol_bwd");
         }
         k_backsub<LM_CHUNK><<<d.nChunks, LM_CHUNK, 0, stream>>>(d); mark("backsub");
         return;

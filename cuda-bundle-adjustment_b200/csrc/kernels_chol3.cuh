@@ -391,4 +391,97 @@ __global__ void __launch_bounds__(UPD3_TPB) k_chol_update3(Dev d, Chol c, int le
     }
     CHOL_STAMP(11);
 }
+
+// ---------------------------------------------------------------------------
+// Backward substitution, one CTA per supernode, levels walked top-down (see k_chol_bwd2).
+// L11 / W are staged asynchronously; the L21^T x_R product issues 4 x CPW independent loads per
+// lane before the first use.
+template <int TPB>
+__global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev) {
+    extern __shared__ double sm[];
+    const LMState* st = d.st;
+    if (st->done) return;
+    const SnInfo n = sn_info(c, c.levelSn[c.levelPtr[lev] + blockIdx.x]);
+    const int nc = n.nc, nt = n.nt, tid = threadIdx.x, nr = 6 * n.rt, ldL = nc + 1;
+    double* L11 = sm;                   // nc columns, leading dimension ldL (odd: conflict-free row reads)
+    double* w = L11 + nc * ldL;         // nc
+    double* Wsm = w + nc;               // 21 nt
+    double* xR = Wsm + 21 * nt;         // 6 rt
+    const double* __restrict__ Pn = c.L + c.Lptr[n.t];
+    const int* __restrict__ Rt = c.snRows + c.snRowPtr[n.t];
+    CHOL_STAMP(16);
+    for (int i = tid; i < nc * nc; i += TPB) {
+        const int r = i % nc, cc = i / nc;
+        if (r > cc) cp_async8(L11 + cc * ldL + r, Pn + (size_t)cc * n.m + r, true);
+    }
+    for (int i = tid; i < 21 * nt; i += TPB) cp_async8(Wsm + i, c.Winv + (size_t)n.s * 21 + i, true);
+    for (int i = tid; i < nr; i += TPB) xR[i] = c.xperm[(size_t)__ldg(Rt + i / 6) * 6 + i % 6];
+    __syncthreads();                    // xR visible; L11 / W are only needed after the product
+    CHOL_STAMP(17);
+    constexpr int NW = TPB / 32;
+    constexpr int CPW = (6 * CHOL_MAXW + NW - 1) / NW;      // columns per warp
+    const int lane = tid & 31, wid = tid >> 5;
+    {
+        double acc[CPW];
+#pragma unroll
+        for (int j = 0; j < CPW; j++) acc[j] = 0.0;
+        for (int r0 = 0; r0 < nr; r0 += 128) {
+            double v[4][CPW], xv[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int r = r0 + 32 * u + lane;
+                const bool ok = r < nr;
+                xv[u] = ok ? xR[r] : 0.0;
+#pragma unroll
+                for (int j = 0; j < CPW; j++) {
+                    const int cc = wid + NW * j;
+                    v[u][j] = (ok && cc < nc) ? Pn[(size_t)cc * n.m + nc + r] : 0.0;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+#pragma unroll
+                for (int j = 0; j < CPW; j++) acc[j] += v[u][j] * xv[u];
+        }
+#pragma unroll
+        for (int j = 0; j < CPW; j++) {
+            const int cc = wid + NW * j;
+            const double s = warp_sum(acc[j]);
+            if (lane == 0 && cc < nc) w[cc] = Pn[(size_t)cc * n.m + n.m - 1] - s;
+        }
+    }
+    cp_async_wait_all();
+    __syncthreads();
+    CHOL_STAMP(18);
+    if (wid == 0) {
+        for (int jb = nt - 1; jb >= 0; jb--) {
+            const int j0 = 6 * jb;
+            double xk = 0.0;
+            if (lane < 6) {
+                const double* Wb = Wsm + 21 * jb;
+#pragma unroll
+                for (int p = 0; p < 6; p++)
+                    if (p >= lane) xk += Wb[tri(p, lane)] * w[j0 + p];
+            }
+            __syncwarp();
+            if (lane < 6) w[j0 + lane] = xk;
+            __syncwarp();
+            for (int cc = lane; cc < j0; cc += 32) {
+                double s = w[cc];
+#pragma unroll
+                for (int k = 0; k < 6; k++) s -= L11[cc * ldL + j0 + k] * w[j0 + k];
+                w[cc] = s;
+            }
+            __syncwarp();
+        }
+    }
+    __syncthreads();
+    CHOL_STAMP(19);
+    for (int i = tid; i < nc; i += TPB) {
+        const double v = w[i];
+        c.xperm[(size_t)(n.s + i / 6) * 6 + i % 6] = v;
+        d.x[(size_t)c.perm[n.s + i / 6] * 6 + i % 6] = v;
+    }
+}
+
 }  // namespace cugo_b200
