@@ -1076,7 +1076,8 @@ int cugo_b200_set_estimates(cugo_b200_solver* s, const double* poses7, const dou
 }
 
 int cugo_b200_build_structure(cugo_b200_solver* s) {
-    return guarded(s, [&](Solver& S) { S.buildStructure(); });
+    // like the reference (src/block_solver.cpp:161-170) the heavy part runs only when the graph changed
+    return guarded(s, [&](Solver& S) { S.ensureStructure(); });
 }
 
 int cugo_b200_compute_errors(cugo_b200_solver* s, double* chi2) {

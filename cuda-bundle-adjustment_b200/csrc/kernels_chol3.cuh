@@ -58,7 +58,8 @@ __device__ __forceinline__ void pull_unit(const Chol& c, const ChildRef* chs, in
 __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int lev) {
     extern __shared__ double A[];                 // PANEL_LD x nc, column-major
     __shared__ ChildRef chs[CHOL_MAXCH];
-    __shared__ double Wsm[24];
+    __shared__ double Wall[21 * CHOL_MAXW];   // W = L_D^-1 of every block column (packed lower)
+    __shared__ int badFlag;
     LMState* st = d.st;
     if (st->done) return;
     const int q0 = c.levelPtr[lev], q1 = c.levelPtr[lev + 1];
@@ -74,6 +75,7 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     const int ch0 = c.childPtr[n.t], nch = c.childPtr[n.t + 1] - ch0;
 
     CHOL_STAMP(0);
+    if (tid == 0) badFlag = 0;
     for (int i = tid; i < nc * PANEL_LD; i += PANEL3_TPB) A[i] = 0.0;
     if (tid < nch && tid < CHOL_MAXCH) chs[tid] = load_child(c, ch0 + tid);
     __syncthreads();
@@ -144,9 +146,12 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     CHOL_STAMP(3);
     // ---- factorisation by 6-column blocks with one block column of look-ahead
     const int fr8 = lane >> 2, fk = lane & 3;
+    const bool dbgT = c.dbg && blockIdx.x == 0 && tid == 0 && lev < 64;
+    long long tF = 0, tW = 0, tS = 0, tU = 0, t0 = 0, t1 = 0;
     for (int jb = 0; jb < nt; jb++) {
         const int j0 = 6 * jb, j1 = j0 + 6;
         const bool more = (jb + 1 < nt);
+        if (dbgT) t0 = clock64();
         // phase F: warp 0 factors D_jj; the others apply the finished columns [0, j0) to block column jb+1
         if (wid == 0) {
             double Ld[21], W[21], invd[6];
@@ -186,20 +191,22 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
 #pragma unroll
                     for (int k = 0; k <= i; k++) A[(j0 + k) * PANEL_LD + j0 + i] = Ld[tri(i, k)];
 #pragma unroll
-                for (int i = 0; i < 21; i++) Wsm[i] = W[i];
-                if (slab == 0) {
-                    double* __restrict__ Wg = c.Winv + (size_t)(n.s + jb) * 21;
-#pragma unroll
-                    for (int i = 0; i < 21; i++) Wg[i] = W[i];
-                    if (bad) st->fail = 1;
-                }
+                for (int i = 0; i < 21; i++) Wall[21 * jb + i] = W[i];
+                if (bad) badFlag = 1;
             }
-        } else if (more && j0 > 0) {
-            const int nmt = (R - j1 + 7) >> 3;
-            const double* Bp = A + j1 + fr8;
-            for (int t = wid - 1; t < nmt; t += PANEL3_NW - 1) {
-                double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0;
-                const double* Ap = A + j1 + 8 * t + fr8;
+        } else if (more && j0 > 0 && (wid & 3) != 0) {
+            // warps 4, 8, 12 share warp 0's scheduler / FP64 pipe: they stay idle so that the DMMAs of the
+            // look-ahead never delay the dependent DFMA chain of the diagonal factor
+            const int nmt = (R - j1 + 7) >> 3;          // <= 19 tiles of 8 rows: at most two per worker warp
+            constexpr int NLA = 3 * (PANEL3_NW / 4);    // 12 look-ahead warps
+            const int ta = (wid >> 2) * 3 + (wid & 3) - 1, tb = ta + NLA;
+            if (ta < nmt) {
+                const bool two = tb < nmt;
+                const double* Bp = A + j1 + fr8;
+                const double* Ap = A + j1 + 8 * ta + fr8;
+                const double* Aq = A + j1 + 8 * (two ? tb : ta) + fr8;
+                double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0, e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
+#pragma unroll 2
                 for (int k0 = 0; k0 < j0; k0 += 8) {
                     const int ka = k0 + fk, kb = k0 + 4 + fk;
                     const bool va = ka < j0, vb = kb < j0;
@@ -207,24 +214,38 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
                     const double b1 = vb ? Bp[kb * PANEL_LD] : 0.0;
                     const double a0 = va ? Ap[ka * PANEL_LD] : 0.0;
                     const double a1 = vb ? Ap[kb * PANEL_LD] : 0.0;
+                    const double q0 = va ? Aq[ka * PANEL_LD] : 0.0;
+                    const double q1 = vb ? Aq[kb * PANEL_LD] : 0.0;
                     dmma884(c00, c01, a0, b0);
                     dmma884(c10, c11, a1, b1);
+                    dmma884(e00, e01, q0, b0);
+                    dmma884(e10, e11, q1, b1);
                 }
-                const int r = j1 + 8 * t + fr8, cl = 2 * fk;
-                if (cl < 6 && r < R) {
-                    A[(j1 + cl) * PANEL_LD + r] -= c00 + c10;
-                    A[(j1 + cl + 1) * PANEL_LD + r] -= c01 + c11;
+                const int cl = 2 * fk;
+                if (cl < 6) {
+                    const int r = j1 + 8 * ta + fr8;
+                    if (r < R) {
+                        A[(j1 + cl) * PANEL_LD + r] -= c00 + c10;
+                        A[(j1 + cl + 1) * PANEL_LD + r] -= c01 + c11;
+                    }
+                    const int r2 = j1 + 8 * tb + fr8;
+                    if (two && r2 < R) {
+                        A[(j1 + cl) * PANEL_LD + r2] -= e00 + e10;
+                        A[(j1 + cl + 1) * PANEL_LD + r2] -= e01 + e11;
+                    }
                 }
             }
         }
+        if (dbgT) { t1 = clock64(); tF += t1 - t0; }
         __syncthreads();
+        if (dbgT) { t0 = clock64(); tW += t0 - t1; }
         // phase S: one thread per row below the diagonal block, x = a W^T
         {
             const int r = j1 + tid;
             if (r < R) {
                 double W[21], a[6], x[6];
 #pragma unroll
-                for (int i = 0; i < 21; i++) W[i] = Wsm[i];
+                for (int i = 0; i < 21; i++) W[i] = Wall[21 * jb + i];
 #pragma unroll
                 for (int k = 0; k < 6; k++) a[k] = A[(j0 + k) * PANEL_LD + r];
 #pragma unroll
@@ -239,6 +260,7 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
             }
         }
         __syncthreads();
+        if (dbgT) { t1 = clock64(); tS += t1 - t0; }
         // phase U: rank-6 update of block column jb+1 with the block column just finished
         if (more) {
             const int nmt = (R - j1 + 7) >> 3;
@@ -259,10 +281,19 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
             }
             __syncthreads();
         }
+        if (dbgT) tU += clock64() - t1;
+    }
+    if (dbgT) {
+        g_cholDbg[lev * 24 + 12] = tF; g_cholDbg[lev * 24 + 13] = tW;
+        g_cholDbg[lev * 24 + 14] = tS; g_cholDbg[lev * 24 + 15] = tU;
     }
     CHOL_STAMP(4);
     // ---- write the panel rows this CTA owns (a warp per column, lanes along the rows)
     double* __restrict__ Pn = c.L + c.Lptr[n.t];
+    if (slab == 0) {
+        for (int i = tid; i < 21 * nt; i += PANEL3_TPB) c.Winv[(size_t)n.s * 21 + i] = Wall[i];
+        if (tid == 0 && badFlag) st->fail = 1;
+    }
     for (int cc = wid; cc < nc; cc += PANEL3_NW) {
         double* __restrict__ dst = Pn + (size_t)cc * n.m;
         const double* src = A + cc * PANEL_LD;

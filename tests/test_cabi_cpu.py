@@ -40,3 +40,21 @@ def test_product_does_not_touch_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")) or f == "Makefile":
                 txt = open(os.path.join(d, f), errors="ignore").read()
                 assert "ba_oracle" not in txt and "import oracle" not in txt and "oracle/" not in txt, os.path.join(d, f)
+
+
+def test_cpp_facade_sample_builds_and_refuses_without_device(tmp_path):
+    """include/cugo_b200.hpp (the reference-style C++ API) compiles with the host compiler alone, links
+    only the C ABI library, and reports the missing device instead of falling back to a CPU path."""
+    import subprocess
+    import torch
+    from cugo_b200 import graphio, synth
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "cuda-bundle-adjustment_b200"), "lib/sample_ba_from_bag"],
+                          stdout=subprocess.DEVNULL)
+    exe = os.path.join(ROOT, "cuda-bundle-adjustment_b200", "lib", "sample_ba_from_bag")
+    assert os.path.exists(exe)
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    bag = str(tmp_path / "tiny.bag")
+    graphio.write_graph(synth.make_graph("tiny"), bag)
+    r = subprocess.run([exe, bag, "3"], capture_output=True, text=True)
+    assert r.returncode == 4 and "no CUDA device" in r.stderr
