@@ -41,6 +41,17 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+FP64_DMMA_FMA_PER_CLK_SM = 127.8    # measured on B200: scripts/micro/fp64_lat.cu, >= 16 warps per SM
+
+
+def ncu_traffic():
+    """dram bytes (read + write) per launch of each kernel, from the committed `ncu --set full` summary."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(p):
+        return json.load(open(p))
+    return {}
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region."""
 
@@ -197,11 +208,33 @@ def run_ours(args, rank, world):
         stages.append(e)
     hbm_stages = [e for e in stages if "frac" in e]
     dom = max(hbm_stages, key=lambda e: e["ms"])
-    roofline = {"kernel": dom["kernel"], "bound": "hbm", "achieved": dom["achieved_gbs"], "peak": hbm_peak,
-                "unit": "GB/s", "frac": dom["frac"], "traffic": None, "peak_source": peak_src,
-                "note": "dominant HBM-stage kernel; the factorisation kernels (chol_*) are latency-bound FP64 "
-                        "work and are listed in 'stages'"}
+    traffic = ncu_traffic()
+    roofline_hbm = {"kernel": dom["kernel"], "bound": "hbm", "achieved": dom["achieved_gbs"], "peak": hbm_peak,
+                    "unit": "GB/s", "frac": dom["frac"], "traffic": traffic.get("k_" + dom["kernel"]),
+                    "peak_source": peak_src, "note": "dominant HBM-stage kernel of the trial"}
+    # the factorisation kernels are FP64 tensor-pipe (DMMA) work: algorithmic flops of the ordering in use
+    fs = s.factor_stats()
+    clk_mhz = (clk.summary()["sm_mhz"] or 1965.0)
+    fp64_peak = FP64_DMMA_FMA_PER_CLK_SM * 148 * 2 * clk_mhz * 1e6 / 1e12
+    for e in stages:
+        fl = {"chol_panel": fs["flops_panel"], "chol_update": fs["flops_update"], "chol_bwd": fs["flops_backward"]}.get(e["kernel"])
+        if fl:
+            tf = fl / (e["ms"] * 1e-3) / 1e12
+            e.update({"bound": "tensor", "algorithmic_flops": fl, "achieved_tflops": round(tf, 4),
+                      "frac": round(tf / fp64_peak, 5)})
     top = max(stages, key=lambda e: e["ms"])
+    if top.get("bound") == "tensor":
+        roofline = {"kernel": top["kernel"], "bound": "tensor", "achieved": top["achieved_tflops"],
+                    "peak": round(fp64_peak, 2), "unit": "TFLOP/s", "frac": top["frac"],
+                    "traffic": traffic.get("k_" + top["kernel"]),
+                    "peak_source": "FP64 DMMA m8n8k4: %.1f FMA/clk/SM measured by scripts/micro/fp64_lat.cu "
+                                   "(profiles/r01b_fp64_microbench.log) x 148 SMs x SM clock under load" % FP64_DMMA_FMA_PER_CLK_SM,
+                    "launches": top["launches"],
+                    "note": "dominant kernel by time; FP64 tensor pipe (DMMA) of the supernodal Cholesky, summed over "
+                            "the %d tree levels: the elimination tree's critical path (latency), not the pipe, bounds "
+                            "it -- see DESIGN.md section 4; HBM-bound stages are in 'roofline_hbm' and 'stages'" % sizes["nlevels"]}
+    else:
+        roofline = roofline_hbm
 
     # ---- CPU baseline: the oracle port on the host cores, bounded sample
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
@@ -232,6 +265,8 @@ def run_ours(args, rank, world):
         "gpu_launches": int(launches),
         "clocks": clk.summary(),
         "roofline": roofline,
+        "roofline_hbm": roofline_hbm,
+        "factor_stats": fs,
         "stages": stages,
         "top_kernel_by_time": top["kernel"],
         "cpu_baseline": cpu_baseline,

@@ -118,6 +118,8 @@ struct Solver {
     DBuf<SymCounts> y_counts;
     DBuf<double> cL, cU, cX, cW;
     DBuf<int> z_levMaxNt;
+    DBuf<double> z_factStats;
+    double factStats[4] = {0, 0, 0, 0};
     // graph of one trial slot
     cudaGraph_t slotGraph = nullptr;
     cudaGraphExec_t slotExec = nullptr;
@@ -442,7 +444,8 @@ void Solver::buildStructure() {
     }
     z_levMaxNt.alloc(counts.nlev + 1);
     k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, CHOL_RS, CHOL_TS, cholGen == 1 ? 0 : CHOL_RB, CHOL_TB,
-                                    z_levMaxNt);
+                                    z_levMaxNt, z_factStats.alloc(4));
+    CK(cudaMemcpyAsync(factStats, z_factStats.p, sizeof(factStats), cudaMemcpyDeviceToHost, stream));
     h_levelPtr.resize(counts.nlev + 1); h_trsmPtr.resize(nsn + 1); h_updPtr.resize(nsn + 1); h_levMaxNt.resize(counts.nlev + 1);
     CK(cudaMemcpyAsync(h_levMaxNt.data(), z_levMaxNt.p, sizeof(int) * counts.nlev, cudaMemcpyDeviceToHost, stream));
     CK(cudaMemcpyAsync(h_levelPtr.data(), z_levelPtr.p, sizeof(int) * (counts.nlev + 1), cudaMemcpyDeviceToHost, stream));
@@ -1163,6 +1166,12 @@ int cugo_b200_profile_trial(cugo_b200_solver* s, int capacity, char* names, int 
 int cugo_b200_update_measurements(cugo_b200_solver* s, int set_id, const double* measurements, const double* omegas,
                                   int nomega) {
     return guarded(s, [&](Solver& S) { S.updateMeasurements(set_id, measurements, omegas, nomega); });
+}
+int cugo_b200_get_factor_stats(cugo_b200_solver* s, double stats[4]) {
+    return guarded(s, [&](Solver& S) {
+        S.ensureStructure();
+        for (int i = 0; i < 4; i++) stats[i] = S.factStats[i];
+    });
 }
 int cugo_b200_debug_counters(long long* out, int n) {
     if (!out || n < 0 || n > 64 * 24) return CUGO_B200_EINVAL;

@@ -214,12 +214,14 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
                     const double b1 = vb ? Bp[kb * PANEL_LD] : 0.0;
                     const double a0 = va ? Ap[ka * PANEL_LD] : 0.0;
                     const double a1 = vb ? Ap[kb * PANEL_LD] : 0.0;
-                    const double q0 = va ? Aq[ka * PANEL_LD] : 0.0;
-                    const double q1 = vb ? Aq[kb * PANEL_LD] : 0.0;
                     dmma884(c00, c01, a0, b0);
                     dmma884(c10, c11, a1, b1);
-                    dmma884(e00, e01, q0, b0);
-                    dmma884(e10, e11, q1, b1);
+                    if (two) {
+                        const double q0 = va ? Aq[ka * PANEL_LD] : 0.0;
+                        const double q1 = vb ? Aq[kb * PANEL_LD] : 0.0;
+                        dmma884(e00, e01, q0, b0);
+                        dmma884(e10, e11, q1, b1);
+                    }
                 }
                 const int cl = 2 * fk;
                 if (cl < 6) {

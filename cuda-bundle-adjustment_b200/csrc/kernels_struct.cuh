@@ -172,11 +172,12 @@ __global__ void k_sym_analyze(SymWork w, SymCounts* out) {
 // block rows, and the widest supernode of every level (levMaxNt) for shared-memory sizing.
 // rb == 0: first-generation tables in scalar rows (rs rows per slab, ts x ts tiles).
 __global__ void k_sym_fill(SymWork w, const SymCounts* c, SymMaps m, int* trsmPtr, int* updPtr, int rs, int ts, int rb,
-                           int tb, int* levMaxNt) {
+                           int tb, int* levMaxNt, double* factStats) {
     if (blockIdx.x != 0 || threadIdx.x != 0) return;
     sym_fill(w, *c, m);
     // task tables of the numeric kernels, in levelSn order
     int a = 0, b = 0;
+    double fPanel = 0.0, fUpd = 0.0, fBwd = 0.0;      // algorithmic flops of one factorisation + solve
     for (int l = 0; l < c->nlev; l++) levMaxNt[l] = 0;
     for (int q = 0; q < c->nsn; q++) {
         const int t = m.levelSn[q];
@@ -184,6 +185,12 @@ __global__ void k_sym_fill(SymWork w, const SymCounts* c, SymMaps m, int* trsmPt
         const int nt = w.snStart[t + 1] - w.snStart[t];
         if (nt > levMaxNt[w.snLevel[t]]) levMaxNt[w.snLevel[t]] = nt;
         trsmPtr[q] = a; updPtr[q] = b;
+        {
+            const double ncd = 6.0 * nt, rd = 6.0 * rt + 1.0;
+            fPanel += ncd * ncd * ncd / 3.0 + rd * ncd * ncd;   // Cholesky of L11 + triangular solves of the rows below (rhs row included)
+            fUpd += rt > 0 ? rd * rd * ncd : 0.0;               // symmetric rank-nc update, lower triangle
+            fBwd += ncd * ncd + 2.0 * 6.0 * rt * ncd;           // backward substitution
+        }
         if (rb > 0) {
             const int ns = (rt + rb - 1) / rb;
             a += ns > 0 ? ns : 1;
@@ -194,6 +201,7 @@ __global__ void k_sym_fill(SymWork w, const SymCounts* c, SymMaps m, int* trsmPt
         }
     }
     trsmPtr[c->nsn] = a; updPtr[c->nsn] = b;
+    factStats[0] = fPanel; factStats[1] = fUpd; factStats[2] = fBwd; factStats[3] = (double)c->lsize;
 }
 
 }  // namespace cugo_b200

@@ -34,7 +34,7 @@ SYMBOLS = (
     "cugo_b200_compute_scale", "cugo_b200_push", "cugo_b200_pop", "cugo_b200_optimize",
     "cugo_b200_get_estimates", "cugo_b200_get_structure", "cugo_b200_get_values", "cugo_b200_get_sizes",
     "cugo_b200_get_last_timing", "cugo_b200_stream", "cugo_b200_profile_trial", "cugo_b200_update_measurements",
-    "cugo_b200_debug_counters",
+    "cugo_b200_debug_counters", "cugo_b200_get_factor_stats",
 )
 
 _lib = None
@@ -226,6 +226,11 @@ class BlockSolver:
         meas, omega = _f64(meas), _f64(omega)
         self._ck(self.lib.cugo_b200_update_measurements(self.h, set_idx, _p(meas, C.c_double), _p(omega, C.c_double),
                                                         int(omega.shape[0])))
+
+    def factor_stats(self):
+        a = (C.c_double * 4)()
+        self._ck(self.lib.cugo_b200_get_factor_stats(self.h, a))
+        return dict(flops_panel=a[0], flops_update=a[1], flops_backward=a[2], l_doubles=a[3])
 
     def debug_counters(self, n=64 * 24):
         a = (C.c_longlong * n)()

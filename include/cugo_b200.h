@@ -129,6 +129,10 @@ int cugo_b200_profile_trial(cugo_b200_solver* s, int capacity, char* names, int 
  * src/optimisable_graph.hpp:574-601) */
 int cugo_b200_update_measurements(cugo_b200_solver* s, int set_id, const double* measurements,
                                   const double* omegas, int nomega);
+/* algorithmic flops of one numeric factorisation under the ordering in use: panel
+ * factorisation (Cholesky of the diagonal blocks + rows below, forward substitution included), symmetric
+ * updates, backward substitution, and the number of doubles stored in L */
+int cugo_b200_get_factor_stats(cugo_b200_solver* s, double stats[4]);
 /* diagnostics: phase timestamps (SM clock) the factorisation kernels record per tree level when the
  * environment has CUGO_B200_DEBUG=1: 8 slots per level, up to 64 levels */
 int cugo_b200_debug_counters(long long* out, int n);
