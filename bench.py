@@ -115,10 +115,22 @@ def run_ours(args, rank, world):
 
     dev = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(dev)
-    g = synth.make_graph(args.workload)
-    prob = pack.pack(g)
-    s = solver.BlockSolver(dev)
-    s.initialize(prob)
+    if world == 1:
+        g = synth.make_graph(args.workload)
+        prob = pack.pack(g)
+        s = solver.BlockSolver(dev)
+        s.initialize(prob)
+        shard_prob = prob
+    else:
+        # weak scaling: the same poses, `world` times the landmarks and edges of the named shape; landmarks
+        # (with their edges) are sharded over the ranks, one NCCL all-reduce of [Hsc | bsc] per LM trial
+        from cugo_b200 import dist as cdist
+        P0, L0, E0, S0 = synth.SHAPES[args.workload][:4]
+        g = synth.make_graph(args.workload, n_landmarks=L0 * world, n_edges=E0 * world, n_stereo=S0 * world)
+        prob = pack.pack(g)
+        ds = cdist.DistBlockSolver(prob, dev)
+        s = ds.s
+        shard_prob = ds.shard.prob
     t0 = time.perf_counter()
     s.build_structure()
     cold_structure_ms = (time.perf_counter() - t0) * 1e3
@@ -133,7 +145,7 @@ def run_ours(args, rank, world):
         torch.cuda.synchronize()
 
     def one_step():
-        s.set_estimates(prob.poses, prob.landmarks)
+        s.set_estimates(shard_prob.poses, shard_prob.landmarks)
         flush.fill_(1.0)
         torch.cuda.synchronize()
         chi, lam, tr = s.optimize(args.iters)
@@ -155,12 +167,12 @@ def run_ours(args, rank, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_ms = float(t.item())
     iters_done = len(chi)
-    value = world * E * iters_done * args.steps / (dev_ms * 1e-3)
+    value = E * iters_done * args.steps / (dev_ms * 1e-3)      # E = edges of the whole job (all ranks)
 
     # ---- e2e through the C ABI with host buffers (pinned), wall clock
     pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
-    h_poses, h_lms = pin(prob.poses), pin(prob.landmarks)
-    h_sets = [(pin(st.meas), pin(st.omega)) for st in prob.sets]
+    h_poses, h_lms = pin(shard_prob.poses), pin(shard_prob.landmarks)
+    h_sets = [(pin(st.meas), pin(st.omega)) for st in shard_prob.sets]
     h2d = h_poses.nbytes + h_lms.nbytes + sum(m.nbytes + w.nbytes for m, w in h_sets)
     d2h = h_poses.nbytes + h_lms.nbytes + 3 * 8 * args.iters
 
@@ -183,12 +195,36 @@ def run_ours(args, rank, world):
         t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
-    e2e_value = world * E * len(c2) * args.steps / e2e_s
+    e2e_value = E * len(c2) * args.steps / e2e_s
+    if world > 1:
+        tb = torch.tensor([float(h2d), float(d2h)], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tb)
+        h2d, d2h = int(tb[0].item()), int(tb[1].item())
 
     if rank != 0:
         return
     # ---- roofline of the dominant kernel (one LM trial, event-timed per kernel)
     hbm_peak, peak_src = peaks()
+    if world > 1:
+        line = {
+            "metric": "edges/s (LM edge-iterations per second), %s shape, %d LM iterations" % (args.workload, args.iters),
+            "value": value, "unit": "edges/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dev_ms / args.steps, "ms_per_lm_iteration": dev_ms / args.steps / iters_done,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic (seeded generator cugo_b200/synth.py; reference inputs are absent)",
+            "config": {"workload": "%s poses with %dx its landmarks/edges: %d poses / %d landmarks / %d edges (%d stereo), "
+                                   "%d LM iterations, FP64; landmarks sharded over %d GPUs, one NCCL all-reduce of "
+                                   "[Hsc | bsc] per LM trial" % (args.workload, world, g.n_poses, g.n_landmarks, E,
+                                                                 len(g.stereo_p), args.iters, world),
+                       "timing": "CUDA events on the solver stream around optimize(), max over ranks; L2 flushed "
+                                 "(256 MB fill) between steps", "sizes_rank0": sizes},
+            "e2e": {"value": e2e_value, "unit": "edges/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "ms_per_step": e2e_s / args.steps * 1e3},
+            "gpu_launches": int(launches) * world, "clocks": clk.summary(),
+            "roofline": None, "cpu_baseline": None, "chi2_final": float(chi[-1]),
+            "note": "roofline / cpu_baseline are reported by the N=1 line (rank-0-at-N=1 only)"}
+        print(json.dumps(line))
+        return
     s.set_estimates(prob.poses, prob.landmarks)
     s.profile_trial()
     s.set_estimates(prob.poses, prob.landmarks)

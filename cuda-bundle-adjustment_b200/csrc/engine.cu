@@ -5,6 +5,8 @@
 
 #include <cub/cub.cuh>
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
 
 #include <algorithm>
 #include <cstdio>
@@ -47,6 +49,41 @@ struct UnsupportedError : std::runtime_error {
     } while (0)
 
 static inline int divUp(long long a, int b) { return (int)((a + b - 1) / b); }
+
+// NCCL is bound at run time (dlopen) the first time a communicator is asked for: a single-GPU process
+// never loads it, and inside a torch.distributed process the already-loaded libnccl.so.2 is reused.
+struct NcclApi {
+    void* lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    bool load(std::string& err) {
+        if (lib) return true;
+        const char* names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char* nm : names) { lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL); if (lib) break; }
+        if (!lib) { err = std::string("cannot load libnccl: ") + dlerror(); return false; }
+        bool ok = true;
+        auto sym = [&](const char* n) { void* p = dlsym(lib, n); if (!p) ok = false; return p; };
+        GetUniqueId = (decltype(GetUniqueId))sym("ncclGetUniqueId");
+        CommInitRank = (decltype(CommInitRank))sym("ncclCommInitRank");
+        CommDestroy = (decltype(CommDestroy))sym("ncclCommDestroy");
+        AllReduce = (decltype(AllReduce))sym("ncclAllReduce");
+        AllGather = (decltype(AllGather))sym("ncclAllGather");
+        GetErrorString = (decltype(GetErrorString))sym("ncclGetErrorString");
+        if (!ok) { err = "libnccl lacks an expected symbol"; lib = nullptr; }
+        return ok;
+    }
+};
+static NcclApi g_nccl;
+#define NK(call)                                                                                   \
+    do {                                                                                           \
+        ncclResult_t r_ = (call);                                                                  \
+        if (r_ != ncclSuccess)                                                                     \
+            throw ::cugo_b200::CudaError(std::string(#call) + ": " + g_nccl.GetErrorString(r_));   \
+    } while (0)
 
 // grow-only device buffer
 template <typename T>
@@ -118,6 +155,20 @@ struct Solver {
     DBuf<SymCounts> y_counts;
     DBuf<double> cL, cU, cX, cW;
     DBuf<int> z_levMaxNt;
+    // multi-GPU
+    int nranks = 1, rank = 0;
+    ncclComm_t comm = nullptr;
+    DBuf<unsigned long long> lkeys, gkeysAll, gkeysSorted, gkeys;
+    DBuf<int> gHead, gIdx, gRowOf, gColInd, gRowPtr, hscSlot, d_cnt;
+    DBuf<double> redA, redC;
+    int nblkG = 0;
+    void commInit(int n, int r, const char* id);
+    void allReduceSum(double* buf, size_t n) {
+        NK(g_nccl.AllReduce(buf, buf, n, ncclFloat64, ncclSum, comm, stream));
+    }
+    void requireSingle(const char* what) {
+        if (nranks > 1) throw StateError(std::string(what) + ": the staged API is single-GPU; with several ranks use optimize()");
+    }
     DBuf<double> z_factStats;
     double factStats[4] = {0, 0, 0, 0};
     // graph of one trial slot
@@ -154,6 +205,7 @@ struct Solver {
         if (h_scalars) cudaFreeHost(h_scalars);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
+        if (comm && g_nccl.CommDestroy) g_nccl.CommDestroy(comm);
         if (stream) cudaStreamDestroy(stream);
     }
 
@@ -411,16 +463,52 @@ void Solver::buildStructure() {
     k_lower_bounds<<<divUp(nP + 1, TB), TB, 0, stream>>>(bRowOf, nblk, nP, bRowPtr);
     nnzSymm = (2 * nblk - nP) * 36;
 
+    // ---- several ranks: the factorisation works on the union of the ranks' block patterns
+    const int* gRowPtrP = bRowPtr;
+    const int* gColIndP = bColInd;
+    nblkG = nblk;
+    if (nranks > 1) {
+        d_cnt.alloc(nranks + 1);
+        CK(cudaMemcpyAsync(d_cnt.p + nranks, &nblk, sizeof(int), cudaMemcpyHostToDevice, stream));
+        NK(g_nccl.AllGather(d_cnt.p + nranks, d_cnt.p, 1, ncclInt32, comm, stream));
+        std::vector<int> cnt(nranks);
+        CK(cudaMemcpyAsync(cnt.data(), d_cnt.p, sizeof(int) * nranks, cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        const int padded = *std::max_element(cnt.begin(), cnt.end());
+        const long long nAllLL = (long long)padded * nranks;
+        if (nAllLL > 0x7fffffff) throw UnsupportedError("global block pattern exceeds 32-bit indexing");
+        const int nAll = (int)nAllLL;
+        lkeys.alloc(padded); gkeysAll.alloc(nAll); gkeysSorted.alloc(nAll); gHead.alloc(nAll + 1); gIdx.alloc(nAll + 1);
+        k_block_keys<<<divUp(padded, TB), TB, 0, stream>>>(bRowOf, bColInd, nblk, padded, (unsigned long long)nP, lkeys);
+        NK(g_nccl.AllGather(lkeys.p, gkeysAll.p, padded, ncclUint64, comm, stream));
+        {
+            size_t bytes = 0;
+            CK(cub::DeviceRadixSort::SortKeys(nullptr, bytes, gkeysAll.p, gkeysSorted.p, nAll, 0, 64, stream));
+            cubTmp.alloc(bytes);
+            CK(cub::DeviceRadixSort::SortKeys(cubTmp.p, bytes, gkeysAll.p, gkeysSorted.p, nAll, 0, 64, stream));
+        }
+        k_key_heads<<<divUp(nAll + 1, TB), TB, 0, stream>>>(gkeysSorted, nAll, gHead);
+        exclusiveScan(*this, gHead.p, gIdx.p, nAll + 1);
+        nblkG = readInt(*this, gIdx.p + nAll);
+        gkeys.alloc(nblkG); gRowOf.alloc(nblkG); gColInd.alloc(nblkG); gRowPtr.alloc(nP + 1); hscSlot.alloc(nblk);
+        k_compact_keys<<<divUp(nAll, TB), TB, 0, stream>>>(gkeysSorted, gHead, gIdx, nAll, (unsigned long long)nP, gkeys,
+                                                           gRowOf, gColInd);
+        k_lower_bounds<<<divUp(nP + 1, TB), TB, 0, stream>>>(gRowOf, nblkG, nP, gRowPtr);
+        k_map_slots<<<divUp(nblk, TB), TB, 0, stream>>>(lkeys, nblk, gkeys, nblkG, hscSlot);
+        gRowPtrP = gRowPtr; gColIndP = gColInd;
+        redA.alloc((size_t)6 * nP + nranks); redC.alloc(2);
+    }
+
     // ---- symbolic factorisation (one device thread runs symbolic.h)
     const int P = nP;
-    y_adjPtr.alloc(P + 1); y_adj.alloc(2 * (size_t)nblk + 1); y_verts.alloc(P); y_iperm.alloc(P); y_mark.alloc(P);
+    y_adjPtr.alloc(P + 1); y_adj.alloc(2 * (size_t)nblkG + 1); y_verts.alloc(P); y_iperm.alloc(P); y_mark.alloc(P);
     y_level.alloc(P); y_queue.alloc(P); y_tmp.alloc(P + 1); y_stack.alloc(4 * (size_t)P + 8); y_snStart.alloc(P + 1);
     y_snParent.alloc(P); y_colToSn.alloc(P); y_snRowPtr.alloc(P + 1); y_snLevel.alloc(P); y_childHead.alloc(P);
     y_childNext.alloc(P);
     const long long rowsCap = sym_rows_cap(P);
     y_snRows.alloc((size_t)rowsCap); y_counts.alloc(1);
     SymWork w{};
-    w.P = P; w.bRowPtr = bRowPtr; w.bColInd = bColInd; w.leaf = CHOL_MAXW; w.maxw = CHOL_MAXW;
+    w.P = P; w.bRowPtr = gRowPtrP; w.bColInd = gColIndP; w.leaf = CHOL_MAXW; w.maxw = CHOL_MAXW;
     w.adjPtr = y_adjPtr; w.adj = y_adj; w.verts = y_verts; w.iperm = y_iperm; w.mark = y_mark; w.level = y_level;
     w.queue = y_queue; w.tmp = y_tmp; w.stack = y_stack; w.snStart = y_snStart; w.snParent = y_snParent;
     w.colToSn = y_colToSn; w.snRowPtr = y_snRowPtr; w.snLevel = y_snLevel; w.childHead = y_childHead;
@@ -432,7 +520,7 @@ void Solver::buildStructure() {
     const int nsn = counts.nsn;
     z_levelPtr.alloc(counts.nlev + 1); z_levelSn.alloc(nsn); z_Lptr.alloc(nsn + 1); z_Uptr.alloc(nsn + 1);
     z_childPtr.alloc(nsn + 1); z_childIdx.alloc(nsn + 1); z_invPtr.alloc(nsn); z_inv.alloc((size_t)counts.ninv + 1);
-    z_snBlkPtr.alloc(nsn + 1); z_asmBlk.alloc(nblk); z_asmRow.alloc(nblk); z_asmCol.alloc(nblk);
+    z_snBlkPtr.alloc(nsn + 1); z_asmBlk.alloc(nblkG); z_asmRow.alloc(nblkG); z_asmCol.alloc(nblkG);
     z_trsmPtr.alloc(nsn + 1); z_updPtr.alloc(nsn + 1);
     SymMaps m{};
     m.levelPtr = z_levelPtr; m.levelSn = z_levelSn; m.Lptr = z_Lptr; m.Uptr = z_Uptr; m.childPtr = z_childPtr;
@@ -459,7 +547,8 @@ void Solver::buildStructure() {
     // ---- system buffers
     Hpp.alloc((size_t)nP * 36); Hll.alloc((size_t)nL * 9); Hpl.alloc((size_t)nHpl * 18);
     b.alloc((size_t)nP * 6 + (size_t)nL * 3); x.alloc((size_t)nP * 6 + (size_t)nL * 3);
-    invHll.alloc((size_t)nL * 9); bsc.alloc((size_t)nP * 6); Hsc.alloc((size_t)nblk * 36);
+    invHll.alloc((size_t)nL * 9);
+    Hsc.alloc((size_t)nblkG * 36 + (size_t)nP * 6);     // [Hsc | bsc] contiguous: one all-reduce with several ranks
     const int errGrid = std::min(divUp(E, 256), 148 * 8);
     chiPartial.alloc(errGrid); scalePartial.alloc(nChunks); maxDiagL.alloc(nChunks); maxDiagP.alloc(nP);
     scalars.alloc(8);
@@ -475,7 +564,10 @@ void Solver::buildStructure() {
     d.cams = perEdgeCam ? cams.p : nullptr;
     d.colPtr = colPtr; d.rowInd = rowInd; d.hplLm = hplLm;
     d.bRowPtr = bRowPtr; d.bColInd = bColInd; d.bRowOf = bRowOf; d.prodPtr = prodPtr; d.prodIJ = prodIJ;
-    d.Hpp = Hpp; d.Hll = Hll; d.Hpl = Hpl; d.b = b; d.x = x; d.invHll = invHll; d.bsc = bsc; d.Hsc = Hsc;
+    d.Hpp = Hpp; d.Hll = Hll; d.Hpl = Hpl; d.b = b; d.x = x; d.invHll = invHll; d.Hsc = Hsc;
+    d.bsc = Hsc.p + (size_t)nblkG * 36;
+    d.nranks = nranks; d.rank = rank; d.nblkG = nblkG; d.hscSlot = nranks > 1 ? hscSlot.p : nullptr;
+    d.redA = nranks > 1 ? redA.p : nullptr; d.redC = nranks > 1 ? redC.p : nullptr;
     d.chiPartial = chiPartial; d.scalePartial = scalePartial; d.maxDiagL = maxDiagL; d.maxDiagP = maxDiagP;
     d.chiEdge = nullptr; d.errGrid = errGrid;
     d.pose[0] = pose0; d.pose[1] = pose1; d.lm[0] = lm0; d.lm[1] = lm1; d.st = state;
@@ -517,13 +609,20 @@ void Solver::buildStructure() {
 void Solver::enqueueBuild() {
     k_build_lm<LM_CHUNK><<<d.nChunks, LM_CHUNK, 0, stream>>>(d, sp); mark("build_lm");
     k_build_pose<128><<<d.nP, 128, 0, stream>>>(d, sp); mark("build_pose");
+    if (nranks > 1) {   // max diagonal of the *global* system for lambda0
+        k_pack_A<256><<<std::min(divUp(6 * d.nP, 256), 148), 256, 0, stream>>>(d); mark("pack_A");
+        allReduceSum(d.redA, (size_t)6 * d.nP + nranks);
+    }
 }
 
 // Schur complement -> multifrontal Cholesky (levels up) -> backward solve (levels
 // down) -> back-substitution (+ landmark part of the update)
 void Solver::enqueueSolve() {
     k_schur_inv<256><<<divUp(d.nL, 256), 256, 0, stream>>>(d); mark("schur_inv");
+    if (nranks > 1) CK(cudaMemsetAsync(d.Hsc, 0, ((size_t)d.nblkG * 36 + (size_t)d.nP * 6) * sizeof(double), stream));
     k_schur_blocks<4><<<divUp(d.nblk, 4), 128, 0, stream>>>(d); mark("schur_blocks");
+    // the one exchange step of a trial: partial reduced camera systems [Hsc | bsc] summed over the ranks
+    if (nranks > 1) allReduceSum(d.Hsc, (size_t)d.nblkG * 36 + (size_t)d.nP * 6);
     const int ncMax = 6 * CHOL_MAXW;
     if (cholGen >= 2) {
         const bool g3 = cholGen == 3;
@@ -578,6 +677,10 @@ void Solver::enqueueSlot() {
     enqueueSolve();
     k_update_poses<128><<<divUp(d.nP, 128), 128, 0, stream>>>(d); mark("update_poses");
     k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 1, 1); mark("errors");
+    if (nranks > 1) {
+        k_lm_sums<256><<<1, 256, 0, stream>>>(d); mark("lm_sums");
+        allReduceSum(d.redC, 2);
+    }
     k_lm_decide<256><<<1, 256, 0, stream>>>(d); mark("lm_decide");
 }
 
@@ -588,6 +691,7 @@ int Solver::profileSlot(int cap, char* names, int nameLen, double* ms) {
     ensureStructure();
     use();
     k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
+    if (nranks > 1) { k_lm_sums<256><<<1, 256, 0, stream>>>(d); allReduceSum(d.redC, 2); }
     k_lm_begin<256><<<1, 256, 0, stream>>>(d, 1);
     const int saved = kernelsPerSlot;
     profiling = true;
@@ -681,7 +785,27 @@ static double readScalar(Solver& S, int slot) {
     return S.h_scalars[slot];
 }
 
+void Solver::commInit(int n, int r, const char* id) {
+    if (n < 1 || r < 0 || r >= n || !id) throw ArgError("comm_init: bad rank / size");
+    if (comm) throw StateError("comm_init: this solver already has a communicator");
+    use();
+    if (n == 1) return;
+    if (!g_nccl.load(err)) throw CudaError(err);
+    ncclUniqueId uid;
+    static_assert(sizeof(uid) == 128, "ncclUniqueId is 128 bytes");
+    memcpy(&uid, id, sizeof(uid));
+    NK(g_nccl.CommInitRank(&comm, n, uid, r));
+    nranks = n; rank = r;
+    // one collective outside any capture: connections are set up before the trial graph is recorded
+    redC.alloc(2);
+    CK(cudaMemsetAsync(redC.p, 0, 2 * sizeof(double), stream));
+    allReduceSum(redC.p, 2);
+    CK(cudaStreamSynchronize(stream));
+    structDirty = true;
+}
+
 double Solver::computeErrors() {
+    requireSingle("compute_errors");
     ensureStructure();
     use();
     k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
@@ -690,6 +814,7 @@ double Solver::computeErrors() {
 }
 
 void Solver::buildSystem() {
+    requireSingle("build_system");
     ensureStructure();
     use();
     k_state_set<<<1, 1, 0, stream>>>(d.st, stagedLambda, 1);
@@ -707,6 +832,7 @@ double Solver::maxDiagonal() {
 }
 
 bool Solver::solve() {
+    requireSingle("solve");
     if (!systemBuilt) throw StateError("solve before build_system");
     use();
     k_state_set<<<1, 1, 0, stream>>>(d.st, stagedLambda, 0);
@@ -747,6 +873,7 @@ int Solver::optimize(int niter, int cap, double* chi2, double* lambda, int* tria
     CK(cudaEventRecord(ev0, stream));
     long launched = 0;
     k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
+    if (nranks > 1) { k_lm_sums<256><<<1, 256, 0, stream>>>(d); allReduceSum(d.redC, 2); launched++; }
     k_lm_begin<256><<<1, 256, 0, stream>>>(d, niter);
     launched += 2;
     int slots = 0;
@@ -940,8 +1067,8 @@ long Solver::getValues(int which, double* out, long cap) {
     case CUGO_B200_HPL: src = Hpl; n = 18L * d.nHpl; break;
     case CUGO_B200_B: src = b; n = 6L * nP + 3L * nL; break;
     case CUGO_B200_X: src = x; n = 6L * nP + 3L * nL; break;
-    case CUGO_B200_BSC: src = bsc; n = 6L * nP; break;
-    case CUGO_B200_HSC: src = Hsc; n = 36L * d.nblk; break;
+    case CUGO_B200_BSC: src = d.bsc; n = 6L * nP; break;
+    case CUGO_B200_HSC: src = Hsc; n = 36L * d.nblkG; break;
     case CUGO_B200_INVHLL: src = invHll; n = 9L * nL; break;
     case CUGO_B200_CHI_PER_EDGE: {
         n = E;
@@ -1166,6 +1293,18 @@ int cugo_b200_profile_trial(cugo_b200_solver* s, int capacity, char* names, int 
 int cugo_b200_update_measurements(cugo_b200_solver* s, int set_id, const double* measurements, const double* omegas,
                                   int nomega) {
     return guarded(s, [&](Solver& S) { S.updateMeasurements(set_id, measurements, omegas, nomega); });
+}
+int cugo_b200_comm_unique_id(char id[128]) {
+    if (!id) return CUGO_B200_EINVAL;
+    std::string err;
+    if (!cugo_b200::g_nccl.load(err)) return CUGO_B200_ECUDA;
+    ncclUniqueId uid;
+    if (cugo_b200::g_nccl.GetUniqueId(&uid) != ncclSuccess) return CUGO_B200_ECUDA;
+    memcpy(id, &uid, 128);
+    return CUGO_B200_OK;
+}
+int cugo_b200_comm_init(cugo_b200_solver* s, int nranks, int rank, const char id[128]) {
+    return guarded(s, [&](Solver& S) { S.commInit(nranks, rank, id); });
 }
 int cugo_b200_get_factor_stats(cugo_b200_solver* s, double stats[4]) {
     return guarded(s, [&](Solver& S) {

@@ -95,6 +95,13 @@ struct Dev {
     double* chiEdge;            // [E] per-edge rho(chi2) in global edge order, or nullptr
     int errGrid;
     LMState* st;
+    // multi-GPU (one process per GPU, landmarks sharded).  Every rank holds all poses
+    // and the *global* Hsc pattern; bRowPtr/bColInd/bRowOf/prodPtr/nblk above describe the LOCAL blocks.
+    int nranks, rank;
+    int nblkG;                  // blocks of the global pattern (== nblk on one GPU)
+    const int* hscSlot;         // [nblk] local block -> global block id, nullptr = identity
+    double* redA;               // [6 nP + nranks] diag(Hpp) partials + one-hot landmark max-diagonal (all-reduced)
+    double* redC;               // [2] chi2, gain denominator (all-reduced)
 };
 
 // multifrontal factorisation data (see symbolic.h)

@@ -22,9 +22,10 @@ __device__ __forceinline__ double sum_array(const double* a, int n, double* sh) 
 template <int TPB>
 __global__ void __launch_bounds__(TPB) k_lm_begin(Dev d, int niter) {
     __shared__ double sh[TPB / 32];
-    const double F = sum_array<TPB>(d.chiPartial, d.errGrid, sh);
+    double F = sum_array<TPB>(d.chiPartial, d.errGrid, sh);
     if (threadIdx.x == 0) {
         LMState* st = d.st;
+        if (d.nranks > 1) F = d.redC[0];
         st->F = F; st->Fhat = F; st->lambda = 0.0; st->nu = 2.0; st->rho = -1.0; st->scale = 0.0;
         st->iter = 0; st->q = 0; st->done = (niter <= 0) ? 1 : 0; st->needBuild = 1; st->fail = 0;
         st->niter = niter; st->nstats = 0; st->slots = 0;
@@ -40,8 +41,12 @@ __global__ void __launch_bounds__(TPB) k_lm_prepare(Dev d) {
     if (st->done) return;
     if (st->needBuild) {
         double m = 0.0;
-        for (int i = threadIdx.x; i < d.nChunks; i += TPB) m = fmax(m, d.maxDiagL[i]);
-        for (int i = threadIdx.x; i < d.nP; i += TPB) m = fmax(m, d.maxDiagP[i]);
+        if (d.nranks > 1) {
+            for (int i = threadIdx.x; i < 6 * d.nP + d.nranks; i += TPB) m = fmax(m, d.redA[i]);
+        } else {
+            for (int i = threadIdx.x; i < d.nChunks; i += TPB) m = fmax(m, d.maxDiagL[i]);
+            for (int i = threadIdx.x; i < d.nP; i += TPB) m = fmax(m, d.maxDiagP[i]);
+        }
         m = block_max<TPB>(m, sh);
         if (threadIdx.x == 0) {
             st->maxDiag = m;
@@ -58,13 +63,14 @@ __global__ void __launch_bounds__(TPB) k_lm_decide(Dev d) {
     __shared__ double sh[TPB / 32];
     LMState* st = d.st;
     if (st->done) return;
-    const double Fhat = sum_array<TPB>(d.chiPartial, d.errGrid, sh);
+    double Fhat = sum_array<TPB>(d.chiPartial, d.errGrid, sh);
     const double lam = st->lambda;
     double s = 0.0;
     for (int i = threadIdx.x; i < 6 * d.nP; i += TPB) s += d.x[i] * (lam * d.x[i] + d.b[i]);
     for (int i = threadIdx.x; i < d.nChunks; i += TPB) s += d.scalePartial[i];
-    const double scaleRaw = block_sum<TPB>(s, sh);
+    double scaleRaw = block_sum<TPB>(s, sh);
     if (threadIdx.x != 0) return;
+    if (d.nranks > 1) { Fhat = d.redC[0]; scaleRaw = d.redC[1]; }   // k_lm_sums + all-reduce ran before
     const int maxq = 10;
     const double F = st->F;
     const double scale = scaleRaw + 1e-3;
@@ -106,6 +112,37 @@ __global__ void __launch_bounds__(TPB) k_lm_decide(Dev d) {
             if (st->iter >= st->niter) st->done = 1;
         }
     }
+}
+
+// ---- multi-GPU: local partial sums that are all-reduced before the LM kernels read them ------------
+// redA = [diag(Hpp_local) (6 nP) | one-hot max diagonal of the local Hll (nranks)]: after a SUM all-reduce
+// every rank can take the max over diag(Hpp_total) and all ranks' landmark maxima.
+template <int TPB>
+__global__ void __launch_bounds__(TPB) k_pack_A(Dev d) {
+    __shared__ double sh[TPB / 32];
+    for (int i = blockIdx.x * TPB + threadIdx.x; i < 6 * d.nP; i += gridDim.x * TPB)
+        d.redA[i] = d.Hpp[(size_t)(i / 6) * 36 + (i % 6) * 7];
+    if (blockIdx.x == 0) {
+        double m = 0.0;
+        for (int i = threadIdx.x; i < d.nChunks; i += TPB) m = fmax(m, d.maxDiagL[i]);
+        m = block_max<TPB>(m, sh);
+        if (threadIdx.x < d.nranks) d.redA[6 * d.nP + threadIdx.x] = 0.0;
+        __syncthreads();
+        if (threadIdx.x == 0) d.redA[6 * d.nP + d.rank] = m;
+    }
+}
+// redC = [chi2 of the rank's edges | gain denominator: pose part with the rank's partial bp (lambda term on
+// rank 0 only) + the rank's landmarks]; both are linear in the per-rank parts, so SUM gives the global values.
+template <int TPB>
+__global__ void __launch_bounds__(TPB) k_lm_sums(Dev d) {
+    __shared__ double sh[TPB / 32];
+    const double chi = sum_array<TPB>(d.chiPartial, d.errGrid, sh);
+    const double lam = d.rank == 0 ? d.st->lambda : 0.0;
+    double s = 0.0;
+    for (int i = threadIdx.x; i < 6 * d.nP; i += TPB) s += d.x[i] * (lam * d.x[i] + d.b[i]);
+    for (int i = threadIdx.x; i < d.nChunks; i += TPB) s += d.scalePartial[i];
+    s = block_sum<TPB>(s, sh);
+    if (threadIdx.x == 0) { d.redC[0] = chi; d.redC[1] = s; }
 }
 
 // ---- helpers of the host-driven (staged) API ---------------------------------

@@ -87,9 +87,10 @@ __global__ void __launch_bounds__(WARPS * 32) k_schur_blocks(Dev d) {
         for (int i = 0; i < 6; i++) accb[i] = warp_sum(accb[i]);
     }
     if (lane == 0) {
-        double* __restrict__ out = d.Hsc + (size_t)blk * 36;
+        double* __restrict__ out = d.Hsc + (size_t)(d.hscSlot ? d.hscSlot[blk] : blk) * 36;
         if (diag) {
-            const double lam = st->lambda;
+            // with several ranks Hpp / bp are partial sums over the rank's edges and lambda is added once
+            const double lam = d.rank == 0 ? st->lambda : 0.0;
             const double* __restrict__ Hp = d.Hpp + (size_t)row * 36;
 #pragma unroll
             for (int i = 0; i < 36; i++) out[i] = Hp[i] + ((i % 7 == 0) ? lam : 0.0) - acc[i];

@@ -164,6 +164,39 @@ __global__ void k_fill_blocks(const unsigned long long* keys, const unsigned lon
     }
 }
 
+// ---- multi-GPU: union of the ranks' Hsc block patterns --------------------------------------------
+constexpr unsigned long long KEY_NONE = 0xffffffffffffffffULL;
+// key of every local block, padded with KEY_NONE up to `padded` entries (equal-size all-gather)
+__global__ void k_block_keys(const int* bRowOf, const int* bColInd, int nblk, int padded, unsigned long long nP,
+                             unsigned long long* keys) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= padded) return;
+    keys[k] = k < nblk ? (unsigned long long)bRowOf[k] * nP + (unsigned long long)bColInd[k] : KEY_NONE;
+}
+__global__ void k_key_heads(const unsigned long long* keys, int n, int* head) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k > n) return;
+    head[k] = (k < n && keys[k] != KEY_NONE && (k == 0 || keys[k] != keys[k - 1])) ? 1 : 0;
+}
+__global__ void k_compact_keys(const unsigned long long* keys, const int* head, const int* idx, int n,
+                               unsigned long long nP, unsigned long long* ukeys, int* rowOf, int* colInd) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n || !head[k]) return;
+    const int g = idx[k];
+    ukeys[g] = keys[k];
+    rowOf[g] = (int)(keys[k] / nP);
+    colInd[g] = (int)(keys[k] % nP);
+}
+__global__ void k_map_slots(const unsigned long long* lkeys, int nblk, const unsigned long long* ukeys, int nblkG,
+                            int* slot) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nblk) return;
+    const unsigned long long key = lkeys[k];
+    int lo = 0, hi = nblkG;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (ukeys[mid] < key) lo = mid + 1; else hi = mid; }
+    slot[k] = lo;
+}
+
 // ---- symbolic factorisation: the shared host/device code run by one thread ----
 __global__ void k_sym_analyze(SymWork w, SymCounts* out) {
     if (blockIdx.x == 0 && threadIdx.x == 0) sym_analyze(w, out);

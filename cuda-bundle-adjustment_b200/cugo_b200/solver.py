@@ -34,7 +34,7 @@ SYMBOLS = (
     "cugo_b200_compute_scale", "cugo_b200_push", "cugo_b200_pop", "cugo_b200_optimize",
     "cugo_b200_get_estimates", "cugo_b200_get_structure", "cugo_b200_get_values", "cugo_b200_get_sizes",
     "cugo_b200_get_last_timing", "cugo_b200_stream", "cugo_b200_profile_trial", "cugo_b200_update_measurements",
-    "cugo_b200_debug_counters", "cugo_b200_get_factor_stats",
+    "cugo_b200_debug_counters", "cugo_b200_get_factor_stats", "cugo_b200_comm_unique_id", "cugo_b200_comm_init",
 )
 
 _lib = None
@@ -226,6 +226,18 @@ class BlockSolver:
         meas, omega = _f64(meas), _f64(omega)
         self._ck(self.lib.cugo_b200_update_measurements(self.h, set_idx, _p(meas, C.c_double), _p(omega, C.c_double),
                                                         int(omega.shape[0])))
+
+    # -- multi-GPU plumbing (see cugo_b200/dist.py) ---------------------------------------------------
+    @staticmethod
+    def comm_unique_id():
+        buf = C.create_string_buffer(128)
+        rc = load_library().cugo_b200_comm_unique_id(buf)
+        if rc != 0:
+            raise CugoError("cugo_b200_comm_unique_id failed with %d (NCCL not loadable?)" % rc)
+        return buf.raw
+
+    def comm_init(self, nranks, rank, uid: bytes):
+        self._ck(self.lib.cugo_b200_comm_init(self.h, int(nranks), int(rank), C.c_char_p(uid)))
 
     def factor_stats(self):
         a = (C.c_double * 4)()

@@ -89,6 +89,16 @@ int cugo_b200_set_outliers(cugo_b200_solver* s, int set_id, const int* mask);
  * src/block_solver.cpp:161-170) */
 int cugo_b200_set_estimates(cugo_b200_solver* s, const double* poses7, const double* landmarks3);
 
+/* -- multi-GPU, one process per GPU (no counterpart in the reference, which is single-GPU): each rank holds
+ * ALL poses and a shard of the landmarks with all their edges (landmark indices local to the shard).  Per LM
+ * trial the ranks' partial reduced camera systems [Hsc | bsc] are summed with one ncclAllReduce on the
+ * solver's stream, every rank factorises redundantly and back-substitutes its own landmarks.  Rank 0 calls
+ * cugo_b200_comm_unique_id and the host distributes the 128 bytes (e.g. torch.distributed.broadcast); every
+ * rank then calls cugo_b200_comm_init before cugo_b200_build_structure.  With nranks > 1 only the
+ * device-resident cugo_b200_optimize path is available (the staged calls return CUGO_B200_ESTATE). */
+int cugo_b200_comm_unique_id(char id[128]);
+int cugo_b200_comm_init(cugo_b200_solver* s, int nranks, int rank, const char id[128]);
+
 /* -- BlockSolver::buildStructure (src/block_solver.cpp:139-248) incl. symbolic analysis */
 int cugo_b200_build_structure(cugo_b200_solver* s);
 

@@ -1,0 +1,78 @@
+"""World-size-2 gloo tests (CPU) of the multi-GPU host logic: landmark sharding (cugo_b200/dist.py) and the
+algebra behind the one exchange step -- the ranks' partial reduced camera systems sum to the full one."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import dist_worker
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def test_landmark_ranges_balance():
+    from cugo_b200 import dist as cdist
+    rng = np.random.default_rng(0)
+    w = rng.integers(1, 15, 1000)
+    for world in (1, 2, 3, 8):
+        b = cdist.landmark_ranges(w, world)
+        assert b[0] == 0 and b[-1] == 1000 and np.all(np.diff(b) >= 0)
+        loads = [w[b[i]:b[i + 1]].sum() for i in range(world)]
+        assert max(loads) - min(loads) <= 2 * w.max()
+    assert cdist.landmark_ranges(np.zeros(0, np.int64), 4).tolist() == [0] * 5
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_shards_partition_the_problem(graphs, world):
+    from cugo_b200 import dist as cdist
+    g, prob = graphs("small", fixed_landmark_frac=0.1, seed=5)
+    seen = np.zeros(prob.landmarks.shape[0], int)
+    n_edges = 0
+    for r in range(world):
+        sh = cdist.shard_problem(prob, world, r)
+        seen[sh.lm_index] += 1
+        n_edges += sh.prob.n_edges
+        nL = sh.prob.nL_act
+        assert np.all(sh.lm_index[:nL] < prob.nL_act) and np.all(sh.lm_index[nL:] >= prob.nL_act)   # free first, then fixed
+        for s in sh.prob.sets:
+            assert s.n == 0 or (s.iL.min() >= 0 and s.iL.max() < sh.lm_index.shape[0])
+        np.testing.assert_array_equal(sh.prob.poses, prob.poses)                                    # poses replicated
+    assert np.all(seen == 1) and n_edges == prob.n_edges
+
+
+def test_partial_reduced_systems_sum_to_the_full_one(graphs, tmp_path):
+    import torch.multiprocessing as mp
+    import oracle as orc
+    world, name, lam = 2, "small", 50.0
+    mp.spawn(dist_worker.run, args=(world, _free_port(), name, lam, str(tmp_path)), nprocs=world, join=True)
+    red = np.load(os.path.join(str(tmp_path), "reduced.npz"))
+    g, prob = graphs(name)
+    P = prob.nP_act
+    o = orc.Oracle(prob)
+    o.build_structure()
+    chi = o.compute_errors()
+    o.build_system()
+    o.set_lambda(lam)
+    assert o.solve() and bool(red["ok"])
+    H = dist_worker.dense_from_bsr(o, P)
+    n = 36 * P * P
+    Hsum = red["sum"][:n].reshape(6 * P, 6 * P) - (world - 1) * lam * np.eye(6 * P)   # every oracle rank added lambda
+    scale = np.abs(H).max()
+    assert np.abs(Hsum - H).max() < 1e-11 * scale
+    bsc = o.values("bsc")
+    assert np.abs(red["sum"][n:n + 6 * P] - bsc).max() < 1e-11 * np.abs(bsc).max()
+    assert red["sum"][n + 6 * P] == pytest.approx(chi, rel=1e-13)
+    assert red["sum"][n + 6 * P + 1] == prob.n_edges and red["sum"][n + 6 * P + 2] == prob.nL_act
+    assert np.all(red["cover"] == 1)
+    np.testing.assert_array_equal(red["gathered"], prob.landmarks)
+    # the reduced system solves for the same pose step as the full oracle
+    Hfull = np.triu(Hsum) + np.triu(Hsum, 1).T
+    xp = np.linalg.solve(Hfull, red["sum"][n:n + 6 * P])
+    assert np.abs(xp - o.values("x")[:6 * P]).max() < 1e-8 * np.abs(xp).max()

@@ -218,3 +218,31 @@ def test_cpp_facade_matches_binding(graphs, tmp_path, name, rk, delta):
     raw = np.fromfile(est, np.float64)
     np.testing.assert_array_equal(raw[:7 * g.n_poses].reshape(-1, 7), np.concatenate([q, t], 1))
     np.testing.assert_array_equal(raw[7 * g.n_poses:].reshape(-1, 3), X)
+
+
+@pytest.mark.parametrize("name,robust,delta", [("small", "none", 1.0), ("kitti07", "none", 1.0), ("small", "huber", 2.4477)])
+def test_two_gpus_match_one(graphs, gpu, tmp_path, name, robust, delta):
+    """Landmarks sharded over 2 GPUs (one process each, NCCL all-reduce of [Hsc | bsc] inside the trial
+    graph): chi2 per iteration within 1e-9 relative of the 1-GPU run, trial counts equal, estimates equal
+    to 1e-9, and the 2-GPU run is bit-reproducible."""
+    import os
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = str(tmp_path / "two.npz")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29731", os.path.join(root, "tests", "dist_gpu_worker.py"), name, "8", out, robust, repr(delta)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-3000:]
+    two = np.load(out)
+    g, prob = graphs(name)
+    s, o = gpu(prob, robust=robust, delta=delta)
+    chi, lam, tr = s.optimize(8)
+    np.testing.assert_array_equal(two["trials"], tr)
+    np.testing.assert_allclose(two["chi2"], chi, rtol=CHI2_RTOL)
+    poses, lms = s.estimates()
+    assert np.abs(two["poses"] - poses).max() < 1e-9 and np.abs(two["lms"] - lms).max() < 1e-9
+    np.testing.assert_array_equal(two["chi2"], two["chi2_again"])
