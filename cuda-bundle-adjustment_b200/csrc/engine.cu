@@ -142,6 +142,11 @@ struct Solver {
     DBuf<unsigned long long> keyA, keyB, valA, valB;
     DBuf<int> ivalA, prodCnt, prodOff, head, blkOf, bRowPtr, bColInd, bRowOf, prodPtr;
     DBuf<int2> prodIJ;
+    DBuf<int> pmFlag, pmPre, poseSlotPtr, poseSlots, slotRank, prodRank, poseDeg, rowWork, rowWorkS, rowIds, rowOrder, unitCnt, unitPtr;
+    DBuf<int2> rowUnits;
+    int nRowUnits = 0;
+    int maxPoseDeg = 0, schurCap = 1;
+    bool schurRows = false;        // k_schur_rows (shared-memory stage fits) or k_schur_blocks
     DBuf<double> Hpp, Hll, Hpl, b, x, invHll, bsc, Hsc, chiPartial, scalePartial, maxDiagL, maxDiagP, chiEdge;
     DBuf<double> scalars;          // small device scratch for reductions
     DBuf<LMState> state;
@@ -463,6 +468,38 @@ void Solver::buildStructure() {
     k_lower_bounds<<<divUp(nP + 1, TB), TB, 0, stream>>>(bRowOf, nblk, nP, bRowPtr);
     nnzSymm = (2 * nblk - nP) * 36;
 
+    // ---- pose-major view of the Hpl blocks + product ranks (k_schur_rows)
+    pmFlag.alloc(E + 1); pmPre.alloc(E + 1); poseSlotPtr.alloc(nP + 1); poseSlots.alloc(std::max(nHpl, 1));
+    slotRank.alloc(std::max(nHpl, 1)); prodRank.alloc(nmulAll); poseDeg.alloc(nP + 1);
+    k_pm_flags<<<gE1, TB, 0, stream>>>(p_src, flag, (int)E, pmFlag);
+    exclusiveScan(*this, pmFlag.p, pmPre.p, (int)E + 1);
+    k_pm_slots<<<gE, TB, 0, stream>>>(p_src, flag, s_hplPre, pmPre, pkeyOut, posePtr, (int)E, poseSlots, slotRank);
+    k_pose_slot_ptr<<<divUp(nP + 1, TB), TB, 0, stream>>>(pmPre, posePtr, nP, poseSlotPtr, poseDeg);
+    k_prod_rank<<<divUp(nmulAll, TB), TB, 0, stream>>>(prodIJ, slotRank, nmulAll, prodRank);
+    {
+        size_t bytes = 0;
+        CK(cub::DeviceReduce::Max(nullptr, bytes, poseDeg.p, poseDeg.p + nP, nP, stream));
+        cubTmp.alloc(bytes);
+        CK(cub::DeviceReduce::Max(cubTmp.p, bytes, poseDeg.p, poseDeg.p + nP, nP, stream));
+        maxPoseDeg = readInt(*this, poseDeg.p + nP);
+        rowWork.alloc(nP); rowWorkS.alloc(nP); rowIds.alloc(nP); rowOrder.alloc(nP);
+        k_row_work<<<divUp(nP, TB), TB, 0, stream>>>(bRowPtr, prodPtr, nP, rowWork, rowIds);
+        CK(cub::DeviceRadixSort::SortPairsDescending(nullptr, bytes, rowWork.p, rowWorkS.p, rowIds.p, rowOrder.p, nP, 0, 32, stream));
+        cubTmp.alloc(bytes);
+        CK(cub::DeviceRadixSort::SortPairsDescending(cubTmp.p, bytes, rowWork.p, rowWorkS.p, rowIds.p, rowOrder.p, nP, 0, 32, stream));
+        unitCnt.alloc(nP + 1); unitPtr.alloc(nP + 1);
+        k_row_unit_count<<<divUp(nP + 1, TB), TB, 0, stream>>>(rowWorkS, nP, unitCnt);
+        exclusiveScan(*this, unitCnt.p, unitPtr.p, nP + 1);
+        nRowUnits = readInt(*this, unitPtr.p + nP);
+        rowUnits.alloc(std::max(nRowUnits, 1));
+        k_row_unit_fill<<<divUp(nP, TB), TB, 0, stream>>>(rowOrder, unitPtr, nP, rowUnits);
+        const char* e = getenv("CUGO_B200_SCHUR");
+        schurRows = !(e && e[0] == '1');
+        schurCap = std::max(1, std::min(maxPoseDeg, SROW_MAX_CAP));
+        if (getenv("CUGO_B200_DEBUG")) fprintf(stderr, "[cugo_b200] max pose degree %d, schur stage %d blocks, %d row units\n", maxPoseDeg, schurCap, nRowUnits);
+        CK(cudaFuncSetAttribute(k_schur_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)srow_smem_bytes(schurCap)));
+    }
+
     // ---- several ranks: the factorisation works on the union of the ranks' block patterns
     const int* gRowPtrP = bRowPtr;
     const int* gColIndP = bColInd;
@@ -564,6 +601,7 @@ void Solver::buildStructure() {
     d.cams = perEdgeCam ? cams.p : nullptr;
     d.colPtr = colPtr; d.rowInd = rowInd; d.hplLm = hplLm;
     d.bRowPtr = bRowPtr; d.bColInd = bColInd; d.bRowOf = bRowOf; d.prodPtr = prodPtr; d.prodIJ = prodIJ;
+    d.poseSlotPtr = poseSlotPtr; d.poseSlots = poseSlots; d.prodRank = prodRank; d.rowUnits = rowUnits;
     d.Hpp = Hpp; d.Hll = Hll; d.Hpl = Hpl; d.b = b; d.x = x; d.invHll = invHll; d.Hsc = Hsc;
     d.bsc = Hsc.p + (size_t)nblkG * 36;
     d.nranks = nranks; d.rank = rank; d.nblkG = nblkG; d.hscSlot = nranks > 1 ? hscSlot.p : nullptr;
@@ -620,7 +658,9 @@ void Solver::enqueueBuild() {
 void Solver::enqueueSolve() {
     k_schur_inv<256><<<divUp(d.nL, 256), 256, 0, stream>>>(d); mark("schur_inv");
     if (nranks > 1) CK(cudaMemsetAsync(d.Hsc, 0, ((size_t)d.nblkG * 36 + (size_t)d.nP * 6) * sizeof(double), stream));
-    k_schur_blocks<4><<<divUp(d.nblk, 4), 128, 0, stream>>>(d); mark("schur_blocks");
+    if (schurRows) k_schur_rows<<<nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), stream>>>(d, schurCap, c.dbg);
+    else k_schur_blocks<4><<<divUp(d.nblk, 4), 128, 0, stream>>>(d);
+    mark("schur_blocks");
     // the one exchange step of a trial: partial reduced camera systems [Hsc | bsc] summed over the ranks
     if (nranks > 1) allReduceSum(d.Hsc, (size_t)d.nblkG * 36 + (size_t)d.nP * 6);
     const int ncMax = 6 * CHOL_MAXW;
@@ -1313,6 +1353,8 @@ int cugo_b200_get_factor_stats(cugo_b200_solver* s, double stats[4]) {
     });
 }
 int cugo_b200_debug_counters(long long* out, int n) {
+    if (out && n == 8192)   // per-row cycles of the Schur kernel
+        return cudaMemcpyFromSymbol(out, cugo_b200::g_schurDbg, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
     if (!out || n < 0 || n > 64 * 24) return CUGO_B200_EINVAL;
     return cudaMemcpyFromSymbol(out, cugo_b200::g_cholDbg, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
 }

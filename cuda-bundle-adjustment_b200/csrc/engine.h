@@ -78,6 +78,11 @@ struct Dev {
     const int* bRowOf;          // [nblk]
     const int* prodPtr;         // [nblk+1]
     const int2* prodIJ;         // [nmul] (Hpl slot of row pose, Hpl slot of col pose); x<0 = none
+    // pose-major view of the Hpl blocks (k_schur_rows)
+    const int* poseSlotPtr;     // [nP+1]
+    const int* poseSlots;       // [nHpl] Hpl slots of every free pose in landmark order
+    const int* prodRank;        // [nmul] rank of the product's row block among its pose's slots, -1 = none
+    const int2* rowUnits;       // [nRowUnits] (block row, unit of the row): work list of k_schur_rows, heavy rows first
     // linear system
     double* Hpp;                // [36 nP]
     double* Hll;                // [9 nL]

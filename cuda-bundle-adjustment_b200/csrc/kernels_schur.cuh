@@ -196,3 +196,340 @@ __global__ void __launch_bounds__(TPB) k_update_poses(Dev d) {
 }
 
 }  // namespace cugo_b200
+
+namespace cugo_b200 {
+
+// ---------------------------------------------------------------------------
+// Second-generation Schur complement: CTAs work on block ROWS of Hsc.
+//   unit     a block row i, or -- for rows with more than SROW_UNIT products -- a run of its blocks
+//            (cut at block boundaries, about SROW_UNIT products each; built by k_row_unit_*).
+//   phase 1  T_e = Hpl_e invHll for every Hpl block of pose i -> shared memory, so that the row's blocks
+//            are read from L2 once per unit instead of once per product; bsc_i = bp_i - sum_e T_e bl.
+//            Poses with more blocks than the stage holds are done in several passes.
+//   phase 2  per product a lane PAIR forms T_i B_j^T (each lane 3 columns, 54 FMAs), 16 products of one
+//            Hsc block per warp round.  Blocks with more than SROW_BIG products are shared by the CTA's
+//            warps (partials combined in warp order); the others are handed to warps one at a time through
+//            a shared counter.  The 16 pair sums are combined by a fixed reduce-scatter tree (19
+//            exchanges), which leaves the 36 totals spread over the lanes for the store.
+// All gathers (Hpl_e, invHll, bl in phase 1; Hpl_j in phase 2) are 16/8-byte cp.async copies issued by
+// CONSECUTIVE lanes for consecutive pieces of a block, into shared memory: a thread-per-block gather costs
+// one L1 tag lookup per lane and instruction (the tag stage, one line per clock, was the bound of both
+// k_schur_blocks and the first row kernel), this one about two per 144-byte block.  Phase 2 keeps two
+// rounds in flight per warp (metadata prefetched one more round ahead).
+// No atomics on data, fixed summation order.  k_schur_blocks stays selectable (CUGO_B200_SCHUR=1).
+// ---------------------------------------------------------------------------
+constexpr int SROW_TPB = 256;
+constexpr int SROW_NW = SROW_TPB / 32;
+constexpr int SROW_RING = 2 * 16 * 18;         // doubles per warp: two stages of 16 Hpl blocks
+constexpr int SROW_SIDE_LD = 14;               // doubles per edge of the phase-1 side stage: invHll 9, bl 3, pad
+constexpr int SROW_REGION = (SROW_NW * SROW_RING > SROW_TPB * SROW_SIDE_LD) ? SROW_NW * SROW_RING : SROW_TPB * SROW_SIDE_LD;
+constexpr int SROW_MAX_CAP = 480;              // Hpl blocks of the T stage: two CTAs per SM
+constexpr int SROW_UNIT = 2048;                // products per work unit
+constexpr int SROW_BIG = 256;                  // blocks with more products are shared by all warps
+
+__host__ __device__ __forceinline__ int srow_units(int nprod) { return nprod > SROW_UNIT ? (nprod + SROW_UNIT - 1) / SROW_UNIT : 1; }
+__host__ __device__ __forceinline__ size_t srow_smem_bytes(int cap) { return ((size_t)cap * 18 + SROW_REGION) * sizeof(double); }
+
+__device__ __forceinline__ void cp_async16(double* smemDst, const double* gsrc) {
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(smemDst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+// final value of element idx (column-major 6x6) of Hsc block b of row i
+__device__ __forceinline__ void srow_store(const Dev& d, const LMState* st, int i, int b, int idx, double s, bool first) {
+    double* __restrict__ out = d.Hsc + (size_t)(d.hscSlot ? d.hscSlot[b] : b) * 36;
+    if (!first) {            // later pass of a pose whose blocks do not fit the shared-memory stage at once
+        out[idx] -= s;
+    } else if (d.bColInd[b] == i) {
+        const double lam = d.rank == 0 ? st->lambda : 0.0;
+        out[idx] = d.Hpp[(size_t)i * 36 + idx] + ((idx % 7 == 0) ? lam : 0.0) - s;
+    } else {
+        out[idx] = -s;
+    }
+}
+
+// element (column-major 6x6) whose total srow_segment leaves in out[j] of this lane, -1 = none
+__device__ __forceinline__ int srow_elem(int lane, int j) {
+    const int k3 = j + ((lane & 16) ? 2 : 0);
+    const int k2 = k3 + ((lane & 8) ? 3 : 0);
+    const int k1 = k2 + ((lane & 4) ? 5 : 0);
+    if (k3 >= 3 || k2 >= 5 || k1 >= 9) return -1;
+    return 18 * (lane & 1) + ((lane & 2) ? 9 : 0) + k1;
+}
+
+// metadata of round r of the segment [pa, pb): sj[m] = Hpl slot whose piece (lane + 32 m) % 9 this lane
+// copies (-1 none), rk = row rank of the product of this lane's pair (-1 none)
+__device__ __forceinline__ void srow_meta(const Dev& d, int pa, int pb, int r, int lane, int sj[5], int& rk) {
+#pragma unroll
+    for (int m = 0; m < 5; m++) {
+        const int x = lane + 32 * m, p = pa + 16 * r + x / 9;
+        sj[m] = (x < 144 && p < pb) ? d.prodIJ[p].y : -1;
+    }
+    const int p = pa + 16 * r + (lane >> 1);
+    rk = p < pb ? d.prodRank[p] : -1;
+}
+__device__ __forceinline__ void srow_issue(const Dev& d, double* buf, int lane, const int sj[5]) {
+#pragma unroll
+    for (int m = 0; m < 5; m++) {
+        const int x = lane + 32 * m;
+        if (sj[m] >= 0) cp_async16(buf + 2 * x, d.Hpl + (size_t)sj[m] * 18 + 2 * (x % 9));
+    }
+    cp_async_commit();
+}
+
+// Sum of T_i(e) B_j(e)^T over the products [pa, pb) whose row rank lies in the stage [c0, c0 + cap).
+// Lane pair lane/2 takes every 16th product, lane parity picks columns 0-2 or 3-5 of the 6x6 result.
+__device__ __forceinline__ void srow_segment(const Dev& d, const double* T, double* ring, int c0, int cap, int pa, int pb,
+                                             int lane, double out[2]) {
+    const int half = lane & 1, pr = lane >> 1;
+    double acc[18];
+#pragma unroll
+    for (int j = 0; j < 18; j++) acc[j] = 0.0;
+    const int nr = (pb - pa + 15) >> 4;
+    if (nr > 0) {
+        int sjn[5], rkc, rkn;
+        srow_meta(d, pa, pb, 0, lane, sjn, rkc);
+        srow_issue(d, ring, lane, sjn);
+        srow_meta(d, pa, pb, 1, lane, sjn, rkn);
+        for (int r = 0; r < nr; r++) {
+            srow_issue(d, ring + ((r + 1) & 1) * (16 * 18), lane, sjn);      // round r + 1 (nothing past the end)
+            int rk2;
+            srow_meta(d, pa, pb, r + 2, lane, sjn, rk2);
+            cp_async_wait_group<1>();                                         // round r has landed
+            __syncwarp();
+            const int e = rkc - c0;
+            const bool ok = e >= 0 && e < cap;
+            if (__any_sync(0xffffffffu, ok)) {
+                if (ok) {
+                    const double* B = ring + (r & 1) * (16 * 18) + pr * 18 + 3 * half;   // element (c, k) at 6 k + c
+                    double bv[3][3];
+#pragma unroll
+                    for (int k = 0; k < 3; k++)
+#pragma unroll
+                        for (int cc = 0; cc < 3; cc++) bv[k][cc] = B[6 * k + cc];
+                    const double2* t2 = reinterpret_cast<const double2*>(T + (size_t)e * 18);
+#pragma unroll
+                    for (int rr = 0; rr < 3; rr++) {
+                        const double2 u0 = t2[rr], u1 = t2[rr + 3], u2 = t2[rr + 6];
+#pragma unroll
+                        for (int cc = 0; cc < 3; cc++) {
+                            acc[cc * 6 + 2 * rr] += u0.x * bv[0][cc] + u1.x * bv[1][cc] + u2.x * bv[2][cc];
+                            acc[cc * 6 + 2 * rr + 1] += u0.y * bv[0][cc] + u1.y * bv[1][cc] + u2.y * bv[2][cc];
+                        }
+                    }
+                }
+            }
+            __syncwarp();                     // the stage is overwritten by the copies of round r + 2
+            rkc = rkn; rkn = rk2;
+        }
+    }
+    // reduce-scatter over the 16 lane pairs: 18 -> 9 -> 5 -> 3 -> 2 values per lane
+    const bool h1 = lane & 2, h2 = lane & 4, h3 = lane & 8, h4 = lane & 16;
+    double a1[9], a2[5], a3[3];
+#pragma unroll
+    for (int j = 0; j < 9; j++) {
+        const double keep = h1 ? acc[j + 9] : acc[j], send = h1 ? acc[j] : acc[j + 9];
+        a1[j] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+    }
+#pragma unroll
+    for (int j = 0; j < 5; j++) {
+        const double lo = a1[j], hi = (j + 5 < 9) ? a1[(j + 5 < 9) ? j + 5 : 0] : 0.0;
+        const double keep = h2 ? hi : lo, send = h2 ? lo : hi;
+        a2[j] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        const double lo = a2[j], hi = (j + 3 < 5) ? a2[(j + 3 < 5) ? j + 3 : 0] : 0.0;
+        const double keep = h3 ? hi : lo, send = h3 ? lo : hi;
+        a3[j] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+        const double lo = a3[j], hi = (j + 2 < 3) ? a3[(j + 2 < 3) ? j + 2 : 0] : 0.0;
+        const double keep = h4 ? hi : lo, send = h4 ? lo : hi;
+        out[j] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+}
+
+__device__ long long g_schurDbg[8192];    // diagnostics: cycles per unit of k_schur_rows
+__global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hpl blocks the stage holds */, int dbg) {
+    extern __shared__ __align__(16) double T[];     // [cap][18], block e at T + 18 e, column-major 6x3
+    double* const region = T + (size_t)cap * 18;    // phase 1: side stage; phase 2: the warps' copy rings
+    __shared__ double part[2][SROW_NW][36];
+    __shared__ double red[SROW_NW][6];
+    __shared__ int nextBlk;
+    const long long tStart = dbg ? clock64() : 0;
+    const LMState* st = d.st;
+    if (st->done) return;
+    const int2 un = d.rowUnits[blockIdx.x];
+    const int i = un.x, u = un.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int s0 = d.poseSlotPtr[i], deg = d.poseSlotPtr[i + 1] - s0;
+    const double* __restrict__ bl = d.b + (size_t)d.nP * 6;
+    const int b0 = d.bRowPtr[i], b1 = d.bRowPtr[i + 1];
+    const int pBeg = d.prodPtr[b0], pEnd = d.prodPtr[b1];
+    // the unit's blocks: those whose first product lies in [pBeg + u q, pBeg + (u + 1) q)
+    const int nun = srow_units(pEnd - pBeg);
+    int ub0 = b0, ub1 = b1;
+    if (nun > 1) {
+        const int q = (pEnd - pBeg + nun - 1) / nun;
+        const int lower = pBeg + u * q;
+        int lo = b0, hi = b1;
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (d.prodPtr[mid] < lower) lo = mid + 1; else hi = mid; }
+        ub0 = lo;
+        if (u + 1 < nun) {
+            hi = b1;
+            while (lo < hi) { const int mid = (lo + hi) >> 1; if (d.prodPtr[mid] < lower + q) lo = mid + 1; else hi = mid; }
+            ub1 = lo;
+        }
+    }
+    if (ub0 >= ub1 && u > 0) return;                // a block larger than the unit size swallowed this unit
+    const int e0 = srow_elem(lane, 0), e1 = srow_elem(lane, 1);
+    double* const ring = region + wid * SROW_RING;
+    double tb[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    int par = 0;
+    for (int c0 = 0; c0 == 0 || c0 < deg; c0 += cap) {     // one pass unless deg > cap (loop-closure poses)
+        const bool first = (c0 == 0);
+        // ---- phase 1: T_e = Hpl_e invHll for the pose's blocks [c0, c0 + cap)
+        const int nE = min(deg - c0, cap);
+        for (int x = tid; x < nE * 9; x += SROW_TPB) {
+            const int e = x / 9, c = x - 9 * e;
+            cp_async16(T + 2 * x, d.Hpl + (size_t)d.poseSlots[s0 + c0 + e] * 18 + 2 * c);
+        }
+        for (int w0 = 0; w0 < nE; w0 += SROW_TPB) {
+            const int nW = min(SROW_TPB, nE - w0);
+            for (int x = tid; x < nW * 12; x += SROW_TPB) {
+                const int e = x / 12, c = x - 12 * e;
+                const int l = d.hplLm[d.poseSlots[s0 + c0 + w0 + e]];
+                cp_async8(region + e * SROW_SIDE_LD + c, c < 9 ? d.invHll + (size_t)l * 9 + c : bl + (size_t)l * 3 + (c - 9), true);
+            }
+            cp_async_wait_all();
+            __syncthreads();
+            if (tid < nW) {
+                double2* t2 = reinterpret_cast<double2*>(T + (size_t)(w0 + tid) * 18);
+                const double* sd = region + tid * SROW_SIDE_LD;
+                double a[18], ih[9];
+#pragma unroll
+                for (int k = 0; k < 9; k++) { const double2 v = t2[k]; a[2 * k] = v.x; a[2 * k + 1] = v.y; }
+#pragma unroll
+                for (int k = 0; k < 9; k++) ih[k] = sd[k];
+                const double g0 = sd[9], g1 = sd[10], g2 = sd[11];
+                double o[18];
+#pragma unroll
+                for (int r = 0; r < 6; r++) {
+                    const double t0 = a[r] * ih[0] + a[r + 6] * ih[1] + a[r + 12] * ih[2];
+                    const double t1 = a[r] * ih[3] + a[r + 6] * ih[4] + a[r + 12] * ih[5];
+                    const double t2v = a[r] * ih[6] + a[r + 6] * ih[7] + a[r + 12] * ih[8];
+                    o[r] = t0; o[r + 6] = t1; o[r + 12] = t2v;
+                    tb[r] += t0 * g0 + t1 * g1 + t2v * g2;
+                }
+#pragma unroll
+                for (int k = 0; k < 9; k++) t2[k] = make_double2(o[2 * k], o[2 * k + 1]);
+            }
+            __syncthreads();        // the side stage is reused; T is complete after the last wave
+        }
+        if (tid == 0) nextBlk = ub0;
+        __syncthreads();
+        // ---- phase 2a: the large blocks, all warps on each
+        for (int b = ub0; b < ub1; b++) {
+            const int bBeg = d.prodPtr[b], n = d.prodPtr[b + 1] - bBeg;
+            if (n <= SROW_BIG) continue;
+            const int qw = ((n + SROW_NW - 1) / SROW_NW + 15) & ~15;
+            const int pa = bBeg + wid * qw;
+            double o[2];
+            srow_segment(d, T, ring, c0, cap, pa, min(pa + qw, bBeg + n), lane, o);
+            if (e0 >= 0) part[par][wid][e0] = o[0];
+            if (e1 >= 0) part[par][wid][e1] = o[1];
+            __syncthreads();
+            if (tid < 36) {
+                double v = 0.0;
+#pragma unroll
+                for (int w = 0; w < SROW_NW; w++) v += part[par][w][tid];
+                srow_store(d, st, i, b, tid, v, first);
+            }
+            par ^= 1;           // the other buffer: its readers are past the barrier above
+        }
+        // ---- phase 2b: the other blocks, one warp each
+        for (;;) {
+            int b = 0;
+            if (lane == 0) b = atomicAdd(&nextBlk, 1);
+            b = __shfl_sync(0xffffffffu, b, 0);
+            if (b >= ub1) break;
+            const int bBeg = d.prodPtr[b], n = d.prodPtr[b + 1] - bBeg;
+            if (n > SROW_BIG) continue;
+            double o[2];
+            srow_segment(d, T, ring, c0, cap, bBeg, bBeg + n, lane, o);
+            if (e0 >= 0) srow_store(d, st, i, b, e0, o[0], first);
+            if (e1 >= 0) srow_store(d, st, i, b, e1, o[1], first);
+        }
+        __syncthreads();            // the stage and the counter are reused by the next pass
+    }
+    if (u == 0) {
+#pragma unroll
+        for (int r = 0; r < 6; r++) {
+            const double v = warp_sum(tb[r]);
+            if (lane == 0) red[wid][r] = v;
+        }
+        __syncthreads();
+        if (tid < 6) {
+            double s = 0.0;
+            for (int w = 0; w < SROW_NW; w++) s += red[w][tid];
+            d.bsc[(size_t)i * 6 + tid] = d.b[(size_t)i * 6 + tid] - s;
+        }
+    }
+    if (dbg && tid == 0 && blockIdx.x < 8192) g_schurDbg[blockIdx.x] = clock64() - tStart;
+}
+
+// work units of k_schur_rows: rows in launch order (heavy first), each cut into srow_units(products) units
+__global__ void k_row_unit_count(const int* workSorted, int nP, int* cnt) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k > nP) return;
+    cnt[k] = k < nP ? srow_units(workSorted[k]) : 0;
+}
+__global__ void k_row_unit_fill(const int* rowOrder, const int* unitPtr, int nP, int2* units) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nP) return;
+    const int beg = unitPtr[k], end = unitPtr[k + 1], row = rowOrder[k];
+    for (int u = beg; u < end; u++) units[u] = make_int2(row, u - beg);
+}
+
+// product count of every block row (sort key of the launch order: heavy rows first)
+__global__ void k_row_work(const int* bRowPtr, const int* prodPtr, int nP, int* work, int* ids) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nP) return;
+    work[i] = prodPtr[bRowPtr[i + 1]] - prodPtr[bRowPtr[i]];
+    ids[i] = i;
+}
+
+// pose-major view of the Hpl blocks for k_schur_rows (structure build)
+__global__ void k_pm_flags(const int* p_src, const int* flag, int E, int* pmFlag) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k > E) return;
+    pmFlag[k] = k < E ? flag[p_src[k]] : 0;
+}
+__global__ void k_pm_slots(const int* p_src, const int* flag, const int* hplPre, const int* pmPre, const int* poseOfPm,
+                           const int* posePtr, int E, int* poseSlots, int* slotRank) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= E) return;
+    const int e = p_src[k];
+    if (!flag[e]) return;
+    const int slot = hplPre[e];
+    poseSlots[pmPre[k]] = slot;
+    slotRank[slot] = pmPre[k] - pmPre[posePtr[poseOfPm[k]]];
+}
+__global__ void k_pose_slot_ptr(const int* pmPre, const int* posePtr, int nP, int* poseSlotPtr, int* deg) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p > nP) return;
+    poseSlotPtr[p] = pmPre[posePtr[p]];
+    if (p < nP) deg[p] = pmPre[posePtr[p + 1]] - pmPre[posePtr[p]];
+}
+__global__ void k_prod_rank(const int2* prodIJ, const int* slotRank, int n, int* prodRank) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const int s = prodIJ[p].x;
+    prodRank[p] = s < 0 ? -1 : slotRank[s];
+}
+
+}  // namespace cugo_b200

@@ -32,6 +32,13 @@ for nm in ("chol_diag", "chol_trsm", "chol_panel", "chol_update", "chol_bwd"):
     if v:
         print("  %-12s" % nm, v)
 if os.environ.get("CUGO_B200_DEBUG") == "1":
+    import ctypes as C
+    a = (C.c_longlong * 8192)()
+    s.lib.cugo_b200_debug_counters(a, 8192)
+    cyc = np.array(a[:s.sizes()["P"]], dtype=np.int64)
+    print("schur rows: cycles per row  mean %.0f  median %.0f  p99 %.0f  max %.0f  (sum/148/2 = %.0f)" % (
+        cyc.mean(), np.median(cyc), np.percentile(cyc, 99), cyc.max(), cyc.sum() / 296))
+    print("  top rows", np.argsort(cyc)[-8:].tolist(), np.sort(cyc)[-8:].tolist())
     dc = s.debug_counters()
     print("panel phases of CTA 0 per level (cycles): zero, hsc scatter, child pull, factor, store")
     for lev in range(s.sizes()["nlevels"]):
