@@ -142,7 +142,7 @@ struct Solver {
     DBuf<unsigned long long> keyA, keyB, valA, valB;
     DBuf<int> ivalA, prodCnt, prodOff, head, blkOf, bRowPtr, bColInd, bRowOf, prodPtr;
     DBuf<int2> prodIJ;
-    DBuf<int> pmFlag, pmPre, poseSlotPtr, poseSlots, slotRank, prodRank, poseDeg, rowWork, rowWorkS, rowIds, rowOrder, unitCnt, unitPtr;
+    DBuf<int> pmFlag, pmPre, poseSlotPtr, poseSlots, slotRank, prodRank, poseDeg, poseLm, rowWork, rowWorkS, rowIds, rowOrder, unitCnt, unitPtr;
     DBuf<int2> rowUnits;
     int nRowUnits = 0;
     int maxPoseDeg = 0, schurCap = 1;
@@ -476,6 +476,8 @@ void Solver::buildStructure() {
     k_pm_slots<<<gE, TB, 0, stream>>>(p_src, flag, s_hplPre, pmPre, pkeyOut, posePtr, (int)E, poseSlots, slotRank);
     k_pose_slot_ptr<<<divUp(nP + 1, TB), TB, 0, stream>>>(pmPre, posePtr, nP, poseSlotPtr, poseDeg);
     k_prod_rank<<<divUp(nmulAll, TB), TB, 0, stream>>>(prodIJ, slotRank, nmulAll, prodRank);
+    poseLm.alloc(std::max(nHpl, 1));
+    k_pose_lm<<<divUp(std::max(nHpl, 1), TB), TB, 0, stream>>>(poseSlots, hplLm, nHpl, poseLm);
     {
         size_t bytes = 0;
         CK(cub::DeviceReduce::Max(nullptr, bytes, poseDeg.p, poseDeg.p + nP, nP, stream));
@@ -601,7 +603,7 @@ void Solver::buildStructure() {
     d.cams = perEdgeCam ? cams.p : nullptr;
     d.colPtr = colPtr; d.rowInd = rowInd; d.hplLm = hplLm;
     d.bRowPtr = bRowPtr; d.bColInd = bColInd; d.bRowOf = bRowOf; d.prodPtr = prodPtr; d.prodIJ = prodIJ;
-    d.poseSlotPtr = poseSlotPtr; d.poseSlots = poseSlots; d.prodRank = prodRank; d.rowUnits = rowUnits;
+    d.poseSlotPtr = poseSlotPtr; d.poseSlots = poseSlots; d.prodRank = prodRank; d.poseLm = poseLm; d.rowUnits = rowUnits;
     d.Hpp = Hpp; d.Hll = Hll; d.Hpl = Hpl; d.b = b; d.x = x; d.invHll = invHll; d.Hsc = Hsc;
     d.bsc = Hsc.p + (size_t)nblkG * 36;
     d.nranks = nranks; d.rank = rank; d.nblkG = nblkG; d.hscSlot = nranks > 1 ? hscSlot.p : nullptr;
@@ -616,7 +618,8 @@ void Solver::buildStructure() {
     c.childIdx = z_childIdx; c.invPtr = z_invPtr; c.inv = z_inv; c.snBlkPtr = z_snBlkPtr; c.asmBlk = z_asmBlk;
     c.asmRow = z_asmRow; c.asmCol = z_asmCol; c.trsmPtr = z_trsmPtr; c.updPtr = z_updPtr;
     c.L = cL; c.U = cU; c.xperm = cX; c.Winv = cW;
-    { const char* e = getenv("CUGO_B200_DEBUG"); c.dbg = (e && e[0] == '1') ? 1 : 0; }
+    { const char* e = getenv("CUGO_B200_DEBUG"); c.dbg = (e && e[0] == '1') ? 1 : 0;
+      const char* x = getenv("CUGO_B200_EXPERIMENT"); if (x) c.dbg |= atoi(x) << 4; }   // timing experiments only
 
     // dynamic shared memory opt-in for the factorisation kernels
     const int ncMax = 6 * CHOL_MAXW;

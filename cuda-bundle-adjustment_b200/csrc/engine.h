@@ -81,6 +81,7 @@ struct Dev {
     // pose-major view of the Hpl blocks (k_schur_rows)
     const int* poseSlotPtr;     // [nP+1]
     const int* poseSlots;       // [nHpl] Hpl slots of every free pose in landmark order
+    const int* poseLm;          // [nHpl] landmark of poseSlots[k]
     const int* prodRank;        // [nmul] rank of the product's row block among its pose's slots, -1 = none
     const int2* rowUnits;       // [nRowUnits] (block row, unit of the row): work list of k_schur_rows, heavy rows first
     // linear system

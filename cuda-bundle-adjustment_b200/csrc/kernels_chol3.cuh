@@ -55,10 +55,45 @@ __device__ __forceinline__ void pull_unit(const Chol& c, const ChildRef* chs, in
     }
 }
 
+// Cholesky factor of the 6x6 diagonal block jb of the shared-memory panel by one warp (every lane the same
+// arithmetic, lane 0 stores): L_D into the panel, the reciprocal diagonal into invAll.
+__device__ __forceinline__ void panel_factor_diag(double* A, double* invAll, int* badFlag, int jb, int lane) {
+    const int j0 = 6 * jb;
+    double Ld[21], invd[6];
+#pragma unroll
+    for (int i = 0; i < 6; i++)
+#pragma unroll
+        for (int k = 0; k <= i; k++) Ld[tri(i, k)] = A[(j0 + k) * PANEL_LD + j0 + i];
+    bool bad = false;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        double x = Ld[tri(k, k)];
+        if (!(x > CHOL_PIVOT_TOL)) { bad = true; x = 1.0; }
+        const double inv = rsqrt(x);
+        invd[k] = inv;
+        Ld[tri(k, k)] = x * inv;
+#pragma unroll
+        for (int i = k + 1; i < 6; i++) Ld[tri(i, k)] *= inv;
+#pragma unroll
+        for (int cc = k + 1; cc < 6; cc++)
+#pragma unroll
+            for (int i = cc; i < 6; i++) Ld[tri(i, cc)] -= Ld[tri(i, k)] * Ld[tri(cc, k)];
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < 6; i++)
+#pragma unroll
+            for (int k = 0; k <= i; k++) A[(j0 + k) * PANEL_LD + j0 + i] = Ld[tri(i, k)];
+#pragma unroll
+        for (int k = 0; k < 6; k++) invAll[6 * jb + k] = invd[k];
+        if (bad) *badFlag = 1;
+    }
+}
+
 __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int lev) {
-    extern __shared__ double A[];                 // PANEL_LD x nc, column-major
+    extern __shared__ __align__(16) double A[];   // PANEL_LD x nc, column-major
     __shared__ ChildRef chs[CHOL_MAXCH];
-    __shared__ double Wall[21 * CHOL_MAXW];   // W = L_D^-1 of every block column (packed lower)
+    __shared__ __align__(16) double invAll[6 * CHOL_MAXW];  // reciprocal diagonal of every factored 6x6 block
     __shared__ int badFlag;
     LMState* st = d.st;
     if (st->done) return;
@@ -144,118 +179,50 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     }
     __syncthreads();
     CHOL_STAMP(3);
-    // ---- factorisation by 6-column blocks with one block column of look-ahead
+    // ---- factorisation by 6-column blocks.  Per block column jb two phases:
+    //   S   every row below the diagonal block solves x L_D^T = a (one thread per row);
+    //   X   warp 0 applies block column jb to the next diagonal block and factors it, while the worker
+    //       warps apply block column jb to the rest of block column jb+1 and then the finished columns
+    //       [0, 6 jb + 6) to block column jb+2 (look-ahead) -- so the chain of dependent diagonal factors
+    //       never waits for the bulk updates.
+    // Warps 4, 8, 12 share warp 0's scheduler / FP64 pipe and sit phase X out.
     const int fr8 = lane >> 2, fk = lane & 3;
     const bool dbgT = c.dbg && blockIdx.x == 0 && tid == 0 && lev < 64;
     long long tF = 0, tW = 0, tS = 0, tU = 0, t0 = 0, t1 = 0;
+    const bool dbgK = (c.dbg & 256) && blockIdx.x == 0 && tid == 32 && lev < 64;   // a worker warp's view
+    long long wU = 0, wL = 0, w0 = 0, w1 = 0;
+    if (wid == 0) panel_factor_diag(A, invAll, &badFlag, 0, lane);
+    __syncthreads();
+    constexpr int NWK = 3 * (PANEL3_NW / 4);        // 12 worker warps
+    const int wk = (wid >> 2) * 3 + (wid & 3) - 1;   // worker index of warps with (wid & 3) != 0
     for (int jb = 0; jb < nt; jb++) {
-        const int j0 = 6 * jb, j1 = j0 + 6;
+        const int j0 = 6 * jb, j1 = j0 + 6, j2 = j1 + 6;
         const bool more = (jb + 1 < nt);
         if (dbgT) t0 = clock64();
-        // phase F: warp 0 factors D_jj; the others apply the finished columns [0, j0) to block column jb+1
-        if (wid == 0) {
-            double Ld[21], W[21], invd[6];
-#pragma unroll
-            for (int i = 0; i < 6; i++)
-#pragma unroll
-                for (int k = 0; k <= i; k++) Ld[tri(i, k)] = A[(j0 + k) * PANEL_LD + j0 + i];
-            bool bad = false;
-#pragma unroll
-            for (int k = 0; k < 6; k++) {
-                double x = Ld[tri(k, k)];
-                if (!(x > CHOL_PIVOT_TOL)) { bad = true; x = 1.0; }
-                const double inv = rsqrt(x);
-                invd[k] = inv;
-                Ld[tri(k, k)] = x * inv;
-#pragma unroll
-                for (int i = k + 1; i < 6; i++) Ld[tri(i, k)] *= inv;
-#pragma unroll
-                for (int cc = k + 1; cc < 6; cc++)
-#pragma unroll
-                    for (int i = cc; i < 6; i++) Ld[tri(i, cc)] -= Ld[tri(i, k)] * Ld[tri(cc, k)];
-            }
-#pragma unroll
-            for (int k = 0; k < 6; k++) {
-                W[tri(k, k)] = invd[k];
-#pragma unroll
-                for (int i = k + 1; i < 6; i++) {
-                    double s = 0.0;
-#pragma unroll
-                    for (int p = k; p < i; p++) s += Ld[tri(i, p)] * W[tri(p, k)];
-                    W[tri(i, k)] = -invd[i] * s;
-                }
-            }
-            if (lane == 0) {
-#pragma unroll
-                for (int i = 0; i < 6; i++)
-#pragma unroll
-                    for (int k = 0; k <= i; k++) A[(j0 + k) * PANEL_LD + j0 + i] = Ld[tri(i, k)];
-#pragma unroll
-                for (int i = 0; i < 21; i++) Wall[21 * jb + i] = W[i];
-                if (bad) badFlag = 1;
-            }
-        } else if (more && j0 > 0 && (wid & 3) != 0) {
-            // warps 4, 8, 12 share warp 0's scheduler / FP64 pipe: they stay idle so that the DMMAs of the
-            // look-ahead never delay the dependent DFMA chain of the diagonal factor
-            const int nmt = (R - j1 + 7) >> 3;          // <= 19 tiles of 8 rows: at most two per worker warp
-            constexpr int NLA = 3 * (PANEL3_NW / 4);    // 12 look-ahead warps
-            const int ta = (wid >> 2) * 3 + (wid & 3) - 1, tb = ta + NLA;
-            if (ta < nmt) {
-                const bool two = tb < nmt;
-                const double* Bp = A + j1 + fr8;
-                const double* Ap = A + j1 + 8 * ta + fr8;
-                const double* Aq = A + j1 + 8 * (two ? tb : ta) + fr8;
-                double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0, e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
-#pragma unroll 2
-                for (int k0 = 0; k0 < j0; k0 += 8) {
-                    const int ka = k0 + fk, kb = k0 + 4 + fk;
-                    const bool va = ka < j0, vb = kb < j0;
-                    const double b0 = va ? Bp[ka * PANEL_LD] : 0.0;
-                    const double b1 = vb ? Bp[kb * PANEL_LD] : 0.0;
-                    const double a0 = va ? Ap[ka * PANEL_LD] : 0.0;
-                    const double a1 = vb ? Ap[kb * PANEL_LD] : 0.0;
-                    dmma884(c00, c01, a0, b0);
-                    dmma884(c10, c11, a1, b1);
-                    if (two) {
-                        const double q0 = va ? Aq[ka * PANEL_LD] : 0.0;
-                        const double q1 = vb ? Aq[kb * PANEL_LD] : 0.0;
-                        dmma884(e00, e01, q0, b0);
-                        dmma884(e10, e11, q1, b1);
-                    }
-                }
-                const int cl = 2 * fk;
-                if (cl < 6) {
-                    const int r = j1 + 8 * ta + fr8;
-                    if (r < R) {
-                        A[(j1 + cl) * PANEL_LD + r] -= c00 + c10;
-                        A[(j1 + cl + 1) * PANEL_LD + r] -= c01 + c11;
-                    }
-                    const int r2 = j1 + 8 * tb + fr8;
-                    if (two && r2 < R) {
-                        A[(j1 + cl) * PANEL_LD + r2] -= e00 + e10;
-                        A[(j1 + cl + 1) * PANEL_LD + r2] -= e01 + e11;
-                    }
-                }
-            }
-        }
-        if (dbgT) { t1 = clock64(); tF += t1 - t0; }
-        __syncthreads();
-        if (dbgT) { t0 = clock64(); tW += t0 - t1; }
-        // phase S: one thread per row below the diagonal block, x = a W^T
+        // phase S
         {
             const int r = j1 + tid;
             if (r < R) {
-                double W[21], a[6], x[6];
+                double x[6], Lc[5][6], iv[6];
 #pragma unroll
-                for (int i = 0; i < 21; i++) W[i] = Wall[21 * jb + i];
+                for (int k = 0; k < 6; k++) x[k] = A[(j0 + k) * PANEL_LD + r];
 #pragma unroll
-                for (int k = 0; k < 6; k++) a[k] = A[(j0 + k) * PANEL_LD + r];
+                for (int p = 0; p < 5; p++) {
+                    const double2* lp = reinterpret_cast<const double2*>(A + (j0 + p) * PANEL_LD + j0);
+#pragma unroll
+                    for (int h = 0; h < 3; h++) { const double2 v = lp[h]; Lc[p][2 * h] = v.x; Lc[p][2 * h + 1] = v.y; }
+                }
+                {
+                    const double2* ip = reinterpret_cast<const double2*>(invAll + 6 * jb);
+#pragma unroll
+                    for (int h = 0; h < 3; h++) { const double2 v = ip[h]; iv[2 * h] = v.x; iv[2 * h + 1] = v.y; }
+                }
 #pragma unroll
                 for (int k = 0; k < 6; k++) {
-                    double s = a[0] * W[tri(k, 0)];
+                    double sv = x[k];
 #pragma unroll
-                    for (int p = 1; p <= k; p++) s += a[p] * W[tri(k, p)];
-                    x[k] = s;
+                    for (int p = 0; p < k; p++) sv -= x[p] * Lc[p][k];
+                    x[k] = sv * iv[k];
                 }
 #pragma unroll
                 for (int k = 0; k < 6; k++) A[(j0 + k) * PANEL_LD + r] = x[k];
@@ -263,28 +230,117 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
         }
         __syncthreads();
         if (dbgT) { t1 = clock64(); tS += t1 - t0; }
-        // phase U: rank-6 update of block column jb+1 with the block column just finished
-        if (more) {
-            const int nmt = (R - j1 + 7) >> 3;
-            const double* Bp = A + j1 + fr8;
-            for (int t = wid; t < nmt; t += PANEL3_NW) {
-                const double* Ap = A + j1 + 8 * t + fr8;
-                const double a0 = Ap[(j0 + fk) * PANEL_LD], b0 = Bp[(j0 + fk) * PANEL_LD];
-                const double a1 = fk < 2 ? Ap[(j0 + 4 + fk) * PANEL_LD] : 0.0;
-                const double b1 = fk < 2 ? Bp[(j0 + 4 + fk) * PANEL_LD] : 0.0;
-                double c0 = 0.0, c1 = 0.0;
-                dmma884(c0, c1, a0, b0);
-                dmma884(c0, c1, a1, b1);
-                const int r = j1 + 8 * t + fr8, cl = 2 * fk;
-                if (cl < 6 && r < R) {
-                    A[(j1 + cl) * PANEL_LD + r] -= c0;
-                    A[(j1 + cl + 1) * PANEL_LD + r] -= c1;
+        if (!more) break;
+        // phase X
+        if (wid == 0) {
+            if (lane < 21) {                          // D_(jb+1) -= L_(jb+1,jb) L_(jb+1,jb)^T, one entry per lane
+                int i = 0;
+#pragma unroll
+                for (int q = 1; q < 6; q++) i += (lane >= tri(q, 0)) ? 1 : 0;
+                const int k = lane - tri(i, 0);
+                double sv = 0.0;
+#pragma unroll
+                for (int p = 0; p < 6; p++) sv += A[(j0 + p) * PANEL_LD + j1 + i] * A[(j0 + p) * PANEL_LD + j1 + k];
+                A[(j1 + k) * PANEL_LD + j1 + i] -= sv;
+            }
+            __syncwarp();
+            panel_factor_diag(A, invAll, &badFlag, jb + 1, lane);
+            if (dbgT) { t0 = clock64(); tF += t0 - t1; }
+        } else if ((wid & 3) != 0) {
+            // block column jb -> rows below the diagonal block of block column jb+1 (8-row tiles from row j2)
+            if (dbgK) w0 = clock64();
+            if (!(c.dbg & 32)) {
+                const int nmt = (R - j2 + 7) >> 3;
+                const double* Bp = A + j1 + fr8;
+                for (int t = wk; t < nmt; t += NWK) {
+                    const double* Ap = A + j2 + 8 * t + fr8;
+                    const double a0 = Ap[(j0 + fk) * PANEL_LD], b0 = Bp[(j0 + fk) * PANEL_LD];
+                    // unconditional loads + select (columns j1, j1+1 exist): a guarded load compiles to a branch
+                    double a1 = Ap[(j0 + 4 + fk) * PANEL_LD], b1 = Bp[(j0 + 4 + fk) * PANEL_LD];
+                    if (fk >= 2) { a1 = 0.0; b1 = 0.0; }
+                    double c0 = 0.0, c1 = 0.0;
+                    dmma884(c0, c1, a0, b0);
+                    dmma884(c0, c1, a1, b1);
+                    const int r = j2 + 8 * t + fr8, cl = 2 * fk;
+                    if (cl < 6 && r < R) {
+                        A[(j1 + cl) * PANEL_LD + r] -= c0;
+                        A[(j1 + cl + 1) * PANEL_LD + r] -= c1;
+                    }
                 }
             }
-            __syncthreads();
+            if (dbgK) { w1 = clock64(); wU += w1 - w0; }
+            // look-ahead: finished columns [0, j1) -> block column jb+2 (all its rows, from j2)
+            if (jb + 2 < nt && !(c.dbg & 16)) {
+                const int nmt = (R - j2 + 7) >> 3;          // <= 19 tiles of 8 rows: at most two per worker warp
+                const int ta = wk, tb = ta + NWK;
+                if (ta < nmt) {
+                    // lane (fr8, fk) reads row (tile base + fr8) of column k0 + fk [+ 4]; pointers advance by
+                    // eight columns per iteration, the partial last group is handled after the loop
+                    const double* Bp = A + j2 + fr8 + fk * PANEL_LD;
+                    const double* Ap = Bp + 8 * ta;
+                    const int nfull = j1 >> 3, rem = j1 & 7;
+                    const bool va = fk < rem, vb = fk + 4 < rem;
+                    double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0;
+                    const int cl = 2 * fk;
+                    if (tb < nmt) {
+                        const double* Aq = Bp + 8 * tb;
+                        double e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
+#pragma unroll 2
+                        for (int it = 0; it < nfull; it++) {
+                            const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
+                            const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                            const double q0 = Aq[0], q1 = Aq[4 * PANEL_LD];
+                            dmma884(c00, c01, a0, b0);
+                            dmma884(c10, c11, a1, b1);
+                            dmma884(e00, e01, q0, b0);
+                            dmma884(e10, e11, q1, b1);
+                            Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD; Aq += 8 * PANEL_LD;
+                        }
+                        if (rem) {                  // columns up to j1 + 7 < nc exist: load, then select
+                            double b0 = Bp[0], b1 = Bp[4 * PANEL_LD], a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                            double q0 = Aq[0], q1 = Aq[4 * PANEL_LD];
+                            if (!va) { b0 = 0.0; a0 = 0.0; q0 = 0.0; }
+                            if (!vb) { b1 = 0.0; a1 = 0.0; q1 = 0.0; }
+                            dmma884(c00, c01, a0, b0);
+                            dmma884(c10, c11, a1, b1);
+                            dmma884(e00, e01, q0, b0);
+                            dmma884(e10, e11, q1, b1);
+                        }
+                        const int r2 = j2 + 8 * tb + fr8;
+                        if (cl < 6 && r2 < R) {
+                            A[(j2 + cl) * PANEL_LD + r2] -= e00 + e10;
+                            A[(j2 + cl + 1) * PANEL_LD + r2] -= e01 + e11;
+                        }
+                    } else {
+#pragma unroll 2
+                        for (int it = 0; it < nfull; it++) {
+                            const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
+                            const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                            dmma884(c00, c01, a0, b0);
+                            dmma884(c10, c11, a1, b1);
+                            Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD;
+                        }
+                        if (rem) {
+                            double b0 = Bp[0], b1 = Bp[4 * PANEL_LD], a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                            if (!va) { b0 = 0.0; a0 = 0.0; }
+                            if (!vb) { b1 = 0.0; a1 = 0.0; }
+                            dmma884(c00, c01, a0, b0);
+                            dmma884(c10, c11, a1, b1);
+                        }
+                    }
+                    const int r = j2 + 8 * ta + fr8;
+                    if (cl < 6 && r < R) {
+                        A[(j2 + cl) * PANEL_LD + r] -= c00 + c10;
+                        A[(j2 + cl + 1) * PANEL_LD + r] -= c01 + c11;
+                    }
+                }
+            }
+            if (dbgK) wL += clock64() - w1;
         }
-        if (dbgT) tU += clock64() - t1;
+        __syncthreads();
+        if (dbgT) { t1 = clock64(); tW += t1 - t0; }
     }
+    if (dbgK) { g_cholDbg[lev * 24 + 20] = wU; g_cholDbg[lev * 24 + 21] = wL; }
     if (dbgT) {
         g_cholDbg[lev * 24 + 12] = tF; g_cholDbg[lev * 24 + 13] = tW;
         g_cholDbg[lev * 24 + 14] = tS; g_cholDbg[lev * 24 + 15] = tU;
@@ -293,7 +349,25 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     // ---- write the panel rows this CTA owns (a warp per column, lanes along the rows)
     double* __restrict__ Pn = c.L + c.Lptr[n.t];
     if (slab == 0) {
-        for (int i = tid; i < 21 * nt; i += PANEL3_TPB) c.Winv[(size_t)n.s * 21 + i] = Wall[i];
+        // W = L_D^-1 of every block column for the solves (k_chol_bwd3): one thread per (block, column)
+        if (tid < 6 * nt) {
+            const int jb = tid / 6, k = tid % 6, j0 = 6 * jb;
+            double w[6];
+#pragma unroll
+            for (int i = 0; i < 6; i++) w[i] = (i == k) ? invAll[6 * jb + i] : 0.0;
+#pragma unroll
+            for (int i = 1; i < 6; i++) {
+                if (i > k) {
+                    double sv = 0.0;
+#pragma unroll
+                    for (int p = 0; p < i; p++) sv += A[(j0 + p) * PANEL_LD + j0 + i] * w[p];   // w[p] = 0 for p < k
+                    w[i] = -invAll[6 * jb + i] * sv;
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 6; i++)
+                if (i >= k) c.Winv[(size_t)(n.s + jb) * 21 + tri(i, k)] = w[i];
+        }
         if (tid == 0 && badFlag) st->fail = 1;
     }
     for (int cc = wid; cc < nc; cc += PANEL3_NW) {

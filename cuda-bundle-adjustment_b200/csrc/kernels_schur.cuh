@@ -394,16 +394,33 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
         const bool first = (c0 == 0);
         // ---- phase 1: T_e = Hpl_e invHll for the pose's blocks [c0, c0 + cap)
         const int nE = min(deg - c0, cap);
-        for (int x = tid; x < nE * 9; x += SROW_TPB) {
-            const int e = x / 9, c = x - 9 * e;
-            cp_async16(T + 2 * x, d.Hpl + (size_t)d.poseSlots[s0 + c0 + e] * 18 + 2 * c);
+        for (int x0 = tid; x0 < nE * 9; x0 += 4 * SROW_TPB) {       // index loads of four copies first
+            int sl[4];
+#pragma unroll
+            for (int v = 0; v < 4; v++) {
+                const int x = x0 + v * SROW_TPB;
+                sl[v] = x < nE * 9 ? d.poseSlots[s0 + c0 + x / 9] : -1;
+            }
+#pragma unroll
+            for (int v = 0; v < 4; v++) {
+                const int x = x0 + v * SROW_TPB;
+                if (sl[v] >= 0) cp_async16(T + 2 * x, d.Hpl + (size_t)sl[v] * 18 + 2 * (x % 9));
+            }
         }
         for (int w0 = 0; w0 < nE; w0 += SROW_TPB) {
             const int nW = min(SROW_TPB, nE - w0);
-            for (int x = tid; x < nW * 12; x += SROW_TPB) {
-                const int e = x / 12, c = x - 12 * e;
-                const int l = d.hplLm[d.poseSlots[s0 + c0 + w0 + e]];
-                cp_async8(region + e * SROW_SIDE_LD + c, c < 9 ? d.invHll + (size_t)l * 9 + c : bl + (size_t)l * 3 + (c - 9), true);
+            int lv[12];                                             // piece x = tid + 256 m: edge x / 12, double x % 12
+#pragma unroll
+            for (int m = 0; m < 12; m++) {
+                const int x = tid + m * SROW_TPB;
+                lv[m] = x < nW * 12 ? d.poseLm[s0 + c0 + w0 + x / 12] : -1;
+            }
+#pragma unroll
+            for (int m = 0; m < 12; m++) {
+                const int x = tid + m * SROW_TPB, e = x / 12, c = x - 12 * e;
+                if (lv[m] >= 0)
+                    cp_async8(region + e * SROW_SIDE_LD + c,
+                              c < 9 ? d.invHll + (size_t)lv[m] * 9 + c : bl + (size_t)lv[m] * 3 + (c - 9), true);
             }
             cp_async_wait_all();
             __syncthreads();
@@ -524,6 +541,10 @@ __global__ void k_pose_slot_ptr(const int* pmPre, const int* posePtr, int nP, in
     if (p > nP) return;
     poseSlotPtr[p] = pmPre[posePtr[p]];
     if (p < nP) deg[p] = pmPre[posePtr[p + 1]] - pmPre[posePtr[p]];
+}
+__global__ void k_pose_lm(const int* poseSlots, const int* hplLm, int n, int* poseLm) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) poseLm[k] = hplLm[poseSlots[k]];
 }
 __global__ void k_prod_rank(const int2* prodIJ, const int* slotRank, int n, int* prodRank) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;

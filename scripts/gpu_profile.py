@@ -44,7 +44,7 @@ if os.environ.get("CUGO_B200_DEBUG") == "1":
     for lev in range(s.sizes()["nlevels"]):
         print("  lev %2d panel" % lev, np.diff(dc[lev, :6]).tolist(), " update (stage, mma, pull+store)",
               np.diff(dc[lev, 8:12]).tolist(), " bwd (load, gemv, trsv)", np.diff(dc[lev, 16:20]).tolist(),
-              " factor loop (warp0 factor, wait lookahead, solve, rank6)", dc[lev, 12:16].tolist())
+              " factor loop (warp0 factor, wait lookahead, solve, rank6)", dc[lev, 12:16].tolist(), " worker (rank6, look-ahead)", dc[lev, 20:22].tolist())
 for rep in range(5):
     s.set_estimates(prob.poses, prob.landmarks)
     chi, lam, tr = s.optimize(10)
