@@ -143,8 +143,8 @@ struct Solver {
     DBuf<int> ivalA, prodCnt, prodOff, head, blkOf, bRowPtr, bColInd, bRowOf, prodPtr;
     DBuf<int2> prodIJ;
     DBuf<int> pmFlag, pmPre, poseSlotPtr, poseSlots, slotRank, prodRank, poseDeg, poseLm, rowWork, rowWorkS, rowIds, rowOrder, unitCnt, unitPtr;
-    DBuf<int2> rowUnits;
-    int nRowUnits = 0;
+    DBuf<int2> rowUnits, blkPass;
+    int nRowUnits = 0, schurPasses = 1, schurUnit = 2048;
     int maxPoseDeg = 0, schurCap = 1;
     bool schurRows = false;        // k_schur_rows (shared-memory stage fits) or k_schur_blocks
     DBuf<double> Hpp, Hll, Hpl, b, x, invHll, bsc, Hsc, chiPartial, scalePartial, maxDiagL, maxDiagP, chiEdge;
@@ -489,15 +489,22 @@ void Solver::buildStructure() {
         CK(cub::DeviceRadixSort::SortPairsDescending(nullptr, bytes, rowWork.p, rowWorkS.p, rowIds.p, rowOrder.p, nP, 0, 32, stream));
         cubTmp.alloc(bytes);
         CK(cub::DeviceRadixSort::SortPairsDescending(cubTmp.p, bytes, rowWork.p, rowWorkS.p, rowIds.p, rowOrder.p, nP, 0, 32, stream));
+        schurCap = std::max(1, std::min(maxPoseDeg, SROW_MAX_CAP));
+        schurPasses = std::max(1, (maxPoseDeg + schurCap - 1) / schurCap);
+        schurUnit = std::max(SROW_UNIT, nmulAll / 1200);
         unitCnt.alloc(nP + 1); unitPtr.alloc(nP + 1);
-        k_row_unit_count<<<divUp(nP + 1, TB), TB, 0, stream>>>(rowWorkS, nP, unitCnt);
+        k_row_unit_count<<<divUp(nP + 1, TB), TB, 0, stream>>>(rowWorkS, nP, schurUnit, unitCnt);
         exclusiveScan(*this, unitCnt.p, unitPtr.p, nP + 1);
         nRowUnits = readInt(*this, unitPtr.p + nP);
         rowUnits.alloc(std::max(nRowUnits, 1));
         k_row_unit_fill<<<divUp(nP, TB), TB, 0, stream>>>(rowOrder, unitPtr, nP, rowUnits);
+        if (schurPasses > 1) {
+            blkPass.alloc((size_t)nblk * schurPasses);
+            k_blk_pass_init<<<divUp(nblk * schurPasses, TB), TB, 0, stream>>>(nblk * schurPasses, blkPass);
+            k_blk_pass<<<divUp(nmulAll, TB), TB, 0, stream>>>(prodRank, head, blkOf, nmulAll, schurCap, schurPasses, blkPass);
+        }
         const char* e = getenv("CUGO_B200_SCHUR");
         schurRows = !(e && e[0] == '1');
-        schurCap = std::max(1, std::min(maxPoseDeg, SROW_MAX_CAP));
         if (getenv("CUGO_B200_DEBUG")) fprintf(stderr, "[cugo_b200] max pose degree %d, schur stage %d blocks, %d row units\n", maxPoseDeg, schurCap, nRowUnits);
         CK(cudaFuncSetAttribute(k_schur_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)srow_smem_bytes(schurCap)));
     }
@@ -618,8 +625,7 @@ void Solver::buildStructure() {
     c.childIdx = z_childIdx; c.invPtr = z_invPtr; c.inv = z_inv; c.snBlkPtr = z_snBlkPtr; c.asmBlk = z_asmBlk;
     c.asmRow = z_asmRow; c.asmCol = z_asmCol; c.trsmPtr = z_trsmPtr; c.updPtr = z_updPtr;
     c.L = cL; c.U = cU; c.xperm = cX; c.Winv = cW;
-    { const char* e = getenv("CUGO_B200_DEBUG"); c.dbg = (e && e[0] == '1') ? 1 : 0;
-      const char* x = getenv("CUGO_B200_EXPERIMENT"); if (x) c.dbg |= atoi(x) << 4; }   // timing experiments only
+    { const char* e = getenv("CUGO_B200_DEBUG"); c.dbg = e ? atoi(e) : 0; }   // 1: phase stamps; 3: also a worker warp's view of the panel loop
 
     // dynamic shared memory opt-in for the factorisation kernels
     const int ncMax = 6 * CHOL_MAXW;
@@ -661,7 +667,8 @@ void Solver::enqueueBuild() {
 void Solver::enqueueSolve() {
     k_schur_inv<256><<<divUp(d.nL, 256), 256, 0, stream>>>(d); mark("schur_inv");
     if (nranks > 1) CK(cudaMemsetAsync(d.Hsc, 0, ((size_t)d.nblkG * 36 + (size_t)d.nP * 6) * sizeof(double), stream));
-    if (schurRows) k_schur_rows<<<nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), stream>>>(d, schurCap, c.dbg);
+    if (schurRows) k_schur_rows<<<nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), stream>>>(d, schurCap, c.dbg, schurUnit, schurPasses,
+                                                                                         schurPasses > 1 ? blkPass.p : nullptr);
     else k_schur_blocks<4><<<divUp(d.nblk, 4), 128, 0, stream>>>(d);
     mark("schur_blocks");
     // the one exchange step of a trial: partial reduced camera systems [Hsc | bsc] summed over the ranks

@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     const int fr8 = lane >> 2, fk = lane & 3;
     const bool dbgT = c.dbg && blockIdx.x == 0 && tid == 0 && lev < 64;
     long long tF = 0, tW = 0, tS = 0, tU = 0, t0 = 0, t1 = 0;
-    const bool dbgK = (c.dbg & 256) && blockIdx.x == 0 && tid == 32 && lev < 64;   // a worker warp's view
+    const bool dbgK = (c.dbg & 2) && blockIdx.x == 0 && tid == 32 && lev < 64;   // a worker warp's view
     long long wU = 0, wL = 0, w0 = 0, w1 = 0;
     if (wid == 0) panel_factor_diag(A, invAll, &badFlag, 0, lane);
     __syncthreads();
@@ -249,7 +249,7 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
         } else if ((wid & 3) != 0) {
             // block column jb -> rows below the diagonal block of block column jb+1 (8-row tiles from row j2)
             if (dbgK) w0 = clock64();
-            if (!(c.dbg & 32)) {
+            {
                 const int nmt = (R - j2 + 7) >> 3;
                 const double* Bp = A + j1 + fr8;
                 for (int t = wk; t < nmt; t += NWK) {
@@ -270,7 +270,7 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
             }
             if (dbgK) { w1 = clock64(); wU += w1 - w0; }
             // look-ahead: finished columns [0, j1) -> block column jb+2 (all its rows, from j2)
-            if (jb + 2 < nt && !(c.dbg & 16)) {
+            if (jb + 2 < nt) {
                 const int nmt = (R - j2 + 7) >> 3;          // <= 19 tiles of 8 rows: at most two per worker warp
                 const int ta = wk, tb = ta + NWK;
                 if (ta < nmt) {

@@ -224,10 +224,10 @@ constexpr int SROW_RING = 2 * 16 * 18;         // doubles per warp: two stages o
 constexpr int SROW_SIDE_LD = 14;               // doubles per edge of the phase-1 side stage: invHll 9, bl 3, pad
 constexpr int SROW_REGION = (SROW_NW * SROW_RING > SROW_TPB * SROW_SIDE_LD) ? SROW_NW * SROW_RING : SROW_TPB * SROW_SIDE_LD;
 constexpr int SROW_MAX_CAP = 480;              // Hpl blocks of the T stage: two CTAs per SM
-constexpr int SROW_UNIT = 2048;                // products per work unit
+constexpr int SROW_UNIT = 2048;                // least products per work unit (engine: max(this, products / 1200))
 constexpr int SROW_BIG = 256;                  // blocks with more products are shared by all warps
 
-__host__ __device__ __forceinline__ int srow_units(int nprod) { return nprod > SROW_UNIT ? (nprod + SROW_UNIT - 1) / SROW_UNIT : 1; }
+__host__ __device__ __forceinline__ int srow_units(int nprod, int unit) { return nprod > unit ? (nprod + unit - 1) / unit : 1; }
 __host__ __device__ __forceinline__ size_t srow_smem_bytes(int cap) { return ((size_t)cap * 18 + SROW_REGION) * sizeof(double); }
 
 __device__ __forceinline__ void cp_async16(double* smemDst, const double* gsrc) {
@@ -355,7 +355,11 @@ __device__ __forceinline__ void srow_segment(const Dev& d, const double* T, doub
 }
 
 __device__ long long g_schurDbg[8192];    // diagnostics: cycles per unit of k_schur_rows
-__global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hpl blocks the stage holds */, int dbg) {
+// blkPass (several passes only): per (block, pass) the range of the block's products whose row rank lies in
+// the pass's stage -- products of a block are ordered by landmark, as are the slots of a pose, so the range
+// is tight; the per-product rank test stays as the guarantee.
+__global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hpl blocks the stage holds */, int dbg,
+                                                            int unitProd, int npass, const int2* __restrict__ blkPass) {
     extern __shared__ __align__(16) double T[];     // [cap][18], block e at T + 18 e, column-major 6x3
     double* const region = T + (size_t)cap * 18;    // phase 1: side stage; phase 2: the warps' copy rings
     __shared__ double part[2][SROW_NW][36];
@@ -371,7 +375,7 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
     const int b0 = d.bRowPtr[i], b1 = d.bRowPtr[i + 1];
     const int pBeg = d.prodPtr[b0], pEnd = d.prodPtr[b1];
     // the unit's blocks: those whose first product lies in [pBeg + u q, pBeg + (u + 1) q)
-    const int nun = srow_units(pEnd - pBeg);
+    const int nun = srow_units(pEnd - pBeg, unitProd);
     int ub0 = b0, ub1 = b1;
     if (nun > 1) {
         const int q = (pEnd - pBeg + nun - 1) / nun;
@@ -450,8 +454,11 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
         if (tid == 0) nextBlk = ub0;
         __syncthreads();
         // ---- phase 2a: the large blocks, all warps on each
+        const int ps = c0 / cap;
         for (int b = ub0; b < ub1; b++) {
-            const int bBeg = d.prodPtr[b], n = d.prodPtr[b + 1] - bBeg;
+            int bBeg, n;
+            if (blkPass) { const int2 rg = blkPass[(size_t)b * npass + ps]; bBeg = rg.x; n = max(rg.y - rg.x, 0); }
+            else { bBeg = d.prodPtr[b]; n = d.prodPtr[b + 1] - bBeg; }
             if (n <= SROW_BIG) continue;
             const int qw = ((n + SROW_NW - 1) / SROW_NW + 15) & ~15;
             const int pa = bBeg + wid * qw;
@@ -474,8 +481,10 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
             if (lane == 0) b = atomicAdd(&nextBlk, 1);
             b = __shfl_sync(0xffffffffu, b, 0);
             if (b >= ub1) break;
-            const int bBeg = d.prodPtr[b], n = d.prodPtr[b + 1] - bBeg;
-            if (n > SROW_BIG) continue;
+            int bBeg, n;
+            if (blkPass) { const int2 rg = blkPass[(size_t)b * npass + ps]; bBeg = rg.x; n = max(rg.y - rg.x, 0); }
+            else { bBeg = d.prodPtr[b]; n = d.prodPtr[b + 1] - bBeg; }
+            if (n > SROW_BIG || (n == 0 && !first)) continue;
             double o[2];
             srow_segment(d, T, ring, c0, cap, bBeg, bBeg + n, lane, o);
             if (e0 >= 0) srow_store(d, st, i, b, e0, o[0], first);
@@ -500,10 +509,24 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
 }
 
 // work units of k_schur_rows: rows in launch order (heavy first), each cut into srow_units(products) units
-__global__ void k_row_unit_count(const int* workSorted, int nP, int* cnt) {
+__global__ void k_row_unit_count(const int* workSorted, int nP, int unitProd, int* cnt) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k > nP) return;
-    cnt[k] = k < nP ? srow_units(workSorted[k]) : 0;
+    cnt[k] = k < nP ? srow_units(workSorted[k], unitProd) : 0;
+}
+// per (block, pass) product range of k_schur_rows
+__global__ void k_blk_pass_init(int n, int2* blkPass) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) blkPass[k] = make_int2(0x7fffffff, 0);
+}
+__global__ void k_blk_pass(const int* prodRank, const int* head, const int* blkOf, int n, int cap, int npass, int2* blkPass) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const int rk = prodRank[p];
+    if (rk < 0) return;
+    int2* rg = blkPass + (size_t)(blkOf[p] + head[p] - 1) * npass + rk / cap;
+    atomicMin(&rg->x, p);
+    atomicMax(&rg->y, p + 1);
 }
 __global__ void k_row_unit_fill(const int* rowOrder, const int* unitPtr, int nP, int2* units) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
