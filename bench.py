@@ -118,7 +118,7 @@ def run_ours(args, rank, world):
     if world == 1:
         g = synth.make_graph(args.workload)
         prob = pack.pack(g)
-        s = solver.BlockSolver(dev)
+        s = solver.BlockSolver(dev, f32=args.f32)
         s.initialize(prob)
         shard_prob = prob
     else:
@@ -292,8 +292,9 @@ def run_ours(args, rank, world):
         "ms_per_step": dev_ms / args.steps, "ms_per_lm_iteration": dev_ms / args.steps / iters_done,
         "higher_is_better": True, "scaling": "weak" if world == 1 else "replicas", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic (seeded generator cugo_b200/synth.py; reference inputs are absent)",
-        "config": {"workload": "%s: %d poses / %d landmarks / %d edges (%d stereo), %d LM iterations, FP64" % (
-            args.workload, g.n_poses, g.n_landmarks, E, len(g.stereo_p), args.iters),
+        "config": {"workload": "%s: %d poses / %d landmarks / %d edges (%d stereo), %d LM iterations, %s" % (
+            args.workload, g.n_poses, g.n_landmarks, E, len(g.stereo_p), args.iters,
+            "FP64 arithmetic, FP32 Hpl storage (USE_FLOAT32 mode)" if args.f32 else "FP64"),
             "timing": "CUDA events on the solver stream around optimize(); L2 flushed (256 MB fill) between steps",
             "sizes": sizes},
         "e2e": {"value": e2e_value, "unit": "edges/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
@@ -379,6 +380,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=WORKLOAD)
+    ap.add_argument("--f32", action="store_true", help="USE_FLOAT32 mode: single-precision Hpl storage (1 GPU)")
     ap.add_argument("--iters", type=int, default=NITER)
     ap.add_argument("--cpu-iters", type=int, default=10)
     args = ap.parse_args()

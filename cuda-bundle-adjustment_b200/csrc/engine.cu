@@ -147,6 +147,8 @@ struct Solver {
     int nRowUnits = 0, schurPasses = 1, schurUnit = 2048;
     int maxPoseDeg = 0, schurCap = 1;
     bool schurRows = false;        // k_schur_rows (shared-memory stage fits) or k_schur_blocks
+    bool f32 = false;              // USE_FLOAT32 mode: Hpl blocks stored in single precision (arithmetic stays FP64)
+    DBuf<float> HplF;
     DBuf<double> Hpp, Hll, Hpl, b, x, invHll, bsc, Hsc, chiPartial, scalePartial, maxDiagL, maxDiagP, chiEdge;
     DBuf<double> scalars;          // small device scratch for reductions
     DBuf<LMState> state;
@@ -506,7 +508,8 @@ void Solver::buildStructure() {
         const char* e = getenv("CUGO_B200_SCHUR");
         schurRows = !(e && e[0] == '1');
         if (getenv("CUGO_B200_DEBUG")) fprintf(stderr, "[cugo_b200] max pose degree %d, schur stage %d blocks, %d row units\n", maxPoseDeg, schurCap, nRowUnits);
-        CK(cudaFuncSetAttribute(k_schur_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)srow_smem_bytes(schurCap)));
+        CK(cudaFuncSetAttribute(k_schur_rows<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)srow_smem_bytes(schurCap)));
+        CK(cudaFuncSetAttribute(k_schur_rows<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)srow_smem_bytes(schurCap)));
     }
 
     // ---- several ranks: the factorisation works on the union of the ranks' block patterns
@@ -591,7 +594,8 @@ void Solver::buildStructure() {
     cL.alloc((size_t)counts.lsize); cU.alloc((size_t)counts.usize); cX.alloc((size_t)P * 6); cW.alloc((size_t)P * 21);
 
     // ---- system buffers
-    Hpp.alloc((size_t)nP * 36); Hll.alloc((size_t)nL * 9); Hpl.alloc((size_t)nHpl * 18);
+    Hpp.alloc((size_t)nP * 36); Hll.alloc((size_t)nL * 9);
+    if (f32) HplF.alloc((size_t)nHpl * 18); else Hpl.alloc((size_t)nHpl * 18);
     b.alloc((size_t)nP * 6 + (size_t)nL * 3); x.alloc((size_t)nP * 6 + (size_t)nL * 3);
     invHll.alloc((size_t)nL * 9);
     Hsc.alloc((size_t)nblkG * 36 + (size_t)nP * 6);     // [Hsc | bsc] contiguous: one all-reduce with several ranks
@@ -611,7 +615,7 @@ void Solver::buildStructure() {
     d.colPtr = colPtr; d.rowInd = rowInd; d.hplLm = hplLm;
     d.bRowPtr = bRowPtr; d.bColInd = bColInd; d.bRowOf = bRowOf; d.prodPtr = prodPtr; d.prodIJ = prodIJ;
     d.poseSlotPtr = poseSlotPtr; d.poseSlots = poseSlots; d.prodRank = prodRank; d.poseLm = poseLm; d.rowUnits = rowUnits;
-    d.Hpp = Hpp; d.Hll = Hll; d.Hpl = Hpl; d.b = b; d.x = x; d.invHll = invHll; d.Hsc = Hsc;
+    d.Hpp = Hpp; d.Hll = Hll; d.Hpl = f32 ? nullptr : Hpl.p; d.HplF = f32 ? HplF.p : nullptr; d.b = b; d.x = x; d.invHll = invHll; d.Hsc = Hsc;
     d.bsc = Hsc.p + (size_t)nblkG * 36;
     d.nranks = nranks; d.rank = rank; d.nblkG = nblkG; d.hscSlot = nranks > 1 ? hscSlot.p : nullptr;
     d.redA = nranks > 1 ? redA.p : nullptr; d.redC = nranks > 1 ? redC.p : nullptr;
@@ -654,7 +658,9 @@ void Solver::buildStructure() {
 // kernel sequences
 // ---------------------------------------------------------------------------
 void Solver::enqueueBuild() {
-    k_build_lm<LM_CHUNK><<<d.nChunks, LM_CHUNK, 0, stream>>>(d, sp); mark("build_lm");
+    if (f32) k_build_lm<LM_CHUNK, float><<<d.nChunks, LM_CHUNK, 0, stream>>>(d, sp);
+    else k_build_lm<LM_CHUNK, double><<<d.nChunks, LM_CHUNK, 0, stream>>>(d, sp);
+    mark("build_lm");
     k_build_pose<128><<<d.nP, 128, 0, stream>>>(d, sp); mark("build_pose");
     if (nranks > 1) {   // max diagonal of the *global* system for lambda0
         k_pack_A<256><<<std::min(divUp(6 * d.nP, 256), 148), 256, 0, stream>>>(d); mark("pack_A");
@@ -667,9 +673,14 @@ void Solver::enqueueBuild() {
 void Solver::enqueueSolve() {
     k_schur_inv<256><<<divUp(d.nL, 256), 256, 0, stream>>>(d); mark("schur_inv");
     if (nranks > 1) CK(cudaMemsetAsync(d.Hsc, 0, ((size_t)d.nblkG * 36 + (size_t)d.nP * 6) * sizeof(double), stream));
-    if (schurRows) k_schur_rows<<<nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), stream>>>(d, schurCap, c.dbg, schurUnit, schurPasses,
-                                                                                         schurPasses > 1 ? blkPass.p : nullptr);
-    else k_schur_blocks<4><<<divUp(d.nblk, 4), 128, 0, stream>>>(d);
+    const int2* bp = schurPasses > 1 ? blkPass.p : nullptr;
+    if (schurRows) {
+        if (f32) k_schur_rows<float><<<nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), stream>>>(d, schurCap, c.dbg, schurUnit, schurPasses, bp);
+        else k_schur_rows<double><<<nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), stream>>>(d, schurCap, c.dbg, schurUnit, schurPasses, bp);
+    } else {
+        if (f32) k_schur_blocks<4, float><<<divUp(d.nblk, 4), 128, 0, stream>>>(d);
+        else k_schur_blocks<4, double><<<divUp(d.nblk, 4), 128, 0, stream>>>(d);
+    }
     mark("schur_blocks");
     // the one exchange step of a trial: partial reduced camera systems [Hsc | bsc] summed over the ranks
     if (nranks > 1) allReduceSum(d.Hsc, (size_t)d.nblkG * 36 + (size_t)d.nP * 6);
@@ -701,7 +712,9 @@ void Solver::enqueueSolve() {
             else k_chol_bwd2<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bytes, stream>>>(d, c, lev);
             mark("chol_bwd");
         }
-        k_backsub<LM_CHUNK><<<d.nChunks, LM_CHUNK, 0, stream>>>(d); mark("backsub");
+        if (f32) k_backsub<LM_CHUNK, float><<<d.nChunks, LM_CHUNK, 0, stream>>>(d);
+        else k_backsub<LM_CHUNK, double><<<d.nChunks, LM_CHUNK, 0, stream>>>(d);
+        mark("backsub");
         return;
     }
     for (int lev = 0; lev < c.nlev; lev++) {
@@ -716,7 +729,9 @@ void Solver::enqueueSolve() {
     for (int lev = c.nlev - 1; lev >= 0; lev--) {
         k_chol_bwd<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bwdBytes, stream>>>(d, c, lev); mark("chol_bwd");
     }
-    k_backsub<LM_CHUNK><<<d.nChunks, LM_CHUNK, 0, stream>>>(d); mark("backsub");
+    if (f32) k_backsub<LM_CHUNK, float><<<d.nChunks, LM_CHUNK, 0, stream>>>(d);
+        else k_backsub<LM_CHUNK, double><<<d.nChunks, LM_CHUNK, 0, stream>>>(d);
+        mark("backsub");
 }
 
 // one LM trial: [build] prepare solve update errors decide
@@ -1035,6 +1050,10 @@ __global__ void k_csr_fill(const int* bRowPtr, const int* bColInd, const int* bR
     }
 }
 // product list in the reference's order: (i, j, k) sorted by (i, j)
+__global__ void k_widen(const float* a, int n, double* out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = (double)a[i];
+}
 __global__ void k_mul_keys(const int2* prodIJ, const int* blkOf, const int* head, int n, unsigned long long nHpl,
                            unsigned long long* keys, int* vals) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1114,7 +1133,17 @@ long Solver::getValues(int which, double* out, long cap) {
     switch (which) {
     case CUGO_B200_HPP: src = Hpp; n = 36L * nP; break;
     case CUGO_B200_HLL: src = Hll; n = 9L * nL; break;
-    case CUGO_B200_HPL: src = Hpl; n = 18L * d.nHpl; break;
+    case CUGO_B200_HPL:
+        n = 18L * d.nHpl;
+        if (f32) {                       // widened copy of the single-precision blocks
+            if (!out || cap < n) return n;
+            chiEdge.alloc((size_t)std::max(n, 1L));
+            k_widen<<<divUp((int)n, 256), 256, 0, stream>>>(HplF.p, (int)n, chiEdge.p);
+            src = chiEdge;
+        } else {
+            src = Hpl;
+        }
+        break;
     case CUGO_B200_B: src = b; n = 6L * nP + 3L * nL; break;
     case CUGO_B200_X: src = x; n = 6L * nP + 3L * nL; break;
     case CUGO_B200_BSC: src = d.bsc; n = 6L * nP; break;
@@ -1177,7 +1206,6 @@ extern "C" {
 int cugo_b200_create(int device, int use_float32, cugo_b200_solver** out) {
     if (!out) return CUGO_B200_EINVAL;
     *out = nullptr;
-    if (use_float32) return CUGO_B200_EUNSUPPORTED;
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return CUGO_B200_ENODEVICE; }
     if (device < 0 || device >= ndev) return CUGO_B200_EINVAL;
@@ -1188,6 +1216,7 @@ int cugo_b200_create(int device, int use_float32, cugo_b200_solver** out) {
         return CUGO_B200_ECUDA;
     }
     s->impl.device = device;
+    s->impl.f32 = use_float32 != 0;
     if (cudaSetDevice(device) != cudaSuccess ||
         cudaStreamCreateWithFlags(&s->impl.stream, cudaStreamNonBlocking) != cudaSuccess) {
         cudaGetLastError();

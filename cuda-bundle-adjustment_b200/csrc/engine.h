@@ -87,7 +87,8 @@ struct Dev {
     // linear system
     double* Hpp;                // [36 nP]
     double* Hll;                // [9 nL]
-    double* Hpl;                // [18 nHpl]
+    double* Hpl;                // [18 nHpl] (FP64 mode)
+    float* HplF;                // [18 nHpl] single-precision storage of the same blocks (USE_FLOAT32 mode), else null
     double* b;                  // [6 nP + 3 nL]
     double* x;                  // [6 nP + 3 nL]
     double* invHll;             // [9 nL]
@@ -137,5 +138,10 @@ struct Chol {
     double* xperm;         // [6P] solution in permuted order
     int dbg;               // 1: kernels record phase timestamps (diagnostics)
 };
+
+// storage type of the Hpl blocks: double, or float in the USE_FLOAT32 mode (arithmetic stays FP64)
+template <typename HT> struct HplOf;
+template <> struct HplOf<double> { static __device__ __forceinline__ double* get(const Dev& d) { return d.Hpl; } };
+template <> struct HplOf<float> { static __device__ __forceinline__ float* get(const Dev& d) { return d.HplF; } };
 
 }  // namespace cugo_b200

@@ -73,11 +73,11 @@ __global__ void __launch_bounds__(TPB) k_errors(Dev d, SetParams sp, int which, 
 // of consecutive edges are consecutive in the CSC); JL^T JL w and JL^T e w are
 // summed per landmark by the segment-head thread in edge order.
 // ---------------------------------------------------------------------------
-template <int TPB>
+template <int TPB, typename HT>
 __global__ void __launch_bounds__(TPB) k_build_lm(Dev d, SetParams sp) {
     __shared__ double acc[LM_CHUNK * 9];      // per landmark: H00 H10 H11 H20 H21 H22 b0 b1 b2
     __shared__ double val[9 * TPB];           // per edge of the tile, component-major
-    __shared__ double hst[TPB * 18];          // Hpl staging
+    __shared__ HT hst[TPB * 18];              // Hpl staging
     __shared__ double shm[TPB / 32];
     const LMState* st = d.st;
     if (st->done || !st->needBuild) return;
@@ -131,12 +131,12 @@ __global__ void __launch_bounds__(TPB) k_build_lm(Dev d, SetParams sp) {
                     // Hpl = JP^T JL w, 6x3 column-major
                     double JP[3][6];
                     jacobian_pose(dim, Xc, cam, JP);
-                    double* h = hst + (size_t)(d.s_hplPre[k] - pre0) * 18;
+                    HT* h = hst + (size_t)(d.s_hplPre[k] - pre0) * 18;
 #pragma unroll
                     for (int c = 0; c < 3; c++)
 #pragma unroll
                         for (int r = 0; r < 6; r++)
-                            h[c * 6 + r] = w * (JP[0][r] * JL[0][c] + JP[1][r] * JL[1][c] + JP[2][r] * JL[2][c]);
+                            h[c * 6 + r] = (HT)(w * (JP[0][r] * JL[0][c] + JP[1][r] * JL[1][c] + JP[2][r] * JL[2][c]));
                 }
             }
         }
@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(TPB) k_build_lm(Dev d, SetParams sp) {
         // coalesced store of this tile's Hpl blocks
         const int last = (base + TPB < e1) ? base + TPB : e1;
         const int cnt = (d.s_hplPre[last] - pre0) * 18;
-        double* __restrict__ dst = d.Hpl + (size_t)pre0 * 18;
+        HT* __restrict__ dst = HplOf<HT>::get(d) + (size_t)pre0 * 18;
         for (int i = tid; i < cnt; i += TPB) dst[i] = hst[i];
         __syncthreads();
     }

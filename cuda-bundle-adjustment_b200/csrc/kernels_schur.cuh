@@ -35,7 +35,7 @@ __global__ void __launch_bounds__(TPB) k_schur_inv(Dev d) {
 // T = Hpl_i invHll (6x3) and accumulates T Hpl_j^T (6x6); diagonal blocks also
 // accumulate T bl for bsc.  Lane partials are combined by a shuffle tree, so the
 // summation order is fixed.  Hsc(i,i) = Hpp_i + lambda I - sum, bsc_i = bp_i - sum.
-template <int WARPS>
+template <int WARPS, typename HT>
 __global__ void __launch_bounds__(WARPS * 32) k_schur_blocks(Dev d) {
     const LMState* st = d.st;
     if (st->done) return;
@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_schur_blocks(Dev d) {
         const int2 ij = d.prodIJ[p];
         if (ij.x < 0) continue;
         const int l = d.hplLm[ij.x];
-        const double* __restrict__ A = d.Hpl + (size_t)ij.x * 18;
+        const HT* __restrict__ A = HplOf<HT>::get(d) + (size_t)ij.x * 18;
         const double* __restrict__ iH = d.invHll + (size_t)l * 9;
         double T[18];
         double ih[9];
@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_schur_blocks(Dev d) {
 #pragma unroll
             for (int c = 0; c < 3; c++) T[c * 6 + r] = a0 * ih[c * 3] + a1 * ih[c * 3 + 1] + a2 * ih[c * 3 + 2];
         }
-        const double* __restrict__ B = d.Hpl + (size_t)ij.y * 18;
+        const HT* __restrict__ B = HplOf<HT>::get(d) + (size_t)ij.y * 18;
 #pragma unroll
         for (int c = 0; c < 6; c++) {
             const double b0 = B[c], b1 = B[c + 6], b2 = B[c + 12];
@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_schur_blocks(Dev d) {
 // xl and the updated landmark into the trial buffer, and adds xl (lambda xl + bl)
 // to the CTA's partial of the LM gain denominator (reference computeScaleKernel
 // :1471-1490).
-template <int TPB>
+template <int TPB, typename HT>
 __global__ void __launch_bounds__(TPB) k_backsub(Dev d) {
     __shared__ double acc[LM_CHUNK * 3];
     __shared__ double part[TPB * 3];
@@ -135,7 +135,7 @@ __global__ void __launch_bounds__(TPB) k_backsub(Dev d) {
         const int nslot = min(TPB, s1 - base);
         for (int it = tid; it < nslot * 3; it += TPB) {
             const int slot = base + it / 3, c = it % 3;
-            const double* __restrict__ h = d.Hpl + (size_t)slot * 18 + c * 6;
+            const HT* __restrict__ h = HplOf<HT>::get(d) + (size_t)slot * 18 + c * 6;
             const double* __restrict__ xr = xp + (size_t)__ldg(d.rowInd + slot) * 6;
             double s = h[0] * xr[0];
 #pragma unroll
@@ -234,6 +234,12 @@ __device__ __forceinline__ void cp_async16(double* smemDst, const double* gsrc) 
     const unsigned dst = (unsigned)__cvta_generic_to_shared(smemDst);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(gsrc));
 }
+// asynchronous copy of two consecutive elements of an Hpl block (16 bytes of doubles, 8 bytes of floats)
+__device__ __forceinline__ void cp_async_pair(double* smemDst, const double* gsrc) { cp_async16(smemDst, gsrc); }
+__device__ __forceinline__ void cp_async_pair(float* smemDst, const float* gsrc) {
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(smemDst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(dst), "l"(gsrc));
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
@@ -271,17 +277,19 @@ __device__ __forceinline__ void srow_meta(const Dev& d, int pa, int pb, int r, i
     const int p = pa + 16 * r + (lane >> 1);
     rk = p < pb ? d.prodRank[p] : -1;
 }
+template <typename HT>
 __device__ __forceinline__ void srow_issue(const Dev& d, double* buf, int lane, const int sj[5]) {
 #pragma unroll
     for (int m = 0; m < 5; m++) {
         const int x = lane + 32 * m;
-        if (sj[m] >= 0) cp_async16(buf + 2 * x, d.Hpl + (size_t)sj[m] * 18 + 2 * (x % 9));
+        if (sj[m] >= 0) cp_async_pair(reinterpret_cast<HT*>(buf) + 2 * x, HplOf<HT>::get(d) + (size_t)sj[m] * 18 + 2 * (x % 9));
     }
     cp_async_commit();
 }
 
 // Sum of T_i(e) B_j(e)^T over the products [pa, pb) whose row rank lies in the stage [c0, c0 + cap).
 // Lane pair lane/2 takes every 16th product, lane parity picks columns 0-2 or 3-5 of the 6x6 result.
+template <typename HT>
 __device__ __forceinline__ void srow_segment(const Dev& d, const double* T, double* ring, int c0, int cap, int pa, int pb,
                                              int lane, double out[2]) {
     const int half = lane & 1, pr = lane >> 1;
@@ -292,10 +300,10 @@ __device__ __forceinline__ void srow_segment(const Dev& d, const double* T, doub
     if (nr > 0) {
         int sjn[5], rkc, rkn;
         srow_meta(d, pa, pb, 0, lane, sjn, rkc);
-        srow_issue(d, ring, lane, sjn);
+        srow_issue<HT>(d, ring, lane, sjn);
         srow_meta(d, pa, pb, 1, lane, sjn, rkn);
         for (int r = 0; r < nr; r++) {
-            srow_issue(d, ring + ((r + 1) & 1) * (16 * 18), lane, sjn);      // round r + 1 (nothing past the end)
+            srow_issue<HT>(d, ring + ((r + 1) & 1) * (16 * 18), lane, sjn);      // round r + 1 (nothing past the end)
             int rk2;
             srow_meta(d, pa, pb, r + 2, lane, sjn, rk2);
             cp_async_wait_group<1>();                                         // round r has landed
@@ -304,12 +312,12 @@ __device__ __forceinline__ void srow_segment(const Dev& d, const double* T, doub
             const bool ok = e >= 0 && e < cap;
             if (__any_sync(0xffffffffu, ok)) {
                 if (ok) {
-                    const double* B = ring + (r & 1) * (16 * 18) + pr * 18 + 3 * half;   // element (c, k) at 6 k + c
+                    const HT* B = reinterpret_cast<const HT*>(ring + (r & 1) * (16 * 18)) + pr * 18 + 3 * half;   // (c, k) at 6 k + c
                     double bv[3][3];
 #pragma unroll
                     for (int k = 0; k < 3; k++)
 #pragma unroll
-                        for (int cc = 0; cc < 3; cc++) bv[k][cc] = B[6 * k + cc];
+                        for (int cc = 0; cc < 3; cc++) bv[k][cc] = (double)B[6 * k + cc];
                     const double2* t2 = reinterpret_cast<const double2*>(T + (size_t)e * 18);
 #pragma unroll
                     for (int rr = 0; rr < 3; rr++) {
@@ -358,6 +366,7 @@ __device__ long long g_schurDbg[8192];    // diagnostics: cycles per unit of k_s
 // blkPass (several passes only): per (block, pass) the range of the block's products whose row rank lies in
 // the pass's stage -- products of a block are ordered by landmark, as are the slots of a pose, so the range
 // is tight; the per-product rank test stays as the guarantee.
+template <typename HT>
 __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hpl blocks the stage holds */, int dbg,
                                                             int unitProd, int npass, const int2* __restrict__ blkPass) {
     extern __shared__ __align__(16) double T[];     // [cap][18], block e at T + 18 e, column-major 6x3
@@ -408,7 +417,8 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
 #pragma unroll
             for (int v = 0; v < 4; v++) {
                 const int x = x0 + v * SROW_TPB;
-                if (sl[v] >= 0) cp_async16(T + 2 * x, d.Hpl + (size_t)sl[v] * 18 + 2 * (x % 9));
+                if (sl[v] >= 0)      // block e lands at the start of its T slot (floats fill half of it)
+                    cp_async_pair(reinterpret_cast<HT*>(T + 18 * (x / 9)) + 2 * (x % 9), HplOf<HT>::get(d) + (size_t)sl[v] * 18 + 2 * (x % 9));
             }
         }
         for (int w0 = 0; w0 < nE; w0 += SROW_TPB) {
@@ -432,8 +442,14 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
                 double2* t2 = reinterpret_cast<double2*>(T + (size_t)(w0 + tid) * 18);
                 const double* sd = region + tid * SROW_SIDE_LD;
                 double a[18], ih[9];
+                if (sizeof(HT) == 8) {
 #pragma unroll
-                for (int k = 0; k < 9; k++) { const double2 v = t2[k]; a[2 * k] = v.x; a[2 * k + 1] = v.y; }
+                    for (int k = 0; k < 9; k++) { const double2 v = t2[k]; a[2 * k] = v.x; a[2 * k + 1] = v.y; }
+                } else {
+                    const float2* f2 = reinterpret_cast<const float2*>(t2);
+#pragma unroll
+                    for (int k = 0; k < 9; k++) { const float2 v = f2[k]; a[2 * k] = v.x; a[2 * k + 1] = v.y; }
+                }
 #pragma unroll
                 for (int k = 0; k < 9; k++) ih[k] = sd[k];
                 const double g0 = sd[9], g1 = sd[10], g2 = sd[11];
@@ -463,7 +479,7 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
             const int qw = ((n + SROW_NW - 1) / SROW_NW + 15) & ~15;
             const int pa = bBeg + wid * qw;
             double o[2];
-            srow_segment(d, T, ring, c0, cap, pa, min(pa + qw, bBeg + n), lane, o);
+            srow_segment<HT>(d, T, ring, c0, cap, pa, min(pa + qw, bBeg + n), lane, o);
             if (e0 >= 0) part[par][wid][e0] = o[0];
             if (e1 >= 0) part[par][wid][e1] = o[1];
             __syncthreads();
@@ -486,7 +502,7 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
             else { bBeg = d.prodPtr[b]; n = d.prodPtr[b + 1] - bBeg; }
             if (n > SROW_BIG || (n == 0 && !first)) continue;
             double o[2];
-            srow_segment(d, T, ring, c0, cap, bBeg, bBeg + n, lane, o);
+            srow_segment<HT>(d, T, ring, c0, cap, bBeg, bBeg + n, lane, o);
             if (e0 >= 0) srow_store(d, st, i, b, e0, o[0], first);
             if (e1 >= 0) srow_store(d, st, i, b, e1, o[1], first);
         }

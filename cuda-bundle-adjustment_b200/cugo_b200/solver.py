@@ -71,10 +71,10 @@ def _i32(a):
 
 
 class BlockSolver:
-    def __init__(self, device=0):
+    def __init__(self, device=0, f32=False):
         self.lib = load_library()
         self.h = C.c_void_p()
-        rc = self.lib.cugo_b200_create(int(device), 0, C.byref(self.h))
+        rc = self.lib.cugo_b200_create(int(device), 1 if f32 else 0, C.byref(self.h))
         if rc != 0:
             raise CugoError("cugo_b200_create failed with %d (%s)" % (
                 rc, {-2: "no CUDA device; this engine has no CPU path", -3: "CUDA error"}.get(rc, "")))

@@ -63,8 +63,13 @@ enum {
 };
 
 /* -- lifetime: replaces CudaDevice (src/cuda_device.cpp:15-42) + BlockSolver ctor. `device` is the
- * CUDA ordinal chosen by the caller (one solver = one device + one stream). use_float32 must be 0
- * in this version (the reference's USE_FLOAT32 build does not compile). */
+ * CUDA ordinal chosen by the caller (one solver = one device + one stream).
+ * use_float32 != 0 selects the counterpart of the reference's USE_FLOAT32 build (include/scalar.h; that
+ * build itself does not compile): the Hpl blocks -- 18 values per edge, the bulk of the bytes
+ * every bandwidth-bound stage moves -- are STORED in single precision; estimates, measurements, residuals,
+ * Jacobians, all accumulation, the Schur complement and the factorisation stay FP64 (as the reference keeps
+ * vertices and measurements double under USE_FLOAT32).  chi2 per iteration stays within 1e-4 relative of the
+ * FP64 run.  cugo_b200_get_values(CUGO_B200_HPL) returns the stored blocks widened to double. */
 int cugo_b200_create(int device, int use_float32, cugo_b200_solver** out);
 int cugo_b200_destroy(cugo_b200_solver* s);
 const char* cugo_b200_last_error(const cugo_b200_solver* s);

@@ -485,7 +485,11 @@ public:
 
 private:
     void open(int device) {
+#ifdef USE_FLOAT32            // the reference's compile-time switch (include/scalar.h): single-precision block storage
+        const int rc = cugo_b200_create(device, 1, &h_);
+#else
         const int rc = cugo_b200_create(device, 0, &h_);
+#endif
         if (rc != CUGO_B200_OK)
             throw std::runtime_error(rc == CUGO_B200_ENODEVICE ? "cugo: no CUDA device (this engine has no CPU path)"
                                                                : "cugo: cannot create the solver");

@@ -30,6 +30,7 @@ def test_no_cpu_fallback_without_device():
     lib = solver.load_library()
     h = C.c_void_p()
     assert lib.cugo_b200_create(0, 0, C.byref(h)) == -2     # CUGO_B200_ENODEVICE
+    assert lib.cugo_b200_create(0, 1, C.byref(h)) == -2     # the USE_FLOAT32 mode is a device mode too
     assert not h.value
 
 

@@ -174,6 +174,37 @@ def test_full_size_properties(graphs, gpu):
     np.testing.assert_allclose(chi_g, chi_o, rtol=CHI2_RTOL)
 
 
+F32_CHI2_RTOL = 1e-4      # north_star: chi2 per iteration within 1e-4 relative under USE_FLOAT32
+
+
+@pytest.mark.parametrize("name,kw,robust,delta", [
+    ("small", {}, "none", 1.0), ("loop", {}, "none", 1.0), ("kitti07", {}, "none", 1.0),
+    ("small", dict(outlier_frac=0.05, seed=7002), "huber", np.sqrt(5.991)),
+    ("kitti00", dict(outlier_frac=0.05, seed=7002), "huber", np.sqrt(5.991))])      # BASELINE.json configs[2]
+def test_float32_mode(graphs, name, kw, robust, delta):
+    """USE_FLOAT32 mode (single-precision Hpl storage) against the FP64 engine, the FP64 oracle and the
+    float build of the oracle (the reference's own USE_FLOAT32 build does not compile: SURVEY.md 8c)."""
+    import oracle as orc
+    from cugo_b200 import solver
+    g, prob = graphs(name, **kw)
+    s64 = solver.BlockSolver(0); s64.initialize(prob, robust=robust, delta=delta)
+    s32 = solver.BlockSolver(0, f32=True); s32.initialize(prob, robust=robust, delta=delta)
+    # one build: the stored blocks are the FP64 blocks rounded to float
+    s64.compute_errors(); s64.build_system(); s32.compute_errors(); s32.build_system()
+    h64, h32 = s64.values("Hpl"), s32.values("Hpl")
+    np.testing.assert_array_equal(h32, h64.astype(np.float32).astype(np.float64))
+    chi64, _, tr64 = s64.optimize(10)
+    chi32, _, tr32 = s32.optimize(10)
+    np.testing.assert_array_equal(tr32, tr64)
+    np.testing.assert_allclose(chi32, chi64, rtol=F32_CHI2_RTOL)
+    p64, l64 = s64.estimates(); p32, l32 = s32.estimates()
+    assert np.sqrt(np.mean((p32 - p64) ** 2)) < 1e-4 and np.sqrt(np.mean((l32 - l64) ** 2)) < 1e-3
+    if name != "kitti00":
+        cf, _, _ = orc.Oracle(prob, robust=robust, delta=delta, f32=True).optimize(10)
+        n = min(len(cf), len(chi32))
+        np.testing.assert_allclose(chi32[:n], cf[:n], rtol=1e-3)   # the all-float oracle is the looser of the two
+
+
 @pytest.mark.parametrize("case", ["tiny", "small", "small_cauchy", "small_tukey", "small_fixedlm", "loop", "kitti07",
                                   "kitti00"])
 def test_engine_matches_reference_goldens(case):
