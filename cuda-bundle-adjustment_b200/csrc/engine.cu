@@ -108,6 +108,7 @@ struct HostSet {
     double delta = 1.0;
     std::vector<int> iP, iL, out;
     std::vector<double> meas, omega, cam;
+    bool stale = false;      // measurements / informations were last updated on the device only (refreshHostSets)
 };
 
 struct Solver {
@@ -197,6 +198,8 @@ struct Solver {
     }
     int profileSlot(int cap, char* names, int nameLen, double* ms);
     void updateMeasurements(int setId, const double* meas, const double* omega, int nomega);
+    void refreshHostSets();
+    DBuf<double> u_meas, u_w;      // staging of one set's interleaved measurements / informations
     bool perEdgeCam_ = false, anyOut_ = false;
     LMState* h_state = nullptr;    // pinned
     double* h_scalars = nullptr;   // pinned
@@ -350,6 +353,7 @@ static int readInt(Solver& S, const int* dptr) {
 void Solver::buildStructure() {
     if (!haveVertices) throw StateError("build_structure before set_vertices");
     use();
+    refreshHostSets();
     if (nL_all == 0 || nL == 0) throw UnsupportedError("graph has no free landmarks: pose-only problems use the reference's dense LU path, outside this engine");
     if (nP == 0) throw UnsupportedError("graph has no free poses");
     E = 0;
@@ -792,28 +796,67 @@ int Solver::profileSlot(int cap, char* names, int nameLen, double* ms) {
 // initialize() of the reference re-uploads the whole edge arena but keeps the
 // structure: src/block_solver.cpp:161-170).  H2D into the raw arrays, then the two
 // gather kernels refresh the landmark-major and pose-major copies.
+// interleaved measurements [n x dim] / informations of one edge set -> the raw SoA arrays
+__global__ void k_scatter_meas(const double* meas, const double* omega, int n, int dim, int nomega, double* m0,
+                               double* m1, double* m2, double* w) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    m0[i] = meas[(size_t)i * dim]; m1[i] = meas[(size_t)i * dim + 1];
+    m2[i] = dim == 3 ? meas[(size_t)i * 3 + 2] : 0.0;
+    w[i] = nomega > 1 ? omega[i] : omega[0];
+}
+__global__ void k_gather_meas(const double* m0, const double* m1, const double* m2, const double* w, int n, int dim,
+                              double* meas, double* omega) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    meas[(size_t)i * dim] = m0[i]; meas[(size_t)i * dim + 1] = m1[i];
+    if (dim == 3) meas[(size_t)i * 3 + 2] = m2[i];
+    omega[i] = w[i];
+}
+
+// Host copies of sets whose measurements were replaced on the device only (the fast path of
+// updateMeasurements) are brought up to date before the raw arrays are rebuilt.
+void Solver::refreshHostSets() {
+    size_t off = 0;
+    for (HostSet& hs : sets) {
+        if (hs.stale && off + hs.n <= (size_t)r_m0.cap) {
+            use();
+            u_meas.alloc((size_t)hs.n * hs.dim); u_w.alloc(hs.n);
+            k_gather_meas<<<divUp(hs.n, 256), 256, 0, stream>>>(r_m0.p + off, r_m1.p + off, r_m2.p + off, r_w.p + off, hs.n,
+                                                               hs.dim, u_meas, u_w);
+            hs.meas.resize((size_t)hs.n * hs.dim); hs.omega.resize(hs.n); hs.nomega = hs.n;
+            CK(cudaMemcpyAsync(hs.meas.data(), u_meas.p, hs.meas.size() * sizeof(double), cudaMemcpyDeviceToHost, stream));
+            CK(cudaMemcpyAsync(hs.omega.data(), u_w.p, hs.omega.size() * sizeof(double), cudaMemcpyDeviceToHost, stream));
+            CK(cudaStreamSynchronize(stream));
+        }
+        hs.stale = false;
+        off += hs.n;
+    }
+}
+
 void Solver::updateMeasurements(int setId, const double* meas, const double* omega, int nomega) {
     if (setId < 0 || setId >= (int)sets.size()) throw ArgError("update_measurements: bad set id");
     HostSet& hs = sets[setId];
     if (!meas || !omega || (nomega != 1 && nomega != hs.n)) throw ArgError("update_measurements: bad arguments");
-    hs.meas.assign(meas, meas + (size_t)hs.n * hs.dim);
-    hs.omega.assign(omega, omega + nomega);
-    hs.nomega = nomega;
-    if (structDirty) return;      // picked up by the next build_structure
+    if (structDirty) {            // no device arrays yet: keep the host copy, the next build_structure uploads it
+        refreshHostSets();
+        hs.meas.assign(meas, meas + (size_t)hs.n * hs.dim);
+        hs.omega.assign(omega, omega + nomega);
+        hs.nomega = nomega;
+        return;
+    }
+    // structure unchanged: the caller's buffers go straight to the device (asynchronous DMA when they are
+    // pinned), are split into the SoA arrays there, and the host copy is only marked stale
     use();
     size_t off = 0;
     for (int i = 0; i < setId; i++) off += sets[i].n;
     const int n = hs.n;
-    std::vector<double> m0(n), m1(n), m2(n), w(n);
-    for (int i = 0; i < n; i++) {
-        m0[i] = meas[(size_t)i * hs.dim]; m1[i] = meas[(size_t)i * hs.dim + 1];
-        m2[i] = hs.dim == 3 ? meas[(size_t)i * 3 + 2] : 0.0;
-        w[i] = nomega > 1 ? omega[i] : omega[0];
-    }
-    CK(cudaMemcpyAsync(r_m0.p + off, m0.data(), n * sizeof(double), cudaMemcpyHostToDevice, stream));
-    CK(cudaMemcpyAsync(r_m1.p + off, m1.data(), n * sizeof(double), cudaMemcpyHostToDevice, stream));
-    CK(cudaMemcpyAsync(r_m2.p + off, m2.data(), n * sizeof(double), cudaMemcpyHostToDevice, stream));
-    CK(cudaMemcpyAsync(r_w.p + off, w.data(), n * sizeof(double), cudaMemcpyHostToDevice, stream));
+    u_meas.alloc((size_t)n * hs.dim); u_w.alloc(std::max(nomega, 1));
+    CK(cudaMemcpyAsync(u_meas.p, meas, (size_t)n * hs.dim * sizeof(double), cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpyAsync(u_w.p, omega, (size_t)nomega * sizeof(double), cudaMemcpyHostToDevice, stream));
+    k_scatter_meas<<<divUp(n, 256), 256, 0, stream>>>(u_meas, u_w, n, hs.dim, nomega, r_m0.p + off, r_m1.p + off,
+                                                      r_m2.p + off, r_w.p + off);
+    hs.stale = true;
     RawEdges raw{(int)E, r_iP, r_iL, r_m0, r_m1, r_m2, r_w, r_set, perEdgeCam_ ? r_cam.p : nullptr,
                  anyOut_ ? r_out.p : nullptr};
     const int TB = 256;

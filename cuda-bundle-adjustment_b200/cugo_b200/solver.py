@@ -178,10 +178,17 @@ class BlockSolver:
         k = min(n.value, cap)
         return chi2[:k].copy(), lam[:k].copy(), trials[:k].copy()
 
-    def estimates(self):
+    def estimates(self, out=None):
+        """(poses [P,7], landmarks [L,3]); `out` = a pair of caller-owned float64 arrays of those shapes (pinned
+        host memory makes the read-back an asynchronous DMA)."""
         P, L = self.prob.poses.shape[0], self.prob.landmarks.shape[0]
-        poses = np.zeros((P, 7), np.float64)
-        lms = np.zeros((L, 3), np.float64)
+        if out is not None:
+            poses, lms = out
+            assert poses.shape == (P, 7) and lms.shape == (L, 3) and poses.dtype == np.float64 and lms.dtype == np.float64
+            assert poses.flags.c_contiguous and lms.flags.c_contiguous
+        else:
+            poses = np.empty((P, 7), np.float64)
+            lms = np.empty((L, 3), np.float64)
         self._ck(self.lib.cugo_b200_get_estimates(self.h, _p(poses, C.c_double), _p(lms, C.c_double)))
         return poses, lms
 

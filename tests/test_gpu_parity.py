@@ -124,6 +124,34 @@ def test_push_pop_and_reinitialise(graphs, gpu):
     np.testing.assert_array_equal(c1, c2)            # bit-reproducible (no atomics anywhere)
 
 
+def test_update_measurements_device_path_and_rebuild(graphs, gpu):
+    """update_measurements with an unchanged structure goes straight to the device (the host copy is only
+    marked stale); a later structure rebuild must pick the new values up again."""
+    import dataclasses
+    from cugo_b200 import pack, solver
+    g, prob = graphs("small")
+    s, _ = gpu(prob)
+    s.optimize(2)
+    rng = np.random.default_rng(5)
+    new_sets = []
+    for i, st in enumerate(prob.sets):
+        m = st.meas + rng.normal(0, 0.3, st.meas.shape)
+        w = st.omega * 0.9
+        s.update_measurements(i, m, w)
+        new_sets.append(dataclasses.replace(st, meas=m, omega=w))
+    s.set_estimates(prob.poses, prob.landmarks)
+    c_fast, _, _ = s.optimize(4)
+    prob2 = pack.Problem(poses=prob.poses, landmarks=prob.landmarks, nP_act=prob.nP_act, nL_act=prob.nL_act,
+                         pose_ids=prob.pose_ids, lm_ids=prob.lm_ids, sets=new_sets)
+    s2 = solver.BlockSolver(0); s2.initialize(prob2)
+    c_ref, _, _ = s2.optimize(4)
+    np.testing.assert_array_equal(c_fast, c_ref)
+    s.set_outliers(0, np.zeros(prob.sets[0].n, np.int32))      # forces a structure rebuild
+    s.set_estimates(prob.poses, prob.landmarks)
+    c_reb, _, _ = s.optimize(4)
+    np.testing.assert_allclose(c_reb, c_ref, rtol=1e-12)
+
+
 def test_outlier_mask(graphs, gpu):
     g, prob = graphs("small", outlier_frac=0.05, seed=7002)
     s, o = gpu(prob)
