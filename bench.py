@@ -88,13 +88,13 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def algorithmic_bytes(prob, sizes):
-    """SURVEY.md section 8(d) per-stage algorithmic bytes (FP64)."""
+def algorithmic_bytes(prob, sizes, f32=False):
+    """SURVEY.md section 8(d) per-stage algorithmic bytes (FP64; Hpl at 4 bytes per value in the USE_FLOAT32 mode)."""
     S = 8
     P, L, E = sizes["P"], sizes["L"], sizes["E"]
     in_e = sum(s.n * (8 + s.dim * S + S) for s in prob.sets)
     V = 7 * S * prob.poses.shape[0] + 3 * S * prob.landmarks.shape[0]
-    Hpl = 18 * S * sizes["nHpl"]
+    Hpl = 18 * (4 if f32 else S) * sizes["nHpl"]
     D_L, d_L, D_P, d_P = 9 * S * L, 3 * S * L, 36 * S * P, 6 * S * P
     IDX = 4 * (L + 1) + 4 * sizes["nHpl"]
     Hsc = 36 * S * sizes["nblk"]
@@ -104,6 +104,7 @@ def algorithmic_bytes(prob, sizes):
         "build_pose": in_e + V + D_P + d_P,                # buildSystem, pose side
         "schur_inv": 2 * D_L,
         "schur_blocks": Hpl + D_L + d_L + D_P + d_P + IDX + Hsc + d_P,
+        "schur_rows": Hpl + D_L + d_L + D_P + d_P + IDX + Hsc + d_P,
         "backsub": Hpl + D_L + 2 * d_L + d_P + IDX + 3 * S * L,
     }
 
@@ -234,7 +235,7 @@ def run_ours(args, rank, world):
     for k, ms in prof:
         a = agg.setdefault(k, [0, 0.0]); a[0] += 1; a[1] += ms
     tot = sum(v[1] for v in agg.values())
-    alg = algorithmic_bytes(prob, sizes)
+    alg = algorithmic_bytes(prob, sizes, args.f32)
     stages = []
     for k, (n, ms) in agg.items():
         e = {"kernel": k, "launches": n, "ms": round(ms, 4), "share": round(ms / tot, 4)}

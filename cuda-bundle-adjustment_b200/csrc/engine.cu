@@ -685,7 +685,7 @@ void Solver::enqueueSolve() {
         if (f32) k_schur_blocks<4, float><<<divUp(d.nblk, 4), 128, 0, stream>>>(d);
         else k_schur_blocks<4, double><<<divUp(d.nblk, 4), 128, 0, stream>>>(d);
     }
-    mark("schur_blocks");
+    mark(schurRows ? "schur_rows" : "schur_blocks");
     // the one exchange step of a trial: partial reduced camera systems [Hsc | bsc] summed over the ranks
     if (nranks > 1) allReduceSum(d.Hsc, (size_t)d.nblkG * 36 + (size_t)d.nP * 6);
     const int ncMax = 6 * CHOL_MAXW;
