@@ -593,6 +593,15 @@ void Solver::buildStructure() {
     CK(cudaMemcpyAsync(h_trsmPtr.data(), z_trsmPtr.p, sizeof(int) * (nsn + 1), cudaMemcpyDeviceToHost, stream));
     CK(cudaMemcpyAsync(h_updPtr.data(), z_updPtr.p, sizeof(int) * (nsn + 1), cudaMemcpyDeviceToHost, stream));
     CK(cudaStreamSynchronize(stream));
+    if (getenv("CUGO_B200_DEBUG")) {
+        fprintf(stderr, "[cugo_b200] elimination tree: %d supernodes, %d levels, max front %d block rows; per level "
+                        "(supernodes / panel CTAs / update tiles / widest):", nsn, counts.nlev, counts.maxFront);
+        for (int lev = 0; lev < counts.nlev; lev++) {
+            const int q0 = h_levelPtr[lev], q1 = h_levelPtr[lev + 1];
+            fprintf(stderr, " %d/%d/%d/%d", q1 - q0, h_trsmPtr[q1] - h_trsmPtr[q0], h_updPtr[q1] - h_updPtr[q0], h_levMaxNt[lev]);
+        }
+        fprintf(stderr, "\n");
+    }
     if (counts.maxCols > CHOL_MAXW) throw CudaError("internal: supernode wider than CHOL_MAXW");
     maxRt = counts.maxFront;   // upper bound of r_t
     cL.alloc((size_t)counts.lsize); cU.alloc((size_t)counts.usize); cX.alloc((size_t)P * 6); cW.alloc((size_t)P * 21);
@@ -1438,6 +1447,8 @@ int cugo_b200_debug_counters(long long* out, int n) {
     if (out && n == 8192)   // per-row cycles of the Schur kernel
         return cudaMemcpyFromSymbol(out, cugo_b200::g_schurDbg, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
     if (!out || n < 0 || n > 64 * 24) return CUGO_B200_EINVAL;
+    if (n == 96)
+        return cudaMemcpyFromSymbol(out, cugo_b200::g_cholTrace, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
     return cudaMemcpyFromSymbol(out, cugo_b200::g_cholDbg, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
 }
 void* cugo_b200_stream(cugo_b200_solver* s) { return s ? (void*)s->impl.stream : nullptr; }

@@ -191,6 +191,7 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     long long tF = 0, tW = 0, tS = 0, tU = 0, t0 = 0, t1 = 0;
     const bool dbgK = (c.dbg & 2) && blockIdx.x == 0 && tid == 32 && lev < 64;   // a worker warp's view
     long long wU = 0, wL = 0, w0 = 0, w1 = 0;
+    const long long tLoop0 = dbgT ? clock64() : 0;
     if (wid == 0) panel_factor_diag(A, invAll, &badFlag, 0, lane);
     __syncthreads();
     constexpr int NWK = 3 * (PANEL3_NW / 4);        // 12 worker warps
@@ -198,10 +199,10 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     for (int jb = 0; jb < nt; jb++) {
         const int j0 = 6 * jb, j1 = j0 + 6, j2 = j1 + 6;
         const bool more = (jb + 1 < nt);
-        if (dbgT) t0 = clock64();
+        if (dbgT) { t0 = clock64(); if (lev == 2 && jb < 16) g_cholTrace[4 * jb] = t0 - tLoop0; }
         // phase S
         {
-            const int r = j1 + tid;
+            const int r = j1 + tid + (dbgT ? (int)((unsigned long long)t0 >> 63) : 0);   // (timing: keeps the phase behind the clock read)
             if (r < R) {
                 double x[6], Lc[5][6], iv[6];
 #pragma unroll
@@ -229,7 +230,7 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
             }
         }
         __syncthreads();
-        if (dbgT) { t1 = clock64(); tS += t1 - t0; }
+        if (dbgT) { t1 = clock64(); tS += t1 - t0; if (lev == 2 && jb < 16) g_cholTrace[4 * jb + 1] = t1 - tLoop0; }
         if (!more) break;
         // phase X
         if (wid == 0) {
@@ -245,46 +246,48 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
             }
             __syncwarp();
             panel_factor_diag(A, invAll, &badFlag, jb + 1, lane);
-            if (dbgT) { t0 = clock64(); tF += t0 - t1; }
+            if (dbgT) { t0 = clock64(); tF += t0 - t1; if (lev == 2 && jb < 16) g_cholTrace[4 * jb + 2] = t0 - tLoop0; }
         } else if ((wid & 3) != 0) {
-            // block column jb -> rows below the diagonal block of block column jb+1 (8-row tiles from row j2)
+            // Worker warp: 8-row tiles ta (and tb) of the rows from j2.  All operand and target loads are issued
+            // before the first store (stores to the panel would otherwise serialise the next tile's loads):
+            //   U: block column jb -> block column jb+1 (rank 6, two DMMAs per tile),
+            //   L: finished columns [0, j1) -> block column jb+2 (look-ahead).
             if (dbgK) w0 = clock64();
-            {
-                const int nmt = (R - j2 + 7) >> 3;
-                const double* Bp = A + j1 + fr8;
-                for (int t = wk; t < nmt; t += NWK) {
-                    const double* Ap = A + j2 + 8 * t + fr8;
-                    const double a0 = Ap[(j0 + fk) * PANEL_LD], b0 = Bp[(j0 + fk) * PANEL_LD];
-                    // unconditional loads + select (columns j1, j1+1 exist): a guarded load compiles to a branch
-                    double a1 = Ap[(j0 + 4 + fk) * PANEL_LD], b1 = Bp[(j0 + 4 + fk) * PANEL_LD];
-                    if (fk >= 2) { a1 = 0.0; b1 = 0.0; }
-                    double c0 = 0.0, c1 = 0.0;
-                    dmma884(c0, c1, a0, b0);
-                    dmma884(c0, c1, a1, b1);
-                    const int r = j2 + 8 * t + fr8, cl = 2 * fk;
-                    if (cl < 6 && r < R) {
-                        A[(j1 + cl) * PANEL_LD + r] -= c0;
-                        A[(j1 + cl + 1) * PANEL_LD + r] -= c1;
-                    }
+            const int nmt = (R - j2 + 7) >> 3;          // <= 19 tiles: at most two per worker warp
+            const int ta = wk, tb = ta + NWK;
+            if (ta < nmt) {
+                const bool two = tb < nmt, la = jb + 2 < nt;
+                const int cl = 2 * fk;
+                const bool st = cl < 6;                 // lanes whose two output columns exist
+                const int ra = j2 + 8 * ta + fr8, rb = j2 + 8 * (two ? tb : ta) + fr8;
+                const int cu = st ? j1 + cl : j1, cv = (st && la) ? j2 + cl : j1;      // valid columns for every lane
+                // ---- U operands (columns j0 + fk and j0 + 4 + fk <= j1 + 1 exist) and targets
+                double bu0 = A[(j0 + fk) * PANEL_LD + j1 + fr8], bu1 = A[(j0 + 4 + fk) * PANEL_LD + j1 + fr8];
+                double au0 = A[(j0 + fk) * PANEL_LD + ra], au1 = A[(j0 + 4 + fk) * PANEL_LD + ra];
+                double qu0 = A[(j0 + fk) * PANEL_LD + rb], qu1 = A[(j0 + 4 + fk) * PANEL_LD + rb];
+                if (fk >= 2) { bu1 = 0.0; au1 = 0.0; qu1 = 0.0; }
+                const double tu0 = A[cu * PANEL_LD + ra], tu1 = A[(cu + 1) * PANEL_LD + ra];
+                const double tv0 = A[cu * PANEL_LD + rb], tv1 = A[(cu + 1) * PANEL_LD + rb];
+                const double tc0 = A[cv * PANEL_LD + ra], tc1 = A[(cv + 1) * PANEL_LD + ra];
+                const double te0 = A[cv * PANEL_LD + rb], te1 = A[(cv + 1) * PANEL_LD + rb];
+                double u0 = 0.0, u1 = 0.0, v0 = 0.0, v1 = 0.0;
+                dmma884(u0, u1, au0, bu0);
+                dmma884(u0, u1, au1, bu1);
+                if (two) {
+                    dmma884(v0, v1, qu0, bu0);
+                    dmma884(v0, v1, qu1, bu1);
                 }
-            }
-            if (dbgK) { w1 = clock64(); wU += w1 - w0; }
-            // look-ahead: finished columns [0, j1) -> block column jb+2 (all its rows, from j2)
-            if (jb + 2 < nt) {
-                const int nmt = (R - j2 + 7) >> 3;          // <= 19 tiles of 8 rows: at most two per worker warp
-                const int ta = wk, tb = ta + NWK;
-                if (ta < nmt) {
-                    // lane (fr8, fk) reads row (tile base + fr8) of column k0 + fk [+ 4]; pointers advance by
-                    // eight columns per iteration, the partial last group is handled after the loop
+                if (dbgK) { w1 = clock64(); wU += w1 - w0; }
+                // ---- L: lane (fr8, fk) reads row (tile base + fr8) of column k0 + fk [+ 4]; pointers advance by
+                // eight columns per iteration, the partial last group is handled after the loop
+                double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0, e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
+                if (la) {
                     const double* Bp = A + j2 + fr8 + fk * PANEL_LD;
-                    const double* Ap = Bp + 8 * ta;
+                    const double* Ap = A + ra + fk * PANEL_LD;
+                    const double* Aq = A + rb + fk * PANEL_LD;
                     const int nfull = j1 >> 3, rem = j1 & 7;
                     const bool va = fk < rem, vb = fk + 4 < rem;
-                    double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0;
-                    const int cl = 2 * fk;
-                    if (tb < nmt) {
-                        const double* Aq = Bp + 8 * tb;
-                        double e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
+                    if (two) {
 #pragma unroll 2
                         for (int it = 0; it < nfull; it++) {
                             const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
@@ -306,11 +309,6 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
                             dmma884(e00, e01, q0, b0);
                             dmma884(e10, e11, q1, b1);
                         }
-                        const int r2 = j2 + 8 * tb + fr8;
-                        if (cl < 6 && r2 < R) {
-                            A[(j2 + cl) * PANEL_LD + r2] -= e00 + e10;
-                            A[(j2 + cl + 1) * PANEL_LD + r2] -= e01 + e11;
-                        }
                     } else {
 #pragma unroll 2
                         for (int it = 0; it < nfull; it++) {
@@ -328,20 +326,33 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
                             dmma884(c10, c11, a1, b1);
                         }
                     }
-                    const int r = j2 + 8 * ta + fr8;
-                    if (cl < 6 && r < R) {
-                        A[(j2 + cl) * PANEL_LD + r] -= c00 + c10;
-                        A[(j2 + cl + 1) * PANEL_LD + r] -= c01 + c11;
+                }
+                // ---- stores
+                if (st && ra < R) {
+                    A[(j1 + cl) * PANEL_LD + ra] = tu0 - u0;
+                    A[(j1 + cl + 1) * PANEL_LD + ra] = tu1 - u1;
+                    if (la) {
+                        A[(j2 + cl) * PANEL_LD + ra] = tc0 - (c00 + c10);
+                        A[(j2 + cl + 1) * PANEL_LD + ra] = tc1 - (c01 + c11);
+                    }
+                }
+                if (two && st && rb < R) {
+                    A[(j1 + cl) * PANEL_LD + rb] = tv0 - v0;
+                    A[(j1 + cl + 1) * PANEL_LD + rb] = tv1 - v1;
+                    if (la) {
+                        A[(j2 + cl) * PANEL_LD + rb] = te0 - (e00 + e10);
+                        A[(j2 + cl + 1) * PANEL_LD + rb] = te1 - (e01 + e11);
                     }
                 }
             }
             if (dbgK) wL += clock64() - w1;
         }
         __syncthreads();
-        if (dbgT) { t1 = clock64(); tW += t1 - t0; }
+        if (dbgT) { t1 = clock64(); tW += t1 - t0; if (lev == 2 && jb < 16) g_cholTrace[4 * jb + 3] = t1 - tLoop0; }
     }
     if (dbgK) { g_cholDbg[lev * 24 + 20] = wU; g_cholDbg[lev * 24 + 21] = wL; }
     if (dbgT) {
+        tU = clock64() - tLoop0;          // whole factor loop incl. the first diagonal factor
         g_cholDbg[lev * 24 + 12] = tF; g_cholDbg[lev * 24 + 13] = tW;
         g_cholDbg[lev * 24 + 14] = tS; g_cholDbg[lev * 24 + 15] = tU;
     }

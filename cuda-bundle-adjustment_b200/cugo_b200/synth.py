@@ -29,6 +29,7 @@ SHAPES = {
     "kitti07": (248, 26127, 95037, 0, 7001, 0),
     "kitti00": (1332, 133383, 561116, 336672, 7000, 900),
     "venice": (1778, 993923, 5001946, 0, 7003, 0),
+    "city": (20000, 5000000, 30000000, 0, 7004, 4000),      # BASELINE.json configs[4]
 }
 
 

@@ -41,10 +41,14 @@ if os.environ.get("CUGO_B200_DEBUG") == "1":
     print("  top rows", np.argsort(cyc)[-8:].tolist(), np.sort(cyc)[-8:].tolist())
     dc = s.debug_counters()
     print("panel phases of CTA 0 per level (cycles): zero, hsc scatter, child pull, factor, store")
-    for lev in range(s.sizes()["nlevels"]):
+    for lev in range(min(s.sizes()["nlevels"], 64)):
         print("  lev %2d panel" % lev, np.diff(dc[lev, :6]).tolist(), " update (stage, mma, pull+store)",
               np.diff(dc[lev, 8:12]).tolist(), " bwd (load, gemv, trsv)", np.diff(dc[lev, 16:20]).tolist(),
-              " factor loop (warp0 factor, wait lookahead, solve, rank6)", dc[lev, 12:16].tolist(), " worker (rank6, look-ahead)", dc[lev, 20:22].tolist())
+              " factor loop (warp 0 diag update + factor, wait for workers, row solve, whole loop)", dc[lev, 12:16].tolist(), " worker (rank6, look-ahead)", dc[lev, 20:22].tolist())
+    tr = s.debug_counters(96).reshape(-1)[:64].reshape(16, 4)
+    print("level 2, CTA 0, thread 0: clock at (step start, after S barrier, after warp-0 work, after X barrier) per step")
+    for jb in range(16):
+        print("   step %2d" % jb, tr[jb].tolist())
 for rep in range(5):
     s.set_estimates(prob.poses, prob.landmarks)
     chi, lam, tr = s.optimize(10)

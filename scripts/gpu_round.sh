@@ -17,3 +17,5 @@ ncu --set full --clock-control none --import-source on -k regex:"k_schur_rows|k_
 ls -la $OUT
 ncu -i $OUT/prof.ncu-rep --page raw --csv > $OUT/ncu_full_raw.csv 2> $OUT/ncu_import.err
 python scripts/ncu_summary.py $OUT/ncu_full_raw.csv $OUT/ncu_full_summary.csv $OUT/ncu_traffic.json
+# gpurun brings back at most 64 MiB: the report itself stays on the box, its CSV exports travel
+rm -f $OUT/prof.ncu-rep; gzip -f $OUT/ncu_full_raw.csv
