@@ -9,6 +9,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>
@@ -353,6 +354,15 @@ static int readInt(Solver& S, const int* dptr) {
 void Solver::buildStructure() {
     if (!haveVertices) throw StateError("build_structure before set_vertices");
     use();
+    const bool dbgT = getenv("CUGO_B200_DEBUG") != nullptr;
+    auto tNow = [&]() { cudaStreamSynchronize(stream); return std::chrono::steady_clock::now(); };
+    auto tPrev = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!dbgT) return;
+        const auto t = tNow();
+        fprintf(stderr, "[cugo_b200] build_structure: %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t - tPrev).count());
+        tPrev = t;
+    };
     refreshHostSets();
     if (nL_all == 0 || nL == 0) throw UnsupportedError("graph has no free landmarks: pose-only problems use the reference's dense LU path, outside this engine");
     if (nP == 0) throw UnsupportedError("graph has no free poses");
@@ -552,6 +562,7 @@ void Solver::buildStructure() {
         redA.alloc((size_t)6 * nP + nranks); redC.alloc(2);
     }
 
+    lap("edge sorts, Hpl, Hsc, products");
     // ---- symbolic factorisation (one device thread runs symbolic.h)
     const int P = nP;
     y_adjPtr.alloc(P + 1); y_adj.alloc(2 * (size_t)nblkG + 1); y_verts.alloc(P); y_iperm.alloc(P); y_mark.alloc(P);
@@ -566,9 +577,16 @@ void Solver::buildStructure() {
     w.queue = y_queue; w.tmp = y_tmp; w.stack = y_stack; w.snStart = y_snStart; w.snParent = y_snParent;
     w.colToSn = y_colToSn; w.snRowPtr = y_snRowPtr; w.snLevel = y_snLevel; w.childHead = y_childHead;
     w.childNext = y_childNext; w.snRows = y_snRows; w.rowsCap = rowsCap;
-    k_sym_analyze<<<1, 1, 0, stream>>>(w, y_counts);
+    {
+        const long long adjCap = 2LL * (nblkG - P) + 2;
+        const long long symBytes = (adjCap + (P + 1) + 3LL * P) * (long long)sizeof(int);
+        const bool inSmem = symBytes <= 200 * 1024;
+        if (inSmem) CK(cudaFuncSetAttribute(k_sym_analyze, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)symBytes));
+        k_sym_analyze<<<1, 1, inSmem ? (size_t)symBytes : 0, stream>>>(w, y_counts, inSmem ? (int)adjCap : 0);
+    }
     CK(cudaMemcpyAsync(&counts, y_counts.p, sizeof(SymCounts), cudaMemcpyDeviceToHost, stream));
     CK(cudaStreamSynchronize(stream));
+    lap("symbolic analysis");
     if (counts.err) throw CudaError("symbolic analysis overflowed its row-structure workspace");
     const int nsn = counts.nsn;
     z_levelPtr.alloc(counts.nlev + 1); z_levelSn.alloc(nsn); z_Lptr.alloc(nsn + 1); z_Uptr.alloc(nsn + 1);
@@ -587,6 +605,7 @@ void Solver::buildStructure() {
     k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, CHOL_RS, CHOL_TS, cholGen == 1 ? 0 : CHOL_RB, CHOL_TB,
                                     z_levMaxNt, z_factStats.alloc(4));
     CK(cudaMemcpyAsync(factStats, z_factStats.p, sizeof(factStats), cudaMemcpyDeviceToHost, stream));
+    lap("symbolic maps + task tables");
     h_levelPtr.resize(counts.nlev + 1); h_trsmPtr.resize(nsn + 1); h_updPtr.resize(nsn + 1); h_levMaxNt.resize(counts.nlev + 1);
     CK(cudaMemcpyAsync(h_levMaxNt.data(), z_levMaxNt.p, sizeof(int) * counts.nlev, cudaMemcpyDeviceToHost, stream));
     CK(cudaMemcpyAsync(h_levelPtr.data(), z_levelPtr.p, sizeof(int) * (counts.nlev + 1), cudaMemcpyDeviceToHost, stream));
@@ -664,7 +683,9 @@ void Solver::buildStructure() {
                             (2 * ncMax * UPD_LD + 2 * 6 * CHOL_TB * UPD_CLD) * 8));
     CK(cudaStreamSynchronize(stream));
     structDirty = false; systemBuilt = false; solved = false;
+    lap("buffers");
     captureSlot();
+    lap("graph capture");
 }
 
 // ---------------------------------------------------------------------------

@@ -198,8 +198,16 @@ __global__ void k_map_slots(const unsigned long long* lkeys, int nblk, const uns
 }
 
 // ---- symbolic factorisation: the shared host/device code run by one thread ----
-__global__ void k_sym_analyze(SymWork w, SymCounts* out) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) sym_analyze(w, out);
+// adjCap > 0: the adjacency and the BFS scratch (the arrays every sweep of the nested dissection walks) live
+// in shared memory -- a single thread pays ~30 cycles per dependent access there instead of an L2 round trip.
+__global__ void k_sym_analyze(SymWork w, SymCounts* out, int adjCap) {
+    extern __shared__ int symSh[];
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    if (adjCap > 0) {
+        w.adj = symSh; w.adjPtr = symSh + adjCap; w.mark = w.adjPtr + (w.P + 1); w.level = w.mark + w.P;
+        w.queue = w.level + w.P;
+    }
+    sym_analyze(w, out);
 }
 // rb > 0: second-generation task tables (kernels_chol2.cuh): slabs of rb block rows, tiles of tb
 // block rows, and the widest supernode of every level (levMaxNt) for shared-memory sizing.
