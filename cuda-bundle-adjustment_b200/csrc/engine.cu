@@ -197,6 +197,19 @@ struct Solver {
         profEvents.push_back(e);
         profNames.push_back(name);
     }
+    // Launch of a trial kernel with programmatic stream serialisation (engine.h: pdl_wait / pdl_trigger);
+    // CUGO_B200_PDL=0 falls back to plain stream order.  Captured into the trial graph as a programmatic edge.
+    bool pdl = true;
+    template <typename... KA, typename... A>
+    void launch(void (*kern)(KA...), dim3 grid, dim3 block, size_t smem, A... args) {
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = (pdl && !profiling) ? 1 : 0;
+        CK(cudaLaunchKernelEx(&cfg, kern, KA(args)...));
+    }
     int profileSlot(int cap, char* names, int nameLen, double* ms);
     void updateMeasurements(int setId, const double* meas, const double* omega, int nomega);
     void refreshHostSets();
@@ -600,6 +613,8 @@ void Solver::buildStructure() {
     {
         const char* g = getenv("CUGO_B200_CHOL");
         cholGen = (g && (g[0] == '1' || g[0] == '2')) ? g[0] - '0' : 3;
+        const char* p = getenv("CUGO_B200_PDL");
+        pdl = !(p && p[0] == '0');
     }
     z_levMaxNt.alloc(counts.nlev + 1);
     k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, CHOL_RS, CHOL_TS, cholGen == 1 ? 0 : CHOL_RB, CHOL_TB,
@@ -692,12 +707,12 @@ void Solver::buildStructure() {
 // kernel sequences
 // ---------------------------------------------------------------------------
 void Solver::enqueueBuild() {
-    if (f32) k_build_lm<LM_CHUNK, float><<<d.nChunks, LM_CHUNK, 0, stream>>>(d, sp);
-    else k_build_lm<LM_CHUNK, double><<<d.nChunks, LM_CHUNK, 0, stream>>>(d, sp);
+    if (f32) launch(k_build_lm<LM_CHUNK, float>, d.nChunks, LM_CHUNK, 0, d, sp);
+    else launch(k_build_lm<LM_CHUNK, double>, d.nChunks, LM_CHUNK, 0, d, sp);
     mark("build_lm");
-    k_build_pose<128><<<d.nP, 128, 0, stream>>>(d, sp); mark("build_pose");
+    launch(k_build_pose<128>, d.nP, 128, 0, d, sp); mark("build_pose");
     if (nranks > 1) {   // max diagonal of the *global* system for lambda0
-        k_pack_A<256><<<std::min(divUp(6 * d.nP, 256), 148), 256, 0, stream>>>(d); mark("pack_A");
+        launch(k_pack_A<256>, std::min(divUp(6 * d.nP, 256), 148), 256, 0, d); mark("pack_A");
         allReduceSum(d.redA, (size_t)6 * d.nP + nranks);
     }
 }
@@ -705,15 +720,15 @@ void Solver::enqueueBuild() {
 // Schur complement -> multifrontal Cholesky (levels up) -> backward solve (levels
 // down) -> back-substitution (+ landmark part of the update)
 void Solver::enqueueSolve() {
-    k_schur_inv<256><<<divUp(d.nL, 256), 256, 0, stream>>>(d); mark("schur_inv");
+    launch(k_schur_inv<256>, divUp(d.nL, 256), 256, 0, d); mark("schur_inv");
     if (nranks > 1) CK(cudaMemsetAsync(d.Hsc, 0, ((size_t)d.nblkG * 36 + (size_t)d.nP * 6) * sizeof(double), stream));
     const int2* bp = schurPasses > 1 ? blkPass.p : nullptr;
     if (schurRows) {
-        if (f32) k_schur_rows<float><<<nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), stream>>>(d, schurCap, c.dbg, schurUnit, schurPasses, bp);
-        else k_schur_rows<double><<<nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), stream>>>(d, schurCap, c.dbg, schurUnit, schurPasses, bp);
+        if (f32) launch(k_schur_rows<float>, nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), d, schurCap, c.dbg, schurUnit, schurPasses, bp);
+        else launch(k_schur_rows<double>, nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), d, schurCap, c.dbg, schurUnit, schurPasses, bp);
     } else {
-        if (f32) k_schur_blocks<4, float><<<divUp(d.nblk, 4), 128, 0, stream>>>(d);
-        else k_schur_blocks<4, double><<<divUp(d.nblk, 4), 128, 0, stream>>>(d);
+        if (f32) launch(k_schur_blocks<4, float>, divUp(d.nblk, 4), 128, 0, d);
+        else launch(k_schur_blocks<4, double>, divUp(d.nblk, 4), 128, 0, d);
     }
     mark(schurRows ? "schur_rows" : "schur_blocks");
     // the one exchange step of a trial: partial reduced camera systems [Hsc | bsc] summed over the ranks
@@ -724,14 +739,15 @@ void Solver::enqueueSolve() {
         for (int lev = 0; lev < c.nlev; lev++) {
             const int q0 = h_levelPtr[lev], q1 = h_levelPtr[lev + 1];
             const int ncLev = 6 * h_levMaxNt[lev];
-            if (g3) k_chol_panel3<<<h_trsmPtr[q1] - h_trsmPtr[q0], PANEL3_TPB, PANEL_LD * ncLev * 8, stream>>>(d, c, lev);
+            if (g3) launch(k_chol_panel3, h_trsmPtr[q1] - h_trsmPtr[q0], PANEL3_TPB, (size_t)PANEL_LD * ncLev * 8, d, c, lev,
+                           (pdl && !profiling && lev > 0) ? 1 : 0);
             else k_chol_panel<<<h_trsmPtr[q1] - h_trsmPtr[q0], PANEL_TPB, PANEL_LD * ncLev * 8, stream>>>(d, c, lev);
             mark("chol_panel");
             const int nUpd = h_updPtr[q1] - h_updPtr[q0];
             if (nUpd > 0) {
                 if (g3) {
                     const int kpad = (ncLev + 15) & ~15;
-                    k_chol_update3<<<nUpd, UPD3_TPB, (2 * kpad * UPD_LD + 2 * 6 * CHOL_TB * UPD_CLD) * 8, stream>>>(d, c, lev, kpad);
+                    launch(k_chol_update3, nUpd, UPD3_TPB, (size_t)(2 * kpad * UPD_LD + 2 * 6 * CHOL_TB * UPD_CLD) * 8, d, c, lev, kpad);
                 } else {
                     const int kpad = (ncLev + 7) & ~7;
                     k_chol_update2<<<nUpd, 128, (2 * kpad * UPD_LD + 6 * CHOL_TB * UPD_CLD) * 8, stream>>>(d, c, lev, kpad);
@@ -742,12 +758,13 @@ void Solver::enqueueSolve() {
         for (int lev = c.nlev - 1; lev >= 0; lev--) {
             const int ncLev = 6 * h_levMaxNt[lev];
             const size_t bytes = ((size_t)ncLev * (ncLev + 1) + ncLev + 21 * CHOL_MAXW + 6 * (size_t)maxRt) * 8;
-            if (g3) k_chol_bwd3<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bytes, stream>>>(d, c, lev);
+            if (g3) launch(k_chol_bwd3<256>, h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bytes, d, c, lev,
+                           (pdl && !profiling && lev < c.nlev - 1) ? 1 : 0);
             else k_chol_bwd2<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bytes, stream>>>(d, c, lev);
             mark("chol_bwd");
         }
-        if (f32) k_backsub<LM_CHUNK, float><<<d.nChunks, LM_CHUNK, 0, stream>>>(d);
-        else k_backsub<LM_CHUNK, double><<<d.nChunks, LM_CHUNK, 0, stream>>>(d);
+        if (f32) launch(k_backsub<LM_CHUNK, float>, d.nChunks, LM_CHUNK, 0, d);
+        else launch(k_backsub<LM_CHUNK, double>, d.nChunks, LM_CHUNK, 0, d);
         mark("backsub");
         return;
     }
@@ -772,15 +789,15 @@ void Solver::enqueueSolve() {
 void Solver::enqueueSlot() {
     kernelsPerSlot = 0;
     enqueueBuild();
-    k_lm_prepare<256><<<1, 256, 0, stream>>>(d); mark("lm_prepare");
+    launch(k_lm_prepare<256>, 1, 256, 0, d); mark("lm_prepare");
     enqueueSolve();
-    k_update_poses<128><<<divUp(d.nP, 128), 128, 0, stream>>>(d); mark("update_poses");
-    k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 1, 1); mark("errors");
+    launch(k_update_poses<128>, divUp(d.nP, 128), 128, 0, d); mark("update_poses");
+    launch(k_errors<256>, d.errGrid, 256, 0, d, sp, 1, 1); mark("errors");
     if (nranks > 1) {
-        k_lm_sums<256><<<1, 256, 0, stream>>>(d); mark("lm_sums");
+        launch(k_lm_sums<256>, 1, 256, 0, d); mark("lm_sums");
         allReduceSum(d.redC, 2);
     }
-    k_lm_decide<256><<<1, 256, 0, stream>>>(d); mark("lm_decide");
+    launch(k_lm_decide<256>, 1, 256, 0, d); mark("lm_decide");
 }
 
 // Runs ONE trial slot outside the graph with an event after every kernel and returns

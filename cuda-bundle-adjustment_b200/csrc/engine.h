@@ -139,6 +139,15 @@ struct Chol {
     int dbg;               // 1: kernels record phase timestamps (diagnostics)
 };
 
+// Programmatic dependent launch (sm_90+).  The kernels of a trial are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization: a kernel may become resident while its predecessor still
+// runs and blocks in pdl_wait() until the predecessor has COMPLETED (memory flushed).  Rules kept by every
+// kernel of the trial: pdl_wait() before the first read of mutable global data and before any global write, so
+// kernels still complete in launch order; what runs before it touches only shared memory and structure arrays.
+// Both are no-ops for a launch without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // storage type of the Hpl blocks: double, or float in the USE_FLOAT32 mode (arithmetic stays FP64)
 template <typename HT> struct HplOf;
 template <> struct HplOf<double> { static __device__ __forceinline__ double* get(const Dev& d) { return d.Hpl; } };

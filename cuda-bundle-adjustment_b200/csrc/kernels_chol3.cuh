@@ -90,13 +90,16 @@ __device__ __forceinline__ void panel_factor_diag(double* A, double* invAll, int
     }
 }
 
-__global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int lev) {
+// `early` (set by the host for lev > 0 under programmatic dependent launch): the predecessor kernel -- the
+// update or panel kernel of the level below -- signals its dependents only after its own pdl_wait(), so when this
+// CTA runs, everything up to the Schur kernels has completed and the Hsc / bsc scatter may run before pdl_wait(),
+// overlapping the predecessor's tail.  Zeroing and the structure reads always do.
+__global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int lev, int early) {
     extern __shared__ __align__(16) double A[];   // PANEL_LD x nc, column-major
     __shared__ ChildRef chs[CHOL_MAXCH];
     __shared__ __align__(16) double invAll[6 * CHOL_MAXW];  // reciprocal diagonal of every factored 6x6 block
     __shared__ int badFlag;
     LMState* st = d.st;
-    if (st->done) return;
     const int q0 = c.levelPtr[lev], q1 = c.levelPtr[lev + 1];
     int q, slab;
     find_task(c.trsmPtr, q0, q1, c.trsmPtr[q0] + blockIdx.x, &q, &slab);
@@ -116,6 +119,10 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     __syncthreads();
     CHOL_STAMP(1);
     // ---- original entries of Hsc: work unit = (entry, block column c6)
+    if (!early) {
+        pdl_wait(); pdl_trigger();
+        if (st->done) return;
+    }
     {
         const int k0 = c.snBlkPtr[n.t], nent = c.snBlkPtr[n.t + 1] - k0;
         for (int u = tid; u < nent * 6; u += PANEL3_TPB) {
@@ -139,6 +146,10 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     if (last)
         for (int cc = tid; cc < nc; cc += PANEL3_TPB)
             A[cc * PANEL_LD + R - 1] = d.bsc[(size_t)c.perm[n.s + cc / 6] * 6 + cc % 6];
+    if (early) {
+        pdl_wait(); pdl_trigger();
+        if (st->done) return;
+    }
     __syncthreads();
     CHOL_STAMP(2);
     // ---- children: pull their update matrices block by block
@@ -411,7 +422,6 @@ __global__ void __launch_bounds__(UPD3_TPB) k_chol_update3(Dev d, Chol c, int le
     extern __shared__ double sm[];
     __shared__ ChildRef chs[CHOL_MAXCH];
     const LMState* st = d.st;
-    if (st->done) return;
     const int q0 = c.levelPtr[lev], q1 = c.levelPtr[lev + 1];
     int q, tile;
     find_task(c.updPtr, q0, q1, c.updPtr[q0] + blockIdx.x, &q, &tile);
@@ -432,6 +442,8 @@ __global__ void __launch_bounds__(UPD3_TPB) k_chol_update3(Dev d, Chol c, int le
     const int ch0 = c.childPtr[n.t], nch = c.childPtr[n.t + 1] - ch0;
     CHOL_STAMP(8);
     if (tid < nch && tid < CHOL_MAXCH) chs[tid] = load_child(c, ch0 + tid);
+    pdl_wait(); pdl_trigger();          // structure reads above; the panel rows below are the predecessor's output
+    if (st->done) return;
     for (int i = tid; i < kp * TS; i += UPD3_TPB) {
         const int r = i % TS, k = i / TS;
         const bool kin = k < nc;
@@ -515,10 +527,13 @@ __global__ void __launch_bounds__(UPD3_TPB) k_chol_update3(Dev d, Chol c, int le
 // L11 / W are staged asynchronously; the L21^T x_R product issues 4 x CPW independent loads per
 // lane before the first use.
 template <int TPB>
-__global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev) {
+__global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int early) {
     extern __shared__ double sm[];
     const LMState* st = d.st;
-    if (st->done) return;
+    // `early` (host: every level but the first one solved, under programmatic dependent launch): the predecessor
+    // is a backward kernel that signals after its own pdl_wait(), so the whole factorisation has completed and
+    // L11 / W can be staged while the predecessor still solves.
+    if (!early) pdl_wait();
     const SnInfo n = sn_info(c, c.levelSn[c.levelPtr[lev] + blockIdx.x]);
     const int nc = n.nc, nt = n.nt, tid = threadIdx.x, nr = 6 * n.rt, ldL = nc + 1;
     double* L11 = sm;                   // nc columns, leading dimension ldL (odd: conflict-free row reads)
@@ -533,6 +548,9 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev) {
         if (r > cc) cp_async8(L11 + cc * ldL + r, Pn + (size_t)cc * n.m + r, true);
     }
     for (int i = tid; i < 21 * nt; i += TPB) cp_async8(Wsm + i, c.Winv + (size_t)n.s * 21 + i, true);
+    if (early) pdl_wait();
+    pdl_trigger();
+    if (st->done) { cp_async_wait_all(); return; }
     for (int i = tid; i < nr; i += TPB) xR[i] = c.xperm[(size_t)__ldg(Rt + i / 6) * 6 + i % 6];
     __syncthreads();                    // xR visible; L11 / W are only needed after the product
     CHOL_STAMP(17);

@@ -38,6 +38,7 @@ __device__ __forceinline__ void load_cam(const Dev& d, const SetParams& sp, cons
 template <int TPB>
 __global__ void __launch_bounds__(TPB) k_errors(Dev d, SetParams sp, int which, int guarded) {
     __shared__ double sh[TPB / 32];
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     const LMState* st = d.st;
     if (guarded && st->done) return;
     const int buf = which ? 1 - st->cur : st->cur;
@@ -79,6 +80,7 @@ __global__ void __launch_bounds__(TPB) k_build_lm(Dev d, SetParams sp) {
     __shared__ double val[9 * TPB];           // per edge of the tile, component-major
     __shared__ HT hst[TPB * 18];              // Hpl staging
     __shared__ double shm[TPB / 32];
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     const LMState* st = d.st;
     if (st->done || !st->needBuild) return;
     const int l0 = d.chunkLm[blockIdx.x], l1 = d.chunkLm[blockIdx.x + 1];
@@ -183,6 +185,7 @@ __global__ void __launch_bounds__(TPB) k_build_lm(Dev d, SetParams sp) {
 template <int TPB>
 __global__ void __launch_bounds__(TPB) k_build_pose(Dev d, SetParams sp) {
     __shared__ double red[TPB / 32][27];
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     const LMState* st = d.st;
     if (st->done || !st->needBuild) return;
     const int p = blockIdx.x;

@@ -37,6 +37,7 @@ __global__ void __launch_bounds__(TPB) k_lm_begin(Dev d, int niter) {
 template <int TPB>
 __global__ void __launch_bounds__(TPB) k_lm_prepare(Dev d) {
     __shared__ double sh[TPB / 32];
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     LMState* st = d.st;
     if (st->done) return;
     if (st->needBuild) {
@@ -61,6 +62,7 @@ __global__ void __launch_bounds__(TPB) k_lm_prepare(Dev d) {
 template <int TPB>
 __global__ void __launch_bounds__(TPB) k_lm_decide(Dev d) {
     __shared__ double sh[TPB / 32];
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     LMState* st = d.st;
     if (st->done) return;
     double Fhat = sum_array<TPB>(d.chiPartial, d.errGrid, sh);
@@ -120,6 +122,7 @@ __global__ void __launch_bounds__(TPB) k_lm_decide(Dev d) {
 template <int TPB>
 __global__ void __launch_bounds__(TPB) k_pack_A(Dev d) {
     __shared__ double sh[TPB / 32];
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     for (int i = blockIdx.x * TPB + threadIdx.x; i < 6 * d.nP; i += gridDim.x * TPB)
         d.redA[i] = d.Hpp[(size_t)(i / 6) * 36 + (i % 6) * 7];
     if (blockIdx.x == 0) {
@@ -136,6 +139,7 @@ __global__ void __launch_bounds__(TPB) k_pack_A(Dev d) {
 template <int TPB>
 __global__ void __launch_bounds__(TPB) k_lm_sums(Dev d) {
     __shared__ double sh[TPB / 32];
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     const double chi = sum_array<TPB>(d.chiPartial, d.errGrid, sh);
     const double lam = d.rank == 0 ? d.st->lambda : 0.0;
     double s = 0.0;

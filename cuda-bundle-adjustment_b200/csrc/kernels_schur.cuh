@@ -16,6 +16,7 @@ namespace cugo_b200 {
 
 template <int TPB>
 __global__ void __launch_bounds__(TPB) k_schur_inv(Dev d) {
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     const LMState* st = d.st;
     if (st->done) return;
     const int l = blockIdx.x * TPB + threadIdx.x;
@@ -37,6 +38,7 @@ __global__ void __launch_bounds__(TPB) k_schur_inv(Dev d) {
 // summation order is fixed.  Hsc(i,i) = Hpp_i + lambda I - sum, bsc_i = bp_i - sum.
 template <int WARPS, typename HT>
 __global__ void __launch_bounds__(WARPS * 32) k_schur_blocks(Dev d) {
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     const LMState* st = d.st;
     if (st->done) return;
     const int blk = blockIdx.x * WARPS + (threadIdx.x >> 5);
@@ -115,6 +117,7 @@ __global__ void __launch_bounds__(TPB) k_backsub(Dev d) {
     __shared__ double acc[LM_CHUNK * 3];
     __shared__ double part[TPB * 3];
     __shared__ double sh[TPB / 32];
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     const LMState* st = d.st;
     if (st->done) return;
     const int l0 = d.chunkLm[blockIdx.x];
@@ -179,6 +182,7 @@ __global__ void __launch_bounds__(TPB) k_backsub(Dev d) {
 
 template <int TPB>
 __global__ void __launch_bounds__(TPB) k_update_poses(Dev d) {
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     const LMState* st = d.st;
     if (st->done) return;
     const int p = blockIdx.x * TPB + threadIdx.x;
@@ -374,6 +378,7 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
     __shared__ double part[2][SROW_NW][36];
     __shared__ double red[SROW_NW][6];
     __shared__ int nextBlk;
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     const long long tStart = dbg ? clock64() : 0;
     const LMState* st = d.st;
     if (st->done) return;
