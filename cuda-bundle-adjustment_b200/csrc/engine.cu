@@ -200,6 +200,7 @@ struct Solver {
     // Launch of a trial kernel with programmatic stream serialisation (engine.h: pdl_wait / pdl_trigger);
     // CUGO_B200_PDL=0 falls back to plain stream order.  Captured into the trial graph as a programmatic edge.
     bool pdl = true;
+    bool fuseBuild = true;         // both passes of the system build in one launch (CUGO_B200_FUSEBUILD=0: two)
     template <typename... KA, typename... A>
     void launch(void (*kern)(KA...), dim3 grid, dim3 block, size_t smem, A... args) {
         cudaLaunchConfig_t cfg{};
@@ -615,6 +616,8 @@ void Solver::buildStructure() {
         cholGen = (g && (g[0] == '1' || g[0] == '2')) ? g[0] - '0' : 3;
         const char* p = getenv("CUGO_B200_PDL");
         pdl = !(p && p[0] == '0');
+        const char* fb = getenv("CUGO_B200_FUSEBUILD");
+        fuseBuild = !(fb && fb[0] == '0');
     }
     z_levMaxNt.alloc(counts.nlev + 1);
     k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, CHOL_RS, CHOL_TS, cholGen == 1 ? 0 : CHOL_RB, CHOL_TB,
@@ -707,10 +710,17 @@ void Solver::buildStructure() {
 // kernel sequences
 // ---------------------------------------------------------------------------
 void Solver::enqueueBuild() {
-    if (f32) launch(k_build_lm<LM_CHUNK, float>, d.nChunks, LM_CHUNK, 0, d, sp);
-    else launch(k_build_lm<LM_CHUNK, double>, d.nChunks, LM_CHUNK, 0, d, sp);
-    mark("build_lm");
-    launch(k_build_pose<128>, d.nP, 128, 0, d, sp); mark("build_pose");
+    static_assert(LM_CHUNK == 128, "k_build runs both passes with 128 threads");
+    if (fuseBuild && !profiling) {
+        if (f32) launch(k_build<LM_CHUNK, float>, d.nP + d.nChunks, LM_CHUNK, 0, d, sp);
+        else launch(k_build<LM_CHUNK, double>, d.nP + d.nChunks, LM_CHUNK, 0, d, sp);
+        mark("build");
+    } else {
+        if (f32) launch(k_build_lm<LM_CHUNK, float>, d.nChunks, LM_CHUNK, 0, d, sp);
+        else launch(k_build_lm<LM_CHUNK, double>, d.nChunks, LM_CHUNK, 0, d, sp);
+        mark("build_lm");
+        launch(k_build_pose<128>, d.nP, 128, 0, d, sp); mark("build_pose");
+    }
     if (nranks > 1) {   // max diagonal of the *global* system for lambda0
         launch(k_pack_A<256>, std::min(divUp(6 * d.nP, 256), 148), 256, 0, d); mark("pack_A");
         allReduceSum(d.redA, (size_t)6 * d.nP + nranks);
@@ -789,7 +799,7 @@ void Solver::enqueueSolve() {
 void Solver::enqueueSlot() {
     kernelsPerSlot = 0;
     enqueueBuild();
-    launch(k_lm_prepare<256>, 1, 256, 0, d); mark("lm_prepare");
+    launch(k_lm_prepare<1024>, 1, 1024, 0, d); mark("lm_prepare");
     enqueueSolve();
     launch(k_update_poses<128>, divUp(d.nP, 128), 128, 0, d); mark("update_poses");
     launch(k_errors<256>, d.errGrid, 256, 0, d, sp, 1, 1); mark("errors");
@@ -797,7 +807,7 @@ void Solver::enqueueSlot() {
         launch(k_lm_sums<256>, 1, 256, 0, d); mark("lm_sums");
         allReduceSum(d.redC, 2);
     }
-    launch(k_lm_decide<256>, 1, 256, 0, d); mark("lm_decide");
+    launch(k_lm_decide<1024>, 1, 1024, 0, d); mark("lm_decide");
 }
 
 // Runs ONE trial slot outside the graph with an event after every kernel and returns

@@ -75,15 +75,14 @@ __global__ void __launch_bounds__(TPB) k_errors(Dev d, SetParams sp, int which, 
 // summed per landmark by the segment-head thread in edge order.
 // ---------------------------------------------------------------------------
 template <int TPB, typename HT>
-__global__ void __launch_bounds__(TPB) k_build_lm(Dev d, SetParams sp) {
+__device__ __forceinline__ void build_lm_cta(const Dev& d, const SetParams& sp, const int blk) {
     __shared__ double acc[LM_CHUNK * 9];      // per landmark: H00 H10 H11 H20 H21 H22 b0 b1 b2
     __shared__ double val[9 * TPB];           // per edge of the tile, component-major
     __shared__ HT hst[TPB * 18];              // Hpl staging
     __shared__ double shm[TPB / 32];
-    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     const LMState* st = d.st;
     if (st->done || !st->needBuild) return;
-    const int l0 = d.chunkLm[blockIdx.x], l1 = d.chunkLm[blockIdx.x + 1];
+    const int l0 = d.chunkLm[blk], l1 = d.chunkLm[blk + 1];
     if (l0 >= l1) return;
     const int nl = l1 - l0;
     const int e0 = d.lmEdgePtr[l0], e1 = d.lmEdgePtr[l1];
@@ -174,7 +173,12 @@ __global__ void __launch_bounds__(TPB) k_build_lm(Dev d, SetParams sp) {
     double mx = 0.0;
     for (int i = tid; i < nlf; i += TPB) mx = fmax(mx, fmax(acc[i * 9], fmax(acc[i * 9 + 2], acc[i * 9 + 5])));
     mx = block_max<TPB>(mx, shm);
-    if (tid == 0) d.maxDiagL[blockIdx.x] = mx;
+    if (tid == 0) d.maxDiagL[blk] = mx;
+}
+template <int TPB, typename HT>
+__global__ void __launch_bounds__(TPB) k_build_lm(Dev d, SetParams sp) {
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
+    build_lm_cta<TPB, HT>(d, sp, blockIdx.x);
 }
 
 // ---------------------------------------------------------------------------
@@ -183,12 +187,10 @@ __global__ void __launch_bounds__(TPB) k_build_lm(Dev d, SetParams sp) {
 // JP^T JP w and the 6 of JP^T e w in registers, then a fixed-order tree.
 // ---------------------------------------------------------------------------
 template <int TPB>
-__global__ void __launch_bounds__(TPB) k_build_pose(Dev d, SetParams sp) {
+__device__ __forceinline__ void build_pose_cta(const Dev& d, const SetParams& sp, const int p) {
     __shared__ double red[TPB / 32][27];
-    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     const LMState* st = d.st;
     if (st->done || !st->needBuild) return;
-    const int p = blockIdx.x;
     const double* __restrict__ pose = d.pose[st->cur];
     const double* __restrict__ lm = d.lm[st->cur];
     double q[4], t[3];
@@ -247,6 +249,19 @@ __global__ void __launch_bounds__(TPB) k_build_pose(Dev d, SetParams sp) {
         for (int c = 0; c < 6; c++) mx = fmax(mx, red[0][c * 6 - c * (c - 1) / 2]);
         d.maxDiagP[p] = mx;
     }
+}
+template <int TPB>
+__global__ void __launch_bounds__(TPB) k_build_pose(Dev d, SetParams sp) {
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
+    build_pose_cta<TPB>(d, sp, blockIdx.x);
+}
+// Both passes in one launch (they share inputs and write disjoint outputs): CTAs [0, nP) take the poses -- the
+// long-running ones (a loop-closure pose has thousands of edges) start first -- the rest the landmark chunks.
+template <int TPB, typename HT>
+__global__ void __launch_bounds__(TPB) k_build(Dev d, SetParams sp) {
+    pdl_trigger(); pdl_wait();
+    if ((int)blockIdx.x < d.nP) build_pose_cta<TPB>(d, sp, blockIdx.x);
+    else build_lm_cta<TPB, HT>(d, sp, blockIdx.x - d.nP);
 }
 
 }  // namespace cugo_b200
