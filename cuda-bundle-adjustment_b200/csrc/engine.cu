@@ -757,7 +757,7 @@ void Solver::enqueueSolve() {
             if (nUpd > 0) {
                 if (g3) {
                     const int kpad = (ncLev + 15) & ~15;
-                    launch(k_chol_update3, nUpd, UPD3_TPB, (size_t)(2 * kpad * UPD_LD + 2 * 6 * CHOL_TB * UPD_CLD) * 8, d, c, lev, kpad);
+                    launch(k_chol_update3, nUpd, UPD3_TPB, (size_t)std::max(2 * kpad * UPD_LD, 2 * 6 * CHOL_TB * UPD_CLD) * 8, d, c, lev, kpad);
                 } else {
                     const int kpad = (ncLev + 7) & ~7;
                     k_chol_update2<<<nUpd, 128, (2 * kpad * UPD_LD + 6 * CHOL_TB * UPD_CLD) * 8, stream>>>(d, c, lev, kpad);
@@ -1495,6 +1495,8 @@ int cugo_b200_debug_counters(long long* out, int n) {
     if (out && n == 8192)   // per-row cycles of the Schur kernel
         return cudaMemcpyFromSymbol(out, cugo_b200::g_schurDbg, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
     if (!out || n < 0 || n > 64 * 24) return CUGO_B200_EINVAL;
+    if (n == 512)
+        return cudaMemcpyFromSymbol(out, cugo_b200::g_cholTime, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
     if (n == 96)
         return cudaMemcpyFromSymbol(out, cugo_b200::g_cholTrace, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
     return cudaMemcpyFromSymbol(out, cugo_b200::g_cholDbg, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;

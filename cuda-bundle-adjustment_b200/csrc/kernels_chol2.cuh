@@ -56,6 +56,9 @@ __device__ __forceinline__ ChildRef load_child(const Chol& c, int q) {
 // phase timestamps of CTA 0 of each panel launch (diagnostics, enabled by Chol::dbg)
 __device__ long long g_cholDbg[64 * 24];
 __device__ long long g_cholTrace[96];       // diagnostics: clock of CTA 0 / thread 0 at four points of every factor-loop step of level 2
+__device__ long long g_cholTime[64 * 8];    // diagnostics: %globaltimer (ns) of CTA 0 per level: panel (after wait, end), update, backward solve
+__device__ __forceinline__ long long global_ns() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define CHOL_GT(slot) do { if (c.dbg && blockIdx.x == 0 && threadIdx.x == 0 && lev < 64) g_cholTime[lev * 8 + (slot)] = global_ns(); } while (0)
 #define CHOL_STAMP(ph) do { if (c.dbg && blockIdx.x == 0 && threadIdx.x == 0 && lev < 64) g_cholDbg[lev * 24 + (ph)] = clock64(); } while (0)
 __device__ __forceinline__ int tri(int i, int k) { return i * (i + 1) / 2 + k; }   // packed lower, k <= i
 

@@ -22,8 +22,8 @@ constexpr int PANEL3_NW = PANEL3_TPB / 32;
 
 // pull the children's contributions to 6 consecutive rows (or the rhs element) of one front column
 __device__ __forceinline__ void pull_unit(const Chol& c, const ChildRef* chs, int ch0, int nch, int fr, int fc, int c6,
-                                          int rmin, double acc[6]) {
-    for (int i0 = 0; i0 < nch; i0 += 4) {
+                                          int rmin, double acc[6], int iStart = 0) {
+    for (int i0 = iStart; i0 < nch; i0 += 4) {
         const double* src[4];
 #pragma unroll
         for (int j = 0; j < 4; j++) {
@@ -52,6 +52,56 @@ __device__ __forceinline__ void pull_unit(const Chol& c, const ChildRef* chs, in
         for (int j = 0; j < 4; j++)
 #pragma unroll
             for (int rr = 0; rr < 6; rr++) acc[rr] += v[j][rr];
+    }
+}
+
+// ---- children pulled through inverse maps staged in shared memory -----------------------------------
+// invS[i * W + k] = row block of child i's update matrix that lands on the k-th front block this CTA touches
+// (-1: none).  One shared-memory lookup replaces the dependent global load of pull_unit, so a unit costs a
+// single L2 round trip, and two units are kept in flight per thread.
+constexpr int PULL_W = CHOL_MAXW + CHOL_RB;        // panel: the nt diagonal blocks + the slab's block rows
+struct PullUnit {
+    const double* src[2];
+    int kr, kc, c6, rmin;
+};
+__device__ __forceinline__ void pull_src(const ChildRef* chs, const int* invS, int W, int i, int nchS, PullUnit& u, int j) {
+    u.src[j] = nullptr;
+    if (i < nchS) {
+        const int kc = invS[i * W + u.kc];
+        if (kc >= 0) {
+            const ChildRef cr = chs[i];
+            if (u.kr >= 0) {
+                const int kr = invS[i * W + u.kr];
+                if (kr >= 0) u.src[j] = cr.U + (size_t)(6 * kc + u.c6) * cr.uc + 6 * kr;
+            } else {
+                u.src[j] = cr.U + (size_t)(6 * kc + u.c6) * cr.uc + cr.uc - 1;
+            }
+        }
+    }
+}
+__device__ __forceinline__ void pull_load(const PullUnit& u, int j, double v[6]) {
+#pragma unroll
+    for (int rr = 0; rr < 6; rr++) v[rr] = (u.src[j] && rr >= u.rmin && (u.kr >= 0 || rr == 0)) ? u.src[j][rr] : 0.0;
+}
+// sums of the children's contributions to two units (children in index order, as pull_unit)
+__device__ __forceinline__ void pull_pair(const ChildRef* chs, const int* invS, int W, int nchS, PullUnit& a, PullUnit& b,
+                                          bool hasB, double accA[6], double accB[6]) {
+    for (int i0 = 0; i0 < nchS; i0 += 2) {
+        pull_src(chs, invS, W, i0, nchS, a, 0);
+        pull_src(chs, invS, W, i0 + 1, nchS, a, 1);
+        if (hasB) {
+            pull_src(chs, invS, W, i0, nchS, b, 0);
+            pull_src(chs, invS, W, i0 + 1, nchS, b, 1);
+        } else {
+            b.src[0] = b.src[1] = nullptr;
+        }
+        double va[2][6], vb[2][6];
+        pull_load(a, 0, va[0]); pull_load(a, 1, va[1]);
+        pull_load(b, 0, vb[0]); pull_load(b, 1, vb[1]);
+#pragma unroll
+        for (int j = 0; j < 2; j++)
+#pragma unroll
+            for (int rr = 0; rr < 6; rr++) { accA[rr] += va[j][rr]; accB[rr] += vb[j][rr]; }
     }
 }
 
@@ -99,6 +149,8 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     __shared__ ChildRef chs[CHOL_MAXCH];
     __shared__ __align__(16) double invAll[6 * CHOL_MAXW];  // reciprocal diagonal of every factored 6x6 block
     __shared__ int badFlag;
+    __shared__ int invS[CHOL_MAXCH * PULL_W];
+    __shared__ int rowTab[4][PANEL_LD];
     LMState* st = d.st;
     const int q0 = c.levelPtr[lev], q1 = c.levelPtr[lev + 1];
     int q, slab;
@@ -118,10 +170,16 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     if (tid < nch && tid < CHOL_MAXCH) chs[tid] = load_child(c, ch0 + tid);
     __syncthreads();
     CHOL_STAMP(1);
+    const int nchS = min(nch, CHOL_MAXCH), pullW = nt + (rb1 - rb0);
+    for (int i = tid; i < nchS * pullW; i += PANEL3_TPB) {         // structure data: may run before pdl_wait
+        const int k = i % pullW;
+        invS[i] = __ldg(chs[i / pullW].inv + (k < nt ? k : rb0 + (k - nt)));
+    }
     // ---- original entries of Hsc: work unit = (entry, block column c6)
     if (!early) {
         pdl_wait(); pdl_trigger();
         if (st->done) return;
+        CHOL_GT(0);
     }
     {
         const int k0 = c.snBlkPtr[n.t], nent = c.snBlkPtr[n.t + 1] - k0;
@@ -149,11 +207,86 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     if (early) {
         pdl_wait(); pdl_trigger();
         if (st->done) return;
+        CHOL_GT(0);
     }
     __syncthreads();
     CHOL_STAMP(2);
-    // ---- children: pull their update matrices block by block
-    if (nch > 0) {
+    // ---- children: extend-add of their update matrices (lower triangle of D, the slab, the rhs row).
+    // Four children at a time: a table rowTab[j][r] = row of child j's update matrix that lands on panel row r
+    // (-1: none) is built first, so the pull itself is ~6 instructions per entry (the block-wise version before it
+    // spent its time on index arithmetic and on the L1 tag stage: one lookup per lane and load).  A warp takes two
+    // panel columns at a time with its lanes along the ROWS -- consecutive panel rows are mostly consecutive rows of
+    // a child's column, so a warp load touches 2-3 lines -- and keeps 16 loads per lane in flight.
+    if (nchS > 0) {
+        const int rhsRow = last ? R - 1 : -1;
+        for (int g0 = 0; g0 < nchS; g0 += 4) {
+            const int ng = min(4, nchS - g0);
+            if (g0 > 0) __syncthreads();
+            for (int idx = tid; idx < ng * R; idx += PANEL3_TPB) {
+                const int j = idx / R, r = idx - j * R;
+                int row;
+                if (r == rhsRow) {
+                    row = chs[g0 + j].uc - 1;
+                } else {
+                    const int la = r < nc ? r : r - nc, b = la / 6;
+                    const int k = invS[(g0 + j) * pullW + (r < nc ? b : nt + b)];
+                    row = k < 0 ? -1 : 6 * k + (la - 6 * b);
+                }
+                rowTab[j][r] = row;
+            }
+            __syncthreads();
+            for (int ca = wid; ca < nc; ca += 2 * PANEL3_NW) {
+                const int cb = ca + PANEL3_NW;
+                const bool hasB = cb < nc;
+                const double* colA[4];
+                const double* colB[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    colA[j] = nullptr; colB[j] = nullptr;
+                    if (j < ng) {
+                        const ChildRef cr = chs[g0 + j];
+                        const int ka = invS[(g0 + j) * pullW + ca / 6];
+                        const int kb = hasB ? invS[(g0 + j) * pullW + cb / 6] : -1;
+                        if (ka >= 0) colA[j] = cr.U + (size_t)(6 * ka + ca % 6) * cr.uc;
+                        if (kb >= 0) colB[j] = cr.U + (size_t)(6 * kb + cb % 6) * cr.uc;
+                    }
+                }
+                for (int off = lane; ca + off < R; off += 128) {
+                    double sA[4] = {0.0, 0.0, 0.0, 0.0}, sB[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+                    for (int jj = 0; jj < 4; jj += 2) {
+                        if (jj < ng) {
+                            double v[2][2][4];
+#pragma unroll
+                            for (int j = 0; j < 2; j++)
+#pragma unroll
+                                for (int u = 0; u < 4; u++) {
+                                    const int ra = ca + off + 32 * u, rb = cb + off + 32 * u;
+                                    const int rowA = ra < R ? rowTab[jj + j][ra] : -1;
+                                    const int rowB = rb < R ? rowTab[jj + j][rb] : -1;
+                                    const bool va = rowA >= 0 && colA[jj + j] != nullptr;
+                                    const bool vb = rowB >= 0 && colB[jj + j] != nullptr;
+                                    v[j][0][u] = va ? __ldcg(colA[jj + j] + rowA) : 0.0;
+                                    v[j][1][u] = vb ? __ldcg(colB[jj + j] + rowB) : 0.0;
+                                }
+#pragma unroll
+                            for (int j = 0; j < 2; j++)
+#pragma unroll
+                                for (int u = 0; u < 4; u++) { sA[u] += v[j][0][u]; sB[u] += v[j][1][u]; }
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        const int ra = ca + off + 32 * u, rb = cb + off + 32 * u;
+                        if (ra < R) A[ca * PANEL_LD + ra] += sA[u];
+                        if (hasB && rb < R) A[cb * PANEL_LD + rb] += sB[u];
+                    }
+                }
+            }
+        }
+    }
+    if (nch > CHOL_MAXCH) {      // descriptors beyond the shared-memory cache: block-wise pull with global map lookups
+        __syncthreads();
         const int nD = nt * nt, nSb = (rb1 - rb0) * nt;
         const int nBlkUnits = (nD + nSb) * 6;
         const int nUnits = nBlkUnits + (last ? nc : 0);
@@ -177,7 +310,7 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
                 fc = col / 6; c6 = col % 6; fr = -1; lr = R - 1;
             }
             double acc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-            pull_unit(c, chs, ch0, nch, fr, fc, c6, rmin, acc);
+            pull_unit(c, chs, ch0, nch, fr, fc, c6, rmin, acc, CHOL_MAXCH);
             double* dst = A + (6 * fc + c6) * PANEL_LD + lr;
             if (fr >= 0) {
 #pragma unroll
@@ -400,6 +533,7 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
         for (int lr = lane; lr < nS; lr += 32) dst[6 * rb0 + lr] = src[nc + lr];
     }
     CHOL_STAMP(5);
+    CHOL_GT(1);
 }
 
 
@@ -421,6 +555,7 @@ constexpr int UPD3_TPB = 256;
 __global__ void __launch_bounds__(UPD3_TPB) k_chol_update3(Dev d, Chol c, int lev, int kpadMax) {
     extern __shared__ double sm[];
     __shared__ ChildRef chs[CHOL_MAXCH];
+    __shared__ int invS[CHOL_MAXCH * 2 * CHOL_TB];
     const LMState* st = d.st;
     const int q0 = c.levelPtr[lev], q1 = c.levelPtr[lev + 1];
     int q, tile;
@@ -436,14 +571,24 @@ __global__ void __launch_bounds__(UPD3_TPB) k_chol_update3(Dev d, Chol c, int le
     const int nc = n.nc, kp = (nc + 15) & ~15;           // two K halves of whole 8-steps
     double* As = sm;
     double* Bs = (ti == tj) ? sm : sm + kpadMax * UPD_LD;
-    double* Cs = sm + 2 * kpadMax * UPD_LD;               // 48 x UPD_CLD
+    double* Cs = sm;                                      // 48 x UPD_CLD, over the operand stage once the MMAs are done
     double* Cs2 = Cs + TS * UPD_CLD;                      // second K half
     const double* __restrict__ Pn = c.L + c.Lptr[n.t];
     const int ch0 = c.childPtr[n.t], nch = c.childPtr[n.t + 1] - ch0;
     CHOL_STAMP(8);
     if (tid < nch && tid < CHOL_MAXCH) chs[tid] = load_child(c, ch0 + tid);
+    const int nchS = min(nch, CHOL_MAXCH);
+    if (nch > 0) {                       // inverse maps of the tile's 8 row blocks and 8 column blocks (pull_pair)
+        __syncthreads();
+        for (int i = tid; i < nchS * 2 * CHOL_TB; i += UPD3_TPB) {
+            const int k = i % (2 * CHOL_TB);
+            const int fb = n.nt + (k < CHOL_TB ? CHOL_TB * ti + k : CHOL_TB * tj + (k - CHOL_TB));
+            invS[i] = fb < n.fb ? __ldg(chs[i / (2 * CHOL_TB)].inv + fb) : -1;
+        }
+    }
     pdl_wait(); pdl_trigger();          // structure reads above; the panel rows below are the predecessor's output
     if (st->done) return;
+    CHOL_GT(2);
     for (int i = tid; i < kp * TS; i += UPD3_TPB) {
         const int r = i % TS, k = i / TS;
         const bool kin = k < nc;
@@ -484,6 +629,9 @@ __global__ void __launch_bounds__(UPD3_TPB) k_chol_update3(Dev d, Chol c, int le
 #pragma unroll
                     for (int y = 0; y < 3; y++) dmma884(acc[h][x][y][0], acc[h][x][y][1], a[h][x], b[h][y]);
         }
+    }
+    __syncthreads();            // every warp has read its operands: the stage becomes the C tiles (two CTAs per SM fit)
+    if (active) {
         double* Cd = kh ? Cs2 : Cs;
 #pragma unroll
         for (int x = 0; x < 3; x++)
@@ -501,25 +649,59 @@ __global__ void __launch_bounds__(UPD3_TPB) k_chol_update3(Dev d, Chol c, int le
     // epilogue: add the children's blocks, store the lower triangle of U_t
     double* __restrict__ Ut = c.U + c.Uptr[n.t];
     const int rt = n.rt;
-    for (int wu = tid; wu < CHOL_TB * CHOL_TB * 6; wu += UPD3_TPB) {
-        const int c6 = wu % 6, item = wu / 6, br = item % CHOL_TB, bc = item / CHOL_TB;
-        const int gbr = CHOL_TB * ti + br, gbc = CHOL_TB * tj + bc;
-        if (gbr > rt || gbc > gbr || gbc >= rt) continue;   // block row rt = the rhs row; the rhs column is never used
-        const bool isRhs = (gbr == rt);
-        const int rmin = (gbr == gbc) ? c6 : 0;
-        double v[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-        pull_unit(c, chs, ch0, nch, isRhs ? -1 : n.nt + gbr, n.nt + gbc, c6, rmin, v);
-        const int o = (6 * bc + c6) * UPD_CLD + 6 * br;
-        double* __restrict__ dst = Ut + (size_t)(6 * gbc + c6) * n.u + 6 * gbr;
-        if (!isRhs) {
+    constexpr int NU = CHOL_TB * CHOL_TB * 6;
+    static_assert(NU <= 2 * UPD3_TPB, "two units per thread");
+    {
+        PullUnit u[2];
+        int o[2];
+        double* dst[2];
+        bool ok[2];
 #pragma unroll
-            for (int rr = 0; rr < 6; rr++)
-                if (rr >= rmin) dst[rr] = v[rr] - (Cs[o + rr] + Cs2[o + rr]);
-        } else {
-            dst[0] = v[0] - (Cs[o] + Cs2[o]);
+        for (int j = 0; j < 2; j++) {
+            const int wu = tid + j * UPD3_TPB;
+            const int c6 = wu % 6, item = wu / 6, br = item % CHOL_TB, bc = item / CHOL_TB;
+            const int gbr = CHOL_TB * ti + br, gbc = CHOL_TB * tj + bc;
+            // block row rt = the rhs row; the rhs column is never used
+            ok[j] = wu < NU && !(gbr > rt || gbc > gbr || gbc >= rt);
+            u[j].kr = (gbr == rt) ? -1 : br;
+            u[j].kc = CHOL_TB + bc;
+            u[j].c6 = c6;
+            u[j].rmin = (gbr == gbc) ? c6 : 0;
+            o[j] = (6 * bc + c6) * UPD_CLD + 6 * br;
+            dst[j] = Ut + (size_t)(6 * gbc + c6) * n.u + 6 * gbr;
+        }
+        if (ok[0] || ok[1]) {
+            if (!ok[0]) { u[0] = u[1]; o[0] = o[1]; dst[0] = dst[1]; ok[0] = true; ok[1] = false; }
+            double v0[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, v1[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+            pull_pair(chs, invS, 2 * CHOL_TB, nchS, u[0], u[1], ok[1], v0, v1);
+            if (nch > CHOL_MAXCH) {
+                const int g0 = n.nt + CHOL_TB * tj + (u[0].kc - CHOL_TB);
+                pull_unit(c, chs, ch0, nch, u[0].kr < 0 ? -1 : n.nt + CHOL_TB * ti + u[0].kr, g0, u[0].c6, u[0].rmin, v0, CHOL_MAXCH);
+                if (ok[1]) {
+                    const int g1 = n.nt + CHOL_TB * tj + (u[1].kc - CHOL_TB);
+                    pull_unit(c, chs, ch0, nch, u[1].kr < 0 ? -1 : n.nt + CHOL_TB * ti + u[1].kr, g1, u[1].c6, u[1].rmin, v1, CHOL_MAXCH);
+                }
+            }
+            if (u[0].kr >= 0) {
+#pragma unroll
+                for (int rr = 0; rr < 6; rr++)
+                    if (rr >= u[0].rmin) dst[0][rr] = v0[rr] - (Cs[o[0] + rr] + Cs2[o[0] + rr]);
+            } else {
+                dst[0][0] = v0[0] - (Cs[o[0]] + Cs2[o[0]]);
+            }
+            if (ok[1]) {
+                if (u[1].kr >= 0) {
+#pragma unroll
+                    for (int rr = 0; rr < 6; rr++)
+                        if (rr >= u[1].rmin) dst[1][rr] = v1[rr] - (Cs[o[1] + rr] + Cs2[o[1] + rr]);
+                } else {
+                    dst[1][0] = v1[0] - (Cs[o[1]] + Cs2[o[1]]);
+                }
+            }
         }
     }
     CHOL_STAMP(11);
+    CHOL_GT(3);
 }
 
 // ---------------------------------------------------------------------------
@@ -551,6 +733,7 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int e
     if (early) pdl_wait();
     pdl_trigger();
     if (st->done) { cp_async_wait_all(); return; }
+    CHOL_GT(4);
     for (int i = tid; i < nr; i += TPB) xR[i] = c.xperm[(size_t)__ldg(Rt + i / 6) * 6 + i % 6];
     __syncthreads();                    // xR visible; L11 / W are only needed after the product
     CHOL_STAMP(17);
@@ -618,6 +801,7 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int e
         c.xperm[(size_t)(n.s + i / 6) * 6 + i % 6] = v;
         d.x[(size_t)c.perm[n.s + i / 6] * 6 + i % 6] = v;
     }
+    CHOL_GT(5);
 }
 
 }  // namespace cugo_b200

@@ -54,3 +54,15 @@ for rep in range(5):
     chi, lam, tr = s.optimize(10)
     ms, nk = s.last_timing()
     print("optimize(10): %.3f ms device, %d kernels, %.3f ms/iter, %.2f M edges/s" % (ms, nk, ms / len(chi), prob.n_edges * len(chi) / ms / 1e3))
+
+if os.environ.get("CUGO_B200_DEBUG"):
+    # timeline of the last trial of the last optimize() (graph, programmatic dependent launch): CTA 0 of every level
+    import ctypes as C
+    a = (C.c_longlong * 512)()
+    s.lib.cugo_b200_debug_counters(a, 512)
+    tm = np.array(a[:], dtype=np.int64).reshape(64, 8)
+    nlev = s.sizes()["nlevels"]
+    t0 = tm[0, 0]
+    print("timeline of the last trial (us since the first panel CTA passed its wait): panel [start, end]  update [start, end]  bwd [start, end]")
+    for lev in range(min(nlev, 64)):
+        print("  lev %2d" % lev, np.round((tm[lev, :6] - t0) / 1e3, 1).tolist())
