@@ -200,6 +200,7 @@ struct Solver {
     // Launch of a trial kernel with programmatic stream serialisation (engine.h: pdl_wait / pdl_trigger);
     // CUGO_B200_PDL=0 falls back to plain stream order.  Captured into the trial graph as a programmatic edge.
     bool pdl = true;
+    bool panelDC = true;           // panel kernel with the decoupled diagonal chain (CUGO_B200_PANELDC=0: CTA-wide barriers)
     bool fuseBuild = true;         // both passes of the system build in one launch (CUGO_B200_FUSEBUILD=0: two)
     template <typename... KA, typename... A>
     void launch(void (*kern)(KA...), dim3 grid, dim3 block, size_t smem, A... args) {
@@ -616,6 +617,8 @@ void Solver::buildStructure() {
         cholGen = (g && (g[0] == '1' || g[0] == '2')) ? g[0] - '0' : 3;
         const char* p = getenv("CUGO_B200_PDL");
         pdl = !(p && p[0] == '0');
+        const char* dc = getenv("CUGO_B200_PANELDC");
+        panelDC = !(dc && dc[0] == '0');
         const char* fb = getenv("CUGO_B200_FUSEBUILD");
         fuseBuild = !(fb && fb[0] == '0');
     }
@@ -696,7 +699,8 @@ void Solver::buildStructure() {
     if (bwd2Bytes > 227 * 1024) throw UnsupportedError("front too large for the shared-memory backward solve of this version");
     CK(cudaFuncSetAttribute(k_chol_bwd2<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd2Bytes));
     CK(cudaFuncSetAttribute(k_chol_bwd3<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd2Bytes));
-    CK(cudaFuncSetAttribute(k_chol_panel3, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_LD * ncMax * 8));
+    CK(cudaFuncSetAttribute(k_chol_panel3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_LD * ncMax * 8));
+    CK(cudaFuncSetAttribute(k_chol_panel3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_LD * ncMax * 8));
     CK(cudaFuncSetAttribute(k_chol_update3, cudaFuncAttributeMaxDynamicSharedMemorySize,
                             (2 * ncMax * UPD_LD + 2 * 6 * CHOL_TB * UPD_CLD) * 8));
     CK(cudaStreamSynchronize(stream));
@@ -749,8 +753,8 @@ void Solver::enqueueSolve() {
         for (int lev = 0; lev < c.nlev; lev++) {
             const int q0 = h_levelPtr[lev], q1 = h_levelPtr[lev + 1];
             const int ncLev = 6 * h_levMaxNt[lev];
-            if (g3) launch(k_chol_panel3, h_trsmPtr[q1] - h_trsmPtr[q0], PANEL3_TPB, (size_t)PANEL_LD * ncLev * 8, d, c, lev,
-                           (pdl && !profiling && lev > 0) ? 1 : 0);
+            if (g3) launch(panelDC ? k_chol_panel3<true> : k_chol_panel3<false>, h_trsmPtr[q1] - h_trsmPtr[q0], PANEL3_TPB,
+                           (size_t)PANEL_LD * ncLev * 8, d, c, lev, (pdl && !profiling && lev > 0) ? 1 : 0);
             else k_chol_panel<<<h_trsmPtr[q1] - h_trsmPtr[q0], PANEL_TPB, PANEL_LD * ncLev * 8, stream>>>(d, c, lev);
             mark("chol_panel");
             const int nUpd = h_updPtr[q1] - h_updPtr[q0];

@@ -140,10 +140,154 @@ __device__ __forceinline__ void panel_factor_diag(double* A, double* invAll, int
     }
 }
 
+// X-phase work of one worker warp (see k_chol_panel3): 8-row tiles ta (and tb, if < nmt) of the rows from j2;
+//   U: block column jb -> block column jb+1 (rank 6), L: finished columns [0, j1) -> block column jb+2.
+__device__ __forceinline__ void panel_worker_tiles(double* A, int R, int nt, int jb, int ta, int tb, int lane) {
+    const int j0 = 6 * jb, j1 = j0 + 6, j2 = j1 + 6;
+    const int fr8 = lane >> 2, fk = lane & 3;
+    const int nmt = (R - j2 + 7) >> 3;
+    if (ta < nmt) {
+        const bool two = tb < nmt, la = jb + 2 < nt;
+        const int cl = 2 * fk;
+        const bool st = cl < 6;                 // lanes whose two output columns exist
+        const int ra = j2 + 8 * ta + fr8, rb = j2 + 8 * (two ? tb : ta) + fr8;
+        const int cu = st ? j1 + cl : j1, cv = (st && la) ? j2 + cl : j1;      // valid columns for every lane
+        // ---- U operands (columns j0 + fk and j0 + 4 + fk <= j1 + 1 exist) and targets
+        double bu0 = A[(j0 + fk) * PANEL_LD + j1 + fr8], bu1 = A[(j0 + 4 + fk) * PANEL_LD + j1 + fr8];
+        double au0 = A[(j0 + fk) * PANEL_LD + ra], au1 = A[(j0 + 4 + fk) * PANEL_LD + ra];
+        double qu0 = A[(j0 + fk) * PANEL_LD + rb], qu1 = A[(j0 + 4 + fk) * PANEL_LD + rb];
+        if (fk >= 2) { bu1 = 0.0; au1 = 0.0; qu1 = 0.0; }
+        const double tu0 = A[cu * PANEL_LD + ra], tu1 = A[(cu + 1) * PANEL_LD + ra];
+        const double tv0 = A[cu * PANEL_LD + rb], tv1 = A[(cu + 1) * PANEL_LD + rb];
+        const double tc0 = A[cv * PANEL_LD + ra], tc1 = A[(cv + 1) * PANEL_LD + ra];
+        const double te0 = A[cv * PANEL_LD + rb], te1 = A[(cv + 1) * PANEL_LD + rb];
+        double u0 = 0.0, u1 = 0.0, v0 = 0.0, v1 = 0.0;
+        dmma884(u0, u1, au0, bu0);
+        dmma884(u0, u1, au1, bu1);
+        if (two) {
+            dmma884(v0, v1, qu0, bu0);
+            dmma884(v0, v1, qu1, bu1);
+        }
+        // ---- L: lane (fr8, fk) reads row (tile base + fr8) of column k0 + fk [+ 4]; pointers advance by
+        // eight columns per iteration, the partial last group is handled after the loop
+        double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0, e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
+        if (la) {
+            const double* Bp = A + j2 + fr8 + fk * PANEL_LD;
+            const double* Ap = A + ra + fk * PANEL_LD;
+            const double* Aq = A + rb + fk * PANEL_LD;
+            const int nfull = j1 >> 3, rem = j1 & 7;
+            const bool va = fk < rem, vb = fk + 4 < rem;
+            if (two) {
+#pragma unroll 2
+                for (int it = 0; it < nfull; it++) {
+                    const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
+                    const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                    const double q0 = Aq[0], q1 = Aq[4 * PANEL_LD];
+                    dmma884(c00, c01, a0, b0);
+                    dmma884(c10, c11, a1, b1);
+                    dmma884(e00, e01, q0, b0);
+                    dmma884(e10, e11, q1, b1);
+                    Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD; Aq += 8 * PANEL_LD;
+                }
+                if (rem) {                  // columns up to j1 + 7 < nc exist: load, then select
+                    double b0 = Bp[0], b1 = Bp[4 * PANEL_LD], a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                    double q0 = Aq[0], q1 = Aq[4 * PANEL_LD];
+                    if (!va) { b0 = 0.0; a0 = 0.0; q0 = 0.0; }
+                    if (!vb) { b1 = 0.0; a1 = 0.0; q1 = 0.0; }
+                    dmma884(c00, c01, a0, b0);
+                    dmma884(c10, c11, a1, b1);
+                    dmma884(e00, e01, q0, b0);
+                    dmma884(e10, e11, q1, b1);
+                }
+            } else {
+#pragma unroll 2
+                for (int it = 0; it < nfull; it++) {
+                    const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
+                    const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                    dmma884(c00, c01, a0, b0);
+                    dmma884(c10, c11, a1, b1);
+                    Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD;
+                }
+                if (rem) {
+                    double b0 = Bp[0], b1 = Bp[4 * PANEL_LD], a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                    if (!va) { b0 = 0.0; a0 = 0.0; }
+                    if (!vb) { b1 = 0.0; a1 = 0.0; }
+                    dmma884(c00, c01, a0, b0);
+                    dmma884(c10, c11, a1, b1);
+                }
+            }
+        }
+        // ---- stores
+        if (st && ra < R) {
+            A[(j1 + cl) * PANEL_LD + ra] = tu0 - u0;
+            A[(j1 + cl + 1) * PANEL_LD + ra] = tu1 - u1;
+            if (la) {
+                A[(j2 + cl) * PANEL_LD + ra] = tc0 - (c00 + c10);
+                A[(j2 + cl + 1) * PANEL_LD + ra] = tc1 - (c01 + c11);
+            }
+        }
+        if (two && st && rb < R) {
+            A[(j1 + cl) * PANEL_LD + rb] = tv0 - v0;
+            A[(j1 + cl + 1) * PANEL_LD + rb] = tv1 - v1;
+            if (la) {
+                A[(j2 + cl) * PANEL_LD + rb] = te0 - (e00 + e10);
+                A[(j2 + cl + 1) * PANEL_LD + rb] = te1 - (e01 + e11);
+            }
+        }
+    }
+}
+
+// S-phase work for one panel row r below the diagonal block jb: x L_D^T = a
+__device__ __forceinline__ void panel_row_solve(double* A, const double* invAll, int jb, int r) {
+    const int j0 = 6 * jb;
+    double x[6], Lc[5][6], iv[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) x[k] = A[(j0 + k) * PANEL_LD + r];
+#pragma unroll
+    for (int p = 0; p < 5; p++) {
+        const double2* lp = reinterpret_cast<const double2*>(A + (j0 + p) * PANEL_LD + j0);
+#pragma unroll
+        for (int h = 0; h < 3; h++) { const double2 v = lp[h]; Lc[p][2 * h] = v.x; Lc[p][2 * h + 1] = v.y; }
+    }
+    {
+        const double2* ip = reinterpret_cast<const double2*>(invAll + 6 * jb);
+#pragma unroll
+        for (int h = 0; h < 3; h++) { const double2 v = ip[h]; iv[2 * h] = v.x; iv[2 * h + 1] = v.y; }
+    }
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        double sv = x[k];
+#pragma unroll
+        for (int p = 0; p < k; p++) sv -= x[p] * Lc[p][k];
+        x[k] = sv * iv[k];
+    }
+#pragma unroll
+    for (int k = 0; k < 6; k++) A[(j0 + k) * PANEL_LD + r] = x[k];
+}
+// D_(jb+1) -= L_(jb+1,jb) L_(jb+1,jb)^T, one entry per lane (lanes < 21)
+__device__ __forceinline__ void panel_diag_update(double* A, int jb, int lane) {
+    const int j0 = 6 * jb, j1 = j0 + 6;
+    if (lane < 21) {
+        int i = 0;
+#pragma unroll
+        for (int q = 1; q < 6; q++) i += (lane >= tri(q, 0)) ? 1 : 0;
+        const int k = lane - tri(i, 0);
+        double sv = 0.0;
+#pragma unroll
+        for (int p = 0; p < 6; p++) sv += A[(j0 + p) * PANEL_LD + j1 + i] * A[(j0 + p) * PANEL_LD + j1 + k];
+        A[(j1 + k) * PANEL_LD + j1 + i] -= sv;
+    }
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+__device__ __forceinline__ void named_bar_arrive(int id, int nthreads) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+
 // `early` (set by the host for lev > 0 under programmatic dependent launch): the predecessor kernel -- the
 // update or panel kernel of the level below -- signals its dependents only after its own pdl_wait(), so when this
 // CTA runs, everything up to the Schur kernels has completed and the Hsc / bsc scatter may run before pdl_wait(),
 // overlapping the predecessor's tail.  Zeroing and the structure reads always do.
+// DC (decoupled chain, the default): warp 0 runs the whole chain of diagonal-block factors and is tied to the
+// worker warps by named barriers only -- see the loop.  DC = false keeps the CTA-wide two-barrier loop.
+template <bool DC>
 __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int lev, int early) {
     extern __shared__ __align__(16) double A[];   // PANEL_LD x nc, column-major
     __shared__ ChildRef chs[CHOL_MAXCH];
@@ -330,175 +474,230 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     //       [0, 6 jb + 6) to block column jb+2 (look-ahead) -- so the chain of dependent diagonal factors
     //       never waits for the bulk updates.
     // Warps 4, 8, 12 share warp 0's scheduler / FP64 pipe and sit phase X out.
-    const int fr8 = lane >> 2, fk = lane & 3;
-    const bool dbgT = c.dbg && blockIdx.x == 0 && tid == 0 && lev < 64;
-    long long tF = 0, tW = 0, tS = 0, tU = 0, t0 = 0, t1 = 0;
-    const bool dbgK = (c.dbg & 2) && blockIdx.x == 0 && tid == 32 && lev < 64;   // a worker warp's view
-    long long wU = 0, wL = 0, w0 = 0, w1 = 0;
-    const long long tLoop0 = dbgT ? clock64() : 0;
-    if (wid == 0) panel_factor_diag(A, invAll, &badFlag, 0, lane);
-    __syncthreads();
-    constexpr int NWK = 3 * (PANEL3_NW / 4);        // 12 worker warps
-    const int wk = (wid >> 2) * 3 + (wid & 3) - 1;   // worker index of warps with (wid & 3) != 0
-    for (int jb = 0; jb < nt; jb++) {
-        const int j0 = 6 * jb, j1 = j0 + 6, j2 = j1 + 6;
-        const bool more = (jb + 1 < nt);
-        if (dbgT) { t0 = clock64(); if (lev == 2 && jb < 16) g_cholTrace[4 * jb] = t0 - tLoop0; }
-        // phase S
-        {
-            const int r = j1 + tid + (dbgT ? (int)((unsigned long long)t0 >> 63) : 0);   // (timing: keeps the phase behind the clock read)
-            if (r < R) {
-                double x[6], Lc[5][6], iv[6];
-#pragma unroll
-                for (int k = 0; k < 6; k++) x[k] = A[(j0 + k) * PANEL_LD + r];
-#pragma unroll
-                for (int p = 0; p < 5; p++) {
-                    const double2* lp = reinterpret_cast<const double2*>(A + (j0 + p) * PANEL_LD + j0);
-#pragma unroll
-                    for (int h = 0; h < 3; h++) { const double2 v = lp[h]; Lc[p][2 * h] = v.x; Lc[p][2 * h + 1] = v.y; }
-                }
-                {
-                    const double2* ip = reinterpret_cast<const double2*>(invAll + 6 * jb);
-#pragma unroll
-                    for (int h = 0; h < 3; h++) { const double2 v = ip[h]; iv[2 * h] = v.x; iv[2 * h + 1] = v.y; }
-                }
-#pragma unroll
-                for (int k = 0; k < 6; k++) {
-                    double sv = x[k];
-#pragma unroll
-                    for (int p = 0; p < k; p++) sv -= x[p] * Lc[p][k];
-                    x[k] = sv * iv[k];
-                }
-#pragma unroll
-                for (int k = 0; k < 6; k++) A[(j0 + k) * PANEL_LD + r] = x[k];
-            }
-        }
-        __syncthreads();
-        if (dbgT) { t1 = clock64(); tS += t1 - t0; if (lev == 2 && jb < 16) g_cholTrace[4 * jb + 1] = t1 - tLoop0; }
-        if (!more) break;
-        // phase X
+    if constexpr (DC) {
+        // Decoupled loop.  Roles: warp 0 = chain, the 12 warps with (wid & 3) != 0 = workers (warps 4, 8, 12 share the
+        // chain's scheduler and FP64 pipe and sit the loop out).  Per block column jb:
+        //   chain    factor D_jb                                         -> arrive B1[jb&1]   "L_D(jb) ready"
+        //            wait B5: worker 0 has finished X(jb-1), i.e. rows j1..j1+7 of block columns jb, jb+1 are up to date
+        //            solve its own six rows j1..j1+5 against L_D(jb)       -> arrive B2[jb&1]   "rows of D_(jb+1) solved"
+        //            D_(jb+1) -= L L^T, next factor
+        //   workers  sync B1: solve the rows from j2 (S); sync B2 (also orders the workers among themselves);
+        //            X(jb): block column jb -> jb+1, finished columns -> jb+2 (panel_worker_tiles); worker 0 arrives B5.
+        // The chain never waits for the bulk updates of its own step, only for the tile of the NEXT diagonal block from
+        // the step before; it can be one step ahead, hence the two parities of B1 / B2.
+        constexpr int NWK = 3 * (PANEL3_NW / 4);
+        constexpr int NB = (NWK + 1) * 32;               // chain + workers
+        const bool dbgT = c.dbg && blockIdx.x == 0 && tid == 0 && lev < 64;
+        const long long tLoop0 = dbgT ? clock64() : 0;
         if (wid == 0) {
-            if (lane < 21) {                          // D_(jb+1) -= L_(jb+1,jb) L_(jb+1,jb)^T, one entry per lane
-                int i = 0;
-#pragma unroll
-                for (int q = 1; q < 6; q++) i += (lane >= tri(q, 0)) ? 1 : 0;
-                const int k = lane - tri(i, 0);
-                double sv = 0.0;
-#pragma unroll
-                for (int p = 0; p < 6; p++) sv += A[(j0 + p) * PANEL_LD + j1 + i] * A[(j0 + p) * PANEL_LD + j1 + k];
-                A[(j1 + k) * PANEL_LD + j1 + i] -= sv;
+            panel_factor_diag(A, invAll, &badFlag, 0, lane);
+            const bool trc = dbgT && lev == 2;      // diagnostics: chain clock at (arrive B1, after B5, after the factor)
+            for (int jb = 0; jb < nt; jb++) {
+                named_bar_arrive(1 + (jb & 1), NB);
+                if (trc && jb < 16) g_cholTrace[6 * jb] = clock64() - tLoop0;
+                if (jb + 1 == nt) break;
+                if (jb > 0) named_bar_sync(5, 64);
+                if (trc && jb < 16) g_cholTrace[6 * jb + 1] = clock64() - tLoop0;
+                if (lane < 6) panel_row_solve(A, invAll, jb, 6 * jb + 6 + lane);
+                __syncwarp();
+                named_bar_arrive(3 + (jb & 1), NB);
+                panel_diag_update(A, jb, lane);
+                __syncwarp();
+                panel_factor_diag(A, invAll, &badFlag, jb + 1, lane);
+                if (trc && jb < 16) g_cholTrace[6 * jb + 2] = clock64() - tLoop0;
             }
-            __syncwarp();
-            panel_factor_diag(A, invAll, &badFlag, jb + 1, lane);
-            if (dbgT) { t0 = clock64(); tF += t0 - t1; if (lev == 2 && jb < 16) g_cholTrace[4 * jb + 2] = t0 - tLoop0; }
         } else if ((wid & 3) != 0) {
-            // Worker warp: 8-row tiles ta (and tb) of the rows from j2.  All operand and target loads are issued
-            // before the first store (stores to the panel would otherwise serialise the next tile's loads):
-            //   U: block column jb -> block column jb+1 (rank 6, two DMMAs per tile),
-            //   L: finished columns [0, j1) -> block column jb+2 (look-ahead).
-            if (dbgK) w0 = clock64();
-            const int nmt = (R - j2 + 7) >> 3;          // <= 19 tiles: at most two per worker warp
-            const int ta = wk, tb = ta + NWK;
-            if (ta < nmt) {
-                const bool two = tb < nmt, la = jb + 2 < nt;
-                const int cl = 2 * fk;
-                const bool st = cl < 6;                 // lanes whose two output columns exist
-                const int ra = j2 + 8 * ta + fr8, rb = j2 + 8 * (two ? tb : ta) + fr8;
-                const int cu = st ? j1 + cl : j1, cv = (st && la) ? j2 + cl : j1;      // valid columns for every lane
-                // ---- U operands (columns j0 + fk and j0 + 4 + fk <= j1 + 1 exist) and targets
-                double bu0 = A[(j0 + fk) * PANEL_LD + j1 + fr8], bu1 = A[(j0 + 4 + fk) * PANEL_LD + j1 + fr8];
-                double au0 = A[(j0 + fk) * PANEL_LD + ra], au1 = A[(j0 + 4 + fk) * PANEL_LD + ra];
-                double qu0 = A[(j0 + fk) * PANEL_LD + rb], qu1 = A[(j0 + 4 + fk) * PANEL_LD + rb];
-                if (fk >= 2) { bu1 = 0.0; au1 = 0.0; qu1 = 0.0; }
-                const double tu0 = A[cu * PANEL_LD + ra], tu1 = A[(cu + 1) * PANEL_LD + ra];
-                const double tv0 = A[cu * PANEL_LD + rb], tv1 = A[(cu + 1) * PANEL_LD + rb];
-                const double tc0 = A[cv * PANEL_LD + ra], tc1 = A[(cv + 1) * PANEL_LD + ra];
-                const double te0 = A[cv * PANEL_LD + rb], te1 = A[(cv + 1) * PANEL_LD + rb];
-                double u0 = 0.0, u1 = 0.0, v0 = 0.0, v1 = 0.0;
-                dmma884(u0, u1, au0, bu0);
-                dmma884(u0, u1, au1, bu1);
-                if (two) {
-                    dmma884(v0, v1, qu0, bu0);
-                    dmma884(v0, v1, qu1, bu1);
-                }
-                if (dbgK) { w1 = clock64(); wU += w1 - w0; }
-                // ---- L: lane (fr8, fk) reads row (tile base + fr8) of column k0 + fk [+ 4]; pointers advance by
-                // eight columns per iteration, the partial last group is handled after the loop
-                double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0, e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
-                if (la) {
-                    const double* Bp = A + j2 + fr8 + fk * PANEL_LD;
-                    const double* Ap = A + ra + fk * PANEL_LD;
-                    const double* Aq = A + rb + fk * PANEL_LD;
-                    const int nfull = j1 >> 3, rem = j1 & 7;
-                    const bool va = fk < rem, vb = fk + 4 < rem;
-                    if (two) {
-#pragma unroll 2
-                        for (int it = 0; it < nfull; it++) {
-                            const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
-                            const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
-                            const double q0 = Aq[0], q1 = Aq[4 * PANEL_LD];
-                            dmma884(c00, c01, a0, b0);
-                            dmma884(c10, c11, a1, b1);
-                            dmma884(e00, e01, q0, b0);
-                            dmma884(e10, e11, q1, b1);
-                            Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD; Aq += 8 * PANEL_LD;
-                        }
-                        if (rem) {                  // columns up to j1 + 7 < nc exist: load, then select
-                            double b0 = Bp[0], b1 = Bp[4 * PANEL_LD], a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
-                            double q0 = Aq[0], q1 = Aq[4 * PANEL_LD];
-                            if (!va) { b0 = 0.0; a0 = 0.0; q0 = 0.0; }
-                            if (!vb) { b1 = 0.0; a1 = 0.0; q1 = 0.0; }
-                            dmma884(c00, c01, a0, b0);
-                            dmma884(c10, c11, a1, b1);
-                            dmma884(e00, e01, q0, b0);
-                            dmma884(e10, e11, q1, b1);
-                        }
-                    } else {
-#pragma unroll 2
-                        for (int it = 0; it < nfull; it++) {
-                            const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
-                            const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
-                            dmma884(c00, c01, a0, b0);
-                            dmma884(c10, c11, a1, b1);
-                            Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD;
-                        }
-                        if (rem) {
-                            double b0 = Bp[0], b1 = Bp[4 * PANEL_LD], a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
-                            if (!va) { b0 = 0.0; a0 = 0.0; }
-                            if (!vb) { b1 = 0.0; a1 = 0.0; }
-                            dmma884(c00, c01, a0, b0);
-                            dmma884(c10, c11, a1, b1);
-                        }
-                    }
-                }
-                // ---- stores
-                if (st && ra < R) {
-                    A[(j1 + cl) * PANEL_LD + ra] = tu0 - u0;
-                    A[(j1 + cl + 1) * PANEL_LD + ra] = tu1 - u1;
-                    if (la) {
-                        A[(j2 + cl) * PANEL_LD + ra] = tc0 - (c00 + c10);
-                        A[(j2 + cl + 1) * PANEL_LD + ra] = tc1 - (c01 + c11);
-                    }
-                }
-                if (two && st && rb < R) {
-                    A[(j1 + cl) * PANEL_LD + rb] = tv0 - v0;
-                    A[(j1 + cl + 1) * PANEL_LD + rb] = tv1 - v1;
-                    if (la) {
-                        A[(j2 + cl) * PANEL_LD + rb] = te0 - (e00 + e10);
-                        A[(j2 + cl + 1) * PANEL_LD + rb] = te1 - (e01 + e11);
-                    }
-                }
+            const int wk = (wid >> 2) * 3 + (wid & 3) - 1;
+            const int wt = wk * 32 + lane;
+            const bool trw = c.dbg && blockIdx.x == 0 && tid == 32 && lev == 2;   // worker 0: clock after (B1, B2, X)
+            const long long tw0 = trw ? clock64() : 0;
+            for (int jb = 0; jb < nt; jb++) {
+                const bool more = jb + 1 < nt;
+                named_bar_sync(1 + (jb & 1), NB);
+                if (trw && jb < 16) g_cholTrace[6 * jb + 3] = clock64() - tw0;
+                const int r = 6 * jb + (more ? 12 : 6) + wt;      // the chain solves the six rows of the next diagonal block
+                if (r < R) panel_row_solve(A, invAll, jb, r);
+                if (!more) break;
+                named_bar_sync(3 + (jb & 1), NB);
+                if (trw && jb < 16) g_cholTrace[6 * jb + 4] = clock64() - tw0;
+                panel_worker_tiles(A, R, nt, jb, wk, NWK + (NWK - 1 - wk), lane);   // worker 0 gets the last extra tile
+                if (wk == 0 && jb + 2 < nt) named_bar_arrive(5, 64);
+                if (trw && jb < 16) g_cholTrace[6 * jb + 5] = clock64() - tw0;
             }
-            if (dbgK) wL += clock64() - w1;
         }
         __syncthreads();
-        if (dbgT) { t1 = clock64(); tW += t1 - t0; if (lev == 2 && jb < 16) g_cholTrace[4 * jb + 3] = t1 - tLoop0; }
-    }
-    if (dbgK) { g_cholDbg[lev * 24 + 20] = wU; g_cholDbg[lev * 24 + 21] = wL; }
-    if (dbgT) {
-        tU = clock64() - tLoop0;          // whole factor loop incl. the first diagonal factor
-        g_cholDbg[lev * 24 + 12] = tF; g_cholDbg[lev * 24 + 13] = tW;
-        g_cholDbg[lev * 24 + 14] = tS; g_cholDbg[lev * 24 + 15] = tU;
+        if (dbgT) g_cholDbg[lev * 24 + 15] = clock64() - tLoop0;
+    } else {
+        const int fr8 = lane >> 2, fk = lane & 3;
+        const bool dbgT = c.dbg && blockIdx.x == 0 && tid == 0 && lev < 64;
+        long long tF = 0, tW = 0, tS = 0, tU = 0, t0 = 0, t1 = 0;
+        const bool dbgK = (c.dbg & 2) && blockIdx.x == 0 && tid == 32 && lev < 64;   // a worker warp's view
+        long long wU = 0, wL = 0, w0 = 0, w1 = 0;
+        const long long tLoop0 = dbgT ? clock64() : 0;
+        if (wid == 0) panel_factor_diag(A, invAll, &badFlag, 0, lane);
+        __syncthreads();
+        constexpr int NWK = 3 * (PANEL3_NW / 4);        // 12 worker warps
+        const int wk = (wid >> 2) * 3 + (wid & 3) - 1;   // worker index of warps with (wid & 3) != 0
+        for (int jb = 0; jb < nt; jb++) {
+            const int j0 = 6 * jb, j1 = j0 + 6, j2 = j1 + 6;
+            const bool more = (jb + 1 < nt);
+            if (dbgT) { t0 = clock64(); if (lev == 2 && jb < 16) g_cholTrace[4 * jb] = t0 - tLoop0; }
+            // phase S
+            {
+                const int r = j1 + tid + (dbgT ? (int)((unsigned long long)t0 >> 63) : 0);   // (timing: keeps the phase behind the clock read)
+                if (r < R) {
+                    double x[6], Lc[5][6], iv[6];
+    #pragma unroll
+                    for (int k = 0; k < 6; k++) x[k] = A[(j0 + k) * PANEL_LD + r];
+    #pragma unroll
+                    for (int p = 0; p < 5; p++) {
+                        const double2* lp = reinterpret_cast<const double2*>(A + (j0 + p) * PANEL_LD + j0);
+    #pragma unroll
+                        for (int h = 0; h < 3; h++) { const double2 v = lp[h]; Lc[p][2 * h] = v.x; Lc[p][2 * h + 1] = v.y; }
+                    }
+                    {
+                        const double2* ip = reinterpret_cast<const double2*>(invAll + 6 * jb);
+    #pragma unroll
+                        for (int h = 0; h < 3; h++) { const double2 v = ip[h]; iv[2 * h] = v.x; iv[2 * h + 1] = v.y; }
+                    }
+    #pragma unroll
+                    for (int k = 0; k < 6; k++) {
+                        double sv = x[k];
+    #pragma unroll
+                        for (int p = 0; p < k; p++) sv -= x[p] * Lc[p][k];
+                        x[k] = sv * iv[k];
+                    }
+    #pragma unroll
+                    for (int k = 0; k < 6; k++) A[(j0 + k) * PANEL_LD + r] = x[k];
+                }
+            }
+            __syncthreads();
+            if (dbgT) { t1 = clock64(); tS += t1 - t0; if (lev == 2 && jb < 16) g_cholTrace[4 * jb + 1] = t1 - tLoop0; }
+            if (!more) break;
+            // phase X
+            if (wid == 0) {
+                if (lane < 21) {                          // D_(jb+1) -= L_(jb+1,jb) L_(jb+1,jb)^T, one entry per lane
+                    int i = 0;
+    #pragma unroll
+                    for (int q = 1; q < 6; q++) i += (lane >= tri(q, 0)) ? 1 : 0;
+                    const int k = lane - tri(i, 0);
+                    double sv = 0.0;
+    #pragma unroll
+                    for (int p = 0; p < 6; p++) sv += A[(j0 + p) * PANEL_LD + j1 + i] * A[(j0 + p) * PANEL_LD + j1 + k];
+                    A[(j1 + k) * PANEL_LD + j1 + i] -= sv;
+                }
+                __syncwarp();
+                panel_factor_diag(A, invAll, &badFlag, jb + 1, lane);
+                if (dbgT) { t0 = clock64(); tF += t0 - t1; if (lev == 2 && jb < 16) g_cholTrace[4 * jb + 2] = t0 - tLoop0; }
+            } else if ((wid & 3) != 0) {
+                // Worker warp: 8-row tiles ta (and tb) of the rows from j2.  All operand and target loads are issued
+                // before the first store (stores to the panel would otherwise serialise the next tile's loads):
+                //   U: block column jb -> block column jb+1 (rank 6, two DMMAs per tile),
+                //   L: finished columns [0, j1) -> block column jb+2 (look-ahead).
+                if (dbgK) w0 = clock64();
+                const int nmt = (R - j2 + 7) >> 3;          // <= 19 tiles: at most two per worker warp
+                const int ta = wk, tb = ta + NWK;
+                if (ta < nmt) {
+                    const bool two = tb < nmt, la = jb + 2 < nt;
+                    const int cl = 2 * fk;
+                    const bool st = cl < 6;                 // lanes whose two output columns exist
+                    const int ra = j2 + 8 * ta + fr8, rb = j2 + 8 * (two ? tb : ta) + fr8;
+                    const int cu = st ? j1 + cl : j1, cv = (st && la) ? j2 + cl : j1;      // valid columns for every lane
+                    // ---- U operands (columns j0 + fk and j0 + 4 + fk <= j1 + 1 exist) and targets
+                    double bu0 = A[(j0 + fk) * PANEL_LD + j1 + fr8], bu1 = A[(j0 + 4 + fk) * PANEL_LD + j1 + fr8];
+                    double au0 = A[(j0 + fk) * PANEL_LD + ra], au1 = A[(j0 + 4 + fk) * PANEL_LD + ra];
+                    double qu0 = A[(j0 + fk) * PANEL_LD + rb], qu1 = A[(j0 + 4 + fk) * PANEL_LD + rb];
+                    if (fk >= 2) { bu1 = 0.0; au1 = 0.0; qu1 = 0.0; }
+                    const double tu0 = A[cu * PANEL_LD + ra], tu1 = A[(cu + 1) * PANEL_LD + ra];
+                    const double tv0 = A[cu * PANEL_LD + rb], tv1 = A[(cu + 1) * PANEL_LD + rb];
+                    const double tc0 = A[cv * PANEL_LD + ra], tc1 = A[(cv + 1) * PANEL_LD + ra];
+                    const double te0 = A[cv * PANEL_LD + rb], te1 = A[(cv + 1) * PANEL_LD + rb];
+                    double u0 = 0.0, u1 = 0.0, v0 = 0.0, v1 = 0.0;
+                    dmma884(u0, u1, au0, bu0);
+                    dmma884(u0, u1, au1, bu1);
+                    if (two) {
+                        dmma884(v0, v1, qu0, bu0);
+                        dmma884(v0, v1, qu1, bu1);
+                    }
+                    if (dbgK) { w1 = clock64(); wU += w1 - w0; }
+                    // ---- L: lane (fr8, fk) reads row (tile base + fr8) of column k0 + fk [+ 4]; pointers advance by
+                    // eight columns per iteration, the partial last group is handled after the loop
+                    double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0, e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
+                    if (la) {
+                        const double* Bp = A + j2 + fr8 + fk * PANEL_LD;
+                        const double* Ap = A + ra + fk * PANEL_LD;
+                        const double* Aq = A + rb + fk * PANEL_LD;
+                        const int nfull = j1 >> 3, rem = j1 & 7;
+                        const bool va = fk < rem, vb = fk + 4 < rem;
+                        if (two) {
+    #pragma unroll 2
+                            for (int it = 0; it < nfull; it++) {
+                                const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
+                                const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                                const double q0 = Aq[0], q1 = Aq[4 * PANEL_LD];
+                                dmma884(c00, c01, a0, b0);
+                                dmma884(c10, c11, a1, b1);
+                                dmma884(e00, e01, q0, b0);
+                                dmma884(e10, e11, q1, b1);
+                                Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD; Aq += 8 * PANEL_LD;
+                            }
+                            if (rem) {                  // columns up to j1 + 7 < nc exist: load, then select
+                                double b0 = Bp[0], b1 = Bp[4 * PANEL_LD], a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                                double q0 = Aq[0], q1 = Aq[4 * PANEL_LD];
+                                if (!va) { b0 = 0.0; a0 = 0.0; q0 = 0.0; }
+                                if (!vb) { b1 = 0.0; a1 = 0.0; q1 = 0.0; }
+                                dmma884(c00, c01, a0, b0);
+                                dmma884(c10, c11, a1, b1);
+                                dmma884(e00, e01, q0, b0);
+                                dmma884(e10, e11, q1, b1);
+                            }
+                        } else {
+    #pragma unroll 2
+                            for (int it = 0; it < nfull; it++) {
+                                const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
+                                const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                                dmma884(c00, c01, a0, b0);
+                                dmma884(c10, c11, a1, b1);
+                                Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD;
+                            }
+                            if (rem) {
+                                double b0 = Bp[0], b1 = Bp[4 * PANEL_LD], a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                                if (!va) { b0 = 0.0; a0 = 0.0; }
+                                if (!vb) { b1 = 0.0; a1 = 0.0; }
+                                dmma884(c00, c01, a0, b0);
+                                dmma884(c10, c11, a1, b1);
+                            }
+                        }
+                    }
+                    // ---- stores
+                    if (st && ra < R) {
+                        A[(j1 + cl) * PANEL_LD + ra] = tu0 - u0;
+                        A[(j1 + cl + 1) * PANEL_LD + ra] = tu1 - u1;
+                        if (la) {
+                            A[(j2 + cl) * PANEL_LD + ra] = tc0 - (c00 + c10);
+                            A[(j2 + cl + 1) * PANEL_LD + ra] = tc1 - (c01 + c11);
+                        }
+                    }
+                    if (two && st && rb < R) {
+                        A[(j1 + cl) * PANEL_LD + rb] = tv0 - v0;
+                        A[(j1 + cl + 1) * PANEL_LD + rb] = tv1 - v1;
+                        if (la) {
+                            A[(j2 + cl) * PANEL_LD + rb] = te0 - (e00 + e10);
+                            A[(j2 + cl + 1) * PANEL_LD + rb] = te1 - (e01 + e11);
+                        }
+                    }
+                }
+                if (dbgK) wL += clock64() - w1;
+            }
+            __syncthreads();
+            if (dbgT) { t1 = clock64(); tW += t1 - t0; if (lev == 2 && jb < 16) g_cholTrace[4 * jb + 3] = t1 - tLoop0; }
+        }
+        if (dbgK) { g_cholDbg[lev * 24 + 20] = wU; g_cholDbg[lev * 24 + 21] = wL; }
+        if (dbgT) {
+            tU = clock64() - tLoop0;          // whole factor loop incl. the first diagonal factor
+            g_cholDbg[lev * 24 + 12] = tF; g_cholDbg[lev * 24 + 13] = tW;
+            g_cholDbg[lev * 24 + 14] = tS; g_cholDbg[lev * 24 + 15] = tU;
+        }
     }
     CHOL_STAMP(4);
     // ---- write the panel rows this CTA owns (a warp per column, lanes along the rows)

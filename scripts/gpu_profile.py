@@ -45,6 +45,10 @@ if os.environ.get("CUGO_B200_DEBUG") == "1":
         print("  lev %2d panel" % lev, np.diff(dc[lev, :6]).tolist(), " update (stage, mma, pull+store)",
               np.diff(dc[lev, 8:12]).tolist(), " bwd (load, gemv, trsv)", np.diff(dc[lev, 16:20]).tolist(),
               " factor loop (warp 0 diag update + factor, wait for workers, row solve, whole loop)", dc[lev, 12:16].tolist(), " worker (rank6, look-ahead)", dc[lev, 20:22].tolist())
+    tr6 = s.debug_counters(96).reshape(-1)[:96].reshape(16, 6)
+    print("decoupled panel loop, level 2, CTA 0, per step: chain clock at (arrive B1, after B5, after factor) | worker 0 clock after (B1, B2, X)")
+    for jb in range(16):
+        print("   step %2d" % jb, tr6[jb, :3].tolist(), tr6[jb, 3:].tolist())
     tr = s.debug_counters(96).reshape(-1)[:64].reshape(16, 4)
     print("level 2, CTA 0, thread 0: clock at (step start, after S barrier, after warp-0 work, after X barrier) per step")
     for jb in range(16):
