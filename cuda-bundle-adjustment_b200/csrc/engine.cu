@@ -115,6 +115,10 @@ struct HostSet {
 struct Solver {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t side = nullptr;   // low-priority branch of the trial graph: k_chol_zinv beside the factorisation
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    bool bwdSplit = true;          // CUGO_B200_BWDSPLIT=0: one CTA per supernode in the backward solve
+    bool zinvOn = true;            // CUGO_B200_ZINV=0: backward solves by blocked substitution on every level
     std::string err;
     // host copies of the problem
     int nP_all = 0, nP = 0, nL_all = 0, nL = 0;
@@ -162,7 +166,8 @@ struct Solver {
         z_asmCol, z_trsmPtr, z_updPtr;
     DBuf<long long> z_Lptr, z_Uptr;
     DBuf<SymCounts> y_counts;
-    DBuf<double> cL, cU, cX, cW;
+    DBuf<double> cL, cU, cX, cW, cZ, cPart;
+    DBuf<int> cCnt;
     DBuf<int> z_levMaxNt;
     // multi-GPU
     int nranks = 1, rank = 0;
@@ -232,6 +237,9 @@ struct Solver {
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
         if (comm && g_nccl.CommDestroy) g_nccl.CommDestroy(comm);
+        if (evFork) cudaEventDestroy(evFork);
+        if (evJoin) cudaEventDestroy(evJoin);
+        if (side) cudaStreamDestroy(side);
         if (stream) cudaStreamDestroy(stream);
     }
 
@@ -619,6 +627,10 @@ void Solver::buildStructure() {
         pdl = !(p && p[0] == '0');
         const char* dc = getenv("CUGO_B200_PANELDC");
         panelDC = !(dc && dc[0] == '0');
+        const char* bs = getenv("CUGO_B200_BWDSPLIT");
+        bwdSplit = !(bs && bs[0] == '0');
+        const char* zi = getenv("CUGO_B200_ZINV");
+        zinvOn = !(zi && zi[0] == '0');
         const char* fb = getenv("CUGO_B200_FUSEBUILD");
         fuseBuild = !(fb && fb[0] == '0');
     }
@@ -645,6 +657,9 @@ void Solver::buildStructure() {
     if (counts.maxCols > CHOL_MAXW) throw CudaError("internal: supernode wider than CHOL_MAXW");
     maxRt = counts.maxFront;   // upper bound of r_t
     cL.alloc((size_t)counts.lsize); cU.alloc((size_t)counts.usize); cX.alloc((size_t)P * 6); cW.alloc((size_t)P * 21);
+    cZ.alloc((size_t)P * 6 * 6 * CHOL_MAXW);
+    cPart.alloc((size_t)nsn * BWD_MAXG * 6 * CHOL_MAXW); cCnt.alloc(nsn);
+    CK(cudaMemsetAsync(cCnt.p, 0, sizeof(int) * nsn, stream));
 
     // ---- system buffers
     Hpp.alloc((size_t)nP * 36); Hll.alloc((size_t)nL * 9);
@@ -681,7 +696,7 @@ void Solver::buildStructure() {
     c.levelPtr = z_levelPtr; c.levelSn = z_levelSn; c.Lptr = z_Lptr; c.Uptr = z_Uptr; c.childPtr = z_childPtr;
     c.childIdx = z_childIdx; c.invPtr = z_invPtr; c.inv = z_inv; c.snBlkPtr = z_snBlkPtr; c.asmBlk = z_asmBlk;
     c.asmRow = z_asmRow; c.asmCol = z_asmCol; c.trsmPtr = z_trsmPtr; c.updPtr = z_updPtr;
-    c.L = cL; c.U = cU; c.xperm = cX; c.Winv = cW;
+    c.L = cL; c.U = cU; c.xperm = cX; c.Winv = cW; c.Zinv = cZ; c.bwdPart = cPart; c.bwdCnt = cCnt;
     { const char* e = getenv("CUGO_B200_DEBUG"); c.dbg = e ? atoi(e) : 0; }   // 1: phase stamps; 3: also a worker warp's view of the panel loop
 
     // dynamic shared memory opt-in for the factorisation kernels
@@ -699,6 +714,15 @@ void Solver::buildStructure() {
     if (bwd2Bytes > 227 * 1024) throw UnsupportedError("front too large for the shared-memory backward solve of this version");
     CK(cudaFuncSetAttribute(k_chol_bwd2<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd2Bytes));
     CK(cudaFuncSetAttribute(k_chol_bwd3<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd2Bytes));
+    CK(cudaFuncSetAttribute(k_chol_zinv<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            (int)((2 * (size_t)ncMax * (ncMax + 1) + 21 * CHOL_MAXW + 36 * 8) * 8)));
+    if (!side) {
+        int lo = 0, hi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));     // lo = lowest priority
+        CK(cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, lo));
+        CK(cudaEventCreateWithFlags(&evFork, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&evJoin, cudaEventDisableTiming));
+    }
     CK(cudaFuncSetAttribute(k_chol_panel3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_LD * ncMax * 8));
     CK(cudaFuncSetAttribute(k_chol_panel3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_LD * ncMax * 8));
     CK(cudaFuncSetAttribute(k_chol_update3, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -750,6 +774,10 @@ void Solver::enqueueSolve() {
     const int ncMax = 6 * CHOL_MAXW;
     if (cholGen >= 2) {
         const bool g3 = cholGen == 3;
+        // levels [0, zTop] solve backward with the inverse of L11 (k_chol_zinv has the whole rest of the factorisation
+        // to finish); the top three keep the blocked substitution
+        const bool zOn = g3 && zinvOn && pdl && !profiling;
+        const int zTop = c.nlev - 4;
         for (int lev = 0; lev < c.nlev; lev++) {
             const int q0 = h_levelPtr[lev], q1 = h_levelPtr[lev + 1];
             const int ncLev = 6 * h_levMaxNt[lev];
@@ -757,6 +785,13 @@ void Solver::enqueueSolve() {
                            (size_t)PANEL_LD * ncLev * 8, d, c, lev, (pdl && !profiling && lev > 0) ? 1 : 0);
             else k_chol_panel<<<h_trsmPtr[q1] - h_trsmPtr[q0], PANEL_TPB, PANEL_LD * ncLev * 8, stream>>>(d, c, lev);
             mark("chol_panel");
+            if (zOn && lev <= zTop) {      // L11^-1 of the level on the low-priority branch, beside the rest of the factorisation
+                CK(cudaEventRecord(evFork, stream));
+                CK(cudaStreamWaitEvent(side, evFork, 0));
+                const size_t zb = (2 * (size_t)ncLev * (ncLev + 1) + 21 * CHOL_MAXW + 36 * 8) * 8;
+                k_chol_zinv<256><<<q1 - q0, 256, zb, side>>>(d, c, lev);
+                kernelsPerSlot++;
+            }
             const int nUpd = h_updPtr[q1] - h_updPtr[q0];
             if (nUpd > 0) {
                 if (g3) {
@@ -772,8 +807,15 @@ void Solver::enqueueSolve() {
         for (int lev = c.nlev - 1; lev >= 0; lev--) {
             const int ncLev = 6 * h_levMaxNt[lev];
             const size_t bytes = ((size_t)ncLev * (ncLev + 1) + ncLev + 21 * CHOL_MAXW + 6 * (size_t)maxRt) * 8;
-            if (g3) launch(k_chol_bwd3<256>, h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bytes, d, c, lev,
-                           (pdl && !profiling && lev < c.nlev - 1) ? 1 : 0);
+            if (zOn && lev == zTop) {
+                CK(cudaEventRecord(evJoin, side));
+                CK(cudaStreamWaitEvent(stream, evJoin, 0));
+            }
+            // few supernodes on a level: several CTAs share the L21^T x_R product of each
+            const int nsnLev = h_levelPtr[lev + 1] - h_levelPtr[lev];
+            const int G = bwdSplit ? std::max(1, std::min(BWD_MAXG, 148 / nsnLev)) : 1;
+            if (g3) launch(k_chol_bwd3<256>, nsnLev * G, 256, bytes, d, c, lev,
+                           (pdl && !profiling && lev < c.nlev - 1) ? 1 : 0, (zOn && lev <= zTop) ? 1 : 0, G);
             else k_chol_bwd2<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bytes, stream>>>(d, c, lev);
             mark("chol_bwd");
         }

@@ -134,8 +134,11 @@ struct Chol {
     const int* updPtr;     // [nsn+1] prefix of update-tile tasks in levelSn order
     double* L;
     double* U;
+    double* Zinv;          // [6 P x 6 MAXW] inverse of every supernode's diagonal block L11 (k_chol_zinv), or unused
     double* Winv;          // [21 P] inverse of each 6x6 diagonal Cholesky block (packed lower), by permuted column block
     double* xperm;         // [6P] solution in permuted order
+    double* bwdPart;       // [nsn x 8 x 6 MAXW] partial L21^T x_R vectors of the CTAs sharing a supernode (k_chol_bwd3)
+    int* bwdCnt;           // [nsn] arrival counters of those CTAs (zero between trials)
     int dbg;               // 1: kernels record phase timestamps (diagnostics)
 };
 

@@ -18,6 +18,7 @@
 namespace cugo_b200 {
 
 constexpr int PANEL3_TPB = 512;
+constexpr int BWD_MAXG = 8;            // CTAs that may share one supernode in the backward solve
 constexpr int PANEL3_NW = PANEL3_TPB / 32;
 
 // pull the children's contributions to 6 consecutive rows (or the rhs element) of one front column
@@ -904,19 +905,110 @@ __global__ void __launch_bounds__(UPD3_TPB) k_chol_update3(Dev d, Chol c, int le
 }
 
 // ---------------------------------------------------------------------------
-// Backward substitution, one CTA per supernode, levels walked top-down (see k_chol_bwd2).
-// L11 / W are staged asynchronously; the L21^T x_R product issues 4 x CPW independent loads per
-// lane before the first use.
+// ---------------------------------------------------------------------------
+// Z = L11^-1 of every supernode of a level -> c.Zinv (block lower triangle, nc x nc column-major per supernode at
+// offset 6 s * 6 MAXW).  Runs on a side branch of the trial graph, concurrently with the rest of the
+// factorisation, so that the backward solve of the level is a product with Z^T instead of a 16-step triangular
+// solve (k_chol_bwd3).  Z_jj = W_j (the 6x6 inverses the panel kernel left), Z_ij = -W_i sum_k L_ik Z_kj.
 template <int TPB>
-__global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int early) {
+__global__ void __launch_bounds__(TPB) k_chol_zinv(Dev d, Chol c, int lev) {
     extern __shared__ double sm[];
+    const LMState* st = d.st;
+    if (st->done) return;
+    const SnInfo n = sn_info(c, c.levelSn[c.levelPtr[lev] + blockIdx.x]);
+    const int nc = n.nc, nt = n.nt, tid = threadIdx.x, ldL = nc + 1;
+    double* L11 = sm;                   // nc columns, leading dimension ldL
+    double* Wsm = L11 + nc * ldL;       // 21 nt
+    double* T = Wsm + 21 * nt;          // per-warp 6x6 scratch
+    double* Zs = T + 36 * (TPB / 32);   // nc columns, leading dimension ldL
+    const double* __restrict__ Pn = c.L + c.Lptr[n.t];
+    for (int i = tid; i < nc * nc; i += TPB) {
+        const int r = i % nc, cc = i / nc;
+        if (r > cc) cp_async8(L11 + cc * ldL + r, Pn + (size_t)cc * n.m + r, true);
+    }
+    for (int i = tid; i < 21 * nt; i += TPB) cp_async8(Wsm + i, c.Winv + (size_t)n.s * 21 + i, true);
+    cp_async_wait_all();
+    __syncthreads();
+    // ---- Z = L11^-1 into its own buffer, block column by block column: Z_jj = W_j, Z_ij = -W_i sum_k L_ik Z_kj.
+    // The block columns are independent, so a warp owns two of them (j and nt-1-j: equal work) and only needs
+    // __syncwarp; 18 lanes hold a 2x1 piece of the 6x6 block each.
+    {
+        const int lane = tid & 31, wid = tid >> 5;
+        double* Sw = T + 36 * wid;                      // per-warp 6x6 scratch (T holds 6 nc >= 36 * 8 only if nc >= 48: see host)
+        const int half = (nt + 1) >> 1;
+        for (int pass = 0; pass < 2; pass++) {
+            const int j = pass == 0 ? wid : nt - 1 - wid;
+            if (pass == 0 ? (wid >= half) : (j < half)) continue;
+            if (lane < 21) {
+                int p = 0;
+#pragma unroll
+                for (int q = 1; q < 6; q++) p += (lane >= tri(q, 0)) ? 1 : 0;
+                const int q = lane - tri(p, 0);
+                Zs[(6 * j + q) * ldL + 6 * j + p] = Wsm[21 * j + lane];
+            }
+            __syncwarp();
+            const int cz = lane / 3, rp = lane - 3 * cz;        // lanes < 18: column cz, rows 2 rp, 2 rp + 1 of the block
+            for (int i = j + 1; i < nt; i++) {
+                if (lane < 18) {
+                    const double* zc = Zs + (6 * j + cz) * ldL;
+                    const double* lr = L11 + 6 * i + 2 * rp;
+                    double s0a = 0.0, s0b = 0.0, s1a = 0.0, s1b = 0.0;
+                    int s2 = 6 * j + cz;
+                    for (; s2 + 1 < 6 * i; s2 += 2) {
+                        const double z0 = zc[s2], z1 = zc[s2 + 1];
+                        s0a += lr[s2 * ldL] * z0; s1a += lr[s2 * ldL + 1] * z0;
+                        s0b += lr[(s2 + 1) * ldL] * z1; s1b += lr[(s2 + 1) * ldL + 1] * z1;
+                    }
+                    if (s2 < 6 * i) { const double z0 = zc[s2]; s0a += lr[s2 * ldL] * z0; s1a += lr[s2 * ldL + 1] * z0; }
+                    Sw[cz * 6 + 2 * rp] = s0a + s0b;
+                    Sw[cz * 6 + 2 * rp + 1] = s1a + s1b;
+                }
+                __syncwarp();
+                if (lane < 18) {
+                    const double* Wb = Wsm + 21 * i;
+#pragma unroll
+                    for (int e = 0; e < 2; e++) {
+                        const int rr = 2 * rp + e;
+                        double sv = 0.0;
+#pragma unroll
+                        for (int k = 0; k < 6; k++)
+                            if (k <= rr) sv += Wb[tri(rr, k)] * Sw[cz * 6 + k];
+                        Zs[(6 * j + cz) * ldL + 6 * i + rr] = -sv;
+                    }
+                }
+                __syncwarp();
+            }
+        }
+    }
+    __syncthreads();
+    double* __restrict__ Zg = c.Zinv + (size_t)(6 * n.s) * (6 * CHOL_MAXW);
+    for (int i = tid; i < nc * nc; i += TPB) {
+        const int r = i % nc, cc = i / nc;
+        if (r / 6 > cc / 6 || (r / 6 == cc / 6 && r >= cc)) Zg[(size_t)cc * nc + r] = Zs[cc * ldL + r];
+    }
+}
+
+// Backward substitution, one CTA per supernode, levels walked top-down: x_t = L11^-T (y_t - L21^T x_R).
+// useZ: Z = L11^-1 is in c.Zinv (k_chol_zinv) and the solve is a product with Z^T; otherwise L11 / W are staged
+// and warp 0 runs the blocked triangular solve.  The L21^T x_R product issues 4 x CPW independent loads per lane
+// before the first use.
+template <int TPB>
+__global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int early, int useZ, int G) {
+    extern __shared__ double sm[];
+    __shared__ int shTicket;
     const LMState* st = d.st;
     // `early` (host: every level but the first one solved, under programmatic dependent launch): the predecessor
     // is a backward kernel that signals after its own pdl_wait(), so the whole factorisation has completed and
     // L11 / W can be staged while the predecessor still solves.
     if (!early) pdl_wait();
-    const SnInfo n = sn_info(c, c.levelSn[c.levelPtr[lev] + blockIdx.x]);
+    // G CTAs share a supernode: each forms the L21^T x_R product over its slice of the rows (a single SM pulls L21 out
+    // of L2 at ~25 B/clk -- that product was 5-8 us of every level), the last one to arrive sums the partial vectors
+    // in slice order and solves.
+    const int q = blockIdx.x / G, g = blockIdx.x - q * G;
+    const SnInfo n = sn_info(c, c.levelSn[c.levelPtr[lev] + q]);
     const int nc = n.nc, nt = n.nt, tid = threadIdx.x, nr = 6 * n.rt, ldL = nc + 1;
+    const int chunk = (((nr + G - 1) / G) + 31) & ~31;
+    const int rLo = min(nr, g * chunk), rHi = min(nr, rLo + chunk);
     double* L11 = sm;                   // nc columns, leading dimension ldL (odd: conflict-free row reads)
     double* w = L11 + nc * ldL;         // nc
     double* Wsm = w + nc;               // 21 nt
@@ -924,18 +1016,27 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int e
     const double* __restrict__ Pn = c.L + c.Lptr[n.t];
     const int* __restrict__ Rt = c.snRows + c.snRowPtr[n.t];
     CHOL_STAMP(16);
-    for (int i = tid; i < nc * nc; i += TPB) {
-        const int r = i % nc, cc = i / nc;
-        if (r > cc) cp_async8(L11 + cc * ldL + r, Pn + (size_t)cc * n.m + r, true);
+    if (useZ) {          // L11 := Z (block lower triangle incl. the diagonal blocks)
+        const double* __restrict__ Zg = c.Zinv + (size_t)(6 * n.s) * (6 * CHOL_MAXW);
+        for (int i = tid; i < nc * nc; i += TPB) {
+            const int r = i % nc, cc = i / nc;
+            if (r >= cc) cp_async8(L11 + cc * ldL + r, Zg + (size_t)cc * nc + r, true);
+        }
+    } else {
+        for (int i = tid; i < nc * nc; i += TPB) {
+            const int r = i % nc, cc = i / nc;
+            if (r > cc) cp_async8(L11 + cc * ldL + r, Pn + (size_t)cc * n.m + r, true);
+        }
+        for (int i = tid; i < 21 * nt; i += TPB) cp_async8(Wsm + i, c.Winv + (size_t)n.s * 21 + i, true);
     }
-    for (int i = tid; i < 21 * nt; i += TPB) cp_async8(Wsm + i, c.Winv + (size_t)n.s * 21 + i, true);
     if (early) pdl_wait();
     pdl_trigger();
     if (st->done) { cp_async_wait_all(); return; }
     CHOL_GT(4);
-    for (int i = tid; i < nr; i += TPB) xR[i] = c.xperm[(size_t)__ldg(Rt + i / 6) * 6 + i % 6];
+    for (int i = rLo + tid; i < rHi; i += TPB) xR[i] = c.xperm[(size_t)__ldg(Rt + i / 6) * 6 + i % 6];
     __syncthreads();                    // xR visible; L11 / W are only needed after the product
     CHOL_STAMP(17);
+    CHOL_GT(7);
     constexpr int NW = TPB / 32;
     constexpr int CPW = (6 * CHOL_MAXW + NW - 1) / NW;      // columns per warp
     const int lane = tid & 31, wid = tid >> 5;
@@ -943,17 +1044,20 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int e
         double acc[CPW];
 #pragma unroll
         for (int j = 0; j < CPW; j++) acc[j] = 0.0;
-        for (int r0 = 0; r0 < nr; r0 += 128) {
+        for (int r0 = rLo; r0 < rHi; r0 += 128) {
             double v[4][CPW], xv[4];
+            // unconditional loads (rows / columns beyond the block are clamped and their products vanish): guarded
+            // loads compile to branches and would serialise the 4 x CPW loads a lane keeps in flight
 #pragma unroll
             for (int u = 0; u < 4; u++) {
                 const int r = r0 + 32 * u + lane;
-                const bool ok = r < nr;
+                const bool ok = r < rHi;
                 xv[u] = ok ? xR[r] : 0.0;
+                const int rc = ok ? r : 0;
 #pragma unroll
                 for (int j = 0; j < CPW; j++) {
                     const int cc = wid + NW * j;
-                    v[u][j] = (ok && cc < nc) ? Pn[(size_t)cc * n.m + nc + r] : 0.0;
+                    v[u][j] = Pn[(size_t)(cc < nc ? cc : 0) * n.m + nc + rc];
                 }
             }
 #pragma unroll
@@ -965,13 +1069,54 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int e
         for (int j = 0; j < CPW; j++) {
             const int cc = wid + NW * j;
             const double s = warp_sum(acc[j]);
-            if (lane == 0 && cc < nc) w[cc] = Pn[(size_t)cc * n.m + n.m - 1] - s;
+            if (lane == 0 && cc < nc) {
+                if (G == 1) w[cc] = Pn[(size_t)cc * n.m + n.m - 1] - s;
+                else c.bwdPart[((size_t)n.t * BWD_MAXG + g) * (6 * CHOL_MAXW) + cc] = s;
+            }
         }
+    }
+    if (G > 1) {
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) shTicket = atomicAdd(c.bwdCnt + n.t, 1);
+        __syncthreads();
+        if (shTicket != G - 1) { cp_async_wait_all(); return; }
+        __threadfence();
+        for (int cc = tid; cc < nc; cc += TPB) {
+            double sv = 0.0;
+            for (int g2 = 0; g2 < G; g2++) sv += __ldcg(c.bwdPart + ((size_t)n.t * BWD_MAXG + g2) * (6 * CHOL_MAXW) + cc);
+            w[cc] = Pn[(size_t)cc * n.m + n.m - 1] - sv;
+        }
+        if (tid == 0) c.bwdCnt[n.t] = 0;       // ready for the next trial
     }
     cp_async_wait_all();
     __syncthreads();
     CHOL_STAMP(18);
-    if (wid == 0) {
+    CHOL_GT(6);
+    if (useZ) {          // x = Z^T w: a warp per column, lanes along the rows r >= c; the result goes to xR's place
+        double acc[CPW];
+#pragma unroll
+        for (int j = 0; j < CPW; j++) {
+            const int cc = wid + NW * j;
+            acc[j] = 0.0;
+            if (cc < nc) {
+                const double* zc = L11 + cc * ldL;
+#pragma unroll
+                for (int u = 0; u < (6 * CHOL_MAXW + 31) / 32; u++) {
+                    const int r = 32 * u + lane;
+                    if (r >= cc && r < nc) acc[j] += zc[r] * w[r];
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < CPW; j++) {
+            const int cc = wid + NW * j;
+            const double sv = warp_sum(acc[j]);
+            if (lane == 0 && cc < nc) Wsm[cc] = sv;       // Wsm (21 nt >= nc doubles) is free in this mode
+        }
+        __syncthreads();
+        for (int i = tid; i < nc; i += TPB) w[i] = Wsm[i];
+    } else if (wid == 0) {
         for (int jb = nt - 1; jb >= 0; jb--) {
             const int j0 = 6 * jb;
             double xk = 0.0;

@@ -31,7 +31,7 @@ for nm in ("chol_diag", "chol_trsm", "chol_panel", "chol_update", "chol_bwd"):
     v = np.round([ms for k, ms in prof if k == nm], 3).tolist()
     if v:
         print("  %-12s" % nm, v)
-if os.environ.get("CUGO_B200_DEBUG") == "1":
+if os.environ.get("CUGO_B200_DEBUG"):
     import ctypes as C
     a = (C.c_longlong * 8192)()
     s.lib.cugo_b200_debug_counters(a, 8192)
@@ -69,4 +69,6 @@ if os.environ.get("CUGO_B200_DEBUG"):
     t0 = tm[0, 0]
     print("timeline of the last trial (us since the first panel CTA passed its wait): panel [start, end]  update [start, end]  bwd [start, end]")
     for lev in range(min(nlev, 64)):
-        print("  lev %2d" % lev, np.round((tm[lev, :6] - t0) / 1e3, 1).tolist())
+        print("  lev %2d" % lev, np.round((tm[lev, :6] - t0) / 1e3, 1).tolist(),
+              " bwd: gather %.1f  product L21^T x %.1f  solve+store %.1f us" % (
+                  (tm[lev, 7] - tm[lev, 4]) / 1e3, (tm[lev, 6] - tm[lev, 7]) / 1e3, (tm[lev, 5] - tm[lev, 6]) / 1e3))
