@@ -67,8 +67,13 @@ if os.environ.get("CUGO_B200_DEBUG"):
     tm = np.array(a[:], dtype=np.int64).reshape(64, 8)
     nlev = s.sizes()["nlevels"]
     t0 = tm[0, 0]
-    print("timeline of the last trial (us since the first panel CTA passed its wait): panel [start, end]  update [start, end]  bwd [start, end]")
+    print("timeline of the last trial, CTA 0 of every level (us since the first panel CTA passed its wait; n/a: that stamp was not "
+          "written in this trial, e.g. CTA 0 of a shared backward solve was not the last arriver): "
+          "panel [start, end]  update [start, end]  bwd [start, end]")
+    def us(a, b):
+        dt = (a - b) / 1e3
+        return "%.1f" % dt if a > 0 and b > 0 and 0 <= dt < 1e5 else "n/a"
     for lev in range(min(nlev, 64)):
-        print("  lev %2d" % lev, np.round((tm[lev, :6] - t0) / 1e3, 1).tolist(),
-              " bwd: gather %.1f  product L21^T x %.1f  solve+store %.1f us" % (
-                  (tm[lev, 7] - tm[lev, 4]) / 1e3, (tm[lev, 6] - tm[lev, 7]) / 1e3, (tm[lev, 5] - tm[lev, 6]) / 1e3))
+        print("  lev %2d  [%s]  bwd: gather %s  product L21^T x %s  solve+store %s us" % (
+            lev, ", ".join(us(tm[lev, k], t0) for k in range(6)),
+            us(tm[lev, 7], tm[lev, 4]), us(tm[lev, 6], tm[lev, 7]), us(tm[lev, 5], tm[lev, 6])))
