@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(TPB) k_build_pose(Dev d, SetParams sp) {
 // Both passes in one launch (they share inputs and write disjoint outputs): CTAs [0, nP) take the poses -- the
 // long-running ones (a loop-closure pose has thousands of edges) start first -- the rest the landmark chunks.
 template <int TPB, typename HT>
-__global__ void __launch_bounds__(TPB) k_build(Dev d, SetParams sp) {
+__global__ void __launch_bounds__(TPB, 5) k_build(Dev d, SetParams sp) {
     pdl_trigger(); pdl_wait();
     if ((int)blockIdx.x < d.nP) build_pose_cta<TPB>(d, sp, blockIdx.x);
     else build_lm_cta<TPB, HT>(d, sp, blockIdx.x - d.nP);

@@ -202,6 +202,31 @@ def test_full_size_properties(graphs, gpu):
     np.testing.assert_allclose(chi_g, chi_o, rtol=CHI2_RTOL)
 
 
+SWITCHES = ["CUGO_B200_PDL", "CUGO_B200_FUSEBUILD", "CUGO_B200_PANELDC", "CUGO_B200_ZINV", "CUGO_B200_BWDSPLIT"]
+
+
+@pytest.mark.parametrize("name", ["loop", "kitti07"])
+def test_engine_switches_agree(graphs, gpu, monkeypatch, name):
+    """Every scheduling variant of the trial (programmatic dependent launch, fused build, decoupled panel chain,
+    inverse-based and shared backward solves; read from the environment when the structure is built) gives the
+    oracle's chi2 trajectory; with all of them off the kernels run in plain stream order."""
+    g, prob = graphs(name)
+    s, o = gpu(prob)
+    chi_ref, _, tr_ref = s.optimize(6)
+    chi_o, _, _ = o.optimize(6)
+    np.testing.assert_allclose(chi_ref, chi_o, rtol=CHI2_RTOL)
+    for off in [[v] for v in SWITCHES] + [SWITCHES]:
+        for v in off:
+            monkeypatch.setenv(v, "0")
+        s2, _ = gpu(prob)
+        chi, _, tr = s2.optimize(6)
+        for v in off:
+            monkeypatch.delenv(v)
+        np.testing.assert_allclose(chi, chi_ref, rtol=CHI2_RTOL, err_msg=str(off))
+        np.testing.assert_array_equal(tr, tr_ref)
+        s2.close()
+
+
 F32_CHI2_RTOL = 1e-4      # north_star: chi2 per iteration within 1e-4 relative under USE_FLOAT32
 
 
