@@ -1007,7 +1007,9 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int e
     const int q = blockIdx.x / G, g = blockIdx.x - q * G;
     const SnInfo n = sn_info(c, c.levelSn[c.levelPtr[lev] + q]);
     const int nc = n.nc, nt = n.nt, tid = threadIdx.x, nr = 6 * n.rt, ldL = nc + 1;
-    const int chunk = (((nr + G - 1) / G) + 31) & ~31;
+    const int Ge = max(1, min(G, nr / 64));        // slices worth their fence + ticket: at least 64 rows each
+    if (g >= Ge) return;
+    const int chunk = (((nr + Ge - 1) / Ge) + 31) & ~31;
     const int rLo = min(nr, g * chunk), rHi = min(nr, rLo + chunk);
     double* L11 = sm;                   // nc columns, leading dimension ldL (odd: conflict-free row reads)
     double* w = L11 + nc * ldL;         // nc
@@ -1070,21 +1072,21 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int e
             const int cc = wid + NW * j;
             const double s = warp_sum(acc[j]);
             if (lane == 0 && cc < nc) {
-                if (G == 1) w[cc] = Pn[(size_t)cc * n.m + n.m - 1] - s;
+                if (Ge == 1) w[cc] = Pn[(size_t)cc * n.m + n.m - 1] - s;
                 else c.bwdPart[((size_t)n.t * BWD_MAXG + g) * (6 * CHOL_MAXW) + cc] = s;
             }
         }
     }
-    if (G > 1) {
+    if (Ge > 1) {
         __threadfence();
         __syncthreads();
         if (tid == 0) shTicket = atomicAdd(c.bwdCnt + n.t, 1);
         __syncthreads();
-        if (shTicket != G - 1) { cp_async_wait_all(); return; }
+        if (shTicket != Ge - 1) { cp_async_wait_all(); return; }
         __threadfence();
         for (int cc = tid; cc < nc; cc += TPB) {
             double sv = 0.0;
-            for (int g2 = 0; g2 < G; g2++) sv += __ldcg(c.bwdPart + ((size_t)n.t * BWD_MAXG + g2) * (6 * CHOL_MAXW) + cc);
+            for (int g2 = 0; g2 < Ge; g2++) sv += __ldcg(c.bwdPart + ((size_t)n.t * BWD_MAXG + g2) * (6 * CHOL_MAXW) + cc);
             w[cc] = Pn[(size_t)cc * n.m + n.m - 1] - sv;
         }
         if (tid == 0) c.bwdCnt[n.t] = 0;       // ready for the next trial
