@@ -148,6 +148,10 @@ struct Solver {
     DBuf<unsigned long long> keyA, keyB, valA, valB;
     DBuf<int> ivalA, prodCnt, prodOff, head, blkOf, bRowPtr, bColInd, bRowOf, prodPtr;
     DBuf<int2> prodIJ;
+    DBuf<int> poseSliceCnt, poseSlicePtr, poseTicket;
+    DBuf<int2> poseUnits;
+    DBuf<double> posePart;
+    int nPoseUnits = 0;
     DBuf<int> pmFlag, pmPre, poseSlotPtr, poseSlots, slotRank, prodRank, poseDeg, poseLm, rowWork, rowWorkS, rowIds, rowOrder, unitCnt, unitPtr;
     DBuf<int2> rowUnits, blkPass;
     int nRowUnits = 0, schurPasses = 1, schurUnit = 2048;
@@ -484,6 +488,14 @@ void Solver::buildStructure() {
                                          perEdgeCam ? p_cam.p : nullptr, anyOut ? p_out.p : nullptr);
     posePtr.alloc(nP_all + 1);
     k_lower_bounds<<<divUp(nP_all + 1, TB), TB, 0, stream>>>(pkeyOut, (int)E, nP_all, posePtr);
+    // pose-major pass in slices (engine.h: POSE_SLICE)
+    poseSliceCnt.alloc(nP + 1); poseSlicePtr.alloc(nP + 1); poseTicket.alloc(std::max(nP, 1));
+    k_pose_slice_count<<<divUp(nP + 1, TB), TB, 0, stream>>>(posePtr, nP, poseSliceCnt);
+    exclusiveScan(*this, poseSliceCnt.p, poseSlicePtr.p, nP + 1);
+    nPoseUnits = readInt(*this, poseSlicePtr.p + nP);
+    poseUnits.alloc(std::max(nPoseUnits, 1)); posePart.alloc((size_t)std::max(nPoseUnits, 1) * 27);
+    k_pose_units_fill<<<divUp(std::max(nP, 1), TB), TB, 0, stream>>>(poseSlicePtr, nP, poseUnits);
+    CK(cudaMemsetAsync(poseTicket.p, 0, sizeof(int) * std::max(nP, 1), stream));
 
     // ---- Hsc block pattern + product lists
     prodCnt.alloc(nL + 1); prodOff.alloc(nL + 1);
@@ -680,6 +692,7 @@ void Solver::buildStructure() {
     d.posePtr = posePtr; d.p_iL = p_iL; d.p_uv = p_uv; d.p_r = p_r; d.p_w = p_w; d.p_set = p_set;
     d.p_cam = perEdgeCam ? p_cam.p : nullptr; d.p_out = anyOut ? p_out.p : nullptr;
     d.cams = perEdgeCam ? cams.p : nullptr;
+    d.nPoseUnits = nPoseUnits; d.poseSlicePtr = poseSlicePtr; d.poseUnits = poseUnits; d.posePart = posePart; d.poseTicket = poseTicket;
     d.colPtr = colPtr; d.rowInd = rowInd; d.hplLm = hplLm;
     d.bRowPtr = bRowPtr; d.bColInd = bColInd; d.bRowOf = bRowOf; d.prodPtr = prodPtr; d.prodIJ = prodIJ;
     d.poseSlotPtr = poseSlotPtr; d.poseSlots = poseSlots; d.prodRank = prodRank; d.poseLm = poseLm; d.rowUnits = rowUnits;
@@ -740,14 +753,14 @@ void Solver::buildStructure() {
 void Solver::enqueueBuild() {
     static_assert(LM_CHUNK == 128, "k_build runs both passes with 128 threads");
     if (fuseBuild && !profiling) {
-        if (f32) launch(k_build<LM_CHUNK, float>, d.nP + d.nChunks, LM_CHUNK, 0, d, sp);
-        else launch(k_build<LM_CHUNK, double>, d.nP + d.nChunks, LM_CHUNK, 0, d, sp);
+        if (f32) launch(k_build<LM_CHUNK, float>, d.nPoseUnits + d.nChunks, LM_CHUNK, 0, d, sp);
+        else launch(k_build<LM_CHUNK, double>, d.nPoseUnits + d.nChunks, LM_CHUNK, 0, d, sp);
         mark("build");
     } else {
         if (f32) launch(k_build_lm<LM_CHUNK, float>, d.nChunks, LM_CHUNK, 0, d, sp);
         else launch(k_build_lm<LM_CHUNK, double>, d.nChunks, LM_CHUNK, 0, d, sp);
         mark("build_lm");
-        launch(k_build_pose<128>, d.nP, 128, 0, d, sp); mark("build_pose");
+        launch(k_build_pose<128>, d.nPoseUnits, 128, 0, d, sp); mark("build_pose");
     }
     if (nranks > 1) {   // max diagonal of the *global* system for lambda0
         launch(k_pack_A<256>, std::min(divUp(6 * d.nP, 256), 148), 256, 0, d); mark("pack_A");

@@ -10,6 +10,7 @@ namespace cugo_b200 {
 constexpr int MAX_SETS = 8;
 constexpr int MAX_STATS = 256;     // outer LM iterations recorded per optimize()
 constexpr int LM_CHUNK = 128;      // landmark-major kernels: edges per CTA (nominal)
+constexpr int POSE_SLICE = 512;    // edges per CTA of the pose-major pass
 constexpr int POSE_STRIDE = 8;     // poses are padded 7 -> 8 doubles (16 B vector loads)
 
 // per edge set parameters (reference: one EdgeSet object each, include/ba_types.h)
@@ -68,6 +69,13 @@ struct Dev {
     const int* p_cam;
     const uint8_t* p_out;
     const double* cams;         // [ncams][5] per-edge camera table (or nullptr)
+    // pose-major pass in slices of POSE_SLICE edges (a loop-closure pose, or any pose of a landmark shard on several
+    // GPUs, has thousands of edges): work unit = (pose, slice); partial sums meet through a ticket per pose
+    int nPoseUnits;
+    const int* poseSlicePtr;    // [nP+1]
+    const int2* poseUnits;      // [nPoseUnits]
+    double* posePart;           // [nPoseUnits][27]
+    int* poseTicket;            // [nP], zero between launches
     // Hpl CSC (reference: gpu::buildHplStructure)
     const int* colPtr;          // [nL+1]
     const int* rowInd;          // [nHpl]

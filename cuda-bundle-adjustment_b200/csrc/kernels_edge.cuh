@@ -187,10 +187,14 @@ __global__ void __launch_bounds__(TPB) k_build_lm(Dev d, SetParams sp) {
 // JP^T JP w and the 6 of JP^T e w in registers, then a fixed-order tree.
 // ---------------------------------------------------------------------------
 template <int TPB>
-__device__ __forceinline__ void build_pose_cta(const Dev& d, const SetParams& sp, const int p) {
+__device__ __forceinline__ void build_pose_cta(const Dev& d, const SetParams& sp, const int unit) {
     __shared__ double red[TPB / 32][27];
+    __shared__ int ticket;
     const LMState* st = d.st;
     if (st->done || !st->needBuild) return;
+    const int2 un = d.poseUnits[unit];
+    const int p = un.x;
+    const int nsl = d.poseSlicePtr[p + 1] - d.poseSlicePtr[p];
     const double* __restrict__ pose = d.pose[st->cur];
     const double* __restrict__ lm = d.lm[st->cur];
     double q[4], t[3];
@@ -198,7 +202,7 @@ __device__ __forceinline__ void build_pose_cta(const Dev& d, const SetParams& sp
     double a[27];
 #pragma unroll
     for (int i = 0; i < 27; i++) a[i] = 0.0;
-    const int k0 = d.posePtr[p], k1 = d.posePtr[p + 1];
+    const int k0 = d.posePtr[p] + un.y * POSE_SLICE, k1 = min(d.posePtr[p + 1], k0 + POSE_SLICE);
     for (int k = k0 + threadIdx.x; k < k1; k += TPB) {
         if (d.p_out && d.p_out[k]) continue;
         const int iL = __ldg(d.p_iL + k);
@@ -237,6 +241,23 @@ __device__ __forceinline__ void build_pose_cta(const Dev& d, const SetParams& sp
         red[0][threadIdx.x] = s;
     }
     __syncthreads();
+    if (nsl > 1) {       // the last slice of the pose to arrive adds the partial sums in slice order
+        if (threadIdx.x < 27) d.posePart[(size_t)unit * 27 + threadIdx.x] = red[0][threadIdx.x];
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) ticket = atomicAdd(d.poseTicket + p, 1);
+        __syncthreads();
+        if (ticket != nsl - 1) return;
+        __threadfence();
+        if (threadIdx.x < 27) {
+            const double* part = d.posePart + (size_t)d.poseSlicePtr[p] * 27 + threadIdx.x;
+            double s = 0;
+            for (int j = 0; j < nsl; j++) s += __ldcg(part + (size_t)j * 27);
+            red[0][threadIdx.x] = s;
+        }
+        if (threadIdx.x == 0) d.poseTicket[p] = 0;
+        __syncthreads();
+    }
     if (threadIdx.x < 36) {
         // full symmetric 6x6, column-major; packed index of (r>=c): c*6 - c(c-1)/2 + (r-c)
         int r = threadIdx.x % 6, c = threadIdx.x / 6;
@@ -255,13 +276,13 @@ __global__ void __launch_bounds__(TPB) k_build_pose(Dev d, SetParams sp) {
     pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     build_pose_cta<TPB>(d, sp, blockIdx.x);
 }
-// Both passes in one launch (they share inputs and write disjoint outputs): CTAs [0, nP) take the poses -- the
-// long-running ones (a loop-closure pose has thousands of edges) start first -- the rest the landmark chunks.
+// Both passes in one launch (they share inputs and write disjoint outputs): CTAs [0, nPoseUnits) take the
+// pose slices, the rest the landmark chunks.
 template <int TPB, typename HT>
 __global__ void __launch_bounds__(TPB, 5) k_build(Dev d, SetParams sp) {
     pdl_trigger(); pdl_wait();
-    if ((int)blockIdx.x < d.nP) build_pose_cta<TPB>(d, sp, blockIdx.x);
-    else build_lm_cta<TPB, HT>(d, sp, blockIdx.x - d.nP);
+    if ((int)blockIdx.x < d.nPoseUnits) build_pose_cta<TPB>(d, sp, blockIdx.x);
+    else build_lm_cta<TPB, HT>(d, sp, blockIdx.x - d.nPoseUnits);
 }
 
 }  // namespace cugo_b200

@@ -197,6 +197,19 @@ __global__ void k_map_slots(const unsigned long long* lkeys, int nblk, const uns
     slot[k] = lo;
 }
 
+// work units of the pose-major build pass: slices of POSE_SLICE edges per pose
+__global__ void k_pose_slice_count(const int* posePtr, int nP, int* cnt) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p > nP) return;
+    const int deg = p < nP ? posePtr[p + 1] - posePtr[p] : 0;
+    cnt[p] = p < nP ? max(1, (deg + POSE_SLICE - 1) / POSE_SLICE) : 0;
+}
+__global__ void k_pose_units_fill(const int* slicePtr, int nP, int2* units) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= nP) return;
+    for (int u = slicePtr[p]; u < slicePtr[p + 1]; u++) units[u] = make_int2(p, u - slicePtr[p]);
+}
+
 // ---- symbolic factorisation: the shared host/device code run by one thread ----
 // adjCap > 0: the adjacency and the BFS scratch (the arrays every sweep of the nested dissection walks) live
 // in shared memory -- a single thread pays ~30 cycles per dependent access there instead of an L2 round trip.
