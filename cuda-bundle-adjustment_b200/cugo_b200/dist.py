@@ -41,17 +41,28 @@ def landmark_ranges(weights: np.ndarray, world: int) -> np.ndarray:
     return np.concatenate([[0], np.maximum.accumulate(cuts), [n]]).astype(np.int64)
 
 
-def shard_problem(prob: Problem, world: int, rank: int) -> Shard:
-    """Rank `rank`'s shard of a packed problem (index order: free vertices first, then fixed ones)."""
+def shard_problem(prob: Problem, world: int, rank: int, mode: str = "strided") -> Shard:
+    """Rank `rank`'s shard of a packed problem (index order: free vertices first, then fixed ones).
+
+    mode "strided" (default): landmark l belongs to rank l % world.  Neighbouring landmarks are seen by the same
+    poses, so every shard is a thinned copy of the whole graph: the same poses, pose degrees and Hsc block pattern
+    as one GPU would have at 1/world of the landmarks -- the per-pose work units of the build and Schur kernels
+    stay balanced.  mode "ranges": contiguous landmark ranges balanced by edge count; a range covers a stretch of
+    the trajectory, so a shard concentrates world x the edges on 1/world of the poses (measured on 8 GPUs, KITTI-00
+    shape: 18.5 ms per optimize(10) against 16.6 ms after slicing the pose-major pass)."""
     L_all, nL = prob.landmarks.shape[0], prob.nL_act
-    deg = np.zeros(L_all, np.int64)
-    for s in prob.sets:
-        np.add.at(deg, s.iL, 1)
-    deg = np.maximum(deg, 1)
-    fb = landmark_ranges(deg[:nL], world)                  # free landmarks
-    xb = landmark_ranges(deg[nL:], world) + nL             # fixed landmarks
-    own_free = np.arange(fb[rank], fb[rank + 1])
-    own_fixed = np.arange(xb[rank], xb[rank + 1])
+    if mode == "strided":
+        own_free = np.arange(rank, nL, world)
+        own_fixed = nL + np.arange(rank, L_all - nL, world)
+    else:
+        deg = np.zeros(L_all, np.int64)
+        for s in prob.sets:
+            np.add.at(deg, s.iL, 1)
+        deg = np.maximum(deg, 1)
+        fb = landmark_ranges(deg[:nL], world)                  # free landmarks
+        xb = landmark_ranges(deg[nL:], world) + nL             # fixed landmarks
+        own_free = np.arange(fb[rank], fb[rank + 1])
+        own_fixed = np.arange(xb[rank], xb[rank + 1])
     lm_index = np.concatenate([own_free, own_fixed]).astype(np.int64)
     local_of = np.full(L_all, -1, np.int64)
     local_of[lm_index] = np.arange(lm_index.shape[0])

@@ -29,14 +29,15 @@ def test_landmark_ranges_balance():
     assert cdist.landmark_ranges(np.zeros(0, np.int64), 4).tolist() == [0] * 5
 
 
+@pytest.mark.parametrize("mode", ["strided", "ranges"])
 @pytest.mark.parametrize("world", [2, 3])
-def test_shards_partition_the_problem(graphs, world):
+def test_shards_partition_the_problem(graphs, world, mode):
     from cugo_b200 import dist as cdist
     g, prob = graphs("small", fixed_landmark_frac=0.1, seed=5)
     seen = np.zeros(prob.landmarks.shape[0], int)
     n_edges = 0
     for r in range(world):
-        sh = cdist.shard_problem(prob, world, r)
+        sh = cdist.shard_problem(prob, world, r, mode=mode)
         seen[sh.lm_index] += 1
         n_edges += sh.prob.n_edges
         nL = sh.prob.nL_act
