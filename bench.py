@@ -215,7 +215,7 @@ def run_ours(args, rank, world):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic (seeded generator cugo_b200/synth.py; reference inputs are absent)",
             "config": {"workload": "%s poses with %dx its landmarks/edges: %d poses / %d landmarks / %d edges (%d stereo), "
-                                   "%d LM iterations, FP64; landmarks sharded over %d GPUs, one NCCL all-reduce of "
+                                   "%d LM iterations, FP64; landmarks dealt strided (l %% N) to %d GPUs, one NCCL all-reduce of "
                                    "[Hsc | bsc] per LM trial" % (args.workload, world, g.n_poses, g.n_landmarks, E,
                                                                  len(g.stereo_p), args.iters, world),
                        "timing": "CUDA events on the solver stream around optimize(), max over ranks; L2 flushed "
