@@ -12,6 +12,7 @@
 #include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -1563,3 +1564,133 @@ int cugo_b200_debug_counters(long long* out, int n) {
 void* cugo_b200_stream(cugo_b200_solver* s) { return s ? (void*)s->impl.stream : nullptr; }
 
 }  // extern "C"
+
+// ===========================================================================
+// Allocation-free chi2 of one edge set (include/cugo_b200.h: cugo_b200_chi2_noalloc).
+// No counterpart in the reference; added for callers that cannot
+// call cudaMalloc (CUDA graph capture, tight serving loops).  The per-CTA partial sums that k_errors keeps
+// in a cudaMalloc'ed buffer (Dev::chiPartial) live here in a file-scope __device__ array that every GPU
+// loading the library holds until exit.  In host code `g_naScratch` is only a stand-in for the symbol: its
+// device address is taken once per device with cudaGetSymbolAddress (that device current) and handed to the
+// kernel as an ordinary pointer.
+// ===========================================================================
+namespace cugo_b200 {
+
+constexpr int NA_TPB = 256;
+constexpr int NA_EDGES_PER_CTA = 4 * NA_TPB;                 // 1024 edges per CTA, one partial each
+constexpr int NA_MAX_CTAS = CUGO_B200_NOALLOC_MAX_EDGES / NA_EDGES_PER_CTA;   // 8192
+constexpr int NA_HEAD = 32;                                   // doubles in front of the partials: [0] = arrival ticket
+static_assert(CUGO_B200_NOALLOC_MAX_EDGES % NA_EDGES_PER_CTA == 0, "maximum is a whole number of CTAs");
+static __device__ __align__(256) double g_naScratch[NA_HEAD + NA_MAX_CTAS];   // 64.25 KB per GPU
+
+struct NaArgs {
+    int dim, n, nomega, rkType;
+    double rkDelta;
+    double cam[5];
+    const int* iP; const int* iL;
+    const double* meas; const double* omega;
+    const double* poses7; const double* lms;
+    double* out;
+};
+
+// same arithmetic per edge as k_errors (world_to_camera, residual, rk_rho), caller-layout inputs: poses 7 doubles
+// AoS, measurements interleaved [n x dim].  CTA partials -> scratch; the last CTA to arrive adds them in CTA order
+// (bit-reproducible), writes the total and leaves the ticket at zero for the next call.
+__global__ void __launch_bounds__(NA_TPB) k_errors_noalloc(NaArgs a, double* scratch) {
+    __shared__ double sh[NA_TPB / 32];
+    __shared__ unsigned last;
+    double sum = 0;
+    const int base = blockIdx.x * NA_EDGES_PER_CTA;
+#pragma unroll
+    for (int j = 0; j < NA_EDGES_PER_CTA / NA_TPB; j++) {
+        const int k = base + j * NA_TPB + threadIdx.x;
+        if (k >= a.n) break;
+        const int iP = __ldg(a.iP + k), iL = __ldg(a.iL + k);
+        const double* p = a.poses7 + 7 * (size_t)iP;
+        const double q[4] = {__ldg(p), __ldg(p + 1), __ldg(p + 2), __ldg(p + 3)};
+        const double t[3] = {__ldg(p + 4), __ldg(p + 5), __ldg(p + 6)};
+        const double X[3] = {__ldg(a.lms + 3 * (size_t)iL), __ldg(a.lms + 3 * (size_t)iL + 1), __ldg(a.lms + 3 * (size_t)iL + 2)};
+        const double* m = a.meas + (size_t)k * a.dim;
+        const double mr = (a.dim == 3) ? __ldg(m + 2) : 0.0;
+        double Xc[3], e[3];
+        world_to_camera(q, t, X, Xc);
+        residual(a.dim, Xc, a.cam, __ldg(m), __ldg(m + 1), mr, e);
+        const double w = __ldg(a.omega + (a.nomega > 1 ? k : 0));
+        sum += rk_rho(a.rkType, a.rkDelta, w * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]));
+    }
+    const double tot = block_sum<NA_TPB>(sum, sh);
+    double* part = scratch + NA_HEAD;
+    unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
+    if (threadIdx.x == 0) {
+        part[blockIdx.x] = tot;
+        __threadfence();
+        last = (atomicAdd(ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    double s = 0;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += NA_TPB) s += __ldcg(part + i);   // fixed assignment, fixed order
+    const double all = block_sum<NA_TPB>(s, sh);
+    if (threadIdx.x == 0) { *a.out = all; *ticket = 0u; }
+}
+
+static double* g_naPtr[64];          // device address of g_naScratch per device ordinal (set once)
+static std::mutex g_naMutex;
+
+static int na_fail(char* errbuf, int len, int code, const std::string& msg) {
+    if (errbuf && len > 0) { strncpy(errbuf, msg.c_str(), (size_t)len - 1); errbuf[len - 1] = 0; }
+    return code;
+}
+
+}  // namespace cugo_b200
+
+extern "C" int cugo_b200_chi2_noalloc(int device, void* stream, int dim, int n, const int* d_iP, const int* d_iL,
+                                      const double* d_measurements, const double* d_omegas, int nomega,
+                                      const double camera5[5], int robust_type, double robust_delta,
+                                      const double* d_poses7, const double* d_landmarks3, double* d_chi2,
+                                      char* errbuf, int errbuf_len) {
+    using namespace cugo_b200;
+    if ((dim != 2 && dim != 3) || n < 0 || (nomega != 1 && nomega != n && n > 0) || robust_type < 0 || robust_type > 3 ||
+        !camera5 || !d_chi2 || (n > 0 && (!d_iP || !d_iL || !d_measurements || !d_omegas || !d_poses7 || !d_landmarks3)))
+        return na_fail(errbuf, errbuf_len, CUGO_B200_EINVAL, "chi2_noalloc: bad argument (dim 2|3, nomega 1|n, non-null device pointers)");
+    if (n > CUGO_B200_NOALLOC_MAX_EDGES)
+        return na_fail(errbuf, errbuf_len, CUGO_B200_EINVAL,
+                       "chi2_noalloc: " + std::to_string(n) + " edges exceed CUGO_B200_NOALLOC_MAX_EDGES = " +
+                           std::to_string(CUGO_B200_NOALLOC_MAX_EDGES) + " (size of the static scratch array); split the set");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return na_fail(errbuf, errbuf_len, CUGO_B200_ENODEVICE, "chi2_noalloc: no CUDA device (there is no CPU path)"); }
+    if (device < 0 || device >= ndev || device >= 64) return na_fail(errbuf, errbuf_len, CUGO_B200_EINVAL, "chi2_noalloc: bad device ordinal");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return na_fail(errbuf, errbuf_len, CUGO_B200_ECUDA, std::string("chi2_noalloc: cudaSetDevice: ") + cudaGetErrorString(e));
+    double* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_naMutex);
+        if (!g_naPtr[device]) {           // once per device, with that device current
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_naScratch);
+            if (e != cudaSuccess || !p)
+                return na_fail(errbuf, errbuf_len, CUGO_B200_ECUDA, std::string("chi2_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+            g_naPtr[device] = static_cast<double*>(p);
+        }
+        scratch = g_naPtr[device];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // the array keeps the last call's contents: the ticket must start at zero (an aborted call may have left it set)
+    e = cudaMemsetAsync(scratch, 0, NA_HEAD * sizeof(double), st);
+    if (e != cudaSuccess) return na_fail(errbuf, errbuf_len, CUGO_B200_ECUDA, std::string("chi2_noalloc: cudaMemsetAsync: ") + cudaGetErrorString(e));
+    if (n == 0) {                         // empty set: chi2 = 0
+        e = cudaMemsetAsync(d_chi2, 0, sizeof(double), st);
+        return e == cudaSuccess ? CUGO_B200_OK : na_fail(errbuf, errbuf_len, CUGO_B200_ECUDA, std::string("chi2_noalloc: cudaMemsetAsync: ") + cudaGetErrorString(e));
+    }
+    NaArgs a{};
+    a.dim = dim; a.n = n; a.nomega = nomega; a.rkType = robust_type; a.rkDelta = robust_delta;
+    for (int i = 0; i < 5; i++) a.cam[i] = camera5[i];
+    a.iP = d_iP; a.iL = d_iL; a.meas = d_measurements; a.omega = d_omegas; a.poses7 = d_poses7; a.lms = d_landmarks3;
+    a.out = d_chi2;
+    const int grid = (n + NA_EDGES_PER_CTA - 1) / NA_EDGES_PER_CTA;
+    k_errors_noalloc<<<grid, NA_TPB, 0, st>>>(a, scratch);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return na_fail(errbuf, errbuf_len, CUGO_B200_ECUDA, std::string("chi2_noalloc: launch: ") + cudaGetErrorString(e));
+    return CUGO_B200_OK;
+}

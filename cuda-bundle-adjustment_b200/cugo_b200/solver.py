@@ -35,6 +35,7 @@ SYMBOLS = (
     "cugo_b200_get_estimates", "cugo_b200_get_structure", "cugo_b200_get_values", "cugo_b200_get_sizes",
     "cugo_b200_get_last_timing", "cugo_b200_stream", "cugo_b200_profile_trial", "cugo_b200_update_measurements",
     "cugo_b200_debug_counters", "cugo_b200_get_factor_stats", "cugo_b200_comm_unique_id", "cugo_b200_comm_init",
+    "cugo_b200_chi2_noalloc",
 )
 
 _lib = None

@@ -154,6 +154,26 @@ int cugo_b200_debug_counters(long long* out, int n);
 /* the solver's CUDA stream (cudaStream_t) for callers that time or chain work on it */
 void* cugo_b200_stream(cugo_b200_solver* s);
 
+/* -- allocation-free chi2 of ONE edge set.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same per-edge arithmetic as cugo_b200_compute_errors (sum over the set of
+ * rho(omega |e|^2)), but every buffer is the caller's and ALL pointers except camera5 / errbuf are DEVICE
+ * pointers in the caller's own layout (poses 7 doubles each, measurements [n x dim] interleaved, vertex
+ * indices as for cugo_b200_add_edge_set).  The per-CTA partial sums live in a static __device__ array inside the
+ * library (64.25 KB, held by every GPU that loads the library until exit) instead of a cudaMalloc'ed buffer, which
+ * bounds the set: n <= CUGO_B200_NOALLOC_MAX_EDGES, larger sets are rejected with CUGO_B200_EINVAL (split them).
+ * The call makes no cudaMalloc / cudaFree / allocating library call; it enqueues one 256-byte memset and one kernel
+ * on `stream` (a cudaStream_t, NULL = default stream) and returns without synchronising: *d_chi2 (one double, device)
+ * is valid once the stream has reached that point.  All calls on a device share the one scratch array: calls that
+ * may OVERLAP on the GPU (different streams, no ordering between them) race -- serialise them.
+ * errbuf (host, may be NULL) receives the error text. */
+#define CUGO_B200_NOALLOC_MAX_EDGES (8 * 1024 * 1024)
+int cugo_b200_chi2_noalloc(int device, void* stream, int dim, int n, const int* d_iP, const int* d_iL,
+                           const double* d_measurements, const double* d_omegas, int nomega,
+                           const double camera5[5], int robust_type, double robust_delta,
+                           const double* d_poses7, const double* d_landmarks3, double* d_chi2,
+                           char* errbuf, int errbuf_len);
+
 #ifdef __cplusplus
 }
 #endif
