@@ -111,6 +111,8 @@ struct HostSet {
     std::vector<int> iP, iL, out;
     std::vector<double> meas, omega, cam;
     bool stale = false;      // measurements / informations were last updated on the device only (refreshHostSets)
+    double outThr = 0.0;     // EdgeSet::setOutlierThreshold (0 = no gating)
+    int outCount = 0;        // EdgeSet::getOutlierCount: edges of the set flagged so far
 };
 
 struct Solver {
@@ -267,6 +269,14 @@ struct Solver {
     bool solve();
     void update();
     double computeScale(double lambda);
+    // outlier gating on the device (reference: computeOutliersKernel + EdgeSet::updateEdges)
+    bool gating() const { for (auto& hs : sets) if (hs.outThr > 0) return true; return false; }
+    bool maskLive = false;         // the device mask holds flags the host sets do not (syncOutliersToHost)
+    DBuf<int> outCnt;
+    void setOutlierThreshold(int setId, double thr);
+    void updateEdges();
+    void syncOutliersToHost();
+    void getOutliers(int setId, int* mask, int* outliers, int* inliers);
     int optimize(int niter, int cap, double* chi2, double* lambda, int* trials);
     void getEstimates(double* poses7, double* lms);
     long getStructure(int which, int* out, long cap);
@@ -392,6 +402,7 @@ void Solver::buildStructure() {
         tPrev = t;
     };
     refreshHostSets();
+    syncOutliersToHost();
     if (nL_all == 0 || nL == 0) throw UnsupportedError("graph has no free landmarks: pose-only problems use the reference's dense LU path, outside this engine");
     if (nP == 0) throw UnsupportedError("graph has no free poses");
     E = 0;
@@ -399,7 +410,7 @@ void Solver::buildStructure() {
     for (auto& s : sets) {
         E += s.n;
         if (s.ncam > 1) perEdgeCam = true;
-        if (!s.out.empty()) anyOut = true;
+        if (!s.out.empty() || s.outThr > 0) anyOut = true;
     }
     if (E == 0) throw StateError("build_structure: no edges");
     if (E > 0x7fffffff / 18) throw UnsupportedError("edge count exceeds 32-bit block indexing");
@@ -742,9 +753,11 @@ void Solver::buildStructure() {
     CK(cudaFuncSetAttribute(k_chol_update3, cudaFuncAttributeMaxDynamicSharedMemorySize,
                             (2 * ncMax * UPD_LD + 2 * 6 * CHOL_TB * UPD_CLD) * 8));
     CK(cudaStreamSynchronize(stream));
-    structDirty = false; systemBuilt = false; solved = false;
+    systemBuilt = false; solved = false;
     lap("buffers");
+    structDirty = true;
     captureSlot();
+    structDirty = false;            // only once the trial graph exists
     lap("graph capture");
 }
 
@@ -936,7 +949,7 @@ __global__ void k_gather_meas(const double* m0, const double* m1, const double* 
 void Solver::refreshHostSets() {
     size_t off = 0;
     for (HostSet& hs : sets) {
-        if (hs.stale && off + hs.n <= (size_t)r_m0.cap) {
+        if (hs.stale && hs.n > 0 && off + hs.n <= (size_t)r_m0.cap) {
             use();
             u_meas.alloc((size_t)hs.n * hs.dim); u_w.alloc(hs.n);
             k_gather_meas<<<divUp(hs.n, 256), 256, 0, stream>>>(r_m0.p + off, r_m1.p + off, r_m2.p + off, r_w.p + off, hs.n,
@@ -954,6 +967,7 @@ void Solver::refreshHostSets() {
 void Solver::updateMeasurements(int setId, const double* meas, const double* omega, int nomega) {
     if (setId < 0 || setId >= (int)sets.size()) throw ArgError("update_measurements: bad set id");
     HostSet& hs = sets[setId];
+    if (hs.n == 0) return;        // the reference skips empty sets
     if (!meas || !omega || (nomega != 1 && nomega != hs.n)) throw ArgError("update_measurements: bad arguments");
     if (structDirty) {            // no device arrays yet: keep the host copy, the next build_structure uploads it
         refreshHostSets();
@@ -994,7 +1008,17 @@ void Solver::captureSlot() {
     if (!h_scalars) CK(cudaMallocHost(&h_scalars, 8 * sizeof(double)));
     if (!ev0) { CK(cudaEventCreate(&ev0)); CK(cudaEventCreate(&ev1)); }
     CK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
-    enqueueSlot();
+    try {
+        enqueueSlot();
+    } catch (...) {
+        // leave neither the stream in capture mode nor a half-recorded graph behind; the structure stays dirty
+        cudaGraph_t partial = nullptr;
+        cudaStreamEndCapture(stream, &partial);
+        if (partial) cudaGraphDestroy(partial);
+        cudaGetLastError();
+        structDirty = true;
+        throw;
+    }
     CK(cudaStreamEndCapture(stream, &slotGraph));
     CK(cudaGetLastError());
     CK(cudaGraphInstantiate(&slotExec, slotGraph, 0));
@@ -1083,8 +1107,11 @@ void Solver::update() {
 double Solver::computeScale(double lambda) {
     if (!systemBuilt) throw StateError("compute_scale before build_system");
     use();
-    (void)lambda;   // the landmark partials were formed with the lambda of the last solve()
-    k_scale_poses<256><<<1, 256, 0, stream>>>(d, stagedLambda, scalars.p + 2);
+    if (lambda == stagedLambda) {   // the landmark partials of k_backsub were formed with the lambda of the last solve()
+        k_scale_poses<256><<<1, 256, 0, stream>>>(d, stagedLambda, scalars.p + 2);
+    } else {                        // any other lambda: the whole sum over [xp | xl] with the caller's value
+        k_scale_full<1024><<<1, 1024, 0, stream>>>(d, lambda, scalars.p + 2);
+    }
     return readScalar(*this, 2);
 }
 
@@ -1094,7 +1121,7 @@ double Solver::computeScale(double lambda) {
 int Solver::optimize(int niter, int cap, double* chi2, double* lambda, int* trials) {
     ensureStructure();
     use();
-    if (niter > MAX_STATS) throw ArgError("optimize: niterations exceeds MAX_STATS");
+    // any iteration count is accepted, as in the reference; statistics are kept for the first MAX_STATS iterations
     CK(cudaEventRecord(ev0, stream));
     long launched = 0;
     k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
@@ -1116,6 +1143,7 @@ int Solver::optimize(int niter, int cap, double* chi2, double* lambda, int* tria
     if (niter <= 0) {
         CK(cudaMemcpyAsync(h_state, d.st, sizeof(LMState), cudaMemcpyDeviceToHost, stream));
     }
+    if (gating()) { updateEdges(); launched += 3; }     // src/cuda_graph_optimisation.cpp:150-151
     CK(cudaEventRecord(ev1, stream));
     CK(cudaStreamSynchronize(stream));
     CK(cudaGetLastError());
@@ -1130,6 +1158,145 @@ int Solver::optimize(int niter, int cap, double* chi2, double* lambda, int* tria
     }
     systemBuilt = false; solved = false;
     return n;
+}
+
+// ---------------------------------------------------------------------------
+// outlier gating.  Reference: EdgeSet::setOutlierThreshold src/optimisable_graph.hpp:415-420,
+// BlockSolver::updateEdges src/block_solver.cpp:423-429 -> EdgeSet::updateEdges src/optimisable_graph.hpp:603-640 ->
+// computeOutliersKernel cuda_block_solver.cu:1135-1149, called at the end of every optimize()
+// (src/cuda_graph_optimisation.cpp:150-151).  There the mask goes to the host, the edges are inactivated and the
+// structure is rebuilt; here the flags stay on the device (raw order r_out + the two sorted copies), flagged edges
+// weigh nothing in every kernel, their Hpl blocks are written as zeros and the structure, its symbolic analysis and
+// the captured trial graph are kept.
+// ---------------------------------------------------------------------------
+struct OutThr { double thr[MAX_SETS]; };
+
+// chi2 of every unflagged edge at the estimates the last k_errors saw (st->lastEval: the reference keeps the
+// chiValues of its last computeErrors, a rejected trial included) against its set's threshold
+template <int TPB>
+__global__ void __launch_bounds__(TPB) k_compute_outliers(Dev d, SetParams sp, OutThr ot, uint8_t* s_out, uint8_t* r_out) {
+    const LMState* st = d.st;
+    const int buf = st->lastEval;
+    const double* __restrict__ pose = d.pose[buf];
+    const double* __restrict__ lm = d.lm[buf];
+    for (int k = blockIdx.x * TPB + threadIdx.x; k < d.E; k += gridDim.x * TPB) {
+        if (s_out[k]) continue;
+        const int set = d.s_set[k];
+        const double thr = ot.thr[set];
+        if (!(thr > 0)) continue;
+        const int iP = __ldg(d.s_iP + k), iL = __ldg(d.s_iL + k);
+        const int dim = sp.dim[set];
+        double q[4], t[3], cam[5], Xc[3], e[3];
+        load_pose(pose, iP, q, t);
+        const double X[3] = {__ldg(lm + 3 * (size_t)iL), __ldg(lm + 3 * (size_t)iL + 1), __ldg(lm + 3 * (size_t)iL + 2)};
+        load_cam(d, sp, d.s_cam, k, set, cam);
+        const double2 uv = __ldg(d.s_uv + k);
+        const double mr = (dim == 3) ? __ldg(d.s_r + k) : 0.0;
+        world_to_camera(q, t, X, Xc);
+        residual(dim, Xc, cam, uv.x, uv.y, mr, e);
+        const double chi = rk_rho(sp.rkType[set], sp.rkDelta[set], __ldg(d.s_w + k) * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]));
+        if (chi > thr) { s_out[k] = 1; r_out[d.s_gid[k]] = 1; }
+    }
+}
+__global__ void k_mask_to_pose(const int* p_src, const uint8_t* s_out, int E, uint8_t* p_out) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < E) p_out[k] = s_out[p_src[k]];
+}
+// flagged edges per set (sets are contiguous ranges of the raw order); one CTA, integer sums
+template <int TPB>
+__global__ void __launch_bounds__(TPB) k_count_mask(const uint8_t* r_out, OutThr bounds /* prefix of set sizes as doubles */, int nsets, int* cnt) {
+    __shared__ int sh[MAX_SETS];
+    if (threadIdx.x < MAX_SETS) sh[threadIdx.x] = 0;
+    __syncthreads();
+    for (int s = 0; s < nsets; s++) {
+        const int b0 = s ? (int)bounds.thr[s - 1] : 0, b1 = (int)bounds.thr[s];
+        int c = 0;
+        for (int i = b0 + threadIdx.x; i < b1; i += TPB) c += r_out[i] ? 1 : 0;
+        if (c) atomicAdd(&sh[s], c);
+    }
+    __syncthreads();
+    if (threadIdx.x < MAX_SETS) cnt[threadIdx.x] = sh[threadIdx.x];
+}
+
+void Solver::setOutlierThreshold(int setId, double thr) {
+    if (setId < 0 || setId >= (int)sets.size()) throw ArgError("set_outlier_threshold: bad set id");
+    if (!(thr >= 0)) throw ArgError("set_outlier_threshold: threshold must be >= 0");
+    sets[setId].outThr = thr;
+    if (structDirty || !(thr > 0) || d.s_out) return;
+    // structure is current but was built without mask arrays: add them (all clear) and re-record the trial graph
+    use();
+    r_out.alloc(E); s_out.alloc(E); p_out.alloc(E);
+    CK(cudaMemsetAsync(r_out.p, 0, E, stream));
+    CK(cudaMemsetAsync(s_out.p, 0, E, stream));
+    CK(cudaMemsetAsync(p_out.p, 0, E, stream));
+    anyOut_ = true;
+    d.s_out = s_out; d.p_out = p_out;
+    if (slotExec) { cudaGraphExecDestroy(slotExec); slotExec = nullptr; }
+    if (slotGraph) { cudaGraphDestroy(slotGraph); slotGraph = nullptr; }
+    captureSlot();
+}
+
+void Solver::updateEdges() {
+    if (!gating()) return;
+    ensureStructure();
+    use();
+    OutThr ot{}, bounds{};
+    size_t off = 0;
+    for (size_t i = 0; i < sets.size(); i++) { ot.thr[i] = sets[i].outThr; off += sets[i].n; bounds.thr[i] = (double)off; }
+    outCnt.alloc(MAX_SETS);
+    k_compute_outliers<256><<<d.errGrid, 256, 0, stream>>>(d, sp, ot, s_out.p, r_out.p);
+    k_mask_to_pose<<<divUp(E, 256), 256, 0, stream>>>(p_src, s_out, (int)E, p_out);
+    k_count_mask<1024><<<1, 1024, 0, stream>>>(r_out, bounds, (int)sets.size(), outCnt);
+    int cnt[MAX_SETS];
+    CK(cudaMemcpyAsync(cnt, outCnt.p, sizeof(cnt), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    CK(cudaGetLastError());
+    for (size_t i = 0; i < sets.size(); i++) {
+        if (cnt[i] != sets[i].outCount) maskLive = true;
+        sets[i].outCount = cnt[i];
+    }
+    systemBuilt = false; solved = false;
+}
+
+// before the raw arrays are rebuilt: flags made on the device become part of the host sets' masks, so a rebuilt
+// structure leaves those edges' Hpl blocks out (the reference's rebuild after updateEdges)
+void Solver::syncOutliersToHost() {
+    if (!maskLive || !r_out.p) { maskLive = false; return; }
+    use();
+    std::vector<uint8_t> m(r_out.cap);
+    size_t tot = 0;
+    for (auto& hs : sets) tot += hs.n;
+    if (tot > r_out.cap) { maskLive = false; return; }
+    CK(cudaMemcpyAsync(m.data(), r_out.p, tot, cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    size_t off = 0;
+    for (auto& hs : sets) {
+        if (hs.outCount > 0) {
+            hs.out.assign(hs.n, 0);
+            for (int i = 0; i < hs.n; i++) hs.out[i] = m[off + i];
+        }
+        off += hs.n;
+    }
+    maskLive = false;
+}
+
+void Solver::getOutliers(int setId, int* mask, int* outliers, int* inliers) {
+    if (setId < 0 || setId >= (int)sets.size()) throw ArgError("get_outliers: bad set id");
+    HostSet& hs = sets[setId];
+    if (outliers) *outliers = hs.outCount;
+    if (inliers) *inliers = hs.n - hs.outCount;
+    if (!mask || hs.n == 0) return;
+    if (structDirty || !d.s_out) {          // nothing on the device yet: the host mask (or all clear)
+        for (int i = 0; i < hs.n; i++) mask[i] = hs.out.empty() ? 0 : (hs.out[i] ? 1 : 0);
+        return;
+    }
+    use();
+    size_t off = 0;
+    for (int i = 0; i < setId; i++) off += sets[i].n;
+    std::vector<uint8_t> m(hs.n);
+    CK(cudaMemcpyAsync(m.data(), r_out.p + off, hs.n, cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    for (int i = 0; i < hs.n; i++) mask[i] = m[i];
 }
 
 void Solver::getEstimates(double* poses7, double* lms) {
@@ -1432,9 +1599,22 @@ int cugo_b200_set_outliers(cugo_b200_solver* s, int set_id, const int* mask) {
     return guarded(s, [&](Solver& S) {
         if (set_id < 0 || set_id >= (int)S.sets.size()) throw cugo_b200::ArgError("set_outliers: bad set id");
         auto& hs = S.sets[set_id];
+        S.syncOutliersToHost();
         if (mask) hs.out.assign(mask, mask + hs.n); else hs.out.clear();
+        hs.outCount = 0;
+        for (int v : hs.out) hs.outCount += v ? 1 : 0;
         S.structDirty = true;
     });
+}
+
+int cugo_b200_set_outlier_threshold(cugo_b200_solver* s, int set_id, double threshold) {
+    return guarded(s, [&](Solver& S) { S.setOutlierThreshold(set_id, threshold); });
+}
+int cugo_b200_update_edges(cugo_b200_solver* s) {
+    return guarded(s, [&](Solver& S) { S.requireSingle("update_edges"); S.updateEdges(); });
+}
+int cugo_b200_get_outliers(cugo_b200_solver* s, int set_id, int* mask, int* n_outliers, int* n_inliers) {
+    return guarded(s, [&](Solver& S) { S.getOutliers(set_id, mask, n_outliers, n_inliers); });
 }
 
 int cugo_b200_set_estimates(cugo_b200_solver* s, const double* poses7, const double* landmarks3) {
@@ -1514,6 +1694,7 @@ int cugo_b200_get_values(cugo_b200_solver* s, int which, double* out, long capac
 }
 int cugo_b200_get_sizes(cugo_b200_solver* s, long sizes[10]) {
     return guarded(s, [&](Solver& S) {
+        if (!sizes) throw cugo_b200::ArgError("get_sizes: null output");
         S.ensureStructure();
         sizes[0] = S.nP; sizes[1] = S.nL; sizes[2] = S.E; sizes[3] = S.d.nHpl; sizes[4] = S.d.nblk;
         sizes[5] = S.nmulRef; sizes[6] = S.nnzSymm; sizes[7] = S.counts.nsn; sizes[8] = S.counts.nlev;
@@ -1547,6 +1728,7 @@ int cugo_b200_comm_init(cugo_b200_solver* s, int nranks, int rank, const char id
 }
 int cugo_b200_get_factor_stats(cugo_b200_solver* s, double stats[4]) {
     return guarded(s, [&](Solver& S) {
+        if (!stats) throw cugo_b200::ArgError("get_factor_stats: null output");
         S.ensureStructure();
         for (int i = 0; i < 4; i++) stats[i] = S.factStats[i];
     });

@@ -34,7 +34,7 @@ struct LMState {
     int niter;       // requested outer iterations
     int nstats;
     int slots;       // trial slots executed (diagnostics)
-    int pad;
+    int lastEval;    // estimate buffer the last k_errors evaluated (the reference's chiValues belong to it)
     double statChi2[MAX_STATS];
     double statLambda[MAX_STATS];
     int statTrials[MAX_STATS];

@@ -39,9 +39,10 @@ template <int TPB>
 __global__ void __launch_bounds__(TPB) k_errors(Dev d, SetParams sp, int which, int guarded) {
     __shared__ double sh[TPB / 32];
     pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
-    const LMState* st = d.st;
+    LMState* st = d.st;
     if (guarded && st->done) return;
     const int buf = which ? 1 - st->cur : st->cur;
+    if (blockIdx.x == 0 && threadIdx.x == 0) st->lastEval = buf;
     const double* __restrict__ pose = d.pose[buf];
     const double* __restrict__ lm = d.lm[buf];
     double sum = 0;
@@ -139,6 +140,11 @@ __device__ __forceinline__ void build_lm_cta(const Dev& d, const SetParams& sp, 
                         for (int r = 0; r < 6; r++)
                             h[c * 6 + r] = (HT)(w * (JP[0][r] * JL[0][c] + JP[1][r] * JL[1][c] + JP[2][r] * JL[2][c]));
                 }
+            } else if (d.s_out && d.s_hplPre[k + 1] != d.s_hplPre[k]) {
+                // an edge flagged on the device after the structure was built keeps its Hpl slot: a zero block
+                HT* h = hst + (size_t)(d.s_hplPre[k] - pre0) * 18;
+#pragma unroll
+                for (int i = 0; i < 18; i++) h[i] = (HT)0;
             }
         }
 #pragma unroll

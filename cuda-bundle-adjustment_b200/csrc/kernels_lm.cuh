@@ -180,4 +180,16 @@ __global__ void __launch_bounds__(TPB) k_scale_poses(Dev d, double lambda, doubl
     if (threadIdx.x == 0) *out = s;
 }
 
+// computeScale with a lambda other than the one of the last solve(): the reference's sum over the whole
+// [xp | xl] / [bp | bl] vectors (computeScaleKernel cuda_block_solver.cu:1471-1490), one CTA, fixed order
+template <int TPB>
+__global__ void __launch_bounds__(TPB) k_scale_full(Dev d, double lambda, double* out) {
+    __shared__ double sh[TPB / 32];
+    double s = 0.0;
+    const size_t n = (size_t)6 * d.nP + (size_t)3 * d.nL;
+    for (size_t i = threadIdx.x; i < n; i += TPB) s += d.x[i] * (lambda * d.x[i] + d.b[i]);
+    s = block_sum<TPB>(s, sh);
+    if (threadIdx.x == 0) *out = s;
+}
+
 }  // namespace cugo_b200

@@ -51,6 +51,18 @@ def shard_problem(prob: Problem, world: int, rank: int, mode: str = "strided") -
     the trajectory, so a shard concentrates world x the edges on 1/world of the poses (measured on 8 GPUs, KITTI-00
     shape: 18.5 ms per optimize(10) against 16.6 ms after slicing the pose-major pass)."""
     L_all, nL = prob.landmarks.shape[0], prob.nL_act
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError("shard_problem: bad rank %d / world %d" % (rank, world))
+    if mode == "strided" and world > 1:
+        # Every rank checks EVERY rank's shard, so all ranks fail together here instead of one rank throwing in
+        # build_structure (no free landmarks / no edges) while its peers block in the first collective.
+        owner_edges = np.zeros(world, np.int64)
+        for s in prob.sets:
+            owner = np.where(s.iL < nL, s.iL % world, (s.iL - nL) % world)
+            owner_edges += np.bincount(owner, minlength=world)
+        if nL < world or np.any(owner_edges == 0):
+            raise ValueError("shard_problem: %d free landmarks / per-rank edge counts %s cannot feed %d ranks "
+                             "(every rank needs a free landmark and an edge)" % (nL, owner_edges.tolist(), world))
     if mode == "strided":
         own_free = np.arange(rank, nL, world)
         own_fixed = nL + np.arange(rank, L_all - nL, world)

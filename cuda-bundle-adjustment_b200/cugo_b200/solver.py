@@ -35,7 +35,7 @@ SYMBOLS = (
     "cugo_b200_get_estimates", "cugo_b200_get_structure", "cugo_b200_get_values", "cugo_b200_get_sizes",
     "cugo_b200_get_last_timing", "cugo_b200_stream", "cugo_b200_profile_trial", "cugo_b200_update_measurements",
     "cugo_b200_debug_counters", "cugo_b200_get_factor_stats", "cugo_b200_comm_unique_id", "cugo_b200_comm_init",
-    "cugo_b200_chi2_noalloc",
+    "cugo_b200_chi2_noalloc", "cugo_b200_set_outlier_threshold", "cugo_b200_update_edges", "cugo_b200_get_outliers",
 )
 
 _lib = None
@@ -124,6 +124,20 @@ class BlockSolver:
     def set_outliers(self, set_idx, mask):
         m = _i32(mask)
         self._ck(self.lib.cugo_b200_set_outliers(self.h, set_idx, _p(m, C.c_int)))
+
+    # -- outlier gating (EdgeSet::setOutlierThreshold / updateEdges / getOutlierCount) -------------------
+    def set_outlier_threshold(self, set_idx, thr):
+        self._ck(self.lib.cugo_b200_set_outlier_threshold(self.h, int(set_idx), C.c_double(thr)))
+
+    def update_edges(self):
+        self._ck(self.lib.cugo_b200_update_edges(self.h))
+
+    def outliers(self, set_idx):
+        """(mask [n] int32 in the set's edge order, outlier count)"""
+        m = np.zeros(self.prob.sets[set_idx].n, np.int32)
+        no, ni = C.c_int(), C.c_int()
+        self._ck(self.lib.cugo_b200_get_outliers(self.h, int(set_idx), _p(m, C.c_int), C.byref(no), C.byref(ni)))
+        return m, no.value
 
     # -- stage API ----------------------------------------------------------------
     def build_structure(self):

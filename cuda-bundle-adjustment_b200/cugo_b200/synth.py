@@ -282,3 +282,19 @@ def make_graph(name="small", *, n_poses=None, n_landmarks=None, n_edges=None,
         stereo_meas=f64(meas[is_stereo]), stereo_info=f64(info[is_stereo]),
         camera=f64([fx, fy, cx, cy, bf]), name=name,
         gt_pose_q=f64(q_gt), gt_pose_t=f64(twc), gt_lm_xyz=f64(lm_gt))
+
+
+def perturb_poses(g: Graph, rot: float, trans: float, seed: int) -> Graph:
+    """Left-multiplies every pose estimate by a random rotation (rotation vector ~ N(0, rot^2) rad) and adds
+    N(0, trans^2) m to its translation: starts far enough from the optimum that Levenberg-Marquardt REJECTS trials
+    (used by the parity cases that pin the reject / lambda * nu path of src/cuda_graph_optimisation.cpp:96-106)."""
+    rng = np.random.default_rng(seed)
+    rv = rot * rng.standard_normal((g.n_poses, 3))
+    th = np.linalg.norm(rv, axis=1, keepdims=True)
+    dq = np.concatenate([np.sin(th / 2) * rv / th, np.cos(th / 2)], 1)
+    x1, y1, z1, w1 = dq.T
+    x2, y2, z2, w2 = g.pose_q.T
+    g.pose_q = np.stack([w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2, w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2,
+                         w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2, w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2], 1)
+    g.pose_t = g.pose_t + trans * rng.standard_normal(g.pose_t.shape)
+    return g

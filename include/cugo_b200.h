@@ -87,9 +87,24 @@ int cugo_b200_add_edge_set(cugo_b200_solver* s, int dim, int n, const int* iP, c
                            int* set_id);
 /* EdgeSet::setRobustKernel (src/optimisable_graph.hpp:401-406); per set here, process-global there */
 int cugo_b200_set_robust_kernel(cugo_b200_solver* s, int set_id, int robust_type, double robust_delta);
-/* outlier mask of a set (reference d_outliers, computeOutliersKernel cuda_block_solver.cu:1135-1149);
- * changing it invalidates the structure */
+/* caller-supplied outlier mask of a set (reference d_outliers / BaseEdge::inactivate, src/optimisable_graph.h:341-408);
+ * changing it invalidates the structure: masked edges own no Hpl block after the rebuild, as in the reference's
+ * buildHplBlockPos (src/optimisable_graph.hpp:642-661) */
 int cugo_b200_set_outliers(cugo_b200_solver* s, int set_id, const int* mask);
+/* -- outlier gating on the device.  EdgeSet::setOutlierThreshold (src/optimisable_graph.hpp:415-420): with a
+ * threshold > 0, the end of every cugo_b200_optimize() flags the set's edges whose robustified chi2 at the last
+ * evaluated estimates exceeds it -- BlockSolver::updateEdges (src/block_solver.cpp:423-429) ->
+ * EdgeSet::updateEdges (src/optimisable_graph.hpp:603-640) -> computeOutliersKernel
+ * (cuda_block_solver.cu:1135-1149), called from src/cuda_graph_optimisation.cpp:150-151.  Flagged edges are
+ * skipped by every later stage.  Unlike the reference (mask to the host, edges inactivated, structure rebuilt)
+ * the structure, its symbolic analysis and the trial graph are KEPT: a flagged edge's Hpl block stays in the
+ * pattern as a zero block.  cugo_b200_update_edges is the staged call (uses the estimates of the last
+ * cugo_b200_compute_errors). */
+int cugo_b200_set_outlier_threshold(cugo_b200_solver* s, int set_id, double threshold);
+int cugo_b200_update_edges(cugo_b200_solver* s);
+/* EdgeSet::getOutlierCount / getInlierCount (src/optimisable_graph.hpp:664-675) and the mask the reference
+ * downloads in updateEdges (edgeOutliers_): mask[n] in the set's edge order (may be NULL) */
+int cugo_b200_get_outliers(cugo_b200_solver* s, int set_id, int* mask, int* n_outliers, int* n_inliers);
 /* re-upload estimates only (a second initialize() on an unchanged graph keeps the structure,
  * src/block_solver.cpp:161-170) */
 int cugo_b200_set_estimates(cugo_b200_solver* s, const double* poses7, const double* landmarks3);

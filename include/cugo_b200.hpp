@@ -27,6 +27,7 @@
 #include <array>
 #include <chrono>
 #include <cstddef>
+#include <cstdint>
 #include <cstdio>
 #include <map>
 #include <memory>
@@ -295,6 +296,13 @@ public:
     virtual void setInformation(Information info) noexcept = 0;
     virtual void setCamera(const Camera& c) noexcept = 0;
     virtual Camera& getCamera() noexcept = 0;
+    // outlier gating (src/optimisable_graph.h:631-633, .hpp:415-426, 603-640, 664-675)
+    virtual void setOutlierThreshold(Scalar errorThreshold) noexcept = 0;
+    virtual Scalar getOutlierThreshold() const noexcept = 0;
+    virtual uint32_t getOutlierCount() const noexcept = 0;
+    virtual uint32_t getInlierCount() const noexcept = 0;
+    // mask[nActiveEdges] in packing order from the engine: flagged edges are inactivated (EdgeSet::updateEdges)
+    virtual void applyOutlierMask(const int* mask, size_t n) = 0;
     // flat arrays handed to cugo_b200_add_edge_set (the reference's EdgeSet::init,
     // src/optimisable_graph.hpp:474-572): active edges = flagged active and not both vertices fixed
     struct Packed {
@@ -320,7 +328,7 @@ public:
     size_t nedges() const noexcept override { return edges_.size(); }
     size_t nActiveEdges() const noexcept override { return nActive_; }
     int dim() const noexcept override { return DIM; }
-    void clearEdges() noexcept override { edges_.clear(); index_.clear(); nActive_ = 0; }
+    void clearEdges() noexcept override { edges_.clear(); packed_.clear(); index_.clear(); nActive_ = 0; outCount_ = 0; }
     void setRobustKernel(RobustKernelType type, Scalar delta) noexcept override { rk_ = type; delta_ = delta; }
     RobustKernelType robustKernelType() const noexcept { return rk_; }
     Scalar robustKernelDelta() const noexcept { return delta_; }
@@ -328,11 +336,24 @@ public:
     void setCamera(const Camera& c) noexcept override { cam_ = c; }
     Camera& getCamera() noexcept override { return cam_; }
     const std::vector<BaseEdge*>& get() const noexcept { return edges_; }
+    void setOutlierThreshold(Scalar t) noexcept override { outThr_ = t; }
+    Scalar getOutlierThreshold() const noexcept override { return outThr_; }
+    uint32_t getOutlierCount() const noexcept override { return outCount_; }
+    uint32_t getInlierCount() const noexcept override { return (uint32_t)nActive_ - outCount_; }
+    void applyOutlierMask(const int* mask, size_t n) override {
+        uint32_t c = 0;
+        for (size_t i = 0; i < n && i < packed_.size(); i++)
+            if (mask[i]) { packed_[i]->inactivate(); c++; }
+        outCount_ = c;
+    }
     void pack(const GraphOptimisationOptions& opt, Packed& out) override {
         out = Packed();
         out.dim = DIM; out.rk = (int)rk_; out.delta = delta_;
+        packed_.clear();
+        outCount_ = 0;
         for (BaseEdge* e : edges_) {
             if (!e->isActive() || e->allVerticesFixed()) continue;
+            packed_.push_back(e);
             out.iP.push_back(e->getVertex(0)->getIndex());
             out.iL.push_back(e->getVertex(1)->getIndex());
             const double* m = e->measurementData();
@@ -354,8 +375,11 @@ public:
     }
 private:
     std::vector<BaseEdge*> edges_;            // insertion order (deterministic packing)
+    std::vector<BaseEdge*> packed_;           // the edges handed to the engine, in packing order
     std::unordered_set<BaseEdge*> index_;
     size_t nActive_ = 0;
+    Scalar outThr_ = 0.0;
+    uint32_t outCount_ = 0;
     RobustKernelType rk_ = RobustKernelType::None;
     Scalar delta_ = 1.0;
     Information info_ = 1.0;
@@ -366,6 +390,181 @@ using StereoEdgeSet = EdgeSet<3>;
 
 using EdgeSetVec = std::vector<BaseEdgeSet*>;
 using VertexSetVec = std::vector<BaseVertexSet*>;
+
+// ---- BlockSolver (src/block_solver.h:24-250): one method per stage, same names and argument meaning --------
+// The reference's BlockSolver owns the device system and is driven stage by stage by the LM loop of
+// CudaGraphOptimisationImpl::optimize; this one forwards every stage to the C ABI.  `optimizeOnDevice` is the one
+// addition: the whole LM loop of src/cuda_graph_optimisation.cpp:48-154 run on the device in one call.
+class BlockSolver {
+public:
+    enum ProfileItem {
+        PROF_ITEM_INITIALIZE, PROF_ITEM_BUILD_STRUCTURE, PROF_ITEM_COMPUTE_ERROR, PROF_ITEM_BUILD_SYSTEM,
+        PROF_ITEM_SCHUR_COMPLEMENT, PROF_ITEM_DECOMP_SYMBOLIC, PROF_ITEM_DECOMP_NUMERICAL, PROF_ITEM_UPDATE,
+        PROF_ITEM_SOLVE_HPP, PROF_ITEM_COUNT
+    };
+    BlockSolver() = delete;
+    // `device`: CUDA ordinal (the reference passes its CudaDevice, which picks "the fastest" GPU: src/cuda_device.cpp:15-42)
+    explicit BlockSolver(GraphOptimisationOptions& options, int device = 0) : options(options) {
+#ifdef USE_FLOAT32            // the reference's compile-time switch (include/scalar.h): single-precision block storage
+        const int rc = cugo_b200_create(device, 1, &h_);
+#else
+        const int rc = cugo_b200_create(device, 0, &h_);
+#endif
+        if (rc != CUGO_B200_OK)
+            throw std::runtime_error(rc == CUGO_B200_ENODEVICE ? "cugo: no CUDA device (this engine has no CPU path)"
+                                                               : "cugo: cannot create the solver");
+        for (double& v : profItems_) v = 0.0;
+    }
+    ~BlockSolver() { if (h_) cugo_b200_destroy(h_); }
+    BlockSolver(const BlockSolver&) = delete;
+    BlockSolver& operator=(const BlockSolver&) = delete;
+
+    // src/block_solver.cpp:21-137: vertex set 0 = poses, 1 = landmarks (include/ba_types.h:46-49).  An unchanged
+    // graph keeps its structure and symbolic analysis and only re-uploads estimates, measurements and informations
+    // (src/block_solver.cpp:161-170).
+    void initialize(const EdgeSetVec& edgeSets, const VertexSetVec& vertexSets) {
+        const auto t0 = now();
+        if (vertexSets.size() != 2 || vertexSets[0]->estimateDim() != 7 || vertexSets[1]->estimateDim() != 3)
+            throw std::runtime_error("cugo: add the pose vertex set first, then the landmark vertex set");
+        for (auto* vs : vertexSets) vs->assignIndices();
+        vertexSets[0]->packEstimates(poses_);
+        vertexSets[1]->packEstimates(landmarks_);
+        std::vector<BaseEdgeSet::Packed> packed(edgeSets.size());
+        nedges_ = 0;
+        for (size_t i = 0; i < edgeSets.size(); i++) { edgeSets[i]->pack(options, packed[i]); nedges_ += packed[i].n; }
+        const int nPa = (int)vertexSets[0]->size(), nP = vertexSets[0]->getActiveSize();
+        const int nLa = (int)vertexSets[1]->size(), nL = vertexSets[1]->getActiveSize();
+        bool same = uploaded_ && nPa == nPa_ && nP == nP_ && nLa == nLa_ && nL == nL_ && packed.size() == last_.size();
+        for (size_t i = 0; same && i < packed.size(); i++)
+            same = packed[i].dim == last_[i].dim && packed[i].iP == last_[i].iP && packed[i].iL == last_[i].iL &&
+                   packed[i].nomega == last_[i].nomega && packed[i].cam == last_[i].cam;
+        if (same) {
+            ck(cugo_b200_set_estimates(h_, poses_.data(), landmarks_.data()));
+            for (size_t i = 0; i < packed.size(); i++) {
+                if (packed[i].meas != last_[i].meas || packed[i].omega != last_[i].omega)
+                    ck(cugo_b200_update_measurements(h_, (int)i, packed[i].meas.data(), packed[i].omega.data(), packed[i].nomega));
+                if (packed[i].rk != last_[i].rk || packed[i].delta != last_[i].delta)
+                    ck(cugo_b200_set_robust_kernel(h_, (int)i, packed[i].rk, packed[i].delta));
+            }
+        } else {
+            ck(cugo_b200_set_vertices(h_, nPa, nP, poses_.data(), nLa, nL, landmarks_.data()));
+            ck(cugo_b200_clear_edge_sets(h_));
+            for (auto& p : packed) {
+                int id = -1;
+                ck(cugo_b200_add_edge_set(h_, p.dim, p.n, p.iP.data(), p.iL.data(), p.meas.data(), p.omega.data(), p.nomega,
+                                          p.cam.data(), p.ncam, p.rk, p.delta, &id));
+            }
+            nPa_ = nPa; nP_ = nP; nLa_ = nLa; nL_ = nL;
+        }
+        for (size_t i = 0; i < edgeSets.size(); i++)
+            ck(cugo_b200_set_outlier_threshold(h_, (int)i, edgeSets[i]->getOutlierThreshold()));
+        last_.swap(packed);
+        uploaded_ = true;
+        profItems_[PROF_ITEM_INITIALIZE] = ms(t0);
+    }
+    void buildStructure(const EdgeSetVec&, const VertexSetVec&) {      // src/block_solver.cpp:139-248 (no-op when current)
+        need();
+        const auto t0 = now();
+        ck(cugo_b200_build_structure(h_));
+        profItems_[PROF_ITEM_BUILD_STRUCTURE] = ms(t0);
+    }
+    double computeErrors(const EdgeSetVec&, const VertexSetVec&) {     // :250-272
+        need();
+        const auto t0 = now();
+        double chi2 = 0;
+        ck(cugo_b200_compute_errors(h_, &chi2));
+        profItems_[PROF_ITEM_COMPUTE_ERROR] = ms(t0);
+        return chi2;
+    }
+    void buildSystem(const EdgeSetVec&, const VertexSetVec&) {         // :274-307
+        need();
+        const auto t0 = now();
+        ck(cugo_b200_build_system(h_));
+        profItems_[PROF_ITEM_BUILD_SYSTEM] = ms(t0);
+    }
+    double maxDiagonal() { double v = 0; ck(cugo_b200_max_diagonal(h_, &v)); return v; }     // :309-320
+    void setLambda(double lambda) { ck(cugo_b200_set_lambda(h_, lambda)); }                   // :322-329
+    void restoreDiagonal() { ck(cugo_b200_restore_diagonal(h_)); }                            // :331-338
+    bool solve() {                                                                            // :340-388
+        const auto t0 = now();
+        int ok = 0;
+        ck(cugo_b200_solve(h_, &ok));
+        // Schur complement, numerical decomposition and back-substitution are one enqueue here
+        profItems_[PROF_ITEM_DECOMP_NUMERICAL] = ms(t0);
+        return ok != 0;
+    }
+    void update(const VertexSetVec&) {                                                        // :390-413
+        const auto t0 = now();
+        ck(cugo_b200_update(h_));
+        profItems_[PROF_ITEM_UPDATE] = ms(t0);
+    }
+    // :423-429 -> EdgeSet::updateEdges (src/optimisable_graph.hpp:603-640).  flagOnDevice = false when the device
+    // LM loop has already flagged (cugo_b200_optimize does it at its end, as the reference's optimize()).
+    void updateEdges(const EdgeSetVec& edgeSets, bool flagOnDevice = true) {
+        bool any = false;
+        for (auto* es : edgeSets) any = any || es->getOutlierThreshold() > 0.0;
+        if (!any) return;
+        if (flagOnDevice) ck(cugo_b200_update_edges(h_));
+        std::vector<int> mask;
+        for (size_t i = 0; i < edgeSets.size(); i++) {
+            if (!(edgeSets[i]->getOutlierThreshold() > 0.0) || edgeSets[i]->nActiveEdges() == 0) continue;
+            mask.assign(edgeSets[i]->nActiveEdges(), 0);
+            int no = 0, ni = 0;
+            ck(cugo_b200_get_outliers(h_, (int)i, mask.data(), &no, &ni));
+            edgeSets[i]->applyOutlierMask(mask.data(), mask.size());
+        }
+    }
+    double computeScale(double lambda) { double v = 0; ck(cugo_b200_compute_scale(h_, lambda, &v)); return v; }   // :415-421
+    void push() { ck(cugo_b200_push(h_)); }                                                   // :431-434
+    void pop() { ck(cugo_b200_pop(h_)); }                                                     // :436-439
+    void clear() noexcept { uploaded_ = false; last_.clear(); nedges_ = 0; }                  // :460-468
+    void finalize(const VertexSetVec& vertexSets) {                                           // :441-458
+        need();
+        ck(cugo_b200_get_estimates(h_, poses_.data(), landmarks_.data()));
+        vertexSets[0]->unpackEstimates(poses_.data());
+        vertexSets[1]->unpackEstimates(landmarks_.data());
+    }
+    // the reference's nine profile strings (src/block_solver.cpp:470-488); host wall-clock ms of the last call of each
+    // stage (every staged call of the C ABI synchronises).  Items 4 and 5 are inside "1" / "6" here.
+    void getTimeProfile(TimeProfile& prof) const {
+        static const char* names[PROF_ITEM_COUNT] = {
+            "0: Initialize Optimizer", "1: Build Structure", "2: Compute Error", "3: Build System", "4: Schur Complement",
+            "5: Symbolic Decomposition", "6: Numerical Decomposition", "7: Update Solution", "8: Hpp linear solver"};
+        prof.clear();
+        for (int i = 0; i < PROF_ITEM_COUNT; i++) prof[names[i]] = profItems_[i];
+    }
+    int nedges() const { return nedges_; }
+    static inline uint8_t makeEdgeFlag(bool fixedP, bool fixedL) { return (uint8_t)((fixedP ? 2 : 0) | (fixedL ? 1 : 0)); }
+
+    // the LM loop of CudaGraphOptimisationImpl::optimize on the device: one entry per outer iteration
+    int optimizeOnDevice(int niterations, std::vector<double>& chi2, std::vector<double>& lambda, std::vector<int>& trials) {
+        need();
+        const int cap = niterations > 0 ? niterations : 1;
+        chi2.assign(cap, 0.0); lambda.assign(cap, 0.0); trials.assign(cap, 0);
+        int n = 0;
+        ck(cugo_b200_optimize(h_, niterations, cap, chi2.data(), lambda.data(), trials.data(), &n));
+        n = n < cap ? n : cap;
+        chi2.resize(n); lambda.resize(n); trials.resize(n);
+        return n;
+    }
+    void lastTiming(double& deviceMs, long& kernels) { ck(cugo_b200_get_last_timing(h_, &deviceMs, &kernels)); }
+    cugo_b200_solver* handle() noexcept { return h_; }
+
+private:
+    using Clock = std::chrono::steady_clock;
+    static Clock::time_point now() { return Clock::now(); }
+    static double ms(Clock::time_point t0) { return std::chrono::duration<double, std::milli>(Clock::now() - t0).count(); }
+    void ck(int rc) { if (rc != CUGO_B200_OK) throw std::runtime_error(std::string("cugo: ") + cugo_b200_last_error(h_)); }
+    void need() const { if (!uploaded_) throw std::runtime_error("cugo: BlockSolver used before initialize()"); }
+    GraphOptimisationOptions& options;      // held by reference, as in the reference (src/block_solver.h:177)
+    cugo_b200_solver* h_ = nullptr;
+    bool uploaded_ = false;
+    int nedges_ = 0;
+    int nPa_ = 0, nP_ = 0, nLa_ = 0, nL_ = 0;
+    std::vector<double> poses_, landmarks_;
+    std::vector<BaseEdgeSet::Packed> last_;
+    double profItems_[PROF_ITEM_COUNT];
+};
 
 // ---- the optimiser (include/cuda_graph_optimisation.h:132-239) ----------------------------------------
 class CudaGraphOptimisationImpl;
@@ -389,11 +588,10 @@ public:
 
 class CudaGraphOptimisationImpl : public CudaGraphOptimisation {
 public:
-    // `device`: CUDA ordinal this optimiser is bound to (the reference picks "the fastest" GPU itself,
-    // src/cuda_device.cpp:15-42).  The options object is held by reference, as in the reference.
-    explicit CudaGraphOptimisationImpl(GraphOptimisationOptions& options, int device = 0) : options_(options) { open(device); }
-    explicit CudaGraphOptimisationImpl(int device = 0) : options_(ownOptions_) { open(device); }
-    ~CudaGraphOptimisationImpl() override { if (h_) cugo_b200_destroy(h_); }
+    // `device`: CUDA ordinal this optimiser is bound to.  The options object is held by reference, as in the reference.
+    explicit CudaGraphOptimisationImpl(GraphOptimisationOptions& options, int device = 0)
+        : options_(options), solver_(new BlockSolver(options, device)) {}
+    explicit CudaGraphOptimisationImpl(int device = 0) : options_(ownOptions_), solver_(new BlockSolver(ownOptions_, device)) {}
     CudaGraphOptimisationImpl(const CudaGraphOptimisationImpl&) = delete;
     CudaGraphOptimisationImpl& operator=(const CudaGraphOptimisationImpl&) = delete;
 
@@ -411,104 +609,49 @@ public:
     BatchStatistics& batchStatistics() override { return stats_; }
     const TimeProfile& timeProfile() override { return timeProfile_; }
 
-    // BlockSolver::initialize (src/block_solver.cpp:21-137): vertex set 0 = poses, 1 = landmarks
-    // (include/ba_types.h:46-49).  An unchanged graph keeps its structure and symbolic analysis and only
-    // re-uploads estimates, measurements and informations (src/block_solver.cpp:161-170).
-    void initialize() override {
-        const auto t0 = std::chrono::steady_clock::now();
-        if (vertexSets_.size() != 2 || vertexSets_[0]->estimateDim() != 7 || vertexSets_[1]->estimateDim() != 3)
-            throw std::runtime_error("cugo: add the pose vertex set first, then the landmark vertex set");
-        for (auto* vs : vertexSets_) vs->assignIndices();
-        vertexSets_[0]->packEstimates(poses_);
-        vertexSets_[1]->packEstimates(landmarks_);
-        std::vector<BaseEdgeSet::Packed> packed(edgeSets_.size());
-        for (size_t i = 0; i < edgeSets_.size(); i++) edgeSets_[i]->pack(options_, packed[i]);
-        const int nPa = (int)vertexSets_[0]->size(), nP = vertexSets_[0]->getActiveSize();
-        const int nLa = (int)vertexSets_[1]->size(), nL = vertexSets_[1]->getActiveSize();
-        bool same = uploaded_ && nPa == nPa_ && nP == nP_ && nLa == nLa_ && nL == nL_ && packed.size() == last_.size();
-        for (size_t i = 0; same && i < packed.size(); i++)
-            same = packed[i].dim == last_[i].dim && packed[i].iP == last_[i].iP && packed[i].iL == last_[i].iL &&
-                   packed[i].nomega == last_[i].nomega && packed[i].cam == last_[i].cam;
-        if (same) {
-            ck(cugo_b200_set_estimates(h_, poses_.data(), landmarks_.data()));
-            for (size_t i = 0; i < packed.size(); i++) {
-                if (packed[i].meas != last_[i].meas || packed[i].omega != last_[i].omega)
-                    ck(cugo_b200_update_measurements(h_, (int)i, packed[i].meas.data(), packed[i].omega.data(), packed[i].nomega));
-                if (packed[i].rk != last_[i].rk || packed[i].delta != last_[i].delta)
-                    ck(cugo_b200_set_robust_kernel(h_, (int)i, packed[i].rk, packed[i].delta));
-            }
-        } else {
-            ck(cugo_b200_set_vertices(h_, nPa, nP, poses_.data(), nLa, nL, landmarks_.data()));
-            ck(cugo_b200_clear_edge_sets(h_));
-            for (auto& p : packed) {
-                int id = -1;
-                ck(cugo_b200_add_edge_set(h_, p.dim, p.n, p.iP.data(), p.iL.data(), p.meas.data(), p.omega.data(), p.nomega,
-                                          p.cam.data(), p.ncam, p.rk, p.delta, &id));
-            }
-            nPa_ = nPa; nP_ = nP; nLa_ = nLa; nL_ = nL;
-        }
-        last_.swap(packed);
-        uploaded_ = true;
+    void initialize() override {                                   // src/cuda_graph_optimisation.cpp:42-46
+        solver_->initialize(edgeSets_, vertexSets_);
         stats_.clear();
-        timeProfile_["0: Initialize (host ms)"] = ms(t0);
+        initialized_ = true;
     }
 
-    // CudaGraphOptimisationImpl::optimize (src/cuda_graph_optimisation.cpp:48-154): the whole LM loop
-    // runs on the device; the estimates are written back into the vertices afterwards (finalize).
+    // CudaGraphOptimisationImpl::optimize (src/cuda_graph_optimisation.cpp:48-154): buildStructure, the LM loop (on
+    // the device here), updateEdges, finalize (estimates written back into the vertices).
     void optimize(int niterations) override {
-        if (!uploaded_) throw std::runtime_error("cugo: optimize() before initialize()");
-        const auto t0 = std::chrono::steady_clock::now();
-        ck(cugo_b200_build_structure(h_));      // no-op when the structure is current
-        timeProfile_["1: Build Structure + Symbolic Decomposition (host ms)"] = ms(t0);
+        if (!initialized_) throw std::runtime_error("cugo: optimize() before initialize()");
+        solver_->buildStructure(edgeSets_, vertexSets_);
         const auto t1 = std::chrono::steady_clock::now();
-        const int cap = niterations > 0 ? niterations : 1;
-        std::vector<double> chi2(cap), lambda(cap);
-        std::vector<int> trials(cap);
-        int n = 0;
-        ck(cugo_b200_optimize(h_, niterations, cap, chi2.data(), lambda.data(), trials.data(), &n));
-        for (int i = 0; i < n && i < cap; i++) {
+        std::vector<double> chi2, lambda;
+        std::vector<int> trials;
+        const int n = solver_->optimizeOnDevice(niterations, chi2, lambda, trials);
+        for (int i = 0; i < n; i++) {
             stats_.addStat({i, chi2[i]});
             if (verbose_) std::printf("iter: %2d, chi2: %.1f, lambda: %.3e, rejected trials: %d\n", i + 1, chi2[i], lambda[i], trials[i]);
         }
-        ck(cugo_b200_get_estimates(h_, poses_.data(), landmarks_.data()));
-        vertexSets_[0]->unpackEstimates(poses_.data());
-        vertexSets_[1]->unpackEstimates(landmarks_.data());
+        solver_->updateEdges(edgeSets_, false);     // flagged at the end of the device loop; here: mask -> edges
+        solver_->finalize(vertexSets_);
+        solver_->getTimeProfile(timeProfile_);
         double devMs = 0; long kernels = 0;
-        ck(cugo_b200_get_last_timing(h_, &devMs, &kernels));
-        timeProfile_["2: LM iterations (device ms)"] = devMs;
-        timeProfile_["3: LM iterations + write-back (host ms)"] = ms(t1);
-        timeProfile_["4: kernels launched"] = (double)kernels;
+        solver_->lastTiming(devMs, kernels);
+        timeProfile_["LM iterations (device ms)"] = devMs;
+        timeProfile_["LM iterations + write-back (host ms)"] =
+            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
+        timeProfile_["kernels launched"] = (double)kernels;
         if (profile_) for (auto& kv : timeProfile_) std::printf("%s:  %f\n", kv.first.c_str(), kv.second);
     }
 
-    cugo_b200_solver* handle() noexcept { return h_; }   // the C ABI handle, for stage-level calls
+    BlockSolver& solver() noexcept { return *solver_; }             // stage-level access (the reference's solver_)
+    cugo_b200_solver* handle() noexcept { return solver_->handle(); }   // the C ABI handle
 
 private:
-    void open(int device) {
-#ifdef USE_FLOAT32            // the reference's compile-time switch (include/scalar.h): single-precision block storage
-        const int rc = cugo_b200_create(device, 1, &h_);
-#else
-        const int rc = cugo_b200_create(device, 0, &h_);
-#endif
-        if (rc != CUGO_B200_OK)
-            throw std::runtime_error(rc == CUGO_B200_ENODEVICE ? "cugo: no CUDA device (this engine has no CPU path)"
-                                                               : "cugo: cannot create the solver");
-    }
-    void ck(int rc) { if (rc != CUGO_B200_OK) throw std::runtime_error(std::string("cugo: ") + cugo_b200_last_error(h_)); }
-    static double ms(std::chrono::steady_clock::time_point t0) {
-        return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-    }
     GraphOptimisationOptions ownOptions_;
     GraphOptimisationOptions& options_;
-    cugo_b200_solver* h_ = nullptr;
+    std::unique_ptr<BlockSolver> solver_;
     EdgeSetVec edgeSets_;
     VertexSetVec vertexSets_;
     BatchStatistics stats_;
     TimeProfile timeProfile_;
-    bool verbose_ = false, profile_ = false, uploaded_ = false;
-    int nPa_ = 0, nP_ = 0, nLa_ = 0, nL_ = 0;
-    std::vector<double> poses_, landmarks_;
-    std::vector<BaseEdgeSet::Packed> last_;
+    bool verbose_ = false, profile_ = false, initialized_ = false;
 };
 
 inline CudaGraphOptimisation::Ptr CudaGraphOptimisation::create() { return Ptr(new CudaGraphOptimisationImpl()); }

@@ -117,6 +117,20 @@ class Oracle:
         m = np.ascontiguousarray(mask, np.int32)
         assert self.lib.bao_set_outliers(self.h, set_idx, _p(m, C.c_int)) == 0
 
+    # outlier gating (EdgeSet::setOutlierThreshold / updateEdges / getOutlierCount, src/optimisable_graph.hpp:415,603-670)
+    def set_outlier_threshold(self, set_idx, thr):
+        assert self.lib.bao_set_outlier_threshold(self.h, set_idx, C.c_double(thr)) == 0
+
+    def update_edges(self):
+        return bool(self.lib.bao_update_edges(self.h))
+
+    def outliers(self, set_idx):
+        """(mask [n] int32 in the set's edge order, outlier count)"""
+        m = np.zeros(self.prob.sets[set_idx].n, np.int32)
+        c = C.c_int()
+        assert self.lib.bao_get_outliers(self.h, set_idx, _p(m, C.c_int), C.byref(c)) == 0
+        return m, c.value
+
     def optimize(self, niter):
         chi2 = np.zeros(niter, np.float64)
         lam = np.zeros(niter, np.float64)

@@ -67,7 +67,7 @@ static void dumpDev(const std::string& prefix, const char* name, const T* d, siz
 
 int main(int argc, char** argv) {
     if (argc < 4) {
-        fprintf(stderr, "usage: ref_driver graph.bag out_prefix niter [rk_type(0 none,1 cauchy,2 tukey) delta] [reps]\n");
+        fprintf(stderr, "usage: ref_driver graph.bag out_prefix niter [rk_type(0 none,1 cauchy,2 tukey) delta] [reps] [outlier_threshold niter2]\n");
         return 1;
     }
     const GraphFile g = readGraph(argv[1]);
@@ -76,6 +76,9 @@ int main(int argc, char** argv) {
     const int rkType = argc > 4 ? atoi(argv[4]) : 0;
     const double rkDelta = argc > 5 ? atof(argv[5]) : 1.0;
     const int reps = argc > 6 ? atoi(argv[6]) : 1;
+    // outlier scenario (EdgeSet::setOutlierThreshold): initialize(); optimize(niter); optimize(niter2)
+    const double outThr = argc > 7 ? atof(argv[7]) : 0.0;
+    const int niter2 = argc > 8 ? atoi(argv[8]) : 0;
 
     cugo::GraphOptimisationOptions options;
     options.perEdgeInformation = true;
@@ -156,8 +159,62 @@ int main(int argc, char** argv) {
             ", \"rk_delta\": " + std::to_string(rkDelta) + ",\n";
     std::vector<double> wallInit, wallOpt;
     std::vector<double> chi2;
+    auto listd0 = [](const std::vector<double>& v) {
+        std::string s = "[";
+        char buf[64];
+        for (size_t i = 0; i < v.size(); i++) { snprintf(buf, sizeof(buf), "%s%.17g", i ? ", " : "", v[i]); s += buf; }
+        return s + "]";
+    };
+    if (outThr > 0) {
+        // optimize -> updateEdges (src/cuda_graph_optimisation.cpp:150-151) -> optimize again WITHOUT initialize():
+        // the device mask persists, flagged edges are inactive, the structure is rebuilt without their Hpl blocks
+        monoSet.setOutlierThreshold(outThr);
+        stereoSet.setOutlierThreshold(outThr);
+        optimizer->initialize();
+        // the packed edge order of this run (unordered_set iteration order) is dumped to key the masks by (pose, landmark)
+        optimizer->setVerbose(true);
+        optimizer->optimize(niter);
+        cudaDeviceSynchronize();
+        dumpDev(prefix, "mono_edge2pl", (const int*)monoSet.d_edge2PL.data(), monoSet.nActiveEdges() * 2);
+        dumpDev(prefix, "stereo_edge2pl", (const int*)stereoSet.d_edge2PL.data(), stereoSet.nActiveEdges() * 2);
+        std::vector<double> chiA, chiB;
+        for (const auto& st : optimizer->batchStatistics().get()) chiA.push_back(st.chi2);
+        const int cntA[2] = {(int)monoSet.getOutlierCount(), (int)stereoSet.getOutlierCount()};
+        dumpDev(prefix, "mono_outliers_a", monoSet.d_outliers.data(), monoSet.nActiveEdges());
+        dumpDev(prefix, "stereo_outliers_a", stereoSet.d_outliers.data(), stereoSet.nActiveEdges());
+        const size_t nA = optimizer->batchStatistics().get().size();
+        optimizer->optimize(niter2);
+        cudaDeviceSynchronize();
+        const auto& all = optimizer->batchStatistics().get();     // optimize() appends to the same statistics object
+        for (size_t i = (all.size() > nA ? nA : 0); i < all.size(); i++) chiB.push_back(all[i].chi2);
+        const int cntB[2] = {(int)monoSet.getOutlierCount(), (int)stereoSet.getOutlierCount()};
+        dumpDev(prefix, "mono_outliers_b", monoSet.d_outliers.data(), monoSet.nActiveEdges());
+        dumpDev(prefix, "stereo_outliers_b", stereoSet.d_outliers.data(), stereoSet.nActiveEdges());
+        std::vector<double> est((size_t)g.P * 7 + (size_t)g.L * 3);
+        for (int i = 0; i < g.P; i++) {
+            const cugo::Se3D& e = pv[i]->getEstimate();
+            for (int k = 0; k < 4; k++) est[7 * (size_t)i + k] = e.r[k];
+            for (int k = 0; k < 3; k++) est[7 * (size_t)i + 4 + k] = e.t[k];
+        }
+        for (int i = 0; i < g.L; i++) {
+            const cugo::Vec3d& e = lv[i]->getEstimate();
+            for (int k = 0; k < 3; k++) est[(size_t)g.P * 7 + 3 * (size_t)i + k] = e[k];
+        }
+        dumpHost(prefix, "final_estimates", est.data(), est.size());
+        char buf[512];
+        snprintf(buf, sizeof(buf), "  \"outlier_threshold\": %.17g, \"niter2\": %d, \"outliers_a\": [%d, %d], \"outliers_b\": [%d, %d],\n",
+                 outThr, niter2, cntA[0], cntA[1], cntB[0], cntB[1]);
+        json += buf;
+        json += "  \"chi2_a\": " + listd0(chiA) + ",\n  \"chi2_b\": " + listd0(chiB) + "\n}\n";
+        FILE* f = fopen((prefix + ".json").c_str(), "w");
+        fputs(json.c_str(), f);
+        fclose(f);
+        printf("%s", json.c_str());
+        return 0;
+    }
     for (int rep = 0; rep < reps; rep++) {
         resetEstimates();
+        optimizer->setVerbose(rep == 0);     // prints "levenberg iterations = q" per outer iteration (trial counts)
         cudaDeviceSynchronize();
         const auto t0 = std::chrono::steady_clock::now();
         optimizer->initialize();

@@ -7,6 +7,7 @@ golden fixtures the tests pin the oracle and the CUDA engine against (tests/gold
 import hashlib
 import json
 import os
+import re
 import subprocess
 import sys
 
@@ -29,7 +30,14 @@ CONFIGS = {
     "small_cauchy": (dict(outlier_frac=0.05, seed=7002), 1, 2.0),
     "small_tukey": (dict(outlier_frac=0.05, seed=7002), 2, 4.0),
     "small_fixedlm": (dict(fixed_landmark_frac=0.15, seed=21), 0, 1.0),
+    # poses start far off (synth.perturb_poses): several outer iterations REJECT trials
+    # (src/cuda_graph_optimisation.cpp:96-106: lambda *= nu, nu *= 2, restoreDiagonal, pop)
+    "tiny_reject": (dict(seed=11), 0, 1.0),
+    # 5 % gross outliers, EdgeSet::setOutlierThreshold(OUTLIER_THR): optimize(5), updateEdges, optimize(5) again
+    "small_outlier": (dict(outlier_frac=0.05, seed=7002), 0, 1.0),
 }
+POSE_NOISE = {"tiny_reject": (0.1, 3.0, 2)}   # synth.perturb_poses(rot [rad], trans [m], seed) before the run
+OUTLIER = {"small_outlier": (30.0, 5, 5)}  # threshold on rho(omega |e|^2), niter of the first and second optimize()
 
 
 def sha(a):
@@ -44,10 +52,33 @@ def main():
         kw, rk, delta = CONFIGS[name]
         base = name.split("_")[0]
         g = synth.make_graph(base, **kw)
+        if name in POSE_NOISE:
+            synth.perturb_poses(g, *POSE_NOISE[name])
         bag = os.path.join(out_dir, name + ".bag")
         graphio.write_graph(g, bag)
         prefix = os.path.join(out_dir, "raw_" + name)
         reps = 4
+        if name in OUTLIER:
+            thr, n1, n2 = OUTLIER[name]
+            r = subprocess.run([DRIVER, bag, prefix, str(n1), str(rk), str(delta), "1", repr(thr), str(n2)],
+                               capture_output=True, text=True)
+            os.remove(bag)
+            if r.returncode != 0 or not os.path.exists(prefix + ".json"):
+                print(name, "reference driver FAILED rc", r.returncode, r.stderr[-2000:], flush=True)
+                continue
+            meta = json.load(open(prefix + ".json"))
+            arrays = {}
+            for a, t in (("mono_edge2pl", np.int32), ("stereo_edge2pl", np.int32), ("mono_outliers_a", np.int32),
+                         ("stereo_outliers_a", np.int32), ("mono_outliers_b", np.int32), ("stereo_outliers_b", np.int32),
+                         ("final_estimates", np.float64)):
+                fn = "%s.%s.bin" % (prefix, a)
+                arrays[a] = np.fromfile(fn, t)
+                os.remove(fn)
+            meta["generator"] = dict(name=base, kwargs=kw)
+            json.dump(meta, open(os.path.join(out_dir, "ref_%s.json" % name), "w"), indent=1)
+            np.savez_compressed(os.path.join(out_dir, "ref_%s.npz" % name), **arrays)
+            print(name, "outliers", meta["outliers_a"], meta["outliers_b"], "chi2_b", meta["chi2_b"][:3], flush=True)
+            continue
         r = subprocess.run([DRIVER, bag, prefix, "10", str(rk), str(delta), str(reps)], capture_output=True, text=True)
         open(prefix + ".stdout", "w").write(r.stdout + "\n--- stderr ---\n" + r.stderr)
         os.remove(bag)
@@ -55,6 +86,11 @@ def main():
             print(name, "reference driver FAILED rc", r.returncode, r.stderr[-2000:], flush=True)
             continue
         meta = json.load(open(prefix + ".json"))
+        # rejected trials per outer iteration of the cold run: the reference's verbose line
+        # (src/cuda_graph_optimisation.cpp:114-132, "levenberg iterations = q")
+        meta["trials"] = [int(v) for v in re.findall(r"levenberg iterations = (\d+)", r.stdout)][:len(meta["chi2"])]
+        if name in POSE_NOISE:
+            meta["pose_noise"] = list(POSE_NOISE[name])
         arrays, digest = {}, {}
         full = g.n_edges <= FULL_LIMIT
         for a in INT_ARRAYS + F64_ARRAYS:

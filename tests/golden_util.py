@@ -7,7 +7,7 @@ import numpy as np
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 RK_NAMES = {0: "none", 1: "cauchy", 2: "tukey"}
-CASES = ["tiny", "small", "small_cauchy", "small_tukey", "small_fixedlm", "loop", "kitti07", "kitti00"]
+CASES = ["tiny", "small", "small_cauchy", "small_tukey", "small_fixedlm", "tiny_reject", "loop", "kitti07", "kitti00"]
 
 
 def load(case):
@@ -19,6 +19,9 @@ def load(case):
 def problem_of(meta):
     from cugo_b200 import pack, synth
     g = synth.make_graph(meta["generator"]["name"], **meta["generator"]["kwargs"])
+    if meta.get("pose_noise"):                  # tiny_reject: a start from which LM rejects trials
+        rot, trans, seed = meta["pose_noise"]
+        synth.perturb_poses(g, rot, trans, int(seed))
     return g, pack.pack(g)
 
 
@@ -104,6 +107,9 @@ def check_all(case, make_solver, value_rtol=1e-9, x_rtol=1e-7, chi_rtol=1e-9):
     chi2, lam, trials = s2.optimize(meta["niter"])
     ref_chi2 = np.array(meta["chi2"])
     assert len(chi2) == len(ref_chi2)
+    if "trials" in meta:                        # rejected trials per outer iteration, from the reference's verbose log
+        np.testing.assert_array_equal(np.asarray(trials), np.asarray(meta["trials"]))
+        report["rejected_trials"] = int(np.sum(meta["trials"]))
     report["chi2"] = float(np.max(np.abs(chi2 - ref_chi2) / ref_chi2))
     assert report["chi2"] <= chi_rtol, "chi2 trajectory relative error %.3e" % report["chi2"]
     poses, lms = s2.estimates()
@@ -113,3 +119,46 @@ def check_all(case, make_solver, value_rtol=1e-9, x_rtol=1e-7, chi_rtol=1e-9):
     mine = fin if "final_estimates" in arrays else fin[::97]
     report["final_rmse"] = float(np.sqrt(np.mean((mine - ref) ** 2)))
     return report
+
+
+def check_outlier_case(case, make_solver, chi_rtol=1e-9):
+    """optimize(n1) -> updateEdges -> optimize(n2) with an outlier threshold on both sets, against the reference's
+    run (oracle/ref_driver.cpp outlier scenario): chi2 of both runs, outlier counts and masks (through the
+    (pose, landmark) key: the reference packs its edges in pointer-hash order), final estimates."""
+    from cugo_b200 import pack
+    meta, arrays = load(case)
+    g, prob = problem_of(meta)
+    s = make_solver(prob, RK_NAMES[meta["rk_type"]], meta["rk_delta"])
+    for i in range(len(prob.sets)):
+        s.set_outlier_threshold(i, meta["outlier_threshold"])
+    rep = {}
+    chiA, _, _ = s.optimize(meta["niter"])
+    refA = np.array(meta["chi2_a"])
+    assert len(chiA) == len(refA)
+    rep["chi2_a"] = float(np.max(np.abs(chiA - refA) / refA))
+    assert rep["chi2_a"] <= chi_rtol
+
+    def masks_equal(tag):
+        n = 0
+        for si, key in enumerate(("mono", "stereo")):
+            mine, cnt = s.outliers(si)
+            assert cnt == meta["outliers_" + tag][si], (key, cnt, meta["outliers_" + tag])
+            ref_pl = arrays[key + "_edge2pl"].reshape(-1, 2)
+            ref = {(int(p), int(l)): int(m) for (p, l), m in zip(ref_pl, arrays["%s_outliers_%s" % (key, tag)])}
+            st = prob.sets[si]
+            for i in range(st.n):
+                assert ref[(int(st.iP[i]), int(st.iL[i]))] == int(mine[i]), (key, i)
+            n += cnt
+        return n
+    rep["outliers_a"] = masks_equal("a")
+    chiB, _, _ = s.optimize(meta["niter2"])
+    refB = np.array(meta["chi2_b"])
+    assert len(chiB) == len(refB)
+    rep["chi2_b"] = float(np.max(np.abs(chiB - refB) / refB))
+    assert rep["chi2_b"] <= chi_rtol
+    rep["outliers_b"] = masks_equal("b")
+    poses, lms = s.estimates()
+    q, t, X = pack.unpack_estimates(prob, poses, lms)
+    fin = np.concatenate([np.concatenate([q, t], 1).reshape(-1), X.reshape(-1)])
+    rep["final_rmse"] = float(np.sqrt(np.mean((fin - arrays["final_estimates"]) ** 2)))
+    return rep

@@ -18,3 +18,12 @@ def test_oracle_matches_reference(case):
     # final estimates after 10 iterations: the oracle and the reference differ only by the
     # elimination order of the Cholesky and by atomic summation order
     assert rep["final_rmse"] < 1e-9
+
+
+def test_oracle_outlier_gating_matches_reference():
+    """EdgeSet::setOutlierThreshold + updateEdges at the end of optimize() (src/optimisable_graph.hpp:415,603-640,
+    src/cuda_graph_optimisation.cpp:150-151): optimize(5), optimize(5) again on the unmodified reference
+    (tests/golden/ref_small_outlier.*) against the oracle -- chi2 of both runs, outlier masks and counts."""
+    rep = golden_util.check_outlier_case("small_outlier", make_oracle)
+    print(rep)
+    assert rep["outliers_a"] > 0 and rep["final_rmse"] < 1e-9
