@@ -41,7 +41,23 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-FP64_DMMA_FMA_PER_CLK_SM = 127.8    # measured on B200: scripts/micro/fp64_lat.cu, >= 16 warps per SM
+FP64_DMMA_FMA_PER_CLK_SM = 127.8    # fallback: measured on B200 in round 1 (profiles/r01b_fp64_microbench.log)
+
+
+def fp64_dmma_rate():
+    """FP64 DMMA m8n8k4 throughput in FMA/clk/SM, measured NOW by scripts/micro/fp64_lat (built by
+    __graft_entry__.build() from scripts/micro/fp64_lat.cu); the best of its thread counts.  Falls back to the
+    round-1 figure when the binary is missing."""
+    exe = os.path.join(ROOT, "scripts", "micro", "fp64_lat")
+    try:
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=60).stdout
+        import re
+        vals = [float(v) for v in re.findall(r"throughput dmma\s+\d+ thr/SM: ([0-9.]+) FMA/clk/SM", out)]
+        if vals:
+            return max(vals), "measured in this run by scripts/micro/fp64_lat (FP64 DMMA m8n8k4, best thread count)"
+    except Exception:
+        pass
+    return FP64_DMMA_FMA_PER_CLK_SM, "round-1 measurement (profiles/r01b_fp64_microbench.log); micro-benchmark binary not available"
 
 
 def ncu_traffic():
@@ -123,11 +139,13 @@ def run_ours(args, rank, world):
         s.initialize(prob)
         shard_prob = prob
     else:
-        # weak scaling: the same poses, `world` times the landmarks and edges of the named shape; landmarks
-        # (with their edges) are sharded over the ranks, one NCCL all-reduce of [Hsc | bsc] per LM trial
+        # weak scaling (default): the same poses, `world` times the landmarks and edges of the named shape;
+        # strong scaling (--scaling strong): the named shape itself.  Landmarks (with their edges) are sharded over
+        # the ranks, one NCCL all-reduce of [Hsc | bsc] per LM trial
         from cugo_b200 import dist as cdist
         P0, L0, E0, S0 = synth.SHAPES[args.workload][:4]
-        g = synth.make_graph(args.workload, n_landmarks=L0 * world, n_edges=E0 * world, n_stereo=S0 * world)
+        mult = world if args.scaling == "weak" else 1
+        g = synth.make_graph(args.workload, n_landmarks=L0 * mult, n_edges=E0 * mult, n_stereo=S0 * mult)
         prob = pack.pack(g)
         ds = cdist.DistBlockSolver(prob, dev)
         s = ds.s
@@ -203,6 +221,53 @@ def run_ours(args, rank, world):
         dist.all_reduce(tb)
         h2d, d2h = int(tb[0].item()), int(tb[1].item())
 
+    # ---- N > 1: (a) parity of the N-GPU answer -- rank 0 solves the SAME graph with a 1-GPU solver outside the
+    # timed region; (b) the other scaling mode of the same shape, timed the same way (device events, max over ranks)
+    parity, other = None, None
+    if world > 1:
+        if rank == 0:
+            s1 = solver.BlockSolver(dev)
+            s1.initialize(prob)
+            chi1, _, tr1 = s1.optimize(args.iters)
+            s.set_estimates(shard_prob.poses, shard_prob.landmarks)
+        else:
+            s.set_estimates(shard_prob.poses, shard_prob.landmarks)
+        chiN, _, trN = s.optimize(args.iters)
+        if rank == 0:
+            n = min(len(chi1), len(chiN))
+            parity = {"chi2_rel_err_vs_1gpu": float(np.max(np.abs(chiN[:n] - chi1[:n]) / chi1[:n])),
+                      "iterations_equal": bool(len(chi1) == len(chiN)),
+                      "trial_counts_equal": bool(len(tr1) == len(trN) and np.array_equal(tr1, trN)),
+                      "chi2_final_1gpu": float(chi1[-1]), "chi2_final_ngpu": float(chiN[-1])}
+            s1.close()
+        barrier()
+        omode = "strong" if args.scaling == "weak" else "weak"
+        omult = world if omode == "weak" else 1
+        g2 = synth.make_graph(args.workload, n_landmarks=L0 * omult, n_edges=E0 * omult, n_stereo=S0 * omult)
+        prob2 = pack.pack(g2)
+        ds2 = cdist.DistBlockSolver(prob2, dev, shard=cdist.shard_problem(prob2, world, rank), share_comm=ds)
+        s2, sp2 = ds2.s, ds2.shard.prob
+        s2.build_structure()
+
+        def step2():
+            s2.set_estimates(sp2.poses, sp2.landmarks)
+            flush.fill_(1.0)
+            torch.cuda.synchronize()
+            c, _, _ = s2.optimize(args.iters)
+            return s2.last_timing()[0], c
+        for _ in range(args.warmup):
+            step2()
+        barrier()
+        t2 = 0.0
+        for _ in range(args.steps):
+            ms, c2o = step2()
+            t2 += ms
+        barrier()
+        tt = torch.tensor([t2], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        other = {"scaling": omode, "value": prob2.n_edges * len(c2o) * args.steps / (float(tt.item()) * 1e-3),
+                 "unit": "edges/s", "ms_per_step": float(tt.item()) / args.steps, "edges": int(prob2.n_edges),
+                 "chi2_final": float(c2o[-1])}
     if rank != 0:
         return
     # ---- roofline of the dominant kernel (one LM trial, event-timed per kernel)
@@ -212,11 +277,11 @@ def run_ours(args, rank, world):
             "metric": "edges/s (LM edge-iterations per second), %s shape, %d LM iterations" % (args.workload, args.iters),
             "value": value, "unit": "edges/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms / args.steps, "ms_per_lm_iteration": dev_ms / args.steps / iters_done,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64",
             "data": "synthetic (seeded generator cugo_b200/synth.py; reference inputs are absent)",
             "config": {"workload": "%s poses with %dx its landmarks/edges: %d poses / %d landmarks / %d edges (%d stereo), "
                                    "%d LM iterations, FP64; landmarks dealt strided (l %% N) to %d GPUs, one NCCL all-reduce of "
-                                   "[Hsc | bsc] per LM trial" % (args.workload, world, g.n_poses, g.n_landmarks, E,
+                                   "[Hsc | bsc] per LM trial" % (args.workload, mult, g.n_poses, g.n_landmarks, E,
                                                                  len(g.stereo_p), args.iters, world),
                        "timing": "CUDA events on the solver stream around optimize(), max over ranks; L2 flushed "
                                  "(256 MB fill) between steps", "sizes_rank0": sizes},
@@ -224,7 +289,12 @@ def run_ours(args, rank, world):
                     "ms_per_step": e2e_s / args.steps * 1e3},
             "gpu_launches": int(launches) * world, "clocks": clk.summary(),
             "roofline": None, "cpu_baseline": None, "chi2_final": float(chi[-1]),
-            "note": "roofline / cpu_baseline are reported by the N=1 line (rank-0-at-N=1 only)"}
+            "value_optimize_only": value,
+            "parity_vs_1gpu": parity, "chi2_rel_err_vs_1gpu": parity["chi2_rel_err_vs_1gpu"] if parity else None,
+            "other_scaling": other,
+            "note": "roofline / cpu_baseline are reported by the N=1 line (rank-0-at-N=1 only); parity_vs_1gpu: the same "
+                    "graph solved by a 1-GPU solver on rank 0 outside the timed region; other_scaling: the %s-scaling "
+                    "run of the same shape in this process group" % (other["scaling"] if other else "-")}
         print(json.dumps(line))
         return
     s.set_estimates(prob.poses, prob.landmarks)
@@ -253,7 +323,8 @@ def run_ours(args, rank, world):
     # the factorisation kernels are FP64 tensor-pipe (DMMA) work: algorithmic flops of the ordering in use
     fs = s.factor_stats()
     clk_mhz = (clk.summary()["sm_mhz"] or 1965.0)
-    fp64_peak = FP64_DMMA_FMA_PER_CLK_SM * 148 * 2 * clk_mhz * 1e6 / 1e12
+    dmma_rate, dmma_src = fp64_dmma_rate()
+    fp64_peak = dmma_rate * 148 * 2 * clk_mhz * 1e6 / 1e12
     for e in stages:
         fl = {"chol_panel": fs["flops_panel"], "chol_update": fs["flops_update"], "chol_bwd": fs["flops_backward"]}.get(e["kernel"])
         if fl:
@@ -265,8 +336,8 @@ def run_ours(args, rank, world):
         roofline = {"kernel": top["kernel"], "bound": "tensor", "achieved": top["achieved_tflops"],
                     "peak": round(fp64_peak, 2), "unit": "TFLOP/s", "frac": top["frac"],
                     "traffic": traffic.get("k_" + top["kernel"]),
-                    "peak_source": "FP64 DMMA m8n8k4: %.1f FMA/clk/SM measured by scripts/micro/fp64_lat.cu "
-                                   "(profiles/r01b_fp64_microbench.log) x 148 SMs x SM clock under load" % FP64_DMMA_FMA_PER_CLK_SM,
+                    "peak_source": "%.1f FMA/clk/SM (%s) x 148 SMs x 2 x SM clock under load (%.0f MHz)" % (
+                        dmma_rate, dmma_src, clk_mhz),
                     "launches": top["launches"],
                     "note": "dominant kernel by time; FP64 tensor pipe (DMMA) of the supernodal Cholesky, summed over "
                             "the %d tree levels: the elimination tree's critical path (latency), not the pipe, bounds "
@@ -291,10 +362,48 @@ def run_ours(args, rank, world):
     else:                       # --cpu-iters 0: exploratory runs of the large shapes only
         cpu_baseline, chi_rel = None, None
 
+    # ---- cold call: a NEW solver on the same host buffers: initialize + build_structure + optimize + read-back
+    t0 = time.perf_counter()
+    sc = solver.BlockSolver(dev, f32=args.f32)
+    sc.initialize(prob)
+    t1 = time.perf_counter()
+    sc.build_structure()
+    t2 = time.perf_counter()
+    sc.optimize(args.iters)
+    sc.estimates(out=(o_poses, o_lms))
+    t3 = time.perf_counter()
+    sc.close()
+    cold = {"ms_total": (t3 - t0) * 1e3, "ms_initialize": (t1 - t0) * 1e3, "ms_build_structure": (t2 - t1) * 1e3,
+            "ms_optimize_and_readback": (t3 - t2) * 1e3,
+            "what": "new solver, host buffers: set_vertices/add_edge_set + build_structure (sorts, symbolic analysis, graph "
+                    "capture) + optimize(%d) + get_estimates, wall clock" % args.iters}
+    # ---- the drop-in claim: initialize() + optimize() through the C++ facade (include/cugo_b200.hpp) from vertex / edge
+    # OBJECTS, as the reference's sample times it (samples/sample_ba_from_file/main.cpp:185-190), after its warm-up run
+    facade = None
+    exe = os.path.join(ROOT, "cuda-bundle-adjustment_b200", "lib", "sample_ba_from_bag")
+    if os.path.exists(exe) and not args.f32:
+        try:
+            from cugo_b200 import graphio
+            with tempfile.TemporaryDirectory() as td:
+                bag = os.path.join(td, "g.bag")
+                graphio.write_graph(g, bag)
+                r = subprocess.run([exe, bag, str(args.iters), "0", "1.0", os.path.join(td, "est.bin"), "1"],
+                                   capture_output=True, text=True, timeout=600)
+                fo = json.loads(r.stdout)
+            fms = fo["ms_initialize"] + fo["ms_optimize"]
+            facade = {"value": E * len(fo["chi2"]) / (fms * 1e-3), "unit": "edges/s", "ms_initialize": fo["ms_initialize"],
+                      "ms_optimize": fo["ms_optimize"], "ms_per_step": fms, "runs": 1,
+                      "what": "samples/sample_ba_from_bag: %d vertex + %d edge objects -> initialize() (re-pack, compare with the "
+                              "last upload, H2D) + optimize(%d) (device LM + write-back into the vertices), wall clock, structure "
+                              "reused after the sample's warm-up run" % (g.n_poses + g.n_landmarks, E, args.iters)}
+        except Exception as ex:
+            facade = {"unavailable": str(ex)[:200]}
+
     line = {
         "metric": "edges/s (LM edge-iterations per second), %s shape, %d LM iterations" % (args.workload, args.iters),
         "value": value, "unit": "edges/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_ms / args.steps, "ms_per_lm_iteration": dev_ms / args.steps / iters_done,
+        "value_optimize_only": value, "e2e_facade": facade, "cold_e2e": cold,
         "higher_is_better": True, "scaling": "weak" if world == 1 else "replicas", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic (seeded generator cugo_b200/synth.py; reference inputs are absent)",
         "config": {"workload": "%s: %d poses / %d landmarks / %d edges (%d stereo), %d LM iterations, %s" % (
@@ -359,7 +468,14 @@ def run_reference(args, rank, world):
                                            len(opt), args.iters)},
             "e2e": {"value": value, "unit": "edges/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "ms_initialize": float(init.mean()), "ms_optimize": float(opt.mean()),
+            "value_optimize_only": E * n_it / (float(opt.mean()) * 1e-3),
+            "cold_e2e": {"ms_total": meta["wall_ms_initialize"][0] + meta["wall_ms_optimize"][0],
+                         "what": "first initialize()+optimize(%d) of the process: structure build, METIS ordering and "
+                                 "symbolic analysis included" % args.iters},
             "chi2_final": meta["chi2"][-1]})
+        if world > 1:
+            base["config"]["note"] = ("the reference is single-GPU: this line is its 1-GPU run of the 1x %s workload whatever "
+                                      "--gpus says; it is NOT the %dx workload of the weak-scaling arm" % (args.workload, world))
     except Exception as ex:   # reference binary missing or failed: time the CPU port instead
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import oracle as orc
@@ -386,6 +502,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=WORKLOAD)
     ap.add_argument("--f32", action="store_true", help="USE_FLOAT32 mode: single-precision Hpl storage (1 GPU)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="N > 1: weak = N x the landmarks/edges of the named shape (default), strong = the named shape itself; "
+                         "the other mode is timed too and reported under other_scaling")
     ap.add_argument("--iters", type=int, default=NITER)
     ap.add_argument("--cpu-iters", type=int, default=10)
     args = ap.parse_args()

@@ -25,6 +25,7 @@
 #include "kernels_lm.cuh"
 #include "kernels_schur.cuh"
 #include "kernels_struct.cuh"
+#include "kernels_sym.cuh"
 #include "symbolic.h"
 
 namespace cugo_b200 {
@@ -136,6 +137,7 @@ struct Solver {
     int nmulRef = 0, nnzSymm = 0, maxRt = 0;
     SymCounts counts{};
     std::vector<int> h_levelPtr, h_trsmPtr, h_updPtr, h_levMaxNt;
+    int h_nchild = 0;              // non-root supernodes
     int cholGen = 3;               // CUGO_B200_CHOL=1|2: earlier generations of the factorisation kernels (A/B timing)
     // buffers
     DBuf<double> pose0, pose1, poseBak, lm0, lm1, lmBak;
@@ -173,6 +175,13 @@ struct Solver {
         z_asmCol, z_trsmPtr, z_updPtr;
     DBuf<long long> z_Lptr, z_Uptr;
     DBuf<SymCounts> y_counts;
+    // parallel symbolic analysis (kernels_sym.cuh)
+    DBuf<int> y_vOf, y_isStart, y_symCnt, y_rcount, y_ak1, y_ak2, y_av1, y_av2;
+    DBuf<int2> y_regA, y_regB;
+    DBuf<int4> y_emits;
+    DBuf<unsigned> y_bits;
+    bool symParallel = true;       // CUGO_B200_SYM=0: the single-thread run of symbolic.h (the twin) on the device
+    void symbolicParallel(const int* gRowOfP, const int* gRowPtrP, const int* gColIndP, int P);
     DBuf<double> cL, cU, cX, cW, cZ, cPart;
     DBuf<int> cCnt;
     DBuf<int> z_levMaxNt;
@@ -456,6 +465,7 @@ void Solver::buildStructure() {
         if (anyOut) up(r_out, out);
         CK(cudaStreamSynchronize(stream));   // host vectors die here
     }
+    lap("raw edge arrays -> device");
     RawEdges raw{(int)E, r_iP, r_iL, r_m0, r_m1, r_m2, r_w, r_set, perEdgeCam ? r_cam.p : nullptr,
                  anyOut ? r_out.p : nullptr};
     const int TB = 256;
@@ -488,6 +498,7 @@ void Solver::buildStructure() {
     chunkLm.alloc(nChunks + 1);
     k_chunk_bounds<<<divUp(nL_all + 1, TB), TB, 0, stream>>>(wexcl, nL_all, nChunks, chunkLm);
 
+    lap("landmark-major order, Hpl CSC, chunks");
     // ---- pose-major copy
     pkeyIn.alloc(E); pkeyOut.alloc(E); pvalIn.alloc(E); p_src.alloc(E);
     k_make_pose_keys<<<gE, TB, 0, stream>>>(s_iP, (int)E, pkeyIn, pvalIn);
@@ -509,6 +520,7 @@ void Solver::buildStructure() {
     k_pose_units_fill<<<divUp(std::max(nP, 1), TB), TB, 0, stream>>>(poseSlicePtr, nP, poseUnits);
     CK(cudaMemsetAsync(poseTicket.p, 0, sizeof(int) * std::max(nP, 1), stream));
 
+    lap("pose-major order, slices");
     // ---- Hsc block pattern + product lists
     prodCnt.alloc(nL + 1); prodOff.alloc(nL + 1);
     k_prod_counts<<<divUp(nL + 1, TB), TB, 0, stream>>>(colPtr, nL, prodCnt);
@@ -531,6 +543,7 @@ void Solver::buildStructure() {
     k_lower_bounds<<<divUp(nP + 1, TB), TB, 0, stream>>>(bRowOf, nblk, nP, bRowPtr);
     nnzSymm = (2 * nblk - nP) * 36;
 
+    lap("Hsc pattern, product lists");
     // ---- pose-major view of the Hpl blocks + product ranks (k_schur_rows)
     pmFlag.alloc(E + 1); pmPre.alloc(E + 1); poseSlotPtr.alloc(nP + 1); poseSlots.alloc(std::max(nHpl, 1));
     slotRank.alloc(std::max(nHpl, 1)); prodRank.alloc(nmulAll); poseDeg.alloc(nP + 1);
@@ -609,9 +622,32 @@ void Solver::buildStructure() {
         redA.alloc((size_t)6 * nP + nranks); redC.alloc(2);
     }
 
-    lap("edge sorts, Hpl, Hsc, products");
-    // ---- symbolic factorisation (one device thread runs symbolic.h)
+    lap("pose-major Hpl view, row units");
+    {
+        const char* g = getenv("CUGO_B200_CHOL");
+        cholGen = (g && (g[0] == '1' || g[0] == '2')) ? g[0] - '0' : 3;
+        const char* p = getenv("CUGO_B200_PDL");
+        pdl = !(p && p[0] == '0');
+        const char* dc = getenv("CUGO_B200_PANELDC");
+        panelDC = !(dc && dc[0] == '0');
+        const char* bs = getenv("CUGO_B200_BWDSPLIT");
+        bwdSplit = !(bs && bs[0] == '0');
+        const char* zi = getenv("CUGO_B200_ZINV");
+        zinvOn = !(zi && zi[0] == '0');
+        const char* fb = getenv("CUGO_B200_FUSEBUILD");
+        fuseBuild = !(fb && fb[0] == '0');
+        const char* sy = getenv("CUGO_B200_SYM");
+        symParallel = !(sy && sy[0] == '0') && cholGen != 1;
+    }
+    // ---- symbolic factorisation
     const int P = nP;
+    int nsn = 0;
+    if (symParallel) {
+        symbolicParallel(nranks > 1 ? gRowOf.p : bRowOf.p, gRowPtrP, gColIndP, P);
+        nsn = counts.nsn;
+        lap("symbolic analysis + maps (parallel)");
+    } else {
+    // the sequential statement of the algorithm (symbolic.h) run by one device thread
     y_adjPtr.alloc(P + 1); y_adj.alloc(2 * (size_t)nblkG + 1); y_verts.alloc(P); y_iperm.alloc(P); y_mark.alloc(P);
     y_level.alloc(P); y_queue.alloc(P); y_tmp.alloc(P + 1); y_stack.alloc(4 * (size_t)P + 8); y_snStart.alloc(P + 1);
     y_snParent.alloc(P); y_colToSn.alloc(P); y_snRowPtr.alloc(P + 1); y_snLevel.alloc(P); y_childHead.alloc(P);
@@ -635,7 +671,7 @@ void Solver::buildStructure() {
     CK(cudaStreamSynchronize(stream));
     lap("symbolic analysis");
     if (counts.err) throw CudaError("symbolic analysis overflowed its row-structure workspace");
-    const int nsn = counts.nsn;
+    nsn = counts.nsn;
     z_levelPtr.alloc(counts.nlev + 1); z_levelSn.alloc(nsn); z_Lptr.alloc(nsn + 1); z_Uptr.alloc(nsn + 1);
     z_childPtr.alloc(nsn + 1); z_childIdx.alloc(nsn + 1); z_invPtr.alloc(nsn); z_inv.alloc((size_t)counts.ninv + 1);
     z_snBlkPtr.alloc(nsn + 1); z_asmBlk.alloc(nblkG); z_asmRow.alloc(nblkG); z_asmCol.alloc(nblkG);
@@ -644,30 +680,18 @@ void Solver::buildStructure() {
     m.levelPtr = z_levelPtr; m.levelSn = z_levelSn; m.Lptr = z_Lptr; m.Uptr = z_Uptr; m.childPtr = z_childPtr;
     m.childIdx = z_childIdx; m.invPtr = z_invPtr; m.inv = z_inv; m.snBlkPtr = z_snBlkPtr; m.asmBlk = z_asmBlk;
     m.asmRow = z_asmRow; m.asmCol = z_asmCol;
-    {
-        const char* g = getenv("CUGO_B200_CHOL");
-        cholGen = (g && (g[0] == '1' || g[0] == '2')) ? g[0] - '0' : 3;
-        const char* p = getenv("CUGO_B200_PDL");
-        pdl = !(p && p[0] == '0');
-        const char* dc = getenv("CUGO_B200_PANELDC");
-        panelDC = !(dc && dc[0] == '0');
-        const char* bs = getenv("CUGO_B200_BWDSPLIT");
-        bwdSplit = !(bs && bs[0] == '0');
-        const char* zi = getenv("CUGO_B200_ZINV");
-        zinvOn = !(zi && zi[0] == '0');
-        const char* fb = getenv("CUGO_B200_FUSEBUILD");
-        fuseBuild = !(fb && fb[0] == '0');
-    }
     z_levMaxNt.alloc(counts.nlev + 1);
     k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, CHOL_RS, CHOL_TS, cholGen == 1 ? 0 : CHOL_RB, CHOL_TB,
                                     z_levMaxNt, z_factStats.alloc(4));
-    CK(cudaMemcpyAsync(factStats, z_factStats.p, sizeof(factStats), cudaMemcpyDeviceToHost, stream));
     lap("symbolic maps + task tables");
+    }
+    CK(cudaMemcpyAsync(factStats, z_factStats.p, sizeof(factStats), cudaMemcpyDeviceToHost, stream));
     h_levelPtr.resize(counts.nlev + 1); h_trsmPtr.resize(nsn + 1); h_updPtr.resize(nsn + 1); h_levMaxNt.resize(counts.nlev + 1);
     CK(cudaMemcpyAsync(h_levMaxNt.data(), z_levMaxNt.p, sizeof(int) * counts.nlev, cudaMemcpyDeviceToHost, stream));
     CK(cudaMemcpyAsync(h_levelPtr.data(), z_levelPtr.p, sizeof(int) * (counts.nlev + 1), cudaMemcpyDeviceToHost, stream));
     CK(cudaMemcpyAsync(h_trsmPtr.data(), z_trsmPtr.p, sizeof(int) * (nsn + 1), cudaMemcpyDeviceToHost, stream));
     CK(cudaMemcpyAsync(h_updPtr.data(), z_updPtr.p, sizeof(int) * (nsn + 1), cudaMemcpyDeviceToHost, stream));
+    CK(cudaMemcpyAsync(&h_nchild, z_childPtr.p + nsn, sizeof(int), cudaMemcpyDeviceToHost, stream));
     CK(cudaStreamSynchronize(stream));
     if (getenv("CUGO_B200_DEBUG")) {
         fprintf(stderr, "[cugo_b200] elimination tree: %d supernodes, %d levels, max front %d block rows; per level "
@@ -759,6 +783,81 @@ void Solver::buildStructure() {
     captureSlot();
     structDirty = false;            // only once the trial graph exists
     lap("graph capture");
+}
+
+// Symbolic analysis as parallel device work (kernels_sym.cuh); the arrays are those of symbolic.h, bit for bit.
+void Solver::symbolicParallel(const int* gRowOfP, const int* gRowPtrP, const int* gColIndP, int P) {
+    (void)gRowPtrP;
+    const int TB = 256;
+    const int nadj = 2 * (nblkG - P);
+    y_adjPtr.alloc(P + 1); y_adj.alloc((size_t)std::max(nadj, 1)); y_vOf.alloc((size_t)std::max(nadj, 1));
+    y_verts.alloc(P); y_iperm.alloc(P); y_mark.alloc(P); y_level.alloc(P); y_queue.alloc(P); y_tmp.alloc(P + 1);
+    y_isStart.alloc(P); y_snStart.alloc(P + 1); y_colToSn.alloc(P); y_snParent.alloc(P); y_snLevel.alloc(P);
+    y_childHead.alloc(P); y_childNext.alloc(P); y_rcount.alloc(P); y_snRowPtr.alloc(P + 1); y_counts.alloc(1);
+    y_regA.alloc(P); y_regB.alloc(P); y_emits.alloc(P); y_symCnt.alloc(4);
+    // adjacency: sorted neighbour lists of the symmetric block graph
+    if (nadj > 0) {
+        keyA.alloc((size_t)nadj); keyB.alloc((size_t)nadj);
+        k_sym_pairs<<<divUp(nblkG, TB), TB, 0, stream>>>(gRowOfP, gColIndP, nblkG, (unsigned long long)P, keyA);
+        size_t bytes = 0;
+        const int bits = bitsFor((unsigned long long)P * (unsigned long long)P);
+        CK(cub::DeviceRadixSort::SortKeys(nullptr, bytes, keyA.p, keyB.p, nadj, 0, bits, stream));
+        cubTmp.alloc(bytes);
+        CK(cub::DeviceRadixSort::SortKeys(cubTmp.p, bytes, keyA.p, keyB.p, nadj, 0, bits, stream));
+        k_sym_adj<<<divUp(nadj, TB), TB, 0, stream>>>(keyB, nadj, (unsigned long long)P, y_adj, y_vOf);
+    }
+    k_lower_bounds<<<divUp(P + 1, TB), TB, 0, stream>>>(y_vOf, nadj, P, y_adjPtr);
+    // nested dissection, supernode column ranges
+    SymPar sp2{};
+    sp2.P = P; sp2.leaf = CHOL_MAXW; sp2.maxw = CHOL_MAXW; sp2.nadj = nadj;
+    sp2.adjPtr = y_adjPtr; sp2.adj = y_adj; sp2.verts = y_verts; sp2.iperm = y_iperm; sp2.isStart = y_isStart;
+    sp2.snStart = y_snStart; sp2.colToSn = y_colToSn; sp2.mark = y_mark; sp2.level = y_level; sp2.queue = y_queue; sp2.tmp = y_tmp;
+    sp2.regA = y_regA; sp2.regB = y_regB; sp2.emits = y_emits; sp2.counters = y_symCnt;
+    const size_t ndBytes = ((size_t)nadj + 6 * (size_t)P + 2) * sizeof(int);
+    sp2.useSmem = ndBytes <= 200 * 1024 ? 1 : 0;
+    if (sp2.useSmem) CK(cudaFuncSetAttribute(k_sym_nd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ndBytes));
+    k_sym_nd<<<1, SYM_TPB, sp2.useSmem ? ndBytes : 0, stream>>>(sp2);
+    int hc[4] = {0, 0, 0, 0};
+    CK(cudaMemcpyAsync(hc, y_symCnt.p, 3 * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    CK(cudaGetLastError());
+    const int nsn = hc[1];
+    // row structures (a bitmap per supernode), parents, levels, sizes
+    const int W = (P + 31) / 32;
+    y_bits.alloc((size_t)nsn * W);
+    CK(cudaMemsetAsync(y_bits.p, 0, (size_t)nsn * W * sizeof(unsigned), stream));
+    SymRowsPar rp{};
+    rp.P = P; rp.maxw = CHOL_MAXW; rp.W = W; rp.adjPtr = y_adjPtr; rp.adj = y_adj; rp.verts = y_verts; rp.iperm = y_iperm;
+    rp.snStart = y_snStart; rp.colToSn = y_colToSn; rp.emits = y_emits; rp.counters = y_symCnt; rp.bits = y_bits;
+    rp.snParent = y_snParent; rp.snLevel = y_snLevel; rp.childHead = y_childHead; rp.childNext = y_childNext;
+    rp.rcount = y_rcount; rp.snRowPtr = y_snRowPtr; rp.out = y_counts;
+    k_sym_rows<<<1, SYM_TPB, 0, stream>>>(rp);
+    CK(cudaMemcpyAsync(&counts, y_counts.p, sizeof(SymCounts), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    CK(cudaGetLastError());
+    y_snRows.alloc((size_t)std::max(counts.nrows, 1));
+    k_sym_extract<<<divUp((long long)nsn * 32, TB), TB, 0, stream>>>(y_bits, W, nsn, y_snRowPtr, y_snRows);
+    // schedule, offsets, children, task tables; inverse maps; assembly lists
+    z_levelPtr.alloc(counts.nlev + 1); z_levelSn.alloc(nsn); z_Lptr.alloc(nsn + 1); z_Uptr.alloc(nsn + 1);
+    z_childPtr.alloc(nsn + 1); z_childIdx.alloc(nsn + 1); z_invPtr.alloc(nsn); z_inv.alloc((size_t)counts.ninv + 1);
+    z_snBlkPtr.alloc(nsn + 1); z_asmBlk.alloc(nblkG); z_asmRow.alloc(nblkG); z_asmCol.alloc(nblkG);
+    z_trsmPtr.alloc(nsn + 1); z_updPtr.alloc(nsn + 1); z_levMaxNt.alloc(counts.nlev + 1);
+    SymMaps m{};
+    m.levelPtr = z_levelPtr; m.levelSn = z_levelSn; m.Lptr = z_Lptr; m.Uptr = z_Uptr; m.childPtr = z_childPtr;
+    m.childIdx = z_childIdx; m.invPtr = z_invPtr; m.inv = z_inv; m.snBlkPtr = z_snBlkPtr; m.asmBlk = z_asmBlk;
+    m.asmRow = z_asmRow; m.asmCol = z_asmCol;
+    const size_t tabBytes = (5 * (size_t)nsn + counts.nlev + 2) * sizeof(int);
+    if (tabBytes > 200 * 1024) throw UnsupportedError("too many supernodes for the shared-memory schedule tables of this version");
+    CK(cudaFuncSetAttribute(k_sym_tables, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tabBytes));
+    k_sym_tables<<<1, SYM_TPB, tabBytes, stream>>>(nsn, counts.nlev, y_snStart, y_snRowPtr, y_snParent, y_snLevel, m, z_trsmPtr,
+                                                   z_updPtr, CHOL_RB, CHOL_TB, z_levMaxNt, z_factStats.alloc(4), counts.lsize);
+    k_sym_inv<<<divUp((long long)nsn * 32, TB), TB, 0, stream>>>(nsn, y_snStart, y_snRowPtr, y_snRows, y_snParent, z_invPtr, z_inv);
+    y_ak1.alloc(nblkG); y_ak2.alloc(nblkG); y_av1.alloc(nblkG); y_av2.alloc(nblkG);
+    k_sym_asm_keys<<<divUp(nblkG, TB), TB, 0, stream>>>(gRowOfP, gColIndP, nblkG, y_iperm, y_colToSn, y_ak1, y_av1);
+    sortPairs(*this, y_ak1.p, y_ak2.p, y_av1.p, y_av2.p, nblkG, bitsFor((unsigned long long)std::max(nsn, 1)));
+    k_lower_bounds<<<divUp(nsn + 1, TB), TB, 0, stream>>>(y_ak2, nblkG, nsn, z_snBlkPtr);
+    k_sym_asm_fill<<<divUp(nblkG, TB), TB, 0, stream>>>(y_ak2, y_av2, nblkG, gRowOfP, gColIndP, y_iperm, y_snStart, y_snRowPtr,
+                                                       y_snRows, z_asmBlk, z_asmRow, z_asmCol);
 }
 
 // ---------------------------------------------------------------------------
@@ -1414,6 +1513,17 @@ long Solver::getStructure(int which, int* out, long cap) {
     case CUGO_B200_HSC_COLIND: return copyOut(bColInd, d.nblk);
     case CUGO_B200_EDGE2HPL: return copyOut(edge2Hpl, E);
     case CUGO_B200_PERM: return copyOut(y_verts, nP);
+    case CUGO_B200_SN_START: return copyOut(y_snStart, counts.nsn + 1);
+    case CUGO_B200_SN_ROWPTR: return copyOut(y_snRowPtr, counts.nsn + 1);
+    case CUGO_B200_SN_ROWS: return copyOut(y_snRows, counts.nrows);
+    case CUGO_B200_SN_PARENT: return copyOut(y_snParent, counts.nsn);
+    case CUGO_B200_SN_LEVEL: return copyOut(y_snLevel, counts.nsn);
+    case CUGO_B200_LEVEL_SN: return copyOut(z_levelSn, counts.nsn);
+    case CUGO_B200_CHILD_IDX: return copyOut(z_childIdx, h_nchild);
+    case CUGO_B200_INV_MAP: return copyOut(z_inv, counts.ninv);
+    case CUGO_B200_ASM_BLK: return copyOut(z_asmBlk, nblkG);
+    case CUGO_B200_ASM_ROW: return copyOut(z_asmRow, nblkG);
+    case CUGO_B200_ASM_COL: return copyOut(z_asmCol, nblkG);
     case CUGO_B200_CSR_ROWPTR:
     case CUGO_B200_CSR_COLIND:
     case CUGO_B200_BSR2CSR: {

@@ -101,7 +101,10 @@ class DistBlockSolver:
     """BlockSolver over `world` GPUs of one node.  Every rank constructs it with the SAME packed problem
     (or with its own shard through `from_shard`); `optimize` runs the device-resident LM loop on all ranks."""
 
-    def __init__(self, prob: Problem, device: int, group=None, robust="none", delta=1.0, shard: Shard | None = None):
+    def __init__(self, prob: Problem, device: int, group=None, robust="none", delta=1.0, shard: Shard | None = None,
+                 share_comm=None):
+        # share_comm is accepted for call-site clarity only: every solver owns its own NCCL communicator (one per
+        # engine stream), created below from a fresh unique id
         import torch
         import torch.distributed as dist
         from . import solver

@@ -20,7 +20,8 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libcugo_b200.so")
 
 RK = dict(none=0, cauchy=1, tukey=2, huber=3)
 STRUCT = dict(hpl_colptr=0, hpl_rowind=1, hsc_rowptr=2, hsc_colind=3, csr_rowptr=4, csr_colind=5,
-              bsr2csr=6, mulids=7, edge2hpl=8, perm=9)
+              bsr2csr=6, mulids=7, edge2hpl=8, perm=9, sn_start=10, sn_rowptr=11, sn_rows=12, sn_parent=13, sn_level=14,
+              level_sn=15, child_idx=16, inv_map=17, asm_blk=18, asm_row=19, asm_col=20)
 VALUES = dict(Hpp=0, Hll=1, Hpl=2, b=3, x=4, bsc=5, Hsc=6, invHll=7, chi_per_edge=8)
 SIZES = ("P", "L", "E", "nHpl", "nblk", "nmul", "nnzSymm", "nsupernodes", "nlevels", "kernels_per_trial")
 

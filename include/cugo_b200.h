@@ -53,7 +53,18 @@ enum {
     CUGO_B200_BSR2CSR = 6,    /* [nnzSymm] Hsc_.BSR2CSR() */
     CUGO_B200_MULIDS = 7,     /* [3 nmul] d_HscMulBlockIds_, sorted by (i,j)  cuda_block_solver.cu:1606-1634 */
     CUGO_B200_EDGE2HPL = 8,   /* [E] d_edge2Hpl_ in input edge order (-1: no block) */
-    CUGO_B200_PERM = 9        /* [P] fill-reducing block ordering, new -> old (ours; the reference's is METIS) */
+    CUGO_B200_PERM = 9,       /* [P] fill-reducing block ordering, new -> old (ours; the reference's is METIS) */
+    /* the rest of the symbolic analysis (no reference counterpart that is visible: it lives inside cuSOLVER's
+     * csrcholInfo_t, src/cholesky.hpp:94-101); compared bit for bit with the host run of csrc/symbolic.h */
+    CUGO_B200_SN_START = 10,  /* [nsn+1] first permuted column of every supernode */
+    CUGO_B200_SN_ROWPTR = 11, /* [nsn+1] */
+    CUGO_B200_SN_ROWS = 12,   /* [nrows] row structure (permuted block rows below the supernode), ascending */
+    CUGO_B200_SN_PARENT = 13, /* [nsn] assembly tree */
+    CUGO_B200_SN_LEVEL = 14,  /* [nsn] */
+    CUGO_B200_LEVEL_SN = 15,  /* [nsn] supernodes grouped by level (the launch schedule) */
+    CUGO_B200_CHILD_IDX = 16, /* [non-roots] children grouped by parent, ascending */
+    CUGO_B200_INV_MAP = 17,   /* [ninv] inverse relative indices child -> parent front */
+    CUGO_B200_ASM_BLK = 18, CUGO_B200_ASM_ROW = 19, CUGO_B200_ASM_COL = 20   /* [nblk] Hsc block -> front scatter */
 };
 
 /* value arrays readable through cugo_b200_get_values (double) */

@@ -177,3 +177,25 @@ extern "C" int cugo_sym_test(int P, const int* bRowPtr, const int* bColInd, int 
     memcpy(perm_out, A.verts.data(), sizeof(int) * P);
     return mf_solve(A, Hsc, rhs, x);
 }
+
+// The host twin of the device symbolic analysis: every array of symbolic.h for a given pattern, flattened into
+// `out` as [count, values...] records in the order
+//   verts snStart snRowPtr snRows snParent snLevel levelSn childIdx inv asmBlk asmRow asmCol
+// Returns the number of ints written (or -1 if `cap` is too small / the analysis failed).
+extern "C" long cugo_sym_twin(int P, const int* bRowPtr, const int* bColInd, int leaf, int maxw, int* out, long cap) {
+    Analysis A;
+    analyze(A, P, bRowPtr, bColInd, leaf, maxw);
+    if (A.c.err) return -1;
+    const int nsn = A.c.nsn, nblk = A.nblk;
+    const int nchild = A.childPtr[nsn];
+    long o = 0;
+    auto put = [&](const int* p, long n) {
+        if (o + 1 + n > cap) { o = cap + 1; return; }
+        out[o++] = (int)n;
+        for (long i = 0; i < n; i++) out[o++] = p[i];
+    };
+    put(A.verts.data(), P); put(A.snStart.data(), nsn + 1); put(A.snRowPtr.data(), nsn + 1); put(A.snRows.data(), A.c.nrows);
+    put(A.snParent.data(), nsn); put(A.snLevel.data(), nsn); put(A.levelSn.data(), nsn); put(A.childIdx.data(), nchild);
+    put(A.inv.data(), A.c.ninv); put(A.asmBlk.data(), nblk); put(A.asmRow.data(), nblk); put(A.asmCol.data(), nblk);
+    return o > cap ? -1 : o;
+}

@@ -205,7 +205,7 @@ def test_full_size_properties(graphs, gpu):
     np.testing.assert_allclose(chi_g, chi_o, rtol=CHI2_RTOL)
 
 
-SWITCHES = ["CUGO_B200_PDL", "CUGO_B200_FUSEBUILD", "CUGO_B200_PANELDC", "CUGO_B200_ZINV", "CUGO_B200_BWDSPLIT"]
+SWITCHES = ["CUGO_B200_PDL", "CUGO_B200_FUSEBUILD", "CUGO_B200_PANELDC", "CUGO_B200_ZINV", "CUGO_B200_BWDSPLIT", "CUGO_B200_SYM"]
 
 
 @pytest.mark.parametrize("name", ["loop", "kitti07"])
@@ -451,3 +451,43 @@ def test_outlier_gating_keeps_structure_and_matches_oracle(graphs, gpu, name, th
     assert s.compute_errors() == pytest.approx(F, rel=1e-12)
     for i in range(len(prob.sets)):
         np.testing.assert_array_equal(s.outliers(i)[0], o.outliers(i)[0])
+
+
+SYM_ARRAYS = ("perm", "sn_start", "sn_rowptr", "sn_rows", "sn_parent", "sn_level", "level_sn", "child_idx", "inv_map",
+              "asm_blk", "asm_row", "asm_col")
+
+
+@pytest.mark.parametrize("name,kw", [("tiny", {}), ("small", {}), ("loop", {}), ("kitti07", {}), ("kitti00", {}),
+                                     ("small", dict(fixed_landmark_frac=0.15, seed=21))])
+def test_device_symbolic_analysis_equals_host_twin(graphs, name, kw):
+    """Row a10: the parallel device analysis (kernels_sym.cuh: ordering, supernodes, row structures, assembly tree, level
+    schedule, inverse maps, assembly lists) against the HOST run of the sequential statement of the same algorithm
+    (csrc/symbolic.h through tests/csrc/mf_host_test.cpp): every array bit for bit."""
+    import ctypes as C
+    import os
+    import subprocess
+    from cugo_b200 import solver
+    here = os.path.dirname(os.path.abspath(__file__))
+    src, out = os.path.join(here, "csrc", "mf_host_test.cpp"), os.path.join(here, "csrc", "libmf_host_test.so")
+    hdr = os.path.join(here, "..", "cuda-bundle-adjustment_b200", "csrc", "symbolic.h")
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", out, src])
+    twin = C.CDLL(out)
+    twin.cugo_sym_twin.restype = C.c_long
+    g, prob = graphs(name, **kw)
+    s = solver.BlockSolver(0)
+    s.initialize(prob)
+    s.build_structure()
+    rp, ci = s.structure("hsc_rowptr"), s.structure("hsc_colind")
+    P = prob.nP_act
+    cap = 64 * 1024 * 1024
+    buf = np.zeros(cap, np.int32)
+    n = twin.cugo_sym_twin(P, rp.ctypes.data_as(C.POINTER(C.c_int)), ci.ctypes.data_as(C.POINTER(C.c_int)), 16, 16,
+                           buf.ctypes.data_as(C.POINTER(C.c_int)), C.c_long(cap))
+    assert n > 0
+    o = 0
+    for key in SYM_ARRAYS:
+        cnt = int(buf[o]); ref = buf[o + 1:o + 1 + cnt]; o += 1 + cnt
+        np.testing.assert_array_equal(s.structure(key), ref, err_msg=key)
+    assert o == n
+    s.close()
