@@ -53,6 +53,24 @@ struct UnsupportedError : std::runtime_error {
 
 static inline int divUp(long long a, int b) { return (int)((a + b - 1) / b); }
 
+// interleaved measurements [n x dim] / informations of one edge set -> the raw SoA arrays
+__global__ void k_scatter_meas(const double* meas, const double* omega, int n, int dim, int nomega, double* m0,
+                               double* m1, double* m2, double* w) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    m0[i] = meas[(size_t)i * dim]; m1[i] = meas[(size_t)i * dim + 1];
+    m2[i] = dim == 3 ? meas[(size_t)i * 3 + 2] : 0.0;
+    w[i] = nomega > 1 ? omega[i] : omega[0];
+}
+__global__ void k_fill_index(int* a, int n, int base, int step) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) a[i] = base + step * i;
+}
+__global__ void k_int_to_flag(const int* in, int n, uint8_t* out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[i] ? 1 : 0;
+}
+
 // NCCL is bound at run time (dlopen) the first time a communicator is asked for: a single-GPU process
 // never loads it, and inside a torch.distributed process the already-loaded libnccl.so.2 is reused.
 struct NcclApi {
@@ -88,17 +106,23 @@ static NcclApi g_nccl;
             throw ::cugo_b200::CudaError(std::string(#call) + ": " + g_nccl.GetErrorString(r_));   \
     } while (0)
 
-// grow-only device buffer
+// Grow-only device buffer.  Allocations are stream-ordered on the stream of the solver in use (Solver::use() sets
+// t_allocStream) out of the device's default memory pool, whose release threshold cugo_b200_create raises: the ~100
+// buffers of a structure build then cost microseconds each, and a solver created after another one was destroyed reuses
+// its memory (a cold build_structure used to spend a third of its time in cudaMalloc).
+static thread_local cudaStream_t t_allocStream = nullptr;
 template <typename T>
 struct DBuf {
     T* p = nullptr;
     size_t cap = 0;
-    ~DBuf() { if (p) cudaFree(p); }
+    ~DBuf() { if (p) cudaFree(p); }          // synchronising free: also valid for stream-ordered allocations
     T* alloc(size_t n) {
         if (n > cap) {
-            if (p) cudaFree(p);
+            if (p) { if (t_allocStream) CK(cudaFreeAsync(p, t_allocStream)); else CK(cudaFree(p)); }
             p = nullptr;
-            CK(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
+            cap = 0;
+            const size_t bytes = std::max<size_t>(n, 1) * sizeof(T);
+            if (t_allocStream) CK(cudaMallocAsync(&p, bytes, t_allocStream)); else CK(cudaMalloc(&p, bytes));
             cap = std::max<size_t>(n, 1);
         }
         return p;
@@ -259,7 +283,7 @@ struct Solver {
         if (stream) cudaStreamDestroy(stream);
     }
 
-    void use() { CK(cudaSetDevice(device)); }
+    void use() { CK(cudaSetDevice(device)); t_allocStream = stream; }
     void uploadPoses(const double* poses7);
     void setVertices(int nPa, int nPact, const double* poses7, int nLa, int nLact, const double* lms);
     void setEstimates(const double* poses7, const double* lms);
@@ -428,42 +452,44 @@ void Solver::buildStructure() {
     if (slotExec) { cudaGraphExecDestroy(slotExec); slotExec = nullptr; }
     if (slotGraph) { cudaGraphDestroy(slotGraph); slotGraph = nullptr; }
 
-    // ---- raw edge arrays (input order) -> device
+    // ---- raw edge arrays (input order) -> device.  The sets' arrays go up as the caller gave them (indices straight
+    // into place, interleaved measurements through a staging buffer) and are split into the SoA arrays on the device.
     {
-        std::vector<int> iP(E), iL(E), cam;
-        std::vector<double> m0(E), m1(E), m2(E), w(E), camTab;
-        std::vector<uint8_t> set(E), out;
-        if (perEdgeCam) { cam.resize(E); camTab.resize(sets.size() * 5); }
-        if (anyOut) out.assign(E, 0);
-        size_t o = 0;
+        r_iP.alloc(E); r_iL.alloc(E); r_m0.alloc(E); r_m1.alloc(E); r_m2.alloc(E); r_w.alloc(E); r_set.alloc(E);
+        size_t nMeas = 0, nOm = 0, nCamRows = sets.size();
+        for (auto& s : sets) { nMeas += (size_t)s.n * s.dim; nOm += s.nomega; if (s.ncam > 1) nCamRows += s.n; }
+        u_meas.alloc(std::max<size_t>(nMeas, 1)); u_w.alloc(std::max<size_t>(nOm, 1));
+        if (perEdgeCam) { r_cam.alloc(E); cams.alloc(nCamRows * 5); }
+        if (anyOut) { r_out.alloc(E); CK(cudaMemsetAsync(r_out.p, 0, E, stream)); }
+        size_t o = 0, om = 0, oo = 0, camRow = sets.size();
         for (size_t si = 0; si < sets.size(); si++) {
             const HostSet& s = sets[si];
-            if (perEdgeCam) for (int k = 0; k < 5; k++) camTab[si * 5 + k] = s.cam[k];
-            for (int i = 0; i < s.n; i++, o++) {
-                iP[o] = s.iP[i]; iL[o] = s.iL[i];
-                m0[o] = s.meas[(size_t)i * s.dim]; m1[o] = s.meas[(size_t)i * s.dim + 1];
-                m2[o] = s.dim == 3 ? s.meas[(size_t)i * 3 + 2] : 0.0;
-                w[o] = s.nomega > 1 ? s.omega[i] : s.omega[0];
-                set[o] = (uint8_t)si;
-                if (perEdgeCam) {
-                    if (s.ncam > 1) {
-                        cam[o] = (int)(camTab.size() / 5);
-                        camTab.insert(camTab.end(), s.cam.begin() + (size_t)i * 5, s.cam.begin() + (size_t)i * 5 + 5);
-                    } else {
-                        cam[o] = (int)si;
-                    }
+            if (perEdgeCam) CK(cudaMemcpyAsync(cams.p + si * 5, s.cam.data(), 5 * sizeof(double), cudaMemcpyHostToDevice, stream));
+            if (s.n == 0) continue;
+            const int g = divUp(s.n, 256);
+            CK(cudaMemcpyAsync(r_iP.p + o, s.iP.data(), (size_t)s.n * sizeof(int), cudaMemcpyHostToDevice, stream));
+            CK(cudaMemcpyAsync(r_iL.p + o, s.iL.data(), (size_t)s.n * sizeof(int), cudaMemcpyHostToDevice, stream));
+            CK(cudaMemcpyAsync(u_meas.p + om, s.meas.data(), (size_t)s.n * s.dim * sizeof(double), cudaMemcpyHostToDevice, stream));
+            CK(cudaMemcpyAsync(u_w.p + oo, s.omega.data(), (size_t)s.nomega * sizeof(double), cudaMemcpyHostToDevice, stream));
+            k_scatter_meas<<<g, 256, 0, stream>>>(u_meas.p + om, u_w.p + oo, s.n, s.dim, s.nomega, r_m0.p + o, r_m1.p + o,
+                                                  r_m2.p + o, r_w.p + o);
+            CK(cudaMemsetAsync(r_set.p + o, (int)si, s.n, stream));
+            if (perEdgeCam) {
+                if (s.ncam > 1) {
+                    CK(cudaMemcpyAsync(cams.p + camRow * 5, s.cam.data(), (size_t)s.n * 5 * sizeof(double), cudaMemcpyHostToDevice, stream));
+                    k_fill_index<<<g, 256, 0, stream>>>(r_cam.p + o, s.n, (int)camRow, 1);
+                    camRow += s.n;
+                } else {
+                    k_fill_index<<<g, 256, 0, stream>>>(r_cam.p + o, s.n, (int)si, 0);
                 }
-                if (anyOut && !s.out.empty()) out[o] = s.out[i] ? 1 : 0;
             }
+            if (anyOut && !s.out.empty()) {
+                ivalA.alloc(std::max<size_t>(E, 1));
+                CK(cudaMemcpyAsync(ivalA.p, s.out.data(), (size_t)s.n * sizeof(int), cudaMemcpyHostToDevice, stream));
+                k_int_to_flag<<<g, 256, 0, stream>>>(ivalA.p, s.n, r_out.p + o);
+            }
+            o += s.n; om += (size_t)s.n * s.dim; oo += s.nomega;
         }
-        auto up = [&](auto& buf, const auto& h) {
-            buf.alloc(h.size());
-            CK(cudaMemcpyAsync(buf.p, h.data(), h.size() * sizeof(h[0]), cudaMemcpyHostToDevice, stream));
-        };
-        up(r_iP, iP); up(r_iL, iL); up(r_m0, m0); up(r_m1, m1); up(r_m2, m2); up(r_w, w); up(r_set, set);
-        if (perEdgeCam) { up(r_cam, cam); up(cams, camTab); }
-        if (anyOut) up(r_out, out);
-        CK(cudaStreamSynchronize(stream));   // host vectors die here
     }
     lap("raw edge arrays -> device");
     RawEdges raw{(int)E, r_iP, r_iL, r_m0, r_m1, r_m2, r_w, r_set, perEdgeCam ? r_cam.p : nullptr,
@@ -1025,15 +1051,6 @@ int Solver::profileSlot(int cap, char* names, int nameLen, double* ms) {
 // initialize() of the reference re-uploads the whole edge arena but keeps the
 // structure: src/block_solver.cpp:161-170).  H2D into the raw arrays, then the two
 // gather kernels refresh the landmark-major and pose-major copies.
-// interleaved measurements [n x dim] / informations of one edge set -> the raw SoA arrays
-__global__ void k_scatter_meas(const double* meas, const double* omega, int n, int dim, int nomega, double* m0,
-                               double* m1, double* m2, double* w) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    m0[i] = meas[(size_t)i * dim]; m1[i] = meas[(size_t)i * dim + 1];
-    m2[i] = dim == 3 ? meas[(size_t)i * 3 + 2] : 0.0;
-    w[i] = nomega > 1 ? omega[i] : omega[0];
-}
 __global__ void k_gather_meas(const double* m0, const double* m1, const double* m2, const double* w, int n, int dim,
                               double* meas, double* omega) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1660,12 +1677,22 @@ int cugo_b200_create(int device, int use_float32, cugo_b200_solver** out) {
         delete s;
         return CUGO_B200_ECUDA;
     }
+    {   // keep freed buffers in the default pool instead of returning them to the driver at every synchronisation
+        cudaMemPool_t pool = nullptr;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess && pool) {
+            unsigned long long keep = ~0ULL;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        cudaGetLastError();
+    }
     *out = s;
     return CUGO_B200_OK;
 }
 
 int cugo_b200_destroy(cugo_b200_solver* s) {
     if (!s) return CUGO_B200_EINVAL;
+    cudaSetDevice(s->impl.device);
+    cugo_b200::t_allocStream = nullptr;      // the solver's stream dies with it
     delete s;
     return CUGO_B200_OK;
 }
