@@ -295,7 +295,7 @@ def run_ours(args, rank, world):
             "note": "roofline / cpu_baseline are reported by the N=1 line (rank-0-at-N=1 only); parity_vs_1gpu: the same "
                     "graph solved by a 1-GPU solver on rank 0 outside the timed region; other_scaling: the %s-scaling "
                     "run of the same shape in this process group" % (other["scaling"] if other else "-")}
-        print(json.dumps(line))
+        emit(line)
         return
     s.set_estimates(prob.poses, prob.landmarks)
     s.profile_trial()
@@ -424,7 +424,7 @@ def run_ours(args, rank, world):
         "chi2_final": float(chi[-1]), "chi2_rel_err_vs_cpu_oracle": chi_rel,
         "cold_build_structure_ms": cold_structure_ms,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_reference(args, rank, world):
@@ -491,10 +491,25 @@ def run_reference(args, rank, world):
                                       "sample": "%d LM iterations, oracle port (reference binary unavailable: %s)" % (
                                           len(cc), str(ex)[:120])},
                      "e2e": {"value": value, "unit": "edges/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
-    print(json.dumps(base))
+    emit(base)
+
+
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The one JSON line goes to the real stdout (libraries such as NCCL print banners to fd 1 during set-up: while the
+    benchmark runs, fd 1 points at stderr)."""
+    sys.stdout.flush()
+    if _REAL_STDOUT is not None:
+        os.dup2(_REAL_STDOUT, 1)
+    print(json.dumps(line), flush=True)
 
 
 def main():
+    global _REAL_STDOUT
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)

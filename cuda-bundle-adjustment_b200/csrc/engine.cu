@@ -214,7 +214,7 @@ struct Solver {
     ncclComm_t comm = nullptr;
     DBuf<unsigned long long> lkeys, gkeysAll, gkeysSorted, gkeys;
     DBuf<int> gHead, gIdx, gRowOf, gColInd, gRowPtr, hscSlot, d_cnt;
-    DBuf<double> redA, redC;
+    DBuf<double> redA, redC, HscPartBuf;
     int nblkG = 0;
     void commInit(int n, int r, const char* id);
     void allReduceSum(double* buf, size_t n) {
@@ -228,6 +228,17 @@ struct Solver {
     // graph of one trial slot
     cudaGraph_t slotGraph = nullptr;
     cudaGraphExec_t slotExec = nullptr;
+    // several ranks: the FIRST trial of an optimize() also exchanges the diagonal maxima (lambda0 = tau * max diag of the
+    // global system, iteration 0 only); every later trial runs the graph without that collective
+    cudaGraph_t slotGraph0 = nullptr;
+    cudaGraphExec_t slotExec0 = nullptr;
+    bool withA = true;
+    void dropGraphs() {
+        if (slotExec) { cudaGraphExecDestroy(slotExec); slotExec = nullptr; }
+        if (slotGraph) { cudaGraphDestroy(slotGraph); slotGraph = nullptr; }
+        if (slotExec0) { cudaGraphExecDestroy(slotExec0); slotExec0 = nullptr; }
+        if (slotGraph0) { cudaGraphDestroy(slotGraph0); slotGraph0 = nullptr; }
+    }
     int kernelsPerSlot = 0;
     // per-kernel profiling of one trial slot (events on the launching stream)
     bool profiling = false;
@@ -270,8 +281,7 @@ struct Solver {
 
     ~Solver() {
         cudaSetDevice(device);
-        if (slotExec) cudaGraphExecDestroy(slotExec);
-        if (slotGraph) cudaGraphDestroy(slotGraph);
+        dropGraphs();
         if (h_state) cudaFreeHost(h_state);
         if (h_scalars) cudaFreeHost(h_scalars);
         if (ev0) cudaEventDestroy(ev0);
@@ -449,8 +459,7 @@ void Solver::buildStructure() {
     if (E > 0x7fffffff / 18) throw UnsupportedError("edge count exceeds 32-bit block indexing");
     perEdgeCam_ = perEdgeCam; anyOut_ = anyOut;
     refreshSetParams();
-    if (slotExec) { cudaGraphExecDestroy(slotExec); slotExec = nullptr; }
-    if (slotGraph) { cudaGraphDestroy(slotGraph); slotGraph = nullptr; }
+    dropGraphs();
 
     // ---- raw edge arrays (input order) -> device.  The sets' arrays go up as the caller gave them (indices straight
     // into place, interleaved measurements through a staging buffer) and are split into the SoA arrays on the device.
@@ -760,6 +769,13 @@ void Solver::buildStructure() {
     d.poseSlotPtr = poseSlotPtr; d.poseSlots = poseSlots; d.prodRank = prodRank; d.poseLm = poseLm; d.rowUnits = rowUnits;
     d.Hpp = Hpp; d.Hll = Hll; d.Hpl = f32 ? nullptr : Hpl.p; d.HplF = f32 ? HplF.p : nullptr; d.b = b; d.x = x; d.invHll = invHll; d.Hsc = Hsc;
     d.bsc = Hsc.p + (size_t)nblkG * 36;
+    d.HscPart = d.Hsc; d.bscPart = d.bsc;
+    if (nranks > 1) {       // partial system of this rank: zeroed once, the blocks it does not own are never written
+        const size_t nred = (size_t)nblkG * 36 + (size_t)nP * 6;
+        HscPartBuf.alloc(nred);
+        CK(cudaMemsetAsync(HscPartBuf.p, 0, nred * sizeof(double), stream));
+        d.HscPart = HscPartBuf.p; d.bscPart = HscPartBuf.p + (size_t)nblkG * 36;
+    }
     d.nranks = nranks; d.rank = rank; d.nblkG = nblkG; d.hscSlot = nranks > 1 ? hscSlot.p : nullptr;
     d.redA = nranks > 1 ? redA.p : nullptr; d.redC = nranks > 1 ? redC.p : nullptr;
     d.chiPartial = chiPartial; d.scalePartial = scalePartial; d.maxDiagL = maxDiagL; d.maxDiagP = maxDiagP;
@@ -901,7 +917,7 @@ void Solver::enqueueBuild() {
         mark("build_lm");
         launch(k_build_pose<128>, d.nPoseUnits, 128, 0, d, sp); mark("build_pose");
     }
-    if (nranks > 1) {   // max diagonal of the *global* system for lambda0
+    if (nranks > 1 && withA) {   // max diagonal of the *global* system for lambda0
         launch(k_pack_A<256>, std::min(divUp(6 * d.nP, 256), 148), 256, 0, d); mark("pack_A");
         allReduceSum(d.redA, (size_t)6 * d.nP + nranks);
     }
@@ -911,7 +927,6 @@ void Solver::enqueueBuild() {
 // down) -> back-substitution (+ landmark part of the update)
 void Solver::enqueueSolve() {
     launch(k_schur_inv<256>, divUp(d.nL, 256), 256, 0, d); mark("schur_inv");
-    if (nranks > 1) CK(cudaMemsetAsync(d.Hsc, 0, ((size_t)d.nblkG * 36 + (size_t)d.nP * 6) * sizeof(double), stream));
     const int2* bp = schurPasses > 1 ? blkPass.p : nullptr;
     if (schurRows) {
         if (f32) launch(k_schur_rows<float>, nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), d, schurCap, c.dbg, schurUnit, schurPasses, bp);
@@ -922,7 +937,8 @@ void Solver::enqueueSolve() {
     }
     mark(schurRows ? "schur_rows" : "schur_blocks");
     // the one exchange step of a trial: partial reduced camera systems [Hsc | bsc] summed over the ranks
-    if (nranks > 1) allReduceSum(d.Hsc, (size_t)d.nblkG * 36 + (size_t)d.nP * 6);
+    if (nranks > 1)
+        NK(g_nccl.AllReduce(d.HscPart, d.Hsc, (size_t)d.nblkG * 36 + (size_t)d.nP * 6, ncclFloat64, ncclSum, comm, stream));
     const int ncMax = 6 * CHOL_MAXW;
     if (cholGen >= 2) {
         const bool g3 = cholGen == 3;
@@ -1123,21 +1139,32 @@ void Solver::captureSlot() {
     if (!h_state) CK(cudaMallocHost(&h_state, sizeof(LMState)));
     if (!h_scalars) CK(cudaMallocHost(&h_scalars, 8 * sizeof(double)));
     if (!ev0) { CK(cudaEventCreate(&ev0)); CK(cudaEventCreate(&ev1)); }
-    CK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
-    try {
-        enqueueSlot();
-    } catch (...) {
-        // leave neither the stream in capture mode nor a half-recorded graph behind; the structure stays dirty
-        cudaGraph_t partial = nullptr;
-        cudaStreamEndCapture(stream, &partial);
-        if (partial) cudaGraphDestroy(partial);
-        cudaGetLastError();
-        structDirty = true;
-        throw;
+    auto capture = [&](bool a, cudaGraph_t* g, cudaGraphExec_t* ex) {
+        withA = a;
+        CK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+        try {
+            enqueueSlot();
+        } catch (...) {
+            // leave neither the stream in capture mode nor a half-recorded graph behind; the structure stays dirty
+            cudaGraph_t partial = nullptr;
+            cudaStreamEndCapture(stream, &partial);
+            if (partial) cudaGraphDestroy(partial);
+            cudaGetLastError();
+            structDirty = true;
+            withA = true;
+            throw;
+        }
+        withA = true;
+        CK(cudaStreamEndCapture(stream, g));
+        CK(cudaGetLastError());
+        CK(cudaGraphInstantiate(ex, *g, 0));
+    };
+    if (nranks > 1) {
+        capture(true, &slotGraph0, &slotExec0);
+        capture(false, &slotGraph, &slotExec);
+    } else {
+        capture(true, &slotGraph, &slotExec);
     }
-    CK(cudaStreamEndCapture(stream, &slotGraph));
-    CK(cudaGetLastError());
-    CK(cudaGraphInstantiate(&slotExec, slotGraph, 0));
 }
 
 // ---------------------------------------------------------------------------
@@ -1248,7 +1275,7 @@ int Solver::optimize(int niter, int cap, double* chi2, double* lambda, int* tria
     const int maxSlots = niter * 10 + 1;
     int batch = niter;
     while (niter > 0) {
-        for (int i = 0; i < batch; i++) CK(cudaGraphLaunch(slotExec, stream));
+        for (int i = 0; i < batch; i++) CK(cudaGraphLaunch((slots == 0 && i == 0 && slotExec0) ? slotExec0 : slotExec, stream));
         slots += batch;
         launched += (long)batch * kernelsPerSlot;
         CK(cudaMemcpyAsync(h_state, d.st, sizeof(LMState), cudaMemcpyDeviceToHost, stream));
@@ -1347,8 +1374,7 @@ void Solver::setOutlierThreshold(int setId, double thr) {
     CK(cudaMemsetAsync(p_out.p, 0, E, stream));
     anyOut_ = true;
     d.s_out = s_out; d.p_out = p_out;
-    if (slotExec) { cudaGraphExecDestroy(slotExec); slotExec = nullptr; }
-    if (slotGraph) { cudaGraphDestroy(slotGraph); slotGraph = nullptr; }
+    dropGraphs();
     captureSlot();
 }
 
@@ -1725,8 +1751,7 @@ int cugo_b200_set_robust_kernel(cugo_b200_solver* s, int set_id, int robust_type
         // kernel parameters are launch arguments: refresh them and re-capture the trial graph
         if (!S.structDirty) {
             S.refreshSetParams();
-            if (S.slotExec) { cudaGraphExecDestroy(S.slotExec); S.slotExec = nullptr; }
-            if (S.slotGraph) { cudaGraphDestroy(S.slotGraph); S.slotGraph = nullptr; }
+            S.dropGraphs();
             S.captureSlot();
         }
     });

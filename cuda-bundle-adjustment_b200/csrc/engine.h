@@ -102,6 +102,10 @@ struct Dev {
     double* invHll;             // [9 nL]
     double* bsc;                // [6 nP]
     double* Hsc;                // [36 nblk]
+    // what the Schur kernels write: the same arrays on one GPU; with several ranks the rank's PARTIAL [Hsc | bsc] in the
+    // global block layout (blocks the rank does not own stay zero), summed into Hsc / bsc by the all-reduce
+    double* HscPart;
+    double* bscPart;
     // reductions
     double* chiPartial;         // [errGrid]
     double* scalePartial;       // [nChunks]

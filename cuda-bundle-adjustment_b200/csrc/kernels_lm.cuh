@@ -42,15 +42,16 @@ __global__ void __launch_bounds__(TPB) k_lm_prepare(Dev d) {
     if (st->done) return;
     if (st->needBuild) {
         double m = 0.0;
-        if (d.nranks > 1) {
-            for (int i = threadIdx.x; i < 6 * d.nP + d.nranks; i += TPB) m = fmax(m, d.redA[i]);
+        if (d.nranks > 1) {     // exchanged in the first trial of an optimize() only: that is when lambda0 is formed
+            if (st->iter == 0)
+                for (int i = threadIdx.x; i < 6 * d.nP + d.nranks; i += TPB) m = fmax(m, d.redA[i]);
         } else {
             for (int i = threadIdx.x; i < d.nChunks; i += TPB) m = fmax(m, d.maxDiagL[i]);
             for (int i = threadIdx.x; i < d.nP; i += TPB) m = fmax(m, d.maxDiagP[i]);
         }
         m = block_max<TPB>(m, sh);
         if (threadIdx.x == 0) {
-            st->maxDiag = m;
+            if (d.nranks == 1 || st->iter == 0) st->maxDiag = m;
             if (st->iter == 0) st->lambda = 1e-5 * m;
             st->needBuild = 0;
         }

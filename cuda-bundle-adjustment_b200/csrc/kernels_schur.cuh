@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_schur_blocks(Dev d) {
         for (int i = 0; i < 6; i++) accb[i] = warp_sum(accb[i]);
     }
     if (lane == 0) {
-        double* __restrict__ out = d.Hsc + (size_t)(d.hscSlot ? d.hscSlot[blk] : blk) * 36;
+        double* __restrict__ out = d.HscPart + (size_t)(d.hscSlot ? d.hscSlot[blk] : blk) * 36;
         if (diag) {
             // with several ranks Hpp / bp are partial sums over the rank's edges and lambda is added once
             const double lam = d.rank == 0 ? st->lambda : 0.0;
@@ -97,7 +97,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_schur_blocks(Dev d) {
 #pragma unroll
             for (int i = 0; i < 36; i++) out[i] = Hp[i] + ((i % 7 == 0) ? lam : 0.0) - acc[i];
 #pragma unroll
-            for (int i = 0; i < 6; i++) d.bsc[(size_t)row * 6 + i] = d.b[(size_t)row * 6 + i] - accb[i];
+            for (int i = 0; i < 6; i++) d.bscPart[(size_t)row * 6 + i] = d.b[(size_t)row * 6 + i] - accb[i];
         } else {
 #pragma unroll
             for (int i = 0; i < 36; i++) out[i] = -acc[i];
@@ -250,7 +250,7 @@ __device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.w
 
 // final value of element idx (column-major 6x6) of Hsc block b of row i
 __device__ __forceinline__ void srow_store(const Dev& d, const LMState* st, int i, int b, int idx, double s, bool first) {
-    double* __restrict__ out = d.Hsc + (size_t)(d.hscSlot ? d.hscSlot[b] : b) * 36;
+    double* __restrict__ out = d.HscPart + (size_t)(d.hscSlot ? d.hscSlot[b] : b) * 36;
     if (!first) {            // later pass of a pose whose blocks do not fit the shared-memory stage at once
         out[idx] -= s;
     } else if (d.bColInd[b] == i) {
@@ -523,7 +523,7 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
         if (tid < 6) {
             double s = 0.0;
             for (int w = 0; w < SROW_NW; w++) s += red[w][tid];
-            d.bsc[(size_t)i * 6 + tid] = d.b[(size_t)i * 6 + tid] - s;
+            d.bscPart[(size_t)i * 6 + tid] = d.b[(size_t)i * 6 + tid] - s;
         }
     }
     if (dbg && tid == 0 && blockIdx.x < 8192) g_schurDbg[blockIdx.x] = clock64() - tStart;

@@ -33,6 +33,7 @@
 #include <memory>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <unordered_set>
 #include <vector>
 
@@ -177,6 +178,21 @@ public:
 };
 
 namespace detail {
+// Host packing walks hundreds of thousands of heap objects (one or two cache misses each): a few threads overlap those
+// misses.  fn(chunk, begin, end) is called once per chunk; chunks are contiguous and ascending.
+inline int packThreads(size_t n) {
+    const unsigned hc = std::thread::hardware_concurrency();
+    const size_t t = n / 16384;
+    return (int)(t < 1 ? 1 : (t > 8 ? 8 : t)) > (int)(hc ? hc : 1) ? (int)(hc ? hc : 1) : (int)(t < 1 ? 1 : (t > 8 ? 8 : t));
+}
+template <typename F>
+inline void parallelChunks(size_t n, int nthreads, F&& fn) {
+    if (nthreads <= 1) { fn(0, (size_t)0, n); return; }
+    std::vector<std::thread> th;
+    th.reserve(nthreads);
+    for (int c = 0; c < nthreads; c++) th.emplace_back([&, c]() { fn(c, n * c / nthreads, n * (c + 1) / nthreads); });
+    for (auto& t : th) t.join();
+}
 inline void packOne(const Se3D& e, double* o) { e.copyTo(o, o + 4); }
 inline void packOne(const Vec3d& e, double* o) { e.copyTo(o); }
 inline void unpackOne(Se3D& e, const double* i) { e = Se3D(i, i + 4); }
@@ -205,21 +221,34 @@ public:
     void clearVertices() noexcept override { vertices_.clear(); order_.clear(); active_ = 0; dirty_ = true; }
     int estimateDim() const noexcept override { return detail::EstDim<typename T::EstimateType>::value; }
     void assignIndices() override {
+        // the order of the last call stands while no vertex was added / removed and no fixed flag moved a vertex across
+        // the free | fixed boundary (checked on the contiguous pointer array, not by walking the map again)
+        if (!dirty_ && order_.size() == vertices_.size()) {
+            bool ok = true;
+            for (size_t i = 0; i < order_.size() && ok; i++) ok = order_[i]->T::isFixed() == (i >= (size_t)active_);
+            if (ok) return;
+        }
         order_.clear();
         order_.reserve(vertices_.size());
         for (auto& kv : vertices_) if (!kv.second->isFixed()) order_.push_back(kv.second);
         active_ = (int)order_.size();
         for (auto& kv : vertices_) if (kv.second->isFixed()) order_.push_back(kv.second);
         for (size_t i = 0; i < order_.size(); i++) order_[i]->setIndex((int)i);
+        dirty_ = false;
     }
     void packEstimates(std::vector<double>& out) const override {
         const int dim = estimateDim();
         out.resize(order_.size() * dim);
-        for (size_t i = 0; i < order_.size(); i++) detail::packOne(order_[i]->getEstimate(), out.data() + i * dim);
+        double* o = out.data();
+        detail::parallelChunks(order_.size(), detail::packThreads(order_.size()), [&](int, size_t b, size_t e) {
+            for (size_t i = b; i < e; i++) detail::packOne(order_[i]->T::getEstimate(), o + i * dim);
+        });
     }
     void unpackEstimates(const double* in) override {
         const int dim = estimateDim();
-        for (size_t i = 0; i < order_.size(); i++) detail::unpackOne(order_[i]->getEstimate(), in + i * dim);
+        detail::parallelChunks(order_.size(), detail::packThreads(order_.size()), [&](int, size_t b, size_t e) {
+            for (size_t i = b; i < e; i++) detail::unpackOne(order_[i]->T::getEstimate(), in + i * dim);
+        });
     }
     const std::map<int, T*>& get() const noexcept { return vertices_; }
 private:
@@ -349,24 +378,49 @@ public:
     void pack(const GraphOptimisationOptions& opt, Packed& out) override {
         out = Packed();
         out.dim = DIM; out.rk = (int)rk_; out.delta = delta_;
-        packed_.clear();
         outCount_ = 0;
-        for (BaseEdge* e : edges_) {
-            if (!e->isActive() || e->allVerticesFixed()) continue;
-            packed_.push_back(e);
-            out.iP.push_back(e->getVertex(0)->getIndex());
-            out.iL.push_back(e->getVertex(1)->getIndex());
-            const double* m = e->measurementData();
-            out.meas.insert(out.meas.end(), m, m + DIM);
-            if (opt.perEdgeInformation) out.omega.push_back(e->getInformation());
-            if (opt.perEdgeCamera) {
-                const Camera& c = e->getCamera();
-                const double v[5] = {c.fx, c.fy, c.cx, c.cy, c.bf};
-                out.cam.insert(out.cam.end(), v, v + 5);
+        // pass 1: which edges go to the engine (active flag set, not both vertices fixed), per chunk; pass 2: fill
+        const size_t ne = edges_.size();
+        const int nth = detail::packThreads(ne);
+        std::vector<size_t> cnt(nth + 1, 0);
+        std::vector<unsigned char> keep(ne);
+        detail::parallelChunks(ne, nth, [&](int c, size_t b, size_t e) {
+            size_t k = 0;
+            for (size_t i = b; i < e; i++) {
+                BaseEdge* ed = edges_[i];
+                const bool on = ed->isActive() && !ed->allVerticesFixed();
+                keep[i] = on;
+                k += on;
             }
-        }
-        out.n = (int)out.iP.size();
-        nActive_ = out.n;
+            cnt[c + 1] = k;
+        });
+        for (int c = 0; c < nth; c++) cnt[c + 1] += cnt[c];
+        const size_t n = cnt[nth];
+        packed_.resize(n);
+        out.iP.resize(n); out.iL.resize(n); out.meas.resize(n * DIM);
+        if (opt.perEdgeInformation) out.omega.resize(n);
+        if (opt.perEdgeCamera) out.cam.resize(n * 5);
+        detail::parallelChunks(ne, nth, [&](int c, size_t b, size_t e) {
+            size_t o = cnt[c];
+            for (size_t i = b; i < e; i++) {
+                if (!keep[i]) continue;
+                BaseEdge* ed = edges_[i];
+                packed_[o] = ed;
+                out.iP[o] = ed->getVertex(0)->getIndex();
+                out.iL[o] = ed->getVertex(1)->getIndex();
+                const double* m = ed->measurementData();
+                for (int k = 0; k < DIM; k++) out.meas[o * DIM + k] = m[k];
+                if (opt.perEdgeInformation) out.omega[o] = ed->getInformation();
+                if (opt.perEdgeCamera) {
+                    const Camera& cm = ed->getCamera();
+                    double* v = &out.cam[o * 5];
+                    v[0] = cm.fx; v[1] = cm.fy; v[2] = cm.cx; v[3] = cm.cy; v[4] = cm.bf;
+                }
+                o++;
+            }
+        });
+        out.n = (int)n;
+        nActive_ = n;
         if (!opt.perEdgeInformation) out.omega.assign(1, info_);
         if (!opt.perEdgeCamera) out.cam = {cam_.fx, cam_.fy, cam_.cx, cam_.cy, cam_.bf};
         out.nomega = opt.perEdgeInformation ? out.n : 1;
