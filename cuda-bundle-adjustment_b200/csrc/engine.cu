@@ -18,8 +18,6 @@
 #include <vector>
 
 #include "engine.h"
-#include "kernels_chol.cuh"
-#include "kernels_chol2.cuh"
 #include "kernels_chol3.cuh"
 #include "kernels_edge.cuh"
 #include "kernels_lm.cuh"
@@ -145,8 +143,8 @@ struct Solver {
     cudaStream_t stream = nullptr;
     cudaStream_t side = nullptr;   // low-priority branch of the trial graph: k_chol_zinv beside the factorisation
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
-    bool bwdSplit = true;          // CUGO_B200_BWDSPLIT=0: one CTA per supernode in the backward solve
-    bool zinvOn = true;            // CUGO_B200_ZINV=0: backward solves by blocked substitution on every level
+    bool bwdSplit = true;          // option "bwd_split" = 0: one CTA per supernode in the backward solve
+    bool zinvOn = true;            // option "zinv" = 0: backward solves by blocked substitution on every level
     std::string err;
     // host copies of the problem
     int nP_all = 0, nP = 0, nL_all = 0, nL = 0;
@@ -162,7 +160,6 @@ struct Solver {
     SymCounts counts{};
     std::vector<int> h_levelPtr, h_trsmPtr, h_updPtr, h_levMaxNt;
     int h_nchild = 0;              // non-root supernodes
-    int cholGen = 3;               // CUGO_B200_CHOL=1|2: earlier generations of the factorisation kernels (A/B timing)
     // buffers
     DBuf<double> pose0, pose1, poseBak, lm0, lm1, lmBak;
     DBuf<int> r_iP, r_iL, r_cam;
@@ -185,7 +182,6 @@ struct Solver {
     DBuf<int2> rowUnits, blkPass;
     int nRowUnits = 0, schurPasses = 1, schurUnit = 2048;
     int maxPoseDeg = 0, schurCap = 1;
-    bool schurRows = false;        // k_schur_rows (shared-memory stage fits) or k_schur_blocks
     bool f32 = false;              // USE_FLOAT32 mode: Hpl blocks stored in single precision (arithmetic stays FP64)
     DBuf<float> HplF;
     DBuf<double> Hpp, Hll, Hpl, b, x, invHll, bsc, Hsc, chiPartial, scalePartial, maxDiagL, maxDiagP, chiEdge;
@@ -204,7 +200,7 @@ struct Solver {
     DBuf<int2> y_regA, y_regB;
     DBuf<int4> y_emits;
     DBuf<unsigned> y_bits;
-    bool symParallel = true;       // CUGO_B200_SYM=0: the single-thread run of symbolic.h (the twin) on the device
+    bool symParallel = true;       // option "parallel_symbolic" = 0: the single-thread run of symbolic.h (the twin) on the device
     void symbolicParallel(const int* gRowOfP, const int* gRowPtrP, const int* gColIndP, int P);
     DBuf<double> cL, cU, cX, cW, cZ, cPart;
     DBuf<int> cCnt;
@@ -254,10 +250,10 @@ struct Solver {
         profNames.push_back(name);
     }
     // Launch of a trial kernel with programmatic stream serialisation (engine.h: pdl_wait / pdl_trigger);
-    // CUGO_B200_PDL=0 falls back to plain stream order.  Captured into the trial graph as a programmatic edge.
+    // option "pdl" = 0 falls back to plain stream order.  Captured into the trial graph as a programmatic edge.
     bool pdl = true;
-    bool panelDC = true;           // panel kernel with the decoupled diagonal chain (CUGO_B200_PANELDC=0: CTA-wide barriers)
-    bool fuseBuild = true;         // both passes of the system build in one launch (CUGO_B200_FUSEBUILD=0: two)
+    bool panelDC = true;           // panel kernel with the decoupled diagonal chain (option "panel_dc" = 0: CTA-wide barriers)
+    bool fuseBuild = true;         // both passes of the system build in one launch (option "fuse_build" = 0: two)
     template <typename... KA, typename... A>
     void launch(void (*kern)(KA...), dim3 grid, dim3 block, size_t smem, A... args) {
         cudaLaunchConfig_t cfg{};
@@ -614,8 +610,6 @@ void Solver::buildStructure() {
             k_blk_pass_init<<<divUp(nblk * schurPasses, TB), TB, 0, stream>>>(nblk * schurPasses, blkPass);
             k_blk_pass<<<divUp(nmulAll, TB), TB, 0, stream>>>(prodRank, head, blkOf, nmulAll, schurCap, schurPasses, blkPass);
         }
-        const char* e = getenv("CUGO_B200_SCHUR");
-        schurRows = !(e && e[0] == '1');
         if (getenv("CUGO_B200_DEBUG")) fprintf(stderr, "[cugo_b200] max pose degree %d, schur stage %d blocks, %d row units\n", maxPoseDeg, schurCap, nRowUnits);
         CK(cudaFuncSetAttribute(k_schur_rows<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)srow_smem_bytes(schurCap)));
         CK(cudaFuncSetAttribute(k_schur_rows<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)srow_smem_bytes(schurCap)));
@@ -658,22 +652,6 @@ void Solver::buildStructure() {
     }
 
     lap("pose-major Hpl view, row units");
-    {
-        const char* g = getenv("CUGO_B200_CHOL");
-        cholGen = (g && (g[0] == '1' || g[0] == '2')) ? g[0] - '0' : 3;
-        const char* p = getenv("CUGO_B200_PDL");
-        pdl = !(p && p[0] == '0');
-        const char* dc = getenv("CUGO_B200_PANELDC");
-        panelDC = !(dc && dc[0] == '0');
-        const char* bs = getenv("CUGO_B200_BWDSPLIT");
-        bwdSplit = !(bs && bs[0] == '0');
-        const char* zi = getenv("CUGO_B200_ZINV");
-        zinvOn = !(zi && zi[0] == '0');
-        const char* fb = getenv("CUGO_B200_FUSEBUILD");
-        fuseBuild = !(fb && fb[0] == '0');
-        const char* sy = getenv("CUGO_B200_SYM");
-        symParallel = !(sy && sy[0] == '0') && cholGen != 1;
-    }
     // ---- symbolic factorisation
     const int P = nP;
     int nsn = 0;
@@ -716,7 +694,7 @@ void Solver::buildStructure() {
     m.childIdx = z_childIdx; m.invPtr = z_invPtr; m.inv = z_inv; m.snBlkPtr = z_snBlkPtr; m.asmBlk = z_asmBlk;
     m.asmRow = z_asmRow; m.asmCol = z_asmCol;
     z_levMaxNt.alloc(counts.nlev + 1);
-    k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, CHOL_RS, CHOL_TS, cholGen == 1 ? 0 : CHOL_RB, CHOL_TB,
+    k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, 0, 0, CHOL_RB, CHOL_TB,
                                     z_levMaxNt, z_factStats.alloc(4));
     lap("symbolic maps + task tables");
     }
@@ -788,22 +766,12 @@ void Solver::buildStructure() {
     c.childIdx = z_childIdx; c.invPtr = z_invPtr; c.inv = z_inv; c.snBlkPtr = z_snBlkPtr; c.asmBlk = z_asmBlk;
     c.asmRow = z_asmRow; c.asmCol = z_asmCol; c.trsmPtr = z_trsmPtr; c.updPtr = z_updPtr;
     c.L = cL; c.U = cU; c.xperm = cX; c.Winv = cW; c.Zinv = cZ; c.bwdPart = cPart; c.bwdCnt = cCnt;
-    { const char* e = getenv("CUGO_B200_DEBUG"); c.dbg = e ? atoi(e) : 0; }   // 1: phase stamps; 3: also a worker warp's view of the panel loop
+    { const char* e = getenv("CUGO_B200_DEBUG"); c.dbg = e ? atoi(e) : 0; }   // diagnostic builds (make DIAG=1): 1 phase stamps, 3 also a worker warp's view
 
     // dynamic shared memory opt-in for the factorisation kernels
     const int ncMax = 6 * CHOL_MAXW;
-    CK(cudaFuncSetAttribute(k_chol_diag<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, ncMax * ncMax * 8));
-    CK(cudaFuncSetAttribute(k_chol_trsm<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                            (ncMax * ncMax + CHOL_RS * ncMax) * 8));
-    const size_t bwdBytes = ((size_t)ncMax * ncMax + ncMax + 6 * (size_t)maxRt) * 8;
-    if (bwdBytes > 227 * 1024) throw UnsupportedError("front too large for the shared-memory backward solve of this version");
-    CK(cudaFuncSetAttribute(k_chol_bwd<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwdBytes));
-    CK(cudaFuncSetAttribute(k_chol_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_LD * ncMax * 8));
-    CK(cudaFuncSetAttribute(k_chol_update2, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                            (2 * ncMax * UPD_LD + 6 * CHOL_TB * UPD_CLD) * 8));
     const size_t bwd2Bytes = ((size_t)ncMax * (ncMax + 1) + ncMax + 21 * CHOL_MAXW + 6 * (size_t)maxRt) * 8;
     if (bwd2Bytes > 227 * 1024) throw UnsupportedError("front too large for the shared-memory backward solve of this version");
-    CK(cudaFuncSetAttribute(k_chol_bwd2<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd2Bytes));
     CK(cudaFuncSetAttribute(k_chol_bwd3<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd2Bytes));
     CK(cudaFuncSetAttribute(k_chol_zinv<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                             (int)((2 * (size_t)ncMax * (ncMax + 1) + 21 * CHOL_MAXW + 36 * 8) * 8)));
@@ -928,85 +896,53 @@ void Solver::enqueueBuild() {
 void Solver::enqueueSolve() {
     launch(k_schur_inv<256>, divUp(d.nL, 256), 256, 0, d); mark("schur_inv");
     const int2* bp = schurPasses > 1 ? blkPass.p : nullptr;
-    if (schurRows) {
-        if (f32) launch(k_schur_rows<float>, nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), d, schurCap, c.dbg, schurUnit, schurPasses, bp);
-        else launch(k_schur_rows<double>, nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), d, schurCap, c.dbg, schurUnit, schurPasses, bp);
-    } else {
-        if (f32) launch(k_schur_blocks<4, float>, divUp(d.nblk, 4), 128, 0, d);
-        else launch(k_schur_blocks<4, double>, divUp(d.nblk, 4), 128, 0, d);
-    }
-    mark(schurRows ? "schur_rows" : "schur_blocks");
+    if (f32) launch(k_schur_rows<float>, nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), d, schurCap, c.dbg, schurUnit, schurPasses, bp);
+    else launch(k_schur_rows<double>, nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), d, schurCap, c.dbg, schurUnit, schurPasses, bp);
+    mark("schur_rows");
     // the one exchange step of a trial: partial reduced camera systems [Hsc | bsc] summed over the ranks
     if (nranks > 1)
         NK(g_nccl.AllReduce(d.HscPart, d.Hsc, (size_t)d.nblkG * 36 + (size_t)d.nP * 6, ncclFloat64, ncclSum, comm, stream));
-    const int ncMax = 6 * CHOL_MAXW;
-    if (cholGen >= 2) {
-        const bool g3 = cholGen == 3;
-        // levels [0, zTop] solve backward with the inverse of L11 (k_chol_zinv has the whole rest of the factorisation
-        // to finish); the top three keep the blocked substitution
-        const bool zOn = g3 && zinvOn && pdl && !profiling;
-        const int zTop = c.nlev - 4;
-        for (int lev = 0; lev < c.nlev; lev++) {
-            const int q0 = h_levelPtr[lev], q1 = h_levelPtr[lev + 1];
-            const int ncLev = 6 * h_levMaxNt[lev];
-            if (g3) launch(panelDC ? k_chol_panel3<true> : k_chol_panel3<false>, h_trsmPtr[q1] - h_trsmPtr[q0], PANEL3_TPB,
-                           (size_t)PANEL_LD * ncLev * 8, d, c, lev, (pdl && !profiling && lev > 0) ? 1 : 0);
-            else k_chol_panel<<<h_trsmPtr[q1] - h_trsmPtr[q0], PANEL_TPB, PANEL_LD * ncLev * 8, stream>>>(d, c, lev);
-            mark("chol_panel");
-            if (zOn && lev <= zTop) {      // L11^-1 of the level on the low-priority branch, beside the rest of the factorisation
-                CK(cudaEventRecord(evFork, stream));
-                CK(cudaStreamWaitEvent(side, evFork, 0));
-                const size_t zb = (2 * (size_t)ncLev * (ncLev + 1) + 21 * CHOL_MAXW + 36 * 8) * 8;
-                k_chol_zinv<256><<<q1 - q0, 256, zb, side>>>(d, c, lev);
-                kernelsPerSlot++;
-            }
-            const int nUpd = h_updPtr[q1] - h_updPtr[q0];
-            if (nUpd > 0) {
-                if (g3) {
-                    const int kpad = (ncLev + 15) & ~15;
-                    launch(k_chol_update3, nUpd, UPD3_TPB, (size_t)std::max(2 * kpad * UPD_LD, 2 * 6 * CHOL_TB * UPD_CLD) * 8, d, c, lev, kpad);
-                } else {
-                    const int kpad = (ncLev + 7) & ~7;
-                    k_chol_update2<<<nUpd, 128, (2 * kpad * UPD_LD + 6 * CHOL_TB * UPD_CLD) * 8, stream>>>(d, c, lev, kpad);
-                }
-                mark("chol_update");
-            }
-        }
-        for (int lev = c.nlev - 1; lev >= 0; lev--) {
-            const int ncLev = 6 * h_levMaxNt[lev];
-            const size_t bytes = ((size_t)ncLev * (ncLev + 1) + ncLev + 21 * CHOL_MAXW + 6 * (size_t)maxRt) * 8;
-            if (zOn && lev == zTop) {
-                CK(cudaEventRecord(evJoin, side));
-                CK(cudaStreamWaitEvent(stream, evJoin, 0));
-            }
-            // few supernodes on a level: several CTAs share the L21^T x_R product of each
-            const int nsnLev = h_levelPtr[lev + 1] - h_levelPtr[lev];
-            const int G = bwdSplit ? std::max(1, std::min(BWD_MAXG, 148 / nsnLev)) : 1;
-            if (g3) launch(k_chol_bwd3<256>, nsnLev * G, 256, bytes, d, c, lev,
-                           (pdl && !profiling && lev < c.nlev - 1) ? 1 : 0, (zOn && lev <= zTop) ? 1 : 0, G);
-            else k_chol_bwd2<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bytes, stream>>>(d, c, lev);
-            mark("chol_bwd");
-        }
-        if (f32) launch(k_backsub<LM_CHUNK, float>, d.nChunks, LM_CHUNK, 0, d);
-        else launch(k_backsub<LM_CHUNK, double>, d.nChunks, LM_CHUNK, 0, d);
-        mark("backsub");
-        return;
-    }
+    // levels [0, zTop] solve backward with the inverse of L11 (k_chol_zinv has the whole rest of the factorisation
+    // to finish); the top three keep the blocked substitution
+    const bool zOn = zinvOn && pdl && !profiling;
+    const int zTop = c.nlev - 4;
     for (int lev = 0; lev < c.nlev; lev++) {
         const int q0 = h_levelPtr[lev], q1 = h_levelPtr[lev + 1];
-        k_chol_diag<256><<<q1 - q0, 256, ncMax * ncMax * 8, stream>>>(d, c, lev); mark("chol_diag");
-        const int nTrsm = h_trsmPtr[q1] - h_trsmPtr[q0];
-        k_chol_trsm<256><<<nTrsm, 256, (ncMax * ncMax + CHOL_RS * ncMax) * 8, stream>>>(d, c, lev); mark("chol_trsm");
+        const int ncLev = 6 * h_levMaxNt[lev];
+        launch(panelDC ? k_chol_panel3<true> : k_chol_panel3<false>, h_trsmPtr[q1] - h_trsmPtr[q0], PANEL3_TPB,
+               (size_t)PANEL_LD * ncLev * 8, d, c, lev, (pdl && !profiling && lev > 0) ? 1 : 0);
+        mark("chol_panel");
+        if (zOn && lev <= zTop) {      // L11^-1 of the level on the low-priority branch, beside the rest of the factorisation
+            CK(cudaEventRecord(evFork, stream));
+            CK(cudaStreamWaitEvent(side, evFork, 0));
+            const size_t zb = (2 * (size_t)ncLev * (ncLev + 1) + 21 * CHOL_MAXW + 36 * 8) * 8;
+            k_chol_zinv<256><<<q1 - q0, 256, zb, side>>>(d, c, lev);
+            kernelsPerSlot++;
+        }
         const int nUpd = h_updPtr[q1] - h_updPtr[q0];
-        if (nUpd > 0) { k_chol_update<<<nUpd, 128, 0, stream>>>(d, c, lev); mark("chol_update"); }
+        if (nUpd > 0) {
+            const int kpad = (ncLev + 15) & ~15;
+            launch(k_chol_update3, nUpd, UPD3_TPB, (size_t)std::max(2 * kpad * UPD_LD, 2 * 6 * CHOL_TB * UPD_CLD) * 8, d, c, lev, kpad);
+            mark("chol_update");
+        }
     }
-    const size_t bwdBytes = ((size_t)ncMax * ncMax + ncMax + 6 * (size_t)maxRt) * 8;
     for (int lev = c.nlev - 1; lev >= 0; lev--) {
-        k_chol_bwd<256><<<h_levelPtr[lev + 1] - h_levelPtr[lev], 256, bwdBytes, stream>>>(d, c, lev); mark("chol_bwd");
+        const int ncLev = 6 * h_levMaxNt[lev];
+        const size_t bytes = ((size_t)ncLev * (ncLev + 1) + ncLev + 21 * CHOL_MAXW + 6 * (size_t)maxRt) * 8;
+        if (zOn && lev == zTop) {
+            CK(cudaEventRecord(evJoin, side));
+            CK(cudaStreamWaitEvent(stream, evJoin, 0));
+        }
+        // few supernodes on a level: several CTAs share the L21^T x_R product of each
+        const int nsnLev = h_levelPtr[lev + 1] - h_levelPtr[lev];
+        const int G = bwdSplit ? std::max(1, std::min(BWD_MAXG, 148 / nsnLev)) : 1;
+        launch(k_chol_bwd3<256>, nsnLev * G, 256, bytes, d, c, lev, (pdl && !profiling && lev < c.nlev - 1) ? 1 : 0,
+               (zOn && lev <= zTop) ? 1 : 0, G);
+        mark("chol_bwd");
     }
-    if (f32) k_backsub<LM_CHUNK, float><<<d.nChunks, LM_CHUNK, 0, stream>>>(d);
-        else k_backsub<LM_CHUNK, double><<<d.nChunks, LM_CHUNK, 0, stream>>>(d);
-        mark("backsub");
+    if (f32) launch(k_backsub<LM_CHUNK, float>, d.nChunks, LM_CHUNK, 0, d);
+    else launch(k_backsub<LM_CHUNK, double>, d.nChunks, LM_CHUNK, 0, d);
+    mark("backsub");
 }
 
 // one LM trial: [build] prepare solve update errors decide
@@ -1896,6 +1832,7 @@ int cugo_b200_get_factor_stats(cugo_b200_solver* s, double stats[4]) {
     });
 }
 int cugo_b200_debug_counters(long long* out, int n) {
+#ifdef CUGO_B200_DIAG
     if (out && n == 8192)   // per-row cycles of the Schur kernel
         return cudaMemcpyFromSymbol(out, cugo_b200::g_schurDbg, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
     if (!out || n < 0 || n > 64 * 24) return CUGO_B200_EINVAL;
@@ -1904,6 +1841,21 @@ int cugo_b200_debug_counters(long long* out, int n) {
     if (n == 96)
         return cudaMemcpyFromSymbol(out, cugo_b200::g_cholTrace, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
     return cudaMemcpyFromSymbol(out, cugo_b200::g_cholDbg, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
+#else
+    (void)out; (void)n;
+    return CUGO_B200_EUNSUPPORTED;      // the phase clocks are compiled in by `make DIAG=1` only
+#endif
+}
+int cugo_b200_set_option(cugo_b200_solver* s, const char* name, int value) {
+    return guarded(s, [&](Solver& S) {
+        if (!name) throw cugo_b200::ArgError("set_option: null name");
+        const std::string n(name);
+        bool* f = n == "pdl" ? &S.pdl : n == "fuse_build" ? &S.fuseBuild : n == "panel_dc" ? &S.panelDC : n == "zinv" ? &S.zinvOn
+                : n == "bwd_split" ? &S.bwdSplit : n == "parallel_symbolic" ? &S.symParallel : nullptr;
+        if (!f) throw cugo_b200::ArgError("set_option: unknown option '" + n + "' (pdl, fuse_build, panel_dc, zinv, bwd_split, parallel_symbolic)");
+        *f = value != 0;
+        S.structDirty = true;           // the options shape the structure and the trial graph
+    });
 }
 void* cugo_b200_stream(cugo_b200_solver* s) { return s ? (void*)s->impl.stream : nullptr; }
 

@@ -1,19 +1,11 @@
-// kernels_chol3.cuh -- third-generation panel kernel of the multifrontal Cholesky.
-// Same task decomposition and storage as k_chol_panel (kernels_chol2.cuh): one CTA per
-// (supernode, slab of <= CHOL_RB block rows of L21), [D; S] assembled and factored in
-// shared memory.  What changed, driven by the phase timestamps of the second generation
-// (profiles/r01b_*): per block column the 6x6 diagonal factor was computed redundantly by
-// all 256 threads (FP64-issue bound, ~3000 cycles) after a DMMA update that sat on the
-// critical path.  Here
-//   * 512 threads; warp 0 alone factors the diagonal block (L_D, W = L_D^-1 -> shared
-//     memory) while warps 1..15 already apply all *finished* columns (< j0) to the NEXT
-//     block column (look-ahead DMMA update, off the critical path);
-//   * one thread per row then applies x = a W^T, and a rank-6 DMMA update brings the next
-//     block column up to date -- three barriers per block column;
-//   * assembly: Hsc blocks scattered by (entry, column) work units, children pulled in
-//     groups of four with all loads issued before the (fixed-order) accumulation.
+// kernels_chol3.cuh -- numeric multifrontal Cholesky of the reduced camera system and its solves
+// (replaces cusolverSpDcsrcholFactor / csrcholSolve, src/cholesky.hpp:109-156): k_chol_panel3 (one CTA per
+// (supernode, slab of <= CHOL_RB block rows of L21): [D; S] assembled and factored in shared memory, a decoupled chain warp
+// factors the 6x6 diagonal blocks while 12 worker warps run the DMMA updates with look-ahead), k_chol_update3 (48x48
+// tiles of the update matrices), k_chol_zinv (inverse of L11 on a side branch) and k_chol_bwd3 (backward solves).
+// DESIGN.md section 4 has the data flow and the measurements behind each choice.
 #pragma once
-#include "kernels_chol2.cuh"
+#include "kernels_chol_common.cuh"
 
 namespace cugo_b200 {
 
@@ -488,7 +480,7 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
         // the step before; it can be one step ahead, hence the two parities of B1 / B2.
         constexpr int NWK = 3 * (PANEL3_NW / 4);
         constexpr int NB = (NWK + 1) * 32;               // chain + workers
-        const bool dbgT = c.dbg && blockIdx.x == 0 && tid == 0 && lev < 64;
+        const bool dbgT = CHOL_DIAG(c) && blockIdx.x == 0 && tid == 0 && lev < 64;
         const long long tLoop0 = dbgT ? clock64() : 0;
         if (wid == 0) {
             panel_factor_diag(A, invAll, &badFlag, 0, lane);
@@ -510,7 +502,7 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
         } else if ((wid & 3) != 0) {
             const int wk = (wid >> 2) * 3 + (wid & 3) - 1;
             const int wt = wk * 32 + lane;
-            const bool trw = c.dbg && blockIdx.x == 0 && tid == 32 && lev == 2;   // worker 0: clock after (B1, B2, X)
+            const bool trw = CHOL_DIAG(c) && blockIdx.x == 0 && tid == 32 && lev == 2;   // worker 0: clock after (B1, B2, X)
             const long long tw0 = trw ? clock64() : 0;
             for (int jb = 0; jb < nt; jb++) {
                 const bool more = jb + 1 < nt;
@@ -530,9 +522,9 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
         if (dbgT) g_cholDbg[lev * 24 + 15] = clock64() - tLoop0;
     } else {
         const int fr8 = lane >> 2, fk = lane & 3;
-        const bool dbgT = c.dbg && blockIdx.x == 0 && tid == 0 && lev < 64;
+        const bool dbgT = CHOL_DIAG(c) && blockIdx.x == 0 && tid == 0 && lev < 64;
         long long tF = 0, tW = 0, tS = 0, tU = 0, t0 = 0, t1 = 0;
-        const bool dbgK = (c.dbg & 2) && blockIdx.x == 0 && tid == 32 && lev < 64;   // a worker warp's view
+        const bool dbgK = (CHOL_DIAG(c) & 2) && blockIdx.x == 0 && tid == 32 && lev < 64;   // a worker warp's view
         long long wU = 0, wL = 0, w0 = 0, w1 = 0;
         const long long tLoop0 = dbgT ? clock64() : 0;
         if (wid == 0) panel_factor_diag(A, invAll, &badFlag, 0, lane);

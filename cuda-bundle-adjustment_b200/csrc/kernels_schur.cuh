@@ -1,16 +1,17 @@
 // kernels_schur.cuh -- Schur complement and back-substitution.
 //   k_schur_inv     invHll = (Hll + lambda I)^-1                (reference computeBschureKernel, Sym3x3Inv
-//   k_schur_blocks  Hsc, bsc                                     cuda_block_solver.cu:639-669, 1286-1345)
+//   k_schur_rows    Hsc, bsc (by block rows, below)              cuda_block_solver.cu:639-669, 1286-1345)
 //   k_backsub       xl = invHll (bl - Hpl^T xp), landmark update (schurComplementPostKernel :1419-1442,
 //                                                                  updateLandmarksKernel :1457-1469)
 //   k_update_poses  T <- Exp(xp) T                               (updatePosesKernel :1444-1455)
 // Damping is applied on the fly (Hpp/Hll stay undamped), so the reference's
 // addLambda / restoreDiagonal passes (:1255-1284) and its backup buffers vanish.
 // The reference subtracts each 6x6 product into Hsc with 36 atomics; here every
-// Hsc block is owned by one warp that walks the block's product list.
+// Hsc block is summed by the warps of one CTA in a fixed order.
 #pragma once
 #include "device_math.cuh"
 #include "engine.h"
+#include "kernels_chol_common.cuh"
 
 namespace cugo_b200 {
 
@@ -29,80 +30,6 @@ __global__ void __launch_bounds__(TPB) k_schur_inv(Dev d) {
     o[0] = B[0]; o[1] = B[1]; o[2] = B[3];
     o[3] = B[1]; o[4] = B[2]; o[5] = B[4];
     o[6] = B[3]; o[7] = B[4]; o[8] = B[5];
-}
-
-// One warp per upper-triangular Hsc block (i,j).  Products (one per landmark seen
-// by both poses) are dealt to lanes round-robin; each lane forms
-// T = Hpl_i invHll (6x3) and accumulates T Hpl_j^T (6x6); diagonal blocks also
-// accumulate T bl for bsc.  Lane partials are combined by a shuffle tree, so the
-// summation order is fixed.  Hsc(i,i) = Hpp_i + lambda I - sum, bsc_i = bp_i - sum.
-template <int WARPS, typename HT>
-__global__ void __launch_bounds__(WARPS * 32) k_schur_blocks(Dev d) {
-    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
-    const LMState* st = d.st;
-    if (st->done) return;
-    const int blk = blockIdx.x * WARPS + (threadIdx.x >> 5);
-    if (blk >= d.nblk) return;
-    const int lane = threadIdx.x & 31;
-    const int row = d.bRowOf[blk], col = d.bColInd[blk];
-    const bool diag = (row == col);
-    const double* __restrict__ bl = d.b + (size_t)d.nP * 6;
-    double acc[36], accb[6];
-#pragma unroll
-    for (int i = 0; i < 36; i++) acc[i] = 0.0;
-#pragma unroll
-    for (int i = 0; i < 6; i++) accb[i] = 0.0;
-    const int p0 = d.prodPtr[blk], p1 = d.prodPtr[blk + 1];
-    for (int p = p0 + lane; p < p1; p += 32) {
-        const int2 ij = d.prodIJ[p];
-        if (ij.x < 0) continue;
-        const int l = d.hplLm[ij.x];
-        const HT* __restrict__ A = HplOf<HT>::get(d) + (size_t)ij.x * 18;
-        const double* __restrict__ iH = d.invHll + (size_t)l * 9;
-        double T[18];
-        double ih[9];
-#pragma unroll
-        for (int i = 0; i < 9; i++) ih[i] = iH[i];
-#pragma unroll
-        for (int r = 0; r < 6; r++) {
-            const double a0 = A[r], a1 = A[r + 6], a2 = A[r + 12];
-#pragma unroll
-            for (int c = 0; c < 3; c++) T[c * 6 + r] = a0 * ih[c * 3] + a1 * ih[c * 3 + 1] + a2 * ih[c * 3 + 2];
-        }
-        const HT* __restrict__ B = HplOf<HT>::get(d) + (size_t)ij.y * 18;
-#pragma unroll
-        for (int c = 0; c < 6; c++) {
-            const double b0 = B[c], b1 = B[c + 6], b2 = B[c + 12];
-#pragma unroll
-            for (int r = 0; r < 6; r++) acc[c * 6 + r] += T[r] * b0 + T[r + 6] * b1 + T[r + 12] * b2;
-        }
-        if (diag) {
-            const double g0 = bl[(size_t)l * 3], g1 = bl[(size_t)l * 3 + 1], g2 = bl[(size_t)l * 3 + 2];
-#pragma unroll
-            for (int r = 0; r < 6; r++) accb[r] += T[r] * g0 + T[r + 6] * g1 + T[r + 12] * g2;
-        }
-    }
-#pragma unroll
-    for (int i = 0; i < 36; i++) acc[i] = warp_sum(acc[i]);
-    if (diag) {
-#pragma unroll
-        for (int i = 0; i < 6; i++) accb[i] = warp_sum(accb[i]);
-    }
-    if (lane == 0) {
-        double* __restrict__ out = d.HscPart + (size_t)(d.hscSlot ? d.hscSlot[blk] : blk) * 36;
-        if (diag) {
-            // with several ranks Hpp / bp are partial sums over the rank's edges and lambda is added once
-            const double lam = d.rank == 0 ? st->lambda : 0.0;
-            const double* __restrict__ Hp = d.Hpp + (size_t)row * 36;
-#pragma unroll
-            for (int i = 0; i < 36; i++) out[i] = Hp[i] + ((i % 7 == 0) ? lam : 0.0) - acc[i];
-#pragma unroll
-            for (int i = 0; i < 6; i++) d.bscPart[(size_t)row * 6 + i] = d.b[(size_t)row * 6 + i] - accb[i];
-        } else {
-#pragma unroll
-            for (int i = 0; i < 36; i++) out[i] = -acc[i];
-        }
-    }
 }
 
 // Back-substitution, landmark-major with the same chunking as k_build_lm.  Work
@@ -220,7 +147,7 @@ namespace cugo_b200 {
 // one L1 tag lookup per lane and instruction (the tag stage, one line per clock, was the bound of both
 // k_schur_blocks and the first row kernel), this one about two per 144-byte block.  Phase 2 keeps two
 // rounds in flight per warp (metadata prefetched one more round ahead).
-// No atomics on data, fixed summation order.  k_schur_blocks stays selectable (CUGO_B200_SCHUR=1).
+// No atomics on data, fixed summation order.
 // ---------------------------------------------------------------------------
 constexpr int SROW_TPB = 256;
 constexpr int SROW_NW = SROW_TPB / 32;
@@ -366,7 +293,6 @@ __device__ __forceinline__ void srow_segment(const Dev& d, const double* T, doub
     }
 }
 
-__device__ long long g_schurDbg[8192];    // diagnostics: cycles per unit of k_schur_rows
 // blkPass (several passes only): per (block, pass) the range of the block's products whose row rank lies in
 // the pass's stage -- products of a block are ordered by landmark, as are the slots of a pose, so the range
 // is tight; the per-product rank test stays as the guarantee.
@@ -379,6 +305,9 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
     __shared__ double red[SROW_NW][6];
     __shared__ int nextBlk;
     pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
+#ifndef CUGO_B200_DIAG
+    dbg = 0;                         // the cycle counters exist in diagnostic builds only (make DIAG=1)
+#endif
     const long long tStart = dbg ? clock64() : 0;
     const LMState* st = d.st;
     if (st->done) return;

@@ -37,6 +37,7 @@ SYMBOLS = (
     "cugo_b200_get_last_timing", "cugo_b200_stream", "cugo_b200_profile_trial", "cugo_b200_update_measurements",
     "cugo_b200_debug_counters", "cugo_b200_get_factor_stats", "cugo_b200_comm_unique_id", "cugo_b200_comm_init",
     "cugo_b200_chi2_noalloc", "cugo_b200_set_outlier_threshold", "cugo_b200_update_edges", "cugo_b200_get_outliers",
+    "cugo_b200_set_option",
 )
 
 _lib = None
@@ -244,6 +245,10 @@ class BlockSolver:
         self._ck(self.lib.cugo_b200_profile_trial(self.h, cap, names, ln, _p(ms, C.c_double), C.byref(n)))
         raw = names.raw
         return [(raw[i * ln:(i + 1) * ln].split(b"\0")[0].decode(), float(ms[i])) for i in range(n.value)]
+
+    def set_option(self, name, value):
+        """Scheduling variants of the trial (include/cugo_b200.h: cugo_b200_set_option)."""
+        self._ck(self.lib.cugo_b200_set_option(self.h, name.encode(), int(value)))
 
     def update_measurements(self, set_idx, meas, omega):
         meas, omega = _f64(meas), _f64(omega)

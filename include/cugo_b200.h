@@ -174,9 +174,15 @@ int cugo_b200_update_measurements(cugo_b200_solver* s, int set_id, const double*
  * factorisation (Cholesky of the diagonal blocks + rows below, forward substitution included), symmetric
  * updates, backward substitution, and the number of doubles stored in L */
 int cugo_b200_get_factor_stats(cugo_b200_solver* s, double stats[4]);
-/* diagnostics: phase timestamps (SM clock) the factorisation kernels record per tree level when the
- * environment has CUGO_B200_DEBUG=1: 8 slots per level, up to 64 levels */
+/* diagnostics: phase timestamps (SM clock) the factorisation kernels record per tree level -- only in a diagnostic build
+ * of the library (make DIAG=1, run with CUGO_B200_DEBUG=1); the shipped build returns CUGO_B200_EUNSUPPORTED */
 int cugo_b200_debug_counters(long long* out, int n);
+/* scheduling variants of the LM trial, for A/B measurements and the parity test that checks every variant: name one of
+ * "pdl" (programmatic dependent launch, else plain stream order), "fuse_build" (both passes of the system build in
+ * one launch), "panel_dc" (decoupled diagonal chain in the panel kernel), "zinv" / "bwd_split" (backward solves with the
+ * inverse of L11 / shared by several CTAs), "parallel_symbolic" (0: the sequential statement of the analysis,
+ * csrc/symbolic.h, run by one device thread).  All default to 1; changing one rebuilds the structure and the graph. */
+int cugo_b200_set_option(cugo_b200_solver* s, const char* name, int value);
 /* the solver's CUDA stream (cudaStream_t) for callers that time or chain work on it */
 void* cugo_b200_stream(cugo_b200_solver* s);
 

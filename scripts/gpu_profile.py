@@ -31,10 +31,14 @@ for nm in ("chol_diag", "chol_trsm", "chol_panel", "chol_update", "chol_bwd"):
     v = np.round([ms for k, ms in prof if k == nm], 3).tolist()
     if v:
         print("  %-12s" % nm, v)
+DIAG = False
 if os.environ.get("CUGO_B200_DEBUG"):
     import ctypes as C
     a = (C.c_longlong * 8192)()
-    s.lib.cugo_b200_debug_counters(a, 8192)
+    DIAG = s.lib.cugo_b200_debug_counters(a, 8192) == 0      # -5: not a diagnostic build (make DIAG=1)
+    if not DIAG:
+        print("(phase clocks need a diagnostic build of the library: make -C cuda-bundle-adjustment_b200 clean all DIAG=1)")
+if DIAG:
     cyc = np.array(a[:s.sizes()["P"]], dtype=np.int64)
     print("schur rows: cycles per row  mean %.0f  median %.0f  p99 %.0f  max %.0f  (sum/148/2 = %.0f)" % (
         cyc.mean(), np.median(cyc), np.percentile(cyc, 99), cyc.max(), cyc.sum() / 296))
@@ -59,7 +63,7 @@ for rep in range(5):
     ms, nk = s.last_timing()
     print("optimize(10): %.3f ms device, %d kernels, %.3f ms/iter, %.2f M edges/s" % (ms, nk, ms / len(chi), prob.n_edges * len(chi) / ms / 1e3))
 
-if os.environ.get("CUGO_B200_DEBUG"):
+if DIAG:
     # timeline of the last trial of the last optimize() (graph, programmatic dependent launch): CTA 0 of every level
     import ctypes as C
     a = (C.c_longlong * 512)()

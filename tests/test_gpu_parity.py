@@ -205,26 +205,24 @@ def test_full_size_properties(graphs, gpu):
     np.testing.assert_allclose(chi_g, chi_o, rtol=CHI2_RTOL)
 
 
-SWITCHES = ["CUGO_B200_PDL", "CUGO_B200_FUSEBUILD", "CUGO_B200_PANELDC", "CUGO_B200_ZINV", "CUGO_B200_BWDSPLIT", "CUGO_B200_SYM"]
+SWITCHES = ["pdl", "fuse_build", "panel_dc", "zinv", "bwd_split", "parallel_symbolic"]
 
 
 @pytest.mark.parametrize("name", ["loop", "kitti07"])
-def test_engine_switches_agree(graphs, gpu, monkeypatch, name):
+def test_engine_switches_agree(graphs, gpu, name):
     """Every scheduling variant of the trial (programmatic dependent launch, fused build, decoupled panel chain,
-    inverse-based and shared backward solves; read from the environment when the structure is built) gives the
-    oracle's chi2 trajectory; with all of them off the kernels run in plain stream order."""
+    inverse-based and shared backward solves, parallel symbolic analysis; cugo_b200_set_option) gives the oracle's chi2
+    trajectory; with all of them off the kernels run in plain stream order."""
     g, prob = graphs(name)
     s, o = gpu(prob)
     chi_ref, _, tr_ref = s.optimize(6)
     chi_o, _, _ = o.optimize(6)
     np.testing.assert_allclose(chi_ref, chi_o, rtol=CHI2_RTOL)
     for off in [[v] for v in SWITCHES] + [SWITCHES]:
-        for v in off:
-            monkeypatch.setenv(v, "0")
         s2, _ = gpu(prob)
-        chi, _, tr = s2.optimize(6)
         for v in off:
-            monkeypatch.delenv(v)
+            s2.set_option(v, 0)
+        chi, _, tr = s2.optimize(6)
         np.testing.assert_allclose(chi, chi_ref, rtol=CHI2_RTOL, err_msg=str(off))
         np.testing.assert_array_equal(tr, tr_ref)
         s2.close()
