@@ -149,6 +149,7 @@ def run_ours(args, rank, world):
         prob = pack.pack(g)
         ds = cdist.DistBlockSolver(prob, dev)
         s = ds.s
+        s.set_option("dist_factor", args.dist_factor)
         shard_prob = ds.shard.prob
     t0 = time.perf_counter()
     s.build_structure()
@@ -241,12 +242,33 @@ def run_ours(args, rank, world):
                       "chi2_final_1gpu": float(chi1[-1]), "chi2_final_ngpu": float(chiN[-1])}
             s1.close()
         barrier()
+        # (c) --dist-compare: the same run with the factorisation replicated on every rank (dist_factor 0)
+        if args.dist_compare:
+            s.set_option("dist_factor", 0)
+            s.build_structure()
+            for _ in range(args.warmup):
+                one_step()
+            barrier()
+            tr_ = 0.0
+            for _ in range(args.steps):
+                ms, _, cr = one_step()
+                tr_ += ms
+            barrier()
+            tt = torch.tensor([tr_], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dist_cmp = {"dist_factor": 0, "ms_per_step": float(tt.item()) / args.steps,
+                        "value": E * len(cr) * args.steps / (float(tt.item()) * 1e-3), "chi2_final": float(cr[-1]),
+                        "what": "same graph and shards, factorisation replicated on every rank"}
+        else:
+            dist_cmp = None
+    if world > 1 and not args.skip_other:
         omode = "strong" if args.scaling == "weak" else "weak"
         omult = world if omode == "weak" else 1
         g2 = synth.make_graph(args.workload, n_landmarks=L0 * omult, n_edges=E0 * omult, n_stereo=S0 * omult)
         prob2 = pack.pack(g2)
         ds2 = cdist.DistBlockSolver(prob2, dev, shard=cdist.shard_problem(prob2, world, rank), share_comm=ds)
         s2, sp2 = ds2.s, ds2.shard.prob
+        s2.set_option("dist_factor", args.dist_factor)
         s2.build_structure()
 
         def step2():
@@ -291,7 +313,7 @@ def run_ours(args, rank, world):
             "roofline": None, "cpu_baseline": None, "chi2_final": float(chi[-1]),
             "value_optimize_only": value,
             "parity_vs_1gpu": parity, "chi2_rel_err_vs_1gpu": parity["chi2_rel_err_vs_1gpu"] if parity else None,
-            "other_scaling": other,
+            "other_scaling": other, "dist_factor": args.dist_factor, "dist_compare": dist_cmp,
             "note": "roofline / cpu_baseline are reported by the N=1 line (rank-0-at-N=1 only); parity_vs_1gpu: the same "
                     "graph solved by a 1-GPU solver on rank 0 outside the timed region; other_scaling: the %s-scaling "
                     "run of the same shape in this process group" % (other["scaling"] if other else "-")}
@@ -517,6 +539,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=WORKLOAD)
     ap.add_argument("--f32", action="store_true", help="USE_FLOAT32 mode: single-precision Hpl storage (1 GPU)")
+    ap.add_argument("--dist-factor", type=int, default=1,
+                    help="N > 1: factorisation distributed by assembly-tree subtree: 0 never, 1 when the factor flops make it pay "
+                         "(default), 2 always")
+    ap.add_argument("--dist-compare", action="store_true", help="N > 1: also time the run with the factorisation replicated")
+    ap.add_argument("--skip-other", action="store_true", help="N > 1: do not time the other scaling mode (large workloads)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: weak = N x the landmarks/edges of the named shape (default), strong = the named shape itself; "
                          "the other mode is timed too and reported under other_scaling")

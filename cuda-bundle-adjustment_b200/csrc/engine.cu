@@ -78,6 +78,9 @@ struct NcclApi {
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
     bool load(std::string& err) {
         if (lib) return true;
@@ -91,6 +94,9 @@ struct NcclApi {
         CommDestroy = (decltype(CommDestroy))sym("ncclCommDestroy");
         AllReduce = (decltype(AllReduce))sym("ncclAllReduce");
         AllGather = (decltype(AllGather))sym("ncclAllGather");
+        Broadcast = (decltype(Broadcast))sym("ncclBroadcast");
+        GroupStart = (decltype(GroupStart))sym("ncclGroupStart");
+        GroupEnd = (decltype(GroupEnd))sym("ncclGroupEnd");
         GetErrorString = (decltype(GetErrorString))sym("ncclGetErrorString");
         if (!ok) { err = "libnccl lacks an expected symbol"; lib = nullptr; }
         return ok;
@@ -211,6 +217,15 @@ struct Solver {
     DBuf<unsigned long long> lkeys, gkeysAll, gkeysSorted, gkeys;
     DBuf<int> gHead, gIdx, gRowOf, gColInd, gRowPtr, hscSlot, d_cnt;
     DBuf<double> redA, redC, HscPartBuf;
+    // factorisation distributed by assembly-tree subtree (several ranks): supernodes on tree levels
+    // >= distLc are factorised by every rank, the subtrees below are dealt to the ranks
+    int distMode = 1;              // option "dist_factor": 0 never, 1 when the factor flops make it pay, 2 always
+    int distLc = 0;                // 0: not distributed
+    std::vector<int> h_own;        // [nsn] owner rank, -1 = every rank
+    struct Bcast { size_t off, count; int root; };
+    std::vector<Bcast> distBcast;  // update matrices of the subtree roots, sent by their owners before level distLc
+    DBuf<int> zr_levelPtr, zr_levelSn, zr_trsmPtr, zr_updPtr, zr_colOwn;
+    void planDistFactor();
     int nblkG = 0;
     void commInit(int n, int r, const char* id);
     void allReduceSum(double* buf, size_t n) {
@@ -648,7 +663,7 @@ void Solver::buildStructure() {
         k_lower_bounds<<<divUp(nP + 1, TB), TB, 0, stream>>>(gRowOf, nblkG, nP, gRowPtr);
         k_map_slots<<<divUp(nblk, TB), TB, 0, stream>>>(lkeys, nblk, gkeys, nblkG, hscSlot);
         gRowPtrP = gRowPtr; gColIndP = gColInd;
-        redA.alloc((size_t)6 * nP + nranks); redC.alloc(2);
+        redA.alloc((size_t)6 * nP + nranks); redC.alloc(4);
     }
 
     lap("pose-major Hpl view, row units");
@@ -706,6 +721,9 @@ void Solver::buildStructure() {
     CK(cudaMemcpyAsync(h_updPtr.data(), z_updPtr.p, sizeof(int) * (nsn + 1), cudaMemcpyDeviceToHost, stream));
     CK(cudaMemcpyAsync(&h_nchild, z_childPtr.p + nsn, sizeof(int), cudaMemcpyDeviceToHost, stream));
     CK(cudaStreamSynchronize(stream));
+    c.levelPtr = z_levelPtr; c.levelSn = z_levelSn; c.trsmPtr = z_trsmPtr; c.updPtr = z_updPtr;
+    distLc = 0; distBcast.clear(); h_own.clear();
+    if (nranks > 1 && distMode > 0) planDistFactor();
     if (getenv("CUGO_B200_DEBUG")) {
         fprintf(stderr, "[cugo_b200] elimination tree: %d supernodes, %d levels, max front %d block rows; per level "
                         "(supernodes / panel CTAs / update tiles / widest):", nsn, counts.nlev, counts.maxFront);
@@ -762,9 +780,9 @@ void Solver::buildStructure() {
 
     c.P = P; c.nsn = nsn; c.nlev = counts.nlev;
     c.perm = y_verts; c.snStart = y_snStart; c.snRowPtr = y_snRowPtr; c.snRows = y_snRows;
-    c.levelPtr = z_levelPtr; c.levelSn = z_levelSn; c.Lptr = z_Lptr; c.Uptr = z_Uptr; c.childPtr = z_childPtr;
+    c.Lptr = z_Lptr; c.Uptr = z_Uptr; c.childPtr = z_childPtr;     // (levelPtr / levelSn / trsmPtr / updPtr: set with the schedule above)
     c.childIdx = z_childIdx; c.invPtr = z_invPtr; c.inv = z_inv; c.snBlkPtr = z_snBlkPtr; c.asmBlk = z_asmBlk;
-    c.asmRow = z_asmRow; c.asmCol = z_asmCol; c.trsmPtr = z_trsmPtr; c.updPtr = z_updPtr;
+    c.asmRow = z_asmRow; c.asmCol = z_asmCol;
     c.L = cL; c.U = cU; c.xperm = cX; c.Winv = cW; c.Zinv = cZ; c.bwdPart = cPart; c.bwdCnt = cCnt;
     { const char* e = getenv("CUGO_B200_DEBUG"); c.dbg = e ? atoi(e) : 0; }   // diagnostic builds (make DIAG=1): 1 phase stamps, 3 also a worker warp's view
 
@@ -793,6 +811,130 @@ void Solver::buildStructure() {
     captureSlot();
     structDirty = false;            // only once the trial graph exists
     lap("graph capture");
+}
+
+// ---------------------------------------------------------------------------
+// Factorisation distributed by assembly-tree subtree (several ranks; no counterpart in the reference, which is
+// single-GPU: src/cuda_device.cpp:264-282).  Every rank holds the same symbolic analysis.  A cut level Lc splits the
+// assembly tree: supernodes on levels >= Lc are factorised by EVERY rank (the replicated top: its fronts are what all
+// subtrees feed, and solving it everywhere saves a broadcast of the top of x), the subtrees hanging below the cut are
+// dealt to the ranks by estimated factor flops (longest-processing-time first).  A rank runs the panel / update /
+// backward kernels of its own and of the replicated supernodes only (filtered level schedule).  Two exchanges per
+// trial carry the coupling: the update matrices of the subtree roots are broadcast by their owners before level Lc,
+// and after the backward solves the owners' pieces of x are summed (every other rank contributes zeros: exact).
+// Lc is chosen to minimise replicated + max-per-rank flops; 0 (= today's fully replicated factorisation) when that does
+// not pay, e.g. at the KITTI-00 size where the tree's critical path, not the flops, is the bound.
+// ---------------------------------------------------------------------------
+__global__ void k_col_owner(const int* colToSn, const int* own, int P, int* colOwn) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < P) colOwn[j] = own[colToSn[j]];
+}
+// zero the pieces of the permuted solution this rank does not answer for (replicated columns: rank 0 answers)
+__global__ void k_x_mask(const int* colOwn, int P, int rank, double* xperm) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 6 * P) return;
+    const int o = colOwn[i / 6];
+    if (!(o == rank || (o < 0 && rank == 0))) xperm[i] = 0.0;
+}
+__global__ void k_x_scatter(const double* xperm, const int* perm, int P, double* x) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 6 * P) x[(size_t)perm[i / 6] * 6 + i % 6] = xperm[i];
+}
+
+void Solver::planDistFactor() {
+    const int nsn = counts.nsn, nlev = counts.nlev;
+    std::vector<int> par(nsn), lev(nsn), st(nsn + 1), rp(nsn + 1), lsn(nsn);
+    std::vector<long long> uptr(nsn + 1);
+    CK(cudaMemcpyAsync(par.data(), y_snParent.p, sizeof(int) * nsn, cudaMemcpyDeviceToHost, stream));
+    CK(cudaMemcpyAsync(lev.data(), y_snLevel.p, sizeof(int) * nsn, cudaMemcpyDeviceToHost, stream));
+    CK(cudaMemcpyAsync(st.data(), y_snStart.p, sizeof(int) * (nsn + 1), cudaMemcpyDeviceToHost, stream));
+    CK(cudaMemcpyAsync(rp.data(), y_snRowPtr.p, sizeof(int) * (nsn + 1), cudaMemcpyDeviceToHost, stream));
+    CK(cudaMemcpyAsync(lsn.data(), z_levelSn.p, sizeof(int) * nsn, cudaMemcpyDeviceToHost, stream));
+    CK(cudaMemcpyAsync(uptr.data(), z_Uptr.p, sizeof(long long) * (nsn + 1), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    std::vector<double> fl(nsn);
+    double total = 0.0;
+    for (int t = 0; t < nsn; t++) {
+        const double ncd = 6.0 * (st[t + 1] - st[t]), rd = 6.0 * (rp[t + 1] - rp[t]) + 1.0;
+        fl[t] = ncd * ncd * ncd / 3.0 + rd * ncd * ncd + rd * rd * ncd;
+        total += fl[t];
+    }
+    // component (subtree below the cut) of every supernode for a cut level L: follow parents while the parent's level < L
+    auto evaluate = [&](int L, std::vector<int>* ownOut) {
+        std::vector<int> root(nsn, -1);
+        std::vector<double> w(nsn, 0.0);
+        double repl = 0.0;
+        for (int t = nsn - 1; t >= 0; t--) {          // parents have larger ids than their children
+            if (lev[t] >= L) { repl += fl[t]; continue; }
+            const int p = par[t];
+            root[t] = (p >= 0 && lev[p] < L) ? root[p] : t;
+        }
+        for (int t = 0; t < nsn; t++) if (root[t] >= 0) w[root[t]] += fl[t];
+        std::vector<int> roots;
+        for (int t = 0; t < nsn; t++) if (root[t] == t) roots.push_back(t);
+        std::sort(roots.begin(), roots.end(), [&](int a, int b) { return w[a] != w[b] ? w[a] > w[b] : a < b; });
+        std::vector<double> load(nranks, 0.0);
+        std::vector<int> rootOwner(nsn, -1);
+        for (int r : roots) {
+            int best = 0;
+            for (int k = 1; k < nranks; k++) if (load[k] < load[best]) best = k;
+            load[best] += w[r];
+            rootOwner[r] = best;
+        }
+        if (ownOut) {
+            ownOut->assign(nsn, -1);
+            for (int t = 0; t < nsn; t++) if (root[t] >= 0) (*ownOut)[t] = rootOwner[root[t]];
+        }
+        return repl + *std::max_element(load.begin(), load.end());
+    };
+    int bestL = 0;
+    double bestT = total;
+    for (int L = 1; L < nlev; L++) {
+        const double T = evaluate(L, nullptr);
+        if (T < bestT) { bestT = T; bestL = L; }
+    }
+    // below ~5 GFLOP per factorisation the tree's critical path is the bound, not the flops: keep it replicated
+    const bool pays = bestL > 0 && bestT < 0.7 * total && (distMode >= 2 || total > 5e9);
+    if (getenv("CUGO_B200_DEBUG"))
+        fprintf(stderr, "[cugo_b200] distributed factorisation: %.2f GFLOP per factorisation, best cut level %d of %d -> %.2f GFLOP "
+                        "per rank (%s)\n", total * 1e-9, bestL, nlev, bestT * 1e-9, pays ? "on" : "off");
+    if (!pays) return;
+    distLc = bestL;
+    evaluate(bestL, &h_own);
+    // filtered level schedule of this rank: its own and the replicated supernodes, in the order of the full schedule
+    std::vector<int> fPtr(nlev + 1, 0), fSn, fTrsm, fUpd;
+    int a = 0, b = 0;
+    for (int l = 0; l < nlev; l++) {
+        for (int q = h_levelPtr[l]; q < h_levelPtr[l + 1]; q++) {
+            const int t = lsn[q];
+            if (h_own[t] >= 0 && h_own[t] != rank) continue;
+            fSn.push_back(t); fTrsm.push_back(a); fUpd.push_back(b);
+            const int rt = rp[t + 1] - rp[t];
+            const int ns = (rt + CHOL_RB - 1) / CHOL_RB;
+            a += ns > 0 ? ns : 1;
+            if (rt > 0) { const int n2 = (rt + CHOL_TB) / CHOL_TB; b += n2 * (n2 + 1) / 2; }
+        }
+        fPtr[l + 1] = (int)fSn.size();
+    }
+    fTrsm.push_back(a); fUpd.push_back(b);
+    const int nf = (int)fSn.size();
+    zr_levelPtr.alloc(nlev + 1); zr_levelSn.alloc(std::max(nf, 1)); zr_trsmPtr.alloc(nf + 1); zr_updPtr.alloc(nf + 1);
+    zr_colOwn.alloc(nP); y_ak1.alloc(std::max(nsn, nblkG));
+    CK(cudaMemcpyAsync(zr_levelPtr.p, fPtr.data(), sizeof(int) * (nlev + 1), cudaMemcpyHostToDevice, stream));
+    if (nf) CK(cudaMemcpyAsync(zr_levelSn.p, fSn.data(), sizeof(int) * nf, cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpyAsync(zr_trsmPtr.p, fTrsm.data(), sizeof(int) * (nf + 1), cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpyAsync(zr_updPtr.p, fUpd.data(), sizeof(int) * (nf + 1), cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpyAsync(y_ak1.p, h_own.data(), sizeof(int) * nsn, cudaMemcpyHostToDevice, stream));
+    k_col_owner<<<divUp(nP, 256), 256, 0, stream>>>(y_colToSn, y_ak1, nP, zr_colOwn);
+    CK(cudaStreamSynchronize(stream));
+    h_levelPtr = fPtr; h_trsmPtr = fTrsm; h_updPtr = fUpd;
+    c.levelPtr = zr_levelPtr; c.levelSn = zr_levelSn; c.trsmPtr = zr_trsmPtr; c.updPtr = zr_updPtr;
+    // what crosses the cut upwards: the update matrix of every subtree root that has a (replicated) parent
+    for (int t = 0; t < nsn; t++) {
+        if (h_own[t] < 0 || par[t] < 0 || lev[par[t]] < distLc) continue;
+        const long long u = 6LL * (rp[t + 1] - rp[t]) + 1;
+        distBcast.push_back({(size_t)uptr[t], (size_t)(u * u), h_own[t]});
+    }
 }
 
 // Symbolic analysis as parallel device work (kernels_sym.cuh); the arrays are those of symbolic.h, bit for bit.
@@ -906,11 +1048,20 @@ void Solver::enqueueSolve() {
     // to finish); the top three keep the blocked substitution
     const bool zOn = zinvOn && pdl && !profiling;
     const int zTop = c.nlev - 4;
+    bool forked = false;             // the side branch carries at least one k_chol_zinv
     for (int lev = 0; lev < c.nlev; lev++) {
         const int q0 = h_levelPtr[lev], q1 = h_levelPtr[lev + 1];
         const int ncLev = 6 * h_levMaxNt[lev];
+        if (distLc > 0 && lev == distLc && !distBcast.empty()) {
+            // the subtrees below the cut are complete on their owners: their roots' update matrices go to every rank
+            NK(g_nccl.GroupStart());
+            for (const Bcast& bc : distBcast)
+                NK(g_nccl.Broadcast(c.U + bc.off, c.U + bc.off, bc.count, ncclFloat64, bc.root, comm, stream));
+            NK(g_nccl.GroupEnd());
+        }
+        if (q1 == q0) continue;          // (distributed: none of this level's supernodes is this rank's)
         launch(panelDC ? k_chol_panel3<true> : k_chol_panel3<false>, h_trsmPtr[q1] - h_trsmPtr[q0], PANEL3_TPB,
-               (size_t)PANEL_LD * ncLev * 8, d, c, lev, (pdl && !profiling && lev > 0) ? 1 : 0);
+               (size_t)PANEL_LD * ncLev * 8, d, c, lev, (pdl && !profiling && lev > 0 && lev != distLc) ? 1 : 0);
         mark("chol_panel");
         if (zOn && lev <= zTop) {      // L11^-1 of the level on the low-priority branch, beside the rest of the factorisation
             CK(cudaEventRecord(evFork, stream));
@@ -918,6 +1069,7 @@ void Solver::enqueueSolve() {
             const size_t zb = (2 * (size_t)ncLev * (ncLev + 1) + 21 * CHOL_MAXW + 36 * 8) * 8;
             k_chol_zinv<256><<<q1 - q0, 256, zb, side>>>(d, c, lev);
             kernelsPerSlot++;
+            forked = true;
         }
         const int nUpd = h_updPtr[q1] - h_updPtr[q0];
         if (nUpd > 0) {
@@ -929,16 +1081,23 @@ void Solver::enqueueSolve() {
     for (int lev = c.nlev - 1; lev >= 0; lev--) {
         const int ncLev = 6 * h_levMaxNt[lev];
         const size_t bytes = ((size_t)ncLev * (ncLev + 1) + ncLev + 21 * CHOL_MAXW + 6 * (size_t)maxRt) * 8;
-        if (zOn && lev == zTop) {
+        if (zOn && forked && lev == zTop) {
             CK(cudaEventRecord(evJoin, side));
             CK(cudaStreamWaitEvent(stream, evJoin, 0));
         }
         // few supernodes on a level: several CTAs share the L21^T x_R product of each
         const int nsnLev = h_levelPtr[lev + 1] - h_levelPtr[lev];
+        if (nsnLev == 0) continue;
         const int G = bwdSplit ? std::max(1, std::min(BWD_MAXG, 148 / nsnLev)) : 1;
         launch(k_chol_bwd3<256>, nsnLev * G, 256, bytes, d, c, lev, (pdl && !profiling && lev < c.nlev - 1) ? 1 : 0,
                (zOn && lev <= zTop) ? 1 : 0, G);
         mark("chol_bwd");
+    }
+    if (distLc > 0) {      // every rank gets the whole x: each piece from the rank that solved it
+        k_x_mask<<<divUp(6 * d.nP, 256), 256, 0, stream>>>(zr_colOwn, d.nP, rank, c.xperm);
+        allReduceSum(c.xperm, (size_t)6 * d.nP);
+        k_x_scatter<<<divUp(6 * d.nP, 256), 256, 0, stream>>>(c.xperm, c.perm, d.nP, d.x);
+        kernelsPerSlot += 2;
     }
     if (f32) launch(k_backsub<LM_CHUNK, float>, d.nChunks, LM_CHUNK, 0, d);
     else launch(k_backsub<LM_CHUNK, double>, d.nChunks, LM_CHUNK, 0, d);
@@ -955,7 +1114,7 @@ void Solver::enqueueSlot() {
     launch(k_errors<256>, d.errGrid, 256, 0, d, sp, 1, 1); mark("errors");
     if (nranks > 1) {
         launch(k_lm_sums<256>, 1, 256, 0, d); mark("lm_sums");
-        allReduceSum(d.redC, 2);
+        allReduceSum(d.redC, 3);
     }
     launch(k_lm_decide<1024>, 1, 1024, 0, d); mark("lm_decide");
 }
@@ -967,7 +1126,7 @@ int Solver::profileSlot(int cap, char* names, int nameLen, double* ms) {
     ensureStructure();
     use();
     k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
-    if (nranks > 1) { k_lm_sums<256><<<1, 256, 0, stream>>>(d); allReduceSum(d.redC, 2); }
+    if (nranks > 1) { k_lm_sums<256><<<1, 256, 0, stream>>>(d); allReduceSum(d.redC, 3); }
     k_lm_begin<256><<<1, 256, 0, stream>>>(d, 1);
     const int saved = kernelsPerSlot;
     profiling = true;
@@ -1125,8 +1284,8 @@ void Solver::commInit(int n, int r, const char* id) {
     NK(g_nccl.CommInitRank(&comm, n, uid, r));
     nranks = n; rank = r;
     // one collective outside any capture: connections are set up before the trial graph is recorded
-    redC.alloc(2);
-    CK(cudaMemsetAsync(redC.p, 0, 2 * sizeof(double), stream));
+    redC.alloc(4);
+    CK(cudaMemsetAsync(redC.p, 0, 4 * sizeof(double), stream));
     allReduceSum(redC.p, 2);
     CK(cudaStreamSynchronize(stream));
     structDirty = true;
@@ -1204,7 +1363,7 @@ int Solver::optimize(int niter, int cap, double* chi2, double* lambda, int* tria
     CK(cudaEventRecord(ev0, stream));
     long launched = 0;
     k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
-    if (nranks > 1) { k_lm_sums<256><<<1, 256, 0, stream>>>(d); allReduceSum(d.redC, 2); launched++; }
+    if (nranks > 1) { k_lm_sums<256><<<1, 256, 0, stream>>>(d); allReduceSum(d.redC, 3); launched++; }
     k_lm_begin<256><<<1, 256, 0, stream>>>(d, niter);
     launched += 2;
     int slots = 0;
@@ -1850,9 +2009,10 @@ int cugo_b200_set_option(cugo_b200_solver* s, const char* name, int value) {
     return guarded(s, [&](Solver& S) {
         if (!name) throw cugo_b200::ArgError("set_option: null name");
         const std::string n(name);
+        if (n == "dist_factor") { S.distMode = value; S.structDirty = true; return; }
         bool* f = n == "pdl" ? &S.pdl : n == "fuse_build" ? &S.fuseBuild : n == "panel_dc" ? &S.panelDC : n == "zinv" ? &S.zinvOn
                 : n == "bwd_split" ? &S.bwdSplit : n == "parallel_symbolic" ? &S.symParallel : nullptr;
-        if (!f) throw cugo_b200::ArgError("set_option: unknown option '" + n + "' (pdl, fuse_build, panel_dc, zinv, bwd_split, parallel_symbolic)");
+        if (!f) throw cugo_b200::ArgError("set_option: unknown option '" + n + "' (pdl, fuse_build, panel_dc, zinv, bwd_split, parallel_symbolic, dist_factor)");
         *f = value != 0;
         S.structDirty = true;           // the options shape the structure and the trial graph
     });

@@ -73,12 +73,13 @@ __global__ void __launch_bounds__(TPB) k_lm_decide(Dev d) {
     for (int i = threadIdx.x; i < d.nChunks; i += TPB) s += d.scalePartial[i];
     double scaleRaw = block_sum<TPB>(s, sh);
     if (threadIdx.x != 0) return;
-    if (d.nranks > 1) { Fhat = d.redC[0]; scaleRaw = d.redC[1]; }   // k_lm_sums + all-reduce ran before
+    bool fail = st->fail != 0;
+    if (d.nranks > 1) { Fhat = d.redC[0]; scaleRaw = d.redC[1]; fail = d.redC[2] > 0.0; }   // k_lm_sums + all-reduce ran before
     const int maxq = 10;
     const double F = st->F;
     const double scale = scaleRaw + 1e-3;
     const double Fdiff = Fhat - F;
-    const double rho = st->fail ? -1.0 : (F - Fhat) / scale;
+    const double rho = fail ? -1.0 : (F - Fhat) / scale;
     st->Fhat = Fhat; st->scale = scale; st->rho = rho;
     bool endIter = false;
     int q = st->q;
@@ -136,7 +137,9 @@ __global__ void __launch_bounds__(TPB) k_pack_A(Dev d) {
     }
 }
 // redC = [chi2 of the rank's edges | gain denominator: pose part with the rank's partial bp (lambda term on
-// rank 0 only) + the rank's landmarks]; both are linear in the per-rank parts, so SUM gives the global values.
+// rank 0 only) + the rank's landmarks | this rank's factorisation hit a non-positive pivot]; the first two are linear
+// in the per-rank parts, so SUM gives the global values; the third is > 0 iff any rank failed (with the factorisation
+// distributed by subtree a pivot fails on its owner only, and every rank must take the same decision).
 template <int TPB>
 __global__ void __launch_bounds__(TPB) k_lm_sums(Dev d) {
     __shared__ double sh[TPB / 32];
@@ -147,7 +150,7 @@ __global__ void __launch_bounds__(TPB) k_lm_sums(Dev d) {
     for (int i = threadIdx.x; i < 6 * d.nP; i += TPB) s += d.x[i] * (lam * d.x[i] + d.b[i]);
     for (int i = threadIdx.x; i < d.nChunks; i += TPB) s += d.scalePartial[i];
     s = block_sum<TPB>(s, sh);
-    if (threadIdx.x == 0) { d.redC[0] = chi; d.redC[1] = s; }
+    if (threadIdx.x == 0) { d.redC[0] = chi; d.redC[1] = s; d.redC[2] = d.st->fail ? 1.0 : 0.0; }
 }
 
 // ---- helpers of the host-driven (staged) API ---------------------------------

@@ -16,7 +16,8 @@ import numpy as np
 from .pack import Problem
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libcugo_b200.so")
+# CUGO_B200_LIB: another build of the same library (A/B measurements of kernel variants: scripts/ab_lib.sh)
+LIB_PATH = os.environ.get("CUGO_B200_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "libcugo_b200.so")
 
 RK = dict(none=0, cauchy=1, tukey=2, huber=3)
 STRUCT = dict(hpl_colptr=0, hpl_rowind=1, hsc_rowptr=2, hsc_colind=3, csr_rowptr=4, csr_colind=5,

@@ -17,12 +17,14 @@ def main():
     name, niter, out = sys.argv[1], int(sys.argv[2]), sys.argv[3]
     robust = sys.argv[4] if len(sys.argv) > 4 else "none"
     delta = float(sys.argv[5]) if len(sys.argv) > 5 else 1.0
+    dist_factor = int(sys.argv[6]) if len(sys.argv) > 6 else 1     # 2: force the subtree-distributed factorisation
     dev = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl")
     try:
         prob = pack.pack(synth.make_graph(name))
         s = cdist.DistBlockSolver(prob, dev, robust=robust, delta=delta)
+        s.s.set_option("dist_factor", dist_factor)
         chi, lam, tr = s.optimize(niter)
         chi2, _, _ = (None, None, None)
         poses, lms = s.estimates()
