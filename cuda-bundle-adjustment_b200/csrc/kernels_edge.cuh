@@ -79,7 +79,7 @@ template <int TPB, typename HT>
 __device__ __forceinline__ void build_lm_cta(const Dev& d, const SetParams& sp, const int blk) {
     __shared__ double acc[LM_CHUNK * 9];      // per landmark: H00 H10 H11 H20 H21 H22 b0 b1 b2
     __shared__ double val[9 * TPB];           // per edge of the tile, component-major
-    __shared__ HT hst[TPB * 18];              // Hpl staging
+    __shared__ __align__(16) HT hst[TPB * 18];   // Hpl staging
     __shared__ double shm[TPB / 32];
     const LMState* st = d.st;
     if (st->done || !st->needBuild) return;
@@ -162,13 +162,26 @@ __device__ __forceinline__ void build_lm_cta(const Dev& d, const SetParams& sp, 
 #pragma unroll
             for (int i = 0; i < 9; i++) a[i] += s[i];
         }
-        // coalesced store of this tile's Hpl blocks
+        // store of this tile's Hpl blocks: they are one contiguous run of the CSC array
         const int last = (base + TPB < e1) ? base + TPB : e1;
         const int cnt = (d.s_hplPre[last] - pre0) * 18;
         HT* __restrict__ dst = HplOf<HT>::get(d) + (size_t)pre0 * 18;
-        for (int i = tid; i < cnt; i += TPB) dst[i] = hst[i];
+        if constexpr (sizeof(HT) == 8) {
+            // FP64 blocks (144 bytes each, 16-byte aligned): ONE bulk copy shared -> global by the TMA unit (SASS: UBLKCP)
+            // instead of 18 load/store pairs per thread; the staging buffer is free again once the copy has read it
+            if (tid == 0 && cnt > 0) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // the generic-proxy writes above -> async proxy
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst),
+                             "r"((unsigned)__cvta_generic_to_shared(hst)), "r"((unsigned)cnt * 8u) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            }
+        } else {
+            for (int i = tid; i < cnt; i += TPB) dst[i] = hst[i];
+        }
         __syncthreads();
     }
+    if (sizeof(HT) == 8 && tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // the bulk stores have landed
     // write Hll (full 3x3, column-major) and bl for the free landmarks of the chunk
     const int nlf = (l1 < d.nL ? l1 : d.nL) - l0;
     const int map9[9] = {0, 1, 3, 1, 2, 4, 3, 4, 5};
