@@ -48,6 +48,19 @@ __global__ void thr(double* out, long long* cyc, double seed) {
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
     if (threadIdx.x == 0 && blockIdx.x == 0) *cyc = t1 - t0;
 }
+// whole-GPU rate: every SM busy, timed with CUDA events (no clock64 involved)
+__global__ void __launch_bounds__(1024) dmma_full(double* out, int iters, double seed) {
+    double x[8], c[8][2];
+    for (int j = 0; j < 8; j++) { x[j] = seed + j + threadIdx.x * 1e-3; c[j][0] = c[j][1] = 0; }
+    double y = 1.0000001;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) dmma(c[j][0], c[j][1], x[j], y);
+    }
+    double s = 0;
+    for (int j = 0; j < 8; j++) s += c[j][0] + c[j][1];
+    out[(blockIdx.x * blockDim.x + threadIdx.x) & 0xffff] = s;
+}
 __global__ void ldslat(double* out, long long* cyc, int stride) {
     __shared__ int idx[1024];
     for (int i = threadIdx.x; i < 1024; i += blockDim.x) idx[i] = (i + stride) & 1023;
@@ -81,6 +94,18 @@ int main() {
     }
     ldslat<<<1, 32>>>(out, cyc, 33); cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost); printf("LDS dependent latency %.1f cycles\n", (double)h / N);
     for (int nt = 64; nt <= 256; nt *= 2) { synclat<<<1, nt>>>(cyc); cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost); printf("__syncthreads %d threads: %.1f cycles\n", nt, (double)h / N); }
+    {
+        int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+        cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+        for (int nt = 256; nt <= 1024; nt *= 2) {
+            const int iters = 1 << 15;
+            dmma_full<<<sms, nt>>>(out, 64, 1.25);
+            cudaEventRecord(e0); dmma_full<<<sms, nt>>>(out, iters, 1.25); cudaEventRecord(e1); cudaEventSynchronize(e1);
+            float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+            const double flop = 2.0 * 256 * 8.0 * iters * (nt / 32) * sms;
+            printf("whole-GPU dmma %4d thr/SM x %d SMs: %.2f TFLOP/s (%.3f ms, CUDA events)\n", nt, sms, flop / (ms * 1e-3) / 1e12, ms);
+        }
+    }
     printf("%s\n", cudaGetErrorString(cudaGetLastError()));
     return 0;
 }
