@@ -149,6 +149,7 @@ struct Solver {
     cudaStream_t stream = nullptr;
     cudaStream_t side = nullptr;   // low-priority branch of the trial graph: k_chol_zinv beside the factorisation
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    int panelRB = CHOL_RB;         // option "panel_rb": block rows of L21 per panel CTA (1..CHOL_RB); set before build_structure
     bool bwdSplit = true;          // option "bwd_split" = 0: one CTA per supernode in the backward solve
     bool zinvOn = true;            // option "zinv" = 0: backward solves by blocked substitution on every level
     std::string err;
@@ -709,7 +710,7 @@ void Solver::buildStructure() {
     m.childIdx = z_childIdx; m.invPtr = z_invPtr; m.inv = z_inv; m.snBlkPtr = z_snBlkPtr; m.asmBlk = z_asmBlk;
     m.asmRow = z_asmRow; m.asmCol = z_asmCol;
     z_levMaxNt.alloc(counts.nlev + 1);
-    k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, 0, 0, CHOL_RB, CHOL_TB,
+    k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, 0, 0, panelRB, CHOL_TB,
                                     z_levMaxNt, z_factStats.alloc(4));
     lap("symbolic maps + task tables");
     }
@@ -784,6 +785,7 @@ void Solver::buildStructure() {
     c.childIdx = z_childIdx; c.invPtr = z_invPtr; c.inv = z_inv; c.snBlkPtr = z_snBlkPtr; c.asmBlk = z_asmBlk;
     c.asmRow = z_asmRow; c.asmCol = z_asmCol;
     c.L = cL; c.U = cU; c.xperm = cX; c.Winv = cW; c.Zinv = cZ; c.bwdPart = cPart; c.bwdCnt = cCnt;
+    c.rb = panelRB;
     { const char* e = getenv("CUGO_B200_DEBUG"); c.dbg = e ? atoi(e) : 0; }   // diagnostic builds (make DIAG=1): 1 phase stamps, 3 also a worker warp's view
 
     // dynamic shared memory opt-in for the factorisation kernels
@@ -910,7 +912,7 @@ void Solver::planDistFactor() {
             if (h_own[t] >= 0 && h_own[t] != rank) continue;
             fSn.push_back(t); fTrsm.push_back(a); fUpd.push_back(b);
             const int rt = rp[t + 1] - rp[t];
-            const int ns = (rt + CHOL_RB - 1) / CHOL_RB;
+            const int ns = (rt + panelRB - 1) / panelRB;
             a += ns > 0 ? ns : 1;
             if (rt > 0) { const int n2 = (rt + CHOL_TB) / CHOL_TB; b += n2 * (n2 + 1) / 2; }
         }
@@ -1002,7 +1004,7 @@ void Solver::symbolicParallel(const int* gRowOfP, const int* gRowPtrP, const int
     if (tabBytes > 200 * 1024) throw UnsupportedError("too many supernodes for the shared-memory schedule tables of this version");
     CK(cudaFuncSetAttribute(k_sym_tables, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tabBytes));
     k_sym_tables<<<1, SYM_TPB, tabBytes, stream>>>(nsn, counts.nlev, y_snStart, y_snRowPtr, y_snParent, y_snLevel, m, z_trsmPtr,
-                                                   z_updPtr, CHOL_RB, CHOL_TB, z_levMaxNt, z_factStats.alloc(4), counts.lsize);
+                                                   z_updPtr, panelRB, CHOL_TB, z_levMaxNt, z_factStats.alloc(4), counts.lsize);
     k_sym_inv<<<divUp((long long)nsn * 32, TB), TB, 0, stream>>>(nsn, y_snStart, y_snRowPtr, y_snRows, y_snParent, z_invPtr, z_inv);
     y_ak1.alloc(nblkG); y_ak2.alloc(nblkG); y_av1.alloc(nblkG); y_av2.alloc(nblkG);
     k_sym_asm_keys<<<divUp(nblkG, TB), TB, 0, stream>>>(gRowOfP, gColIndP, nblkG, y_iperm, y_colToSn, y_ak1, y_av1);
@@ -1997,7 +1999,7 @@ int cugo_b200_debug_counters(long long* out, int n) {
     if (!out || n < 0 || n > 64 * 24) return CUGO_B200_EINVAL;
     if (n == 512)
         return cudaMemcpyFromSymbol(out, cugo_b200::g_cholTime, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
-    if (n == 96)
+    if (n == 176)
         return cudaMemcpyFromSymbol(out, cugo_b200::g_cholTrace, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
     return cudaMemcpyFromSymbol(out, cugo_b200::g_cholDbg, sizeof(long long) * n) == cudaSuccess ? CUGO_B200_OK : CUGO_B200_ECUDA;
 #else
@@ -2010,9 +2012,13 @@ int cugo_b200_set_option(cugo_b200_solver* s, const char* name, int value) {
         if (!name) throw cugo_b200::ArgError("set_option: null name");
         const std::string n(name);
         if (n == "dist_factor") { S.distMode = value; S.structDirty = true; return; }
+        if (n == "panel_rb") {
+            if (value < 1 || value > cugo_b200::CHOL_RB) throw cugo_b200::ArgError("set_option: panel_rb must be in [1, 10]");
+            S.panelRB = value; S.structDirty = true; return;
+        }
         bool* f = n == "pdl" ? &S.pdl : n == "fuse_build" ? &S.fuseBuild : n == "panel_dc" ? &S.panelDC : n == "zinv" ? &S.zinvOn
                 : n == "bwd_split" ? &S.bwdSplit : n == "parallel_symbolic" ? &S.symParallel : nullptr;
-        if (!f) throw cugo_b200::ArgError("set_option: unknown option '" + n + "' (pdl, fuse_build, panel_dc, zinv, bwd_split, parallel_symbolic, dist_factor)");
+        if (!f) throw cugo_b200::ArgError("set_option: unknown option '" + n + "' (pdl, fuse_build, panel_dc, zinv, bwd_split, parallel_symbolic, dist_factor, panel_rb)");
         *f = value != 0;
         S.structDirty = true;           // the options shape the structure and the trial graph
     });

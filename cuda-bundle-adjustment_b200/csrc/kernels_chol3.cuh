@@ -100,7 +100,7 @@ __device__ __forceinline__ void pull_pair(const ChildRef* chs, const int* invS, 
 
 // Cholesky factor of the 6x6 diagonal block jb of the shared-memory panel by one warp (every lane the same
 // arithmetic, lane 0 stores): L_D into the panel, the reciprocal diagonal into invAll.
-__device__ __forceinline__ void panel_factor_diag(double* A, double* invAll, int* badFlag, int jb, int lane) {
+__device__ __forceinline__ void panel_factor_diag(double* A, double* invAll, int* badFlag, int jb, int lane, double* Wsm = nullptr) {
     const int j0 = 6 * jb;
     double Ld[21], invd[6];
 #pragma unroll
@@ -131,11 +131,50 @@ __device__ __forceinline__ void panel_factor_diag(double* A, double* invAll, int
         for (int k = 0; k < 6; k++) invAll[6 * jb + k] = invd[k];
         if (bad) *badFlag = 1;
     }
+    if (Wsm != nullptr) {
+        // W = L_D^-1 (lower triangular), column k = lane by forward substitution on the unit vector e_k:
+        // w_i = ([i == k] - sum_{p<i} l_ip w_p) / l_ii -- the same instruction stream in every lane (entries above the
+        // diagonal come out as exact zeros), lanes 0..5 store.  Dense, row-major: the worker warps multiply their
+        // rows by W^T on the FP64 tensor pipe instead of substituting (panel_tile_solve).
+        double w[6];
+#pragma unroll
+        for (int i = 0; i < 6; i++) {
+            double sv = (lane == i) ? 1.0 : 0.0;
+#pragma unroll
+            for (int p2 = 0; p2 < i; p2++) sv -= Ld[tri(i, p2)] * w[p2];
+            w[i] = sv * invd[i];
+        }
+        if (lane < 6) {
+#pragma unroll
+            for (int i = 0; i < 6; i++) Wsm[i * 6 + lane] = w[i];
+        }
+    }
+}
+
+// S-phase of one 8-row tile on the tensor pipe: X = A_blk W^T for rows [r0, r0 + 8) of block column jb (W = L_D(jb)^-1 from
+// panel_factor_diag).  Fragment layout of m8n8k4: lane (g = lane >> 2, q = lane & 3) holds A[g][q] / B[q][g] and receives
+// C[g][2q], C[g][2q + 1]; K = 6 takes two instructions, the second with k = 4, 5 only.
+__device__ __forceinline__ void panel_tile_solve(double* A, const double* Wsm, int jb, int r0, int R, int lane, int nrows = 8) {
+    const int j0 = 6 * jb, g = lane >> 2, q = lane & 3;
+    const int r = r0 + g;
+    double a0 = A[(j0 + q) * PANEL_LD + r], a1 = A[(j0 + 4 + (q & 1)) * PANEL_LD + r];
+    const int n = g < 6 ? g : 0;
+    double b0 = Wsm[n * 6 + q], b1 = Wsm[n * 6 + 4 + (q & 1)];
+    if (q >= 2) { a1 = 0.0; b1 = 0.0; }
+    if (g >= 6) { b0 = 0.0; b1 = 0.0; }
+    double x0 = 0.0, x1 = 0.0;
+    dmma884(x0, x1, a0, b0);
+    dmma884(x0, x1, a1, b1);
+    if (q < 3 && r < R && g < nrows) {
+        A[(j0 + 2 * q) * PANEL_LD + r] = x0;
+        A[(j0 + 2 * q + 1) * PANEL_LD + r] = x1;
+    }
 }
 
 // X-phase work of one worker warp (see k_chol_panel3): 8-row tiles ta (and tb, if < nmt) of the rows from j2;
 //   U: block column jb -> block column jb+1 (rank 6), L: finished columns [0, j1) -> block column jb+2.
-__device__ __forceinline__ void panel_worker_tiles(double* A, int R, int nt, int jb, int ta, int tb, int lane) {
+__device__ __forceinline__ void panel_worker_tiles(double* A, int R, int nt, int jb, int ta, int tb, int lane, long long* trc = nullptr) {
+    if (trc) trc[0] = clock64();
     const int j0 = 6 * jb, j1 = j0 + 6, j2 = j1 + 6;
     const int fr8 = lane >> 2, fk = lane & 3;
     const int nmt = (R - j2 + 7) >> 3;
@@ -164,6 +203,7 @@ __device__ __forceinline__ void panel_worker_tiles(double* A, int R, int nt, int
         // ---- L: lane (fr8, fk) reads row (tile base + fr8) of column k0 + fk [+ 4]; pointers advance by
         // eight columns per iteration, the partial last group is handled after the loop
         double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0, e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
+        if (trc) trc[1] = clock64() + (long long)(u0 == 12345.678);
         if (la) {
             const double* Bp = A + j2 + fr8 + fk * PANEL_LD;
             const double* Ap = A + ra + fk * PANEL_LD;
@@ -193,7 +233,7 @@ __device__ __forceinline__ void panel_worker_tiles(double* A, int R, int nt, int
                     dmma884(e10, e11, q1, b1);
                 }
             } else {
-#pragma unroll 2
+#pragma unroll 4
                 for (int it = 0; it < nfull; it++) {
                     const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
                     const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
@@ -211,6 +251,7 @@ __device__ __forceinline__ void panel_worker_tiles(double* A, int R, int nt, int
             }
         }
         // ---- stores
+        if (trc) trc[2] = clock64() + (long long)(c00 + c10 == 12345.678);
         if (st && ra < R) {
             A[(j1 + cl) * PANEL_LD + ra] = tu0 - u0;
             A[(j1 + cl + 1) * PANEL_LD + ra] = tu1 - u1;
@@ -228,6 +269,81 @@ __device__ __forceinline__ void panel_worker_tiles(double* A, int R, int nt, int
             }
         }
     }
+}
+
+// Rows below the diagonal part (the slab rows and the rhs row) are nobody's operand inside the panel: X = S L11^-T can lag
+// behind the factorisation of D.  A slab warp owns one or two fixed 8-row tiles and runs its own left-looking loop over the
+// block columns, tied to the chain only by the published step counter: for block column cb
+//   C = A[tile, cb] - sum_{k < 6 cb} X[tile, k] L[6 cb .., k]^T        (FP64 DMMA, K = 6 cb, two accumulators per tile)
+//   X[tile, cb] = C W_cb^T                                            (panel_tile_solve, through the panel itself)
+// Reads: its own rows, and rows [6 cb, 6 cb + 8) of the finished columns -- final once the chain has factored D_cb.
+__device__ __forceinline__ void panel_slab_tiles(double* A, const double* Wcb, int cb, int ra0, int rb0, bool two, int R, int lane) {
+    const int g = lane >> 2, q = lane & 3, cl = 2 * q;
+    const bool st = cl < 6;
+    const int c0 = 6 * cb, ra = ra0 + g, rb = rb0 + g;
+    const int cu = st ? c0 + cl : c0;
+    if (cb > 0) {
+        const double ta0 = A[cu * PANEL_LD + ra], ta1 = A[(cu + 1) * PANEL_LD + ra];
+        const double tb0 = A[cu * PANEL_LD + rb], tb1 = A[(cu + 1) * PANEL_LD + rb];
+        double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0, e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
+        const double* Bp = A + c0 + g + q * PANEL_LD;
+        const double* Ap = A + ra + q * PANEL_LD;
+        const double* Aq = A + rb + q * PANEL_LD;
+        const int nfull = c0 >> 3, rem = c0 & 7;
+        const bool va = q < rem, vb = q + 4 < rem;
+        if (two) {
+#pragma unroll 2
+            for (int it = 0; it < nfull; it++) {
+                const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
+                const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                const double q0 = Aq[0], q1 = Aq[4 * PANEL_LD];
+                dmma884(c00, c01, a0, b0);
+                dmma884(c10, c11, a1, b1);
+                dmma884(e00, e01, q0, b0);
+                dmma884(e10, e11, q1, b1);
+                Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD; Aq += 8 * PANEL_LD;
+            }
+            if (rem) {                      // columns up to c0 + 7 exist only for cb + 1 < nt: clamp the second half
+                const int o1 = (q + 4 < rem) ? 4 * PANEL_LD : 0;
+                double b0 = Bp[0], b1 = Bp[o1], a0 = Ap[0], a1 = Ap[o1], q0 = Aq[0], q1 = Aq[o1];
+                if (!va) { b0 = 0.0; a0 = 0.0; q0 = 0.0; }
+                if (!vb) { b1 = 0.0; a1 = 0.0; q1 = 0.0; }
+                dmma884(c00, c01, a0, b0);
+                dmma884(c10, c11, a1, b1);
+                dmma884(e00, e01, q0, b0);
+                dmma884(e10, e11, q1, b1);
+            }
+        } else {
+#pragma unroll 2
+            for (int it = 0; it < nfull; it++) {
+                const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
+                const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                dmma884(c00, c01, a0, b0);
+                dmma884(c10, c11, a1, b1);
+                Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD;
+            }
+            if (rem) {
+                const int o1 = (q + 4 < rem) ? 4 * PANEL_LD : 0;
+                double b0 = Bp[0], b1 = Bp[o1], a0 = Ap[0], a1 = Ap[o1];
+                if (!va) { b0 = 0.0; a0 = 0.0; }
+                if (!vb) { b1 = 0.0; a1 = 0.0; }
+                dmma884(c00, c01, a0, b0);
+                dmma884(c10, c11, a1, b1);
+            }
+        }
+        if (st && ra < R) {
+            A[(c0 + cl) * PANEL_LD + ra] = ta0 - (c00 + c10);
+            A[(c0 + cl + 1) * PANEL_LD + ra] = ta1 - (c01 + c11);
+        }
+        if (two && st && rb < R) {
+            A[(c0 + cl) * PANEL_LD + rb] = tb0 - (e00 + e10);
+            A[(c0 + cl + 1) * PANEL_LD + rb] = tb1 - (e01 + e11);
+        }
+        __syncwarp();
+    }
+    panel_tile_solve(A, Wcb, cb, ra0, R, lane);
+    if (two) panel_tile_solve(A, Wcb, cb, rb0, R, lane);
+    __syncwarp();
 }
 
 // S-phase work for one panel row r below the diagonal block jb: x L_D^T = a
@@ -271,6 +387,15 @@ __device__ __forceinline__ void panel_diag_update(double* A, int jb, int lane) {
         A[(j1 + k) * PANEL_LD + j1 + i] -= sv;
     }
 }
+// publish / observe a step counter in shared memory with release / acquire semantics at CTA scope
+__device__ __forceinline__ void st_release_cta(int* p, int v) {
+    asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_cta(const int* p) {
+    int v;
+    asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+    return v;
+}
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
 __device__ __forceinline__ void named_bar_arrive(int id, int nthreads) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
 
@@ -288,21 +413,24 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     __shared__ int badFlag;
     __shared__ int invS[CHOL_MAXCH * PULL_W];
     __shared__ int rowTab[4][PANEL_LD];
+    __shared__ long long tBaseS;
+    __shared__ __align__(16) double Wall[CHOL_MAXW][36];   // L_D^-1 of every block column (panel_factor_diag)
+    __shared__ int pubStep;                                // block columns the chain has factored (slab warps poll it)
     LMState* st = d.st;
     const int q0 = c.levelPtr[lev], q1 = c.levelPtr[lev + 1];
     int q, slab;
     find_task(c.trsmPtr, q0, q1, c.trsmPtr[q0] + blockIdx.x, &q, &slab);
     const SnInfo n = sn_info(c, c.levelSn[q]);
     const int nc = n.nc, nt = n.nt, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int rb0 = nt + slab * CHOL_RB;          // first front block row of the slab
-    const int rb1 = min(rb0 + CHOL_RB, n.fb);
+    const int rb0 = nt + slab * c.rb;          // first front block row of the slab
+    const int rb1 = min(rb0 + c.rb, n.fb);
     const bool last = (rb1 == n.fb);              // the last slab carries the rhs row
     const int nS = 6 * (rb1 - rb0) + (last ? 1 : 0);
     const int R = nc + nS;
     const int ch0 = c.childPtr[n.t], nch = c.childPtr[n.t + 1] - ch0;
 
     CHOL_STAMP(0);
-    if (tid == 0) badFlag = 0;
+    if (tid == 0) { badFlag = 0; pubStep = 0; }
     for (int i = tid; i < nc * PANEL_LD; i += PANEL3_TPB) A[i] = 0.0;
     if (tid < nch && tid < CHOL_MAXCH) chs[tid] = load_child(c, ch0 + tid);
     __syncthreads();
@@ -468,54 +596,85 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     //       never waits for the bulk updates.
     // Warps 4, 8, 12 share warp 0's scheduler / FP64 pipe and sit phase X out.
     if constexpr (DC) {
-        // Decoupled loop.  Roles: warp 0 = chain, the 12 warps with (wid & 3) != 0 = workers (warps 4, 8, 12 share the
-        // chain's scheduler and FP64 pipe and sit the loop out).  Per block column jb:
-        //   chain    factor D_jb                                         -> arrive B1[jb&1]   "L_D(jb) ready"
-        //            wait B5: worker 0 has finished X(jb-1), i.e. rows j1..j1+7 of block columns jb, jb+1 are up to date
-        //            solve its own six rows j1..j1+5 against L_D(jb)       -> arrive B2[jb&1]   "rows of D_(jb+1) solved"
-        //            D_(jb+1) -= L L^T, next factor
-        //   workers  sync B1: solve the rows from j2 (S); sync B2 (also orders the workers among themselves);
-        //            X(jb): block column jb -> jb+1, finished columns -> jb+2 (panel_worker_tiles); worker 0 arrives B5.
+        // Decoupled loop.  Roles (16 warps): warp 0 = chain; warps 4, 8, 12 share its scheduler and sit the loop out;
+        // of the other twelve, D-workers 0..7 keep the DIAGONAL part (rows < nc) in step with the chain, slab warps 0..3
+        // own the rows below it (two fixed 8-row tiles each) and follow at their own pace (panel_slab_tiles).
+        // Per block column jb:
+        //   chain     factor D_jb, W_jb = L_D(jb)^-1, publish "jb done"    -> arrive B1[jb&1]
+        //             wait B5: D-worker 0 has finished X(jb-1), i.e. rows j1..j1+7 of block columns jb, jb+1 are up to date
+        //             its own six rows j1..j1+5 times W_jb^T                 -> arrive B2[jb&1]
+        //             D_(jb+1) -= L L^T, next factor
+        //   D-workers sync B1: their tiles of the rows [j2, nc) times W_jb^T (S); sync B2 (also orders them among themselves);
+        //             X(jb): block column jb -> jb+1, finished columns -> jb+2 (panel_worker_tiles); D-worker 0 arrives B5.
+        //   slab warp waits for "jb done", then block column jb of its tiles by all finished columns, times W_jb^T.
         // The chain never waits for the bulk updates of its own step, only for the tile of the NEXT diagonal block from
-        // the step before; it can be one step ahead, hence the two parities of B1 / B2.
-        constexpr int NWK = 3 * (PANEL3_NW / 4);
-        constexpr int NB = (NWK + 1) * 32;               // chain + workers
+        // the step before; it can be one step ahead, hence the two parities of B1 / B2.  W is kept for every block
+        // column because a slab warp may lag several steps.
+        constexpr int NWD = 8, NWS = 4;                  // D-workers, slab warps
+        constexpr int NB = (NWD + 1) * 32;               // chain + D-workers
         const bool dbgT = CHOL_DIAG(c) && blockIdx.x == 0 && tid == 0 && lev < 64;
         const long long tLoop0 = dbgT ? clock64() : 0;
+        // diagnostics (make DIAG=1): clocks of one level (CUGO_B200_DEBUG = 1 + 256 (level + 1); default level 2), CTA 0, per step,
+        // all against the chain's loop start --
+        //   chain    [0] arrive B1  [1] (unused)    [2] rows solved (arrive B2)  [3] next factor done
+        //   D-worker [4] arrives B1 [5] own S done  [6] (unused)                 [7] X done
+        const bool trAny = CHOL_DIAG(c) && blockIdx.x == 0 && lev == ((CHOL_DIAG(c) >> 8) ? (CHOL_DIAG(c) >> 8) - 1 : 2);
+        if (trAny && tid == 0) { g_cholTrace[126] = R; g_cholTrace[127] = nt; tBaseS = tLoop0; }
+        if (trAny) __syncthreads();
+        const long long tB = trAny ? tBaseS : 0;
+        const int wk = (wid >> 2) * 3 + (wid & 3) - 1;   // 0..11 over the warps with (wid & 3) != 0
         if (wid == 0) {
-            panel_factor_diag(A, invAll, &badFlag, 0, lane);
-            const bool trc = dbgT && lev == 2;      // diagnostics: chain clock at (arrive B1, after B5, after the factor)
+            panel_factor_diag(A, invAll, &badFlag, 0, lane, Wall[0]);
+            const bool trc = trAny && lane == 0;
             for (int jb = 0; jb < nt; jb++) {
-                named_bar_arrive(1 + (jb & 1), NB);
-                if (trc && jb < 16) g_cholTrace[6 * jb] = clock64() - tLoop0;
+                __syncwarp();
+                if (lane == 0) st_release_cta(&pubStep, jb + 1);
+                if (trc && jb < 16) g_cholTrace[8 * jb] = clock64() - tB;
                 if (jb + 1 == nt) break;
+                named_bar_arrive(1 + (jb & 1), NB);
                 if (jb > 0) named_bar_sync(5, 64);
-                if (trc && jb < 16) g_cholTrace[6 * jb + 1] = clock64() - tLoop0;
-                if (lane < 6) panel_row_solve(A, invAll, jb, 6 * jb + 6 + lane);
+                panel_tile_solve(A, Wall[jb], jb, 6 * jb + 6, R, lane, 6);     // the six rows of the next diagonal block
                 __syncwarp();
                 named_bar_arrive(3 + (jb & 1), NB);
+                if (trc && jb < 16) g_cholTrace[8 * jb + 2] = clock64() - tB;
                 panel_diag_update(A, jb, lane);
                 __syncwarp();
-                panel_factor_diag(A, invAll, &badFlag, jb + 1, lane);
-                if (trc && jb < 16) g_cholTrace[6 * jb + 2] = clock64() - tLoop0;
+                panel_factor_diag(A, invAll, &badFlag, jb + 1, lane, Wall[jb + 1]);
+                if (trc && jb < 16) g_cholTrace[8 * jb + 3] = clock64() - tB;
+            }
+        } else if ((wid & 3) != 0 && wk < NWD) {
+            const bool trw = trAny && tid == 32;
+            const int tb = NWD + (NWD - 1 - wk);         // D-worker 0 (whose tile the chain waits for) gets the last extra tile
+            for (int jb = 0; jb + 1 < nt; jb++) {        // nothing of D is left below the last diagonal block
+                if (trw && jb < 16) g_cholTrace[8 * jb + 4] = clock64() - tB;
+                if (trAny && lane == 0 && jb == 8) g_cholTrace[160 + wk] = clock64() - tB;      // every D-worker: arrives at B1(8)
+                named_bar_sync(1 + (jb & 1), NB);
+                // S: the rows of this warp's own X tiles (the chain solves the six rows of the next diagonal block)
+                const int rS = 6 * jb + 12;
+                const int nmtS = (nc - rS + 7) >> 3;
+                if (wk < nmtS) panel_tile_solve(A, Wall[jb], jb, rS + 8 * wk, nc, lane);
+                if (tb < nmtS) panel_tile_solve(A, Wall[jb], jb, rS + 8 * tb, nc, lane);
+                if (trw && jb < 16) g_cholTrace[8 * jb + 5] = clock64() - tB;
+                if (trAny && lane == 0 && jb == 8) g_cholTrace[144 + wk] = clock64() - tB;      // every D-worker: S(8) done
+                named_bar_sync(3 + (jb & 1), NB);
+                panel_worker_tiles(A, nc, nt, jb, wk, tb, lane, (trw && jb == 8) ? g_cholTrace + 168 : nullptr);
+                if (trw && jb == 8) g_cholTrace[171] = clock64();
+                if (wk == 0 && jb + 2 < nt) named_bar_arrive(5, 64);
+                if (trw && jb < 16) g_cholTrace[8 * jb + 7] = clock64() - tB;
+                if (trAny && lane == 0 && jb == 8) g_cholTrace[136 + wk] = clock64() - tB;      // every D-worker: X(8) done
             }
         } else if ((wid & 3) != 0) {
-            const int wk = (wid >> 2) * 3 + (wid & 3) - 1;
-            const int wt = wk * 32 + lane;
-            const bool trw = CHOL_DIAG(c) && blockIdx.x == 0 && tid == 32 && lev == 2;   // worker 0: clock after (B1, B2, X)
-            const long long tw0 = trw ? clock64() : 0;
-            for (int jb = 0; jb < nt; jb++) {
-                const bool more = jb + 1 < nt;
-                named_bar_sync(1 + (jb & 1), NB);
-                if (trw && jb < 16) g_cholTrace[6 * jb + 3] = clock64() - tw0;
-                const int r = 6 * jb + (more ? 12 : 6) + wt;      // the chain solves the six rows of the next diagonal block
-                if (r < R) panel_row_solve(A, invAll, jb, r);
-                if (!more) break;
-                named_bar_sync(3 + (jb & 1), NB);
-                if (trw && jb < 16) g_cholTrace[6 * jb + 4] = clock64() - tw0;
-                panel_worker_tiles(A, R, nt, jb, wk, NWK + (NWK - 1 - wk), lane);   // worker 0 gets the last extra tile
-                if (wk == 0 && jb + 2 < nt) named_bar_arrive(5, 64);
-                if (trw && jb < 16) g_cholTrace[6 * jb + 5] = clock64() - tw0;
+            const int sw = wk - NWD;                     // slab warp 0..3: tiles sw and sw + 4 of the rows from nc
+            const int nTs = (nS + 7) >> 3;
+            if (sw < nTs) {
+                const bool two = sw + NWS < nTs;
+                const int ra0 = nc + 8 * sw, rb0 = nc + 8 * (two ? sw + NWS : sw);
+                for (int cb = 0; cb < nt; cb++) {
+                    while (ld_acquire_cta(&pubStep) < cb + 1) __nanosleep(64);
+                    __syncwarp();
+                    panel_slab_tiles(A, Wall[cb], cb, ra0, rb0, two, R, lane);
+                }
+                if (trAny && lane == 0) g_cholTrace[128 + sw] = clock64() - tB;      // slab warp done
             }
         }
         __syncthreads();

@@ -69,7 +69,7 @@ __device__ __forceinline__ ChildRef load_child(const Chol& c, int q) {
 // library carries neither the device arrays nor the stamps.
 #ifdef CUGO_B200_DIAG
 __device__ long long g_cholDbg[64 * 24];
-__device__ long long g_cholTrace[96];       // clock of CTA 0 / thread 0 at points of every factor-loop step of level 2
+__device__ long long g_cholTrace[176];       // clock of CTA 0 / thread 0 at points of every factor-loop step of level 2
 __device__ long long g_cholTime[64 * 8];    // %globaltimer (ns) of CTA 0 per level: panel (after wait, end), update, backward solve
 __device__ long long g_schurDbg[8192];      // cycles per unit of k_schur_rows
 __device__ __forceinline__ long long global_ns() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }

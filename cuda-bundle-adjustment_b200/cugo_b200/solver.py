@@ -276,7 +276,8 @@ class BlockSolver:
     def debug_counters(self, n=64 * 24):
         a = (C.c_longlong * n)()
         self._ck(self.lib.cugo_b200_debug_counters(a, n))
-        return np.array(a[:], dtype=np.int64).reshape(-1, 24)
+        v = np.array(a[:], dtype=np.int64)
+        return v.reshape(-1, 24) if n % 24 == 0 else v
 
     def stream(self):
         return self.lib.cugo_b200_stream(self.h)

@@ -13,6 +13,8 @@ name = sys.argv[1] if len(sys.argv) > 1 else "kitti00"
 prob = pack.pack(synth.make_graph(name))
 s = solver.BlockSolver(0)
 s.initialize(prob)
+for kv in filter(None, os.environ.get("CUGO_OPTS", "").split(",")):      # e.g. CUGO_OPTS=panel_rb=5,zinv=0
+    s.set_option(kv.split("=")[0], int(kv.split("=")[1]))
 s.build_structure()
 print(s.sizes())
 for rep in range(3):
@@ -49,14 +51,15 @@ if DIAG:
         print("  lev %2d panel" % lev, np.diff(dc[lev, :6]).tolist(), " update (stage, mma, pull+store)",
               np.diff(dc[lev, 8:12]).tolist(), " bwd (load, gemv, trsv)", np.diff(dc[lev, 16:20]).tolist(),
               " factor loop (warp 0 diag update + factor, wait for workers, row solve, whole loop)", dc[lev, 12:16].tolist(), " worker (rank6, look-ahead)", dc[lev, 20:22].tolist())
-    tr6 = s.debug_counters(96).reshape(-1)[:96].reshape(16, 6)
-    print("decoupled panel loop, level 2, CTA 0, per step: chain clock at (arrive B1, after B5, after factor) | worker 0 clock after (B1, B2, X)")
+    trAll = s.debug_counters(176).reshape(-1)
+    tr8 = trAll[:128].reshape(16, 8)
+    print("traced CTA: R = %d rows, nt = %d block columns; slab warps done at" % (trAll[126], trAll[127]), trAll[128:132].tolist(),
+          "\n   D-workers at step 8: arrive at B1", trAll[160:168].tolist(), " S done", trAll[144:152].tolist(), " X done", trAll[136:144].tolist(),
+          "\n   D-worker 0, X(8): U part %d, L part %d, stores %d cycles" % (trAll[169] - trAll[168], trAll[170] - trAll[169], trAll[171] - trAll[170]))
+    print("decoupled panel loop, level 2, CTA 0, per step, cycles since the loop start: chain (arrive B1, -, rows solved = arrive B2, "
+          "next factor done) | D-worker 0 (arrives at B1, own S done, -, X done)")
     for jb in range(16):
-        print("   step %2d" % jb, tr6[jb, :3].tolist(), tr6[jb, 3:].tolist())
-    tr = s.debug_counters(96).reshape(-1)[:64].reshape(16, 4)
-    print("level 2, CTA 0, thread 0: clock at (step start, after S barrier, after warp-0 work, after X barrier) per step")
-    for jb in range(16):
-        print("   step %2d" % jb, tr[jb].tolist())
+        print("   step %2d" % jb, tr8[jb, :4].tolist(), tr8[jb, 4:].tolist())
 for rep in range(5):
     s.set_estimates(prob.poses, prob.landmarks)
     chi, lam, tr = s.optimize(10)
