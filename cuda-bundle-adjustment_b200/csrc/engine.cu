@@ -149,7 +149,7 @@ struct Solver {
     cudaStream_t stream = nullptr;
     cudaStream_t side = nullptr;   // low-priority branch of the trial graph: k_chol_zinv beside the factorisation
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
-    int panelRB = CHOL_RB;         // option "panel_rb": block rows of L21 per panel CTA (1..CHOL_RB); set before build_structure
+    int panelRB = 0;               // option "panel_rb": block rows of L21 per panel CTA; 0 = per tree level (planPanelSlabs), else 1..CHOL_RB
     bool bwdSplit = true;          // option "bwd_split" = 0: one CTA per supernode in the backward solve
     bool zinvOn = true;            // option "zinv" = 0: backward solves by blocked substitution on every level
     std::string err;
@@ -227,6 +227,8 @@ struct Solver {
     std::vector<Bcast> distBcast;  // update matrices of the subtree roots, sent by their owners before level distLc
     DBuf<int> zr_levelPtr, zr_levelSn, zr_trsmPtr, zr_updPtr, zr_colOwn;
     void planDistFactor();
+    void planPanelSlabs();
+    DBuf<int> zs_trsmPtr, zs_rbLev;    // panel-slab task table / slab height per level when chosen per level (planPanelSlabs)
     int nblkG = 0;
     void commInit(int n, int r, const char* id);
     void allReduceSum(double* buf, size_t n) {
@@ -710,7 +712,7 @@ void Solver::buildStructure() {
     m.childIdx = z_childIdx; m.invPtr = z_invPtr; m.inv = z_inv; m.snBlkPtr = z_snBlkPtr; m.asmBlk = z_asmBlk;
     m.asmRow = z_asmRow; m.asmCol = z_asmCol;
     z_levMaxNt.alloc(counts.nlev + 1);
-    k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, 0, 0, panelRB, CHOL_TB,
+    k_sym_fill<<<1, 1, 0, stream>>>(w, y_counts, m, z_trsmPtr, z_updPtr, 0, 0, panelRB > 0 ? panelRB : CHOL_RB, CHOL_TB,
                                     z_levMaxNt, z_factStats.alloc(4));
     lap("symbolic maps + task tables");
     }
@@ -725,6 +727,7 @@ void Solver::buildStructure() {
     c.levelPtr = z_levelPtr; c.levelSn = z_levelSn; c.trsmPtr = z_trsmPtr; c.updPtr = z_updPtr;
     distLc = 0; distBcast.clear(); h_own.clear();
     if (nranks > 1 && distMode > 0) planDistFactor();
+    planPanelSlabs();
     if (getenv("CUGO_B200_DEBUG")) {
         fprintf(stderr, "[cugo_b200] elimination tree: %d supernodes, %d levels, max front %d block rows; per level "
                         "(supernodes / panel CTAs / update tiles / widest):", nsn, counts.nlev, counts.maxFront);
@@ -785,7 +788,6 @@ void Solver::buildStructure() {
     c.childIdx = z_childIdx; c.invPtr = z_invPtr; c.inv = z_inv; c.snBlkPtr = z_snBlkPtr; c.asmBlk = z_asmBlk;
     c.asmRow = z_asmRow; c.asmCol = z_asmCol;
     c.L = cL; c.U = cU; c.xperm = cX; c.Winv = cW; c.Zinv = cZ; c.bwdPart = cPart; c.bwdCnt = cCnt;
-    c.rb = panelRB;
     { const char* e = getenv("CUGO_B200_DEBUG"); c.dbg = e ? atoi(e) : 0; }   // diagnostic builds (make DIAG=1): 1 phase stamps, 3 also a worker warp's view
 
     // dynamic shared memory opt-in for the factorisation kernels
@@ -912,7 +914,8 @@ void Solver::planDistFactor() {
             if (h_own[t] >= 0 && h_own[t] != rank) continue;
             fSn.push_back(t); fTrsm.push_back(a); fUpd.push_back(b);
             const int rt = rp[t + 1] - rp[t];
-            const int ns = (rt + panelRB - 1) / panelRB;
+            const int rbU = panelRB > 0 ? panelRB : CHOL_RB;
+            const int ns = (rt + rbU - 1) / rbU;
             a += ns > 0 ? ns : 1;
             if (rt > 0) { const int n2 = (rt + CHOL_TB) / CHOL_TB; b += n2 * (n2 + 1) / 2; }
         }
@@ -937,6 +940,50 @@ void Solver::planDistFactor() {
         const long long u = 6LL * (rp[t + 1] - rp[t]) + 1;
         distBcast.push_back({(size_t)uptr[t], (size_t)(u * u), h_own[t]});
     }
+}
+
+// Slab height of the panel kernel per tree level.  A panel CTA factors the diagonal part of its supernode and one slab
+// of the rows below; the rows below are independent of each other, so on levels with few supernodes (the top of the
+// tree, where most SMs idle) short slabs spread them over more SMs, while the leaf levels keep tall slabs so that
+// the level still fits one wave.  panel_rb > 0 fixes the height for every level.
+void Solver::planPanelSlabs() {
+    int sms = 148;
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    const int nlev = counts.nlev, cap = std::max(16, (sms * 9) / 10);
+    const int nq = h_levelPtr[nlev];
+    const int nsn = counts.nsn;
+    std::vector<int> lsn(std::max(nq, 1)), rp(nsn + 1), rbLev(nlev + 1, CHOL_RB), tr(nq + 1, 0);
+    if (nq) CK(cudaMemcpyAsync(lsn.data(), c.levelSn, sizeof(int) * nq, cudaMemcpyDeviceToHost, stream));
+    CK(cudaMemcpyAsync(rp.data(), y_snRowPtr.p, sizeof(int) * (nsn + 1), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    static const int cand[] = {2, 3, 4, 5, 6, 8, 10, 12, 14, 16};
+    int a = 0;
+    for (int l = 0; l < nlev; l++) {
+        int rb = panelRB > 0 ? panelRB : 10;        // no single wave even with the tallest slab: the round-1 height
+        if (panelRB == 0) {
+            for (int cnd : cand) {
+                int ctas = 0;
+                for (int q = h_levelPtr[l]; q < h_levelPtr[l + 1]; q++) {
+                    const int rt = rp[lsn[q] + 1] - rp[lsn[q]];
+                    ctas += std::max(1, (rt + cnd - 1) / cnd);
+                }
+                if (ctas <= cap) { rb = cnd; break; }
+            }
+        }
+        rbLev[l] = rb;
+        for (int q = h_levelPtr[l]; q < h_levelPtr[l + 1]; q++) {
+            const int rt = rp[lsn[q] + 1] - rp[lsn[q]];
+            tr[q] = a;
+            a += std::max(1, (rt + rb - 1) / rb);
+        }
+    }
+    tr[nq] = a;
+    zs_trsmPtr.alloc(nq + 1); zs_rbLev.alloc(nlev + 1);
+    CK(cudaMemcpyAsync(zs_trsmPtr.p, tr.data(), sizeof(int) * (nq + 1), cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpyAsync(zs_rbLev.p, rbLev.data(), sizeof(int) * (nlev + 1), cudaMemcpyHostToDevice, stream));
+    CK(cudaStreamSynchronize(stream));
+    h_trsmPtr = tr;
+    c.trsmPtr = zs_trsmPtr; c.rbLev = zs_rbLev;
 }
 
 // Symbolic analysis as parallel device work (kernels_sym.cuh); the arrays are those of symbolic.h, bit for bit.
@@ -1004,7 +1051,7 @@ void Solver::symbolicParallel(const int* gRowOfP, const int* gRowPtrP, const int
     if (tabBytes > 200 * 1024) throw UnsupportedError("too many supernodes for the shared-memory schedule tables of this version");
     CK(cudaFuncSetAttribute(k_sym_tables, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tabBytes));
     k_sym_tables<<<1, SYM_TPB, tabBytes, stream>>>(nsn, counts.nlev, y_snStart, y_snRowPtr, y_snParent, y_snLevel, m, z_trsmPtr,
-                                                   z_updPtr, panelRB, CHOL_TB, z_levMaxNt, z_factStats.alloc(4), counts.lsize);
+                                                   z_updPtr, panelRB > 0 ? panelRB : CHOL_RB, CHOL_TB, z_levMaxNt, z_factStats.alloc(4), counts.lsize);
     k_sym_inv<<<divUp((long long)nsn * 32, TB), TB, 0, stream>>>(nsn, y_snStart, y_snRowPtr, y_snRows, y_snParent, z_invPtr, z_inv);
     y_ak1.alloc(nblkG); y_ak2.alloc(nblkG); y_av1.alloc(nblkG); y_av2.alloc(nblkG);
     k_sym_asm_keys<<<divUp(nblkG, TB), TB, 0, stream>>>(gRowOfP, gColIndP, nblkG, y_iperm, y_colToSn, y_ak1, y_av1);
@@ -2013,7 +2060,7 @@ int cugo_b200_set_option(cugo_b200_solver* s, const char* name, int value) {
         const std::string n(name);
         if (n == "dist_factor") { S.distMode = value; S.structDirty = true; return; }
         if (n == "panel_rb") {
-            if (value < 1 || value > cugo_b200::CHOL_RB) throw cugo_b200::ArgError("set_option: panel_rb must be in [1, 10]");
+            if (value < 0 || value > cugo_b200::CHOL_RB) throw cugo_b200::ArgError("set_option: panel_rb must be in [0, 16] (0: chosen per tree level)");
             S.panelRB = value; S.structDirty = true; return;
         }
         bool* f = n == "pdl" ? &S.pdl : n == "fuse_build" ? &S.fuseBuild : n == "panel_dc" ? &S.panelDC : n == "zinv" ? &S.zinvOn

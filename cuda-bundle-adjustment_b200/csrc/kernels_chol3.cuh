@@ -98,6 +98,15 @@ __device__ __forceinline__ void pull_pair(const ChildRef* chs, const int* invS, 
     }
 }
 
+// publish / observe a step counter in shared memory with release / acquire semantics at CTA scope
+__device__ __forceinline__ void st_release_cta(int* p, int v) {
+    asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_cta(const int* p) {
+    int v;
+    asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+    return v;
+}
 // Cholesky factor of the 6x6 diagonal block jb of the shared-memory panel by one warp (every lane the same
 // arithmetic, lane 0 stores): L_D into the panel, the reciprocal diagonal into invAll.
 __device__ __forceinline__ void panel_factor_diag(double* A, double* invAll, int* badFlag, int jb, int lane, double* Wsm = nullptr) {
@@ -148,6 +157,54 @@ __device__ __forceinline__ void panel_factor_diag(double* A, double* invAll, int
 #pragma unroll
             for (int i = 0; i < 6; i++) Wsm[i * 6 + lane] = w[i];
         }
+    }
+}
+
+// The chain's factor of the data-flow loop: Cholesky of D_jb AND W = L_D^-1 in one pass (row k of W needs row k of L and
+// the rows of W above it, so it fills the bubbles of the next pivot's rsqrt), W published through `pub` (value jb + 1)
+// BEFORE L_D and the reciprocal diagonal are stored -- nothing inside the loop reads those two.
+// Lane `lane` carries column min(lane, 5)... every lane runs the same instruction stream: column k = lane of W is
+// w_i = ([i == k] - sum_{p<i} l_ip w_p) / l_ii, exact zeros above the diagonal; lanes 0..5 store.
+__device__ __forceinline__ void panel_chain_factor(double* A, double* invAll, int* badFlag, int jb, int lane, double* Wsm, int* pub) {
+    const int j0 = 6 * jb;
+    double Ld[21], invd[6], w[6];
+#pragma unroll
+    for (int i = 0; i < 6; i++)
+#pragma unroll
+        for (int k = 0; k <= i; k++) Ld[tri(i, k)] = A[(j0 + k) * PANEL_LD + j0 + i];
+    bool bad = false;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        double x = Ld[tri(k, k)];
+        if (!(x > CHOL_PIVOT_TOL)) { bad = true; x = 1.0; }
+        double sv = (lane == k) ? 1.0 : 0.0;            // row k of W: independent of this pivot's rsqrt up to the last product
+#pragma unroll
+        for (int p2 = 0; p2 < k; p2++) sv -= Ld[tri(k, p2)] * w[p2];
+        const double inv = rsqrt(x);
+        invd[k] = inv;
+        w[k] = sv * inv;
+        Ld[tri(k, k)] = x * inv;
+#pragma unroll
+        for (int i = k + 1; i < 6; i++) Ld[tri(i, k)] *= inv;
+#pragma unroll
+        for (int cc = k + 1; cc < 6; cc++)
+#pragma unroll
+            for (int i = cc; i < 6; i++) Ld[tri(i, cc)] -= Ld[tri(i, k)] * Ld[tri(cc, k)];
+    }
+    if (lane < 6) {
+#pragma unroll
+        for (int i = 0; i < 6; i++) Wsm[i * 6 + lane] = w[i];
+    }
+    __syncwarp();
+    if (lane == 0) {
+        st_release_cta(pub, jb + 1);
+#pragma unroll
+        for (int i = 0; i < 6; i++)
+#pragma unroll
+            for (int k = 0; k <= i; k++) A[(j0 + k) * PANEL_LD + j0 + i] = Ld[tri(i, k)];
+#pragma unroll
+        for (int k = 0; k < 6; k++) invAll[6 * jb + k] = invd[k];
+        if (bad) *badFlag = 1;
     }
 }
 
@@ -346,6 +403,158 @@ __device__ __forceinline__ void panel_slab_tiles(double* A, const double* Wcb, i
     __syncwarp();
 }
 
+// Left-looking accumulate of one 8-row group into column block cb by the first K finished columns:
+//   A[r0 + g, 6 cb + n] -= sum_{K0 <= k < K1} A[r0 + g, k] A[6 cb + n, k]        (g < 8 rows, n < 6 columns)
+// stores limited to the first `nrows` rows (a 6-row block row computes 8 and keeps 6).  K0, K1 are multiples of 6.
+__device__ __forceinline__ void panel_lag_acc(double* A, int cb, int K0, int K1, int r0, int nrows, int R, int lane) {
+    const int K = K1 - K0;
+    if (K <= 0) return;
+    const int g = lane >> 2, q = lane & 3, cl = 2 * q;
+    const bool st = cl < 6;
+    const int c0 = 6 * cb, ra = r0 + g;
+    const int cu = st ? c0 + cl : c0;
+    const double t0 = A[cu * PANEL_LD + ra], t1 = A[(cu + 1) * PANEL_LD + ra];
+    double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0;
+    const double* Bp = A + c0 + g + (K0 + q) * PANEL_LD;
+    const double* Ap = A + ra + (K0 + q) * PANEL_LD;
+    const int nfull = K >> 3, rem = K & 7;
+#pragma unroll 4
+    for (int it = 0; it < nfull; it++) {
+        const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
+        const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+        dmma884(c00, c01, a0, b0);
+        dmma884(c10, c11, a1, b1);
+        Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD;
+    }
+    if (rem) {
+        const bool va = q < rem, vb = q + 4 < rem;
+        const int o1 = vb ? 4 * PANEL_LD : 0;
+        double b0 = Bp[0], b1 = Bp[o1], a0 = Ap[0], a1 = Ap[o1];
+        if (!va) { b0 = 0.0; a0 = 0.0; }
+        if (!vb) { b1 = 0.0; a1 = 0.0; }
+        dmma884(c00, c01, a0, b0);
+        dmma884(c10, c11, a1, b1);
+    }
+    if (st && g < nrows && ra < R) {
+        A[(c0 + cl) * PANEL_LD + ra] = t0 - (c00 + c10);
+        A[(c0 + cl + 1) * PANEL_LD + ra] = t1 - (c01 + c11);
+    }
+    __syncwarp();
+}
+// Two left-looking accumulates in one instruction stream (the pair of block rows a row warp owns): job x in {a, b} does
+//   A[r0x + g, 6 cbx + n] -= sum_{K0 <= k < K1} A[r0x + g, k] A[brx + n, k]
+// with its own target column block cbx and operand rows brx; job b only if `two`.  Four independent accumulator chains,
+// all operand loads of a round ahead of its DMMAs.
+struct LagJob { int cb, br, r0; };
+__device__ __forceinline__ void panel_lag_acc2(double* A, int K0, int K1, LagJob ja, LagJob jb, bool two, int nrows, int R, int lane) {
+    const int K = K1 - K0;
+    if (K <= 0) return;
+    if (!two) jb = ja;
+    const int g = lane >> 2, q = lane & 3, cl = 2 * q;
+    const bool st = cl < 6;
+    const int ra = ja.r0 + g, rb = jb.r0 + g;
+    const int cua = 6 * ja.cb + (st ? cl : 0), cub = 6 * jb.cb + (st ? cl : 0);
+    const double ta0 = A[cua * PANEL_LD + ra], ta1 = A[(cua + 1) * PANEL_LD + ra];
+    const double tb0 = A[cub * PANEL_LD + rb], tb1 = A[(cub + 1) * PANEL_LD + rb];
+    double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0, e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
+    const double* Bpa = A + ja.br + g + (K0 + q) * PANEL_LD;
+    const double* Bpb = A + jb.br + g + (K0 + q) * PANEL_LD;
+    const double* Apa = A + ra + (K0 + q) * PANEL_LD;
+    const double* Apb = A + rb + (K0 + q) * PANEL_LD;
+    const int nfull = K >> 3, rem = K & 7;
+    if (two) {
+#pragma unroll 2
+        for (int it = 0; it < nfull; it++) {
+            const double b0 = Bpa[0], b1 = Bpa[4 * PANEL_LD], d0 = Bpb[0], d1 = Bpb[4 * PANEL_LD];
+            const double a0 = Apa[0], a1 = Apa[4 * PANEL_LD], q0 = Apb[0], q1 = Apb[4 * PANEL_LD];
+            dmma884(c00, c01, a0, b0);
+            dmma884(e00, e01, q0, d0);
+            dmma884(c10, c11, a1, b1);
+            dmma884(e10, e11, q1, d1);
+            Bpa += 8 * PANEL_LD; Bpb += 8 * PANEL_LD; Apa += 8 * PANEL_LD; Apb += 8 * PANEL_LD;
+        }
+        if (rem) {
+            const bool va = q < rem, vb = q + 4 < rem;
+            const int o1 = vb ? 4 * PANEL_LD : 0;
+            double b0 = Bpa[0], b1 = Bpa[o1], d0 = Bpb[0], d1 = Bpb[o1];
+            double a0 = Apa[0], a1 = Apa[o1], q0 = Apb[0], q1 = Apb[o1];
+            if (!va) { b0 = 0.0; a0 = 0.0; d0 = 0.0; q0 = 0.0; }
+            if (!vb) { b1 = 0.0; a1 = 0.0; d1 = 0.0; q1 = 0.0; }
+            dmma884(c00, c01, a0, b0);
+            dmma884(e00, e01, q0, d0);
+            dmma884(c10, c11, a1, b1);
+            dmma884(e10, e11, q1, d1);
+        }
+    } else {
+#pragma unroll 4
+        for (int it = 0; it < nfull; it++) {
+            const double b0 = Bpa[0], b1 = Bpa[4 * PANEL_LD];
+            const double a0 = Apa[0], a1 = Apa[4 * PANEL_LD];
+            dmma884(c00, c01, a0, b0);
+            dmma884(c10, c11, a1, b1);
+            Bpa += 8 * PANEL_LD; Apa += 8 * PANEL_LD;
+        }
+        if (rem) {
+            const bool va = q < rem, vb = q + 4 < rem;
+            const int o1 = vb ? 4 * PANEL_LD : 0;
+            double b0 = Bpa[0], b1 = Bpa[o1], a0 = Apa[0], a1 = Apa[o1];
+            if (!va) { b0 = 0.0; a0 = 0.0; }
+            if (!vb) { b1 = 0.0; a1 = 0.0; }
+            dmma884(c00, c01, a0, b0);
+            dmma884(c10, c11, a1, b1);
+        }
+    }
+    if (st && g < nrows) {
+        if (ra < R) {
+            A[cua * PANEL_LD + ra] = ta0 - (c00 + c10);
+            A[(cua + 1) * PANEL_LD + ra] = ta1 - (c01 + c11);
+        }
+        if (two && rb < R) {
+            A[cub * PANEL_LD + rb] = tb0 - (e00 + e10);
+            A[(cub + 1) * PANEL_LD + rb] = tb1 - (e01 + e11);
+        }
+    }
+    __syncwarp();
+}
+// two tile solves in one instruction stream (rows r0a.. and, if `two`, r0b..), see panel_tile_solve
+__device__ __forceinline__ void panel_tile_solve2(double* A, const double* Wsm, int jb, int r0a, int r0b, bool two, int R, int lane, int nrows) {
+    const int j0 = 6 * jb, g = lane >> 2, q = lane & 3;
+    const int ra = r0a + g, rb = (two ? r0b : r0a) + g;
+    double a0 = A[(j0 + q) * PANEL_LD + ra], a1 = A[(j0 + 4 + (q & 1)) * PANEL_LD + ra];
+    double p0 = A[(j0 + q) * PANEL_LD + rb], p1 = A[(j0 + 4 + (q & 1)) * PANEL_LD + rb];
+    const int n = g < 6 ? g : 0;
+    double b0 = Wsm[n * 6 + q], b1 = Wsm[n * 6 + 4 + (q & 1)];
+    if (q >= 2) { a1 = 0.0; p1 = 0.0; b1 = 0.0; }
+    if (g >= 6) { b0 = 0.0; b1 = 0.0; }
+    double x0 = 0.0, x1 = 0.0, y0 = 0.0, y1 = 0.0;
+    dmma884(x0, x1, a0, b0);
+    dmma884(y0, y1, p0, b0);
+    dmma884(x0, x1, a1, b1);
+    dmma884(y0, y1, p1, b1);
+    if (q < 3 && g < nrows) {
+        if (ra < R) {
+            A[(j0 + 2 * q) * PANEL_LD + ra] = x0;
+            A[(j0 + 2 * q + 1) * PANEL_LD + ra] = x1;
+        }
+        if (two && rb < R) {
+            A[(j0 + 2 * q) * PANEL_LD + rb] = y0;
+            A[(j0 + 2 * q + 1) * PANEL_LD + rb] = y1;
+        }
+    }
+    __syncwarp();
+}
+
+// spin until a published counter reaches `need` (every lane acquires)
+__device__ __forceinline__ void wait_counter(const int* p, int need, bool nap) {
+    int v;
+    for (;;) {
+        asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+        if (v >= need) break;
+        if (nap) __nanosleep(40);
+    }
+    __syncwarp();
+}
+
 // S-phase work for one panel row r below the diagonal block jb: x L_D^T = a
 __device__ __forceinline__ void panel_row_solve(double* A, const double* invAll, int jb, int r) {
     const int j0 = 6 * jb;
@@ -387,15 +596,6 @@ __device__ __forceinline__ void panel_diag_update(double* A, int jb, int lane) {
         A[(j1 + k) * PANEL_LD + j1 + i] -= sv;
     }
 }
-// publish / observe a step counter in shared memory with release / acquire semantics at CTA scope
-__device__ __forceinline__ void st_release_cta(int* p, int v) {
-    asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
-}
-__device__ __forceinline__ int ld_acquire_cta(const int* p) {
-    int v;
-    asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
-    return v;
-}
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
 __device__ __forceinline__ void named_bar_arrive(int id, int nthreads) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
 
@@ -415,22 +615,24 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     __shared__ int rowTab[4][PANEL_LD];
     __shared__ long long tBaseS;
     __shared__ __align__(16) double Wall[CHOL_MAXW][36];   // L_D^-1 of every block column (panel_factor_diag)
-    __shared__ int pubStep;                                // block columns the chain has factored (slab warps poll it)
+    __shared__ int pubW, pubL, preReady[CHOL_MAXW], rowProg[CHOL_MAXW];   // counters / flags of the data-flow loop (see there)
     LMState* st = d.st;
     const int q0 = c.levelPtr[lev], q1 = c.levelPtr[lev + 1];
     int q, slab;
     find_task(c.trsmPtr, q0, q1, c.trsmPtr[q0] + blockIdx.x, &q, &slab);
     const SnInfo n = sn_info(c, c.levelSn[q]);
     const int nc = n.nc, nt = n.nt, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int rb0 = nt + slab * c.rb;          // first front block row of the slab
-    const int rb1 = min(rb0 + c.rb, n.fb);
+    const int rbL = c.rbLev[lev];
+    const int rb0 = nt + slab * rbL;           // first front block row of the slab
+    const int rb1 = min(rb0 + rbL, n.fb);
     const bool last = (rb1 == n.fb);              // the last slab carries the rhs row
     const int nS = 6 * (rb1 - rb0) + (last ? 1 : 0);
     const int R = nc + nS;
     const int ch0 = c.childPtr[n.t], nch = c.childPtr[n.t + 1] - ch0;
 
     CHOL_STAMP(0);
-    if (tid == 0) { badFlag = 0; pubStep = 0; }
+    if (tid == 0) { badFlag = 0; pubW = 0; pubL = 0; }
+    if (tid < CHOL_MAXW) { preReady[tid] = 0; rowProg[tid] = 0; }
     for (int i = tid; i < nc * PANEL_LD; i += PANEL3_TPB) A[i] = 0.0;
     if (tid < nch && tid < CHOL_MAXCH) chs[tid] = load_child(c, ch0 + tid);
     __syncthreads();
@@ -596,83 +798,102 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
     //       never waits for the bulk updates.
     // Warps 4, 8, 12 share warp 0's scheduler / FP64 pipe and sit phase X out.
     if constexpr (DC) {
-        // Decoupled loop.  Roles (16 warps): warp 0 = chain; warps 4, 8, 12 share its scheduler and sit the loop out;
-        // of the other twelve, D-workers 0..7 keep the DIAGONAL part (rows < nc) in step with the chain, slab warps 0..3
-        // own the rows below it (two fixed 8-row tiles each) and follow at their own pace (panel_slab_tiles).
-        // Per block column jb:
-        //   chain     factor D_jb, W_jb = L_D(jb)^-1, publish "jb done"    -> arrive B1[jb&1]
-        //             wait B5: D-worker 0 has finished X(jb-1), i.e. rows j1..j1+7 of block columns jb, jb+1 are up to date
-        //             its own six rows j1..j1+5 times W_jb^T                 -> arrive B2[jb&1]
-        //             D_(jb+1) -= L L^T, next factor
-        //   D-workers sync B1: their tiles of the rows [j2, nc) times W_jb^T (S); sync B2 (also orders them among themselves);
-        //             X(jb): block column jb -> jb+1, finished columns -> jb+2 (panel_worker_tiles); D-worker 0 arrives B5.
-        //   slab warp waits for "jb done", then block column jb of its tiles by all finished columns, times W_jb^T.
-        // The chain never waits for the bulk updates of its own step, only for the tile of the NEXT diagonal block from
-        // the step before; it can be one step ahead, hence the two parities of B1 / B2.  W is kept for every block
-        // column because a slab warp may lag several steps.
-        constexpr int NWD = 8, NWS = 4;                  // D-workers, slab warps
-        constexpr int NB = (NWD + 1) * 32;               // chain + D-workers
+        // Data-flow loop: no barrier inside it, three published counters in shared memory (release / acquire at CTA scope).
+        // Roles (16 warps): warp 0 = chain; warps 4, 8, 12 share its scheduler and sit the loop out; of the other twelve,
+        // row warps 0..7 own the block rows of the DIAGONAL part (row warp w: block rows w + 1 and w + 9), slab warps 0..3
+        // own the rows below it (two fixed 8-row tiles each).  Everything but the 6x6 diagonal blocks is LEFT-looking
+        // and lags behind the chain at its own pace:
+        //   chain     step r (block row r = 1 .. nt-1), having factored D_(r-1) and published W_(r-1) (pubW = r):
+        //               wait preReady[r]; X[r, r-1] = C[r, r-1] W_(r-1)^T; publish "block row r final" (pubL = r);
+        //               D_r -= X X^T; factor D_r, W_r = L_D(r)^-1; publish (pubW = r + 1)
+        //   row warp  block row r, column blocks t = 0 .. r-2 in turn: C[r, t+1] -= sum_{m < t} X[r, m] L[t+1, m]^T as soon as
+        //               rowProg[t+1] >= t says those entries of block row t+1 are final (the long sum, two steps ahead of
+        //               its need; rowProg[r] = columns of block row r solved so far); wait pubW > t, X[r, t] = C[r, t] W_t^T; wait pubL > t, the rank-6 rest X[r, t] L[t+1, t]^T.
+        //               D_r -= sum_m X[r, m] X[r, m]^T likewise in a long and a rank-6 part; then preReady[r] = 1.
+        //   slab warp column block cb: wait pubW > cb, C = A[tile, cb] - sum_{m < cb} X[tile, m] L[cb, m]^T, X = C W_cb^T.
+        // W is kept for every block column because row and slab warps may lag several steps.
+        // Warps: 0 = chain; 4, 8, 12 share its scheduler and sit the loop out (work there was measured to slow the chain by
+        // half).  Of the other twelve, NWS take the slab tiles (pairs of tiles, stride NWS; a CTA of the upper levels has one
+        // to three: planPanelSlabs), NWR = 12 - NWS the block rows 1 .. 15 of the diagonal part: rows 1-4 (short sums) one
+        // after the other on row warp 0, then as many adjacent pairs as it takes, the late rows (long sums) a warp each.
+        const int nTs = (nS + 7) >> 3;
+        const int NWS = nTs <= 3 ? 1 : (nTs <= 6 ? 2 : 4), NWR = 12 - NWS;
         const bool dbgT = CHOL_DIAG(c) && blockIdx.x == 0 && tid == 0 && lev < 64;
         const long long tLoop0 = dbgT ? clock64() : 0;
-        // diagnostics (make DIAG=1): clocks of one level (CUGO_B200_DEBUG = 1 + 256 (level + 1); default level 2), CTA 0, per step,
-        // all against the chain's loop start --
-        //   chain    [0] arrive B1  [1] (unused)    [2] rows solved (arrive B2)  [3] next factor done
-        //   D-worker [4] arrives B1 [5] own S done  [6] (unused)                 [7] X done
+        // diagnostics (make DIAG=1): clocks of one level (CUGO_B200_DEBUG = 1 + 256 (level + 1); default level 2), CTA 0, per step r,
+        // against the loop start: chain [0] pubW = r  [1] preReady[r] seen  [2] pubL = r  [3] D_r factored;
+        // [4] the row warp's preReady[r] = 1.  [128..131] slab warps done, [136..143] row warps done.
         const bool trAny = CHOL_DIAG(c) && blockIdx.x == 0 && lev == ((CHOL_DIAG(c) >> 8) ? (CHOL_DIAG(c) >> 8) - 1 : 2);
         if (trAny && tid == 0) { g_cholTrace[126] = R; g_cholTrace[127] = nt; tBaseS = tLoop0; }
         if (trAny) __syncthreads();
         const long long tB = trAny ? tBaseS : 0;
         const int wk = (wid >> 2) * 3 + (wid & 3) - 1;   // 0..11 over the warps with (wid & 3) != 0
         if (wid == 0) {
-            panel_factor_diag(A, invAll, &badFlag, 0, lane, Wall[0]);
             const bool trc = trAny && lane == 0;
-            for (int jb = 0; jb < nt; jb++) {
+            panel_chain_factor(A, invAll, &badFlag, 0, lane, Wall[0], &pubW);
+            for (int r = 1; r < nt; r++) {
+                if (trc && r < 16) g_cholTrace[8 * r] = clock64() - tB;
+                wait_counter(&preReady[r], 1, false);
+                if (trc && r < 16) g_cholTrace[8 * r + 1] = clock64() - tB;
+                panel_tile_solve(A, Wall[r - 1], r - 1, 6 * r, R, lane, 6);
                 __syncwarp();
-                if (lane == 0) st_release_cta(&pubStep, jb + 1);
-                if (trc && jb < 16) g_cholTrace[8 * jb] = clock64() - tB;
-                if (jb + 1 == nt) break;
-                named_bar_arrive(1 + (jb & 1), NB);
-                if (jb > 0) named_bar_sync(5, 64);
-                panel_tile_solve(A, Wall[jb], jb, 6 * jb + 6, R, lane, 6);     // the six rows of the next diagonal block
+                if (lane == 0) st_release_cta(&pubL, r);
+                if (trc && r < 16) g_cholTrace[8 * r + 2] = clock64() - tB;
+                panel_diag_update(A, r - 1, lane);
                 __syncwarp();
-                named_bar_arrive(3 + (jb & 1), NB);
-                if (trc && jb < 16) g_cholTrace[8 * jb + 2] = clock64() - tB;
-                panel_diag_update(A, jb, lane);
-                __syncwarp();
-                panel_factor_diag(A, invAll, &badFlag, jb + 1, lane, Wall[jb + 1]);
-                if (trc && jb < 16) g_cholTrace[8 * jb + 3] = clock64() - tB;
+                panel_chain_factor(A, invAll, &badFlag, r, lane, Wall[r], &pubW);
+                if (trc && r < 16) g_cholTrace[8 * r + 3] = clock64() - tB;
             }
-        } else if ((wid & 3) != 0 && wk < NWD) {
-            const bool trw = trAny && tid == 32;
-            const int tb = NWD + (NWD - 1 - wk);         // D-worker 0 (whose tile the chain waits for) gets the last extra tile
-            for (int jb = 0; jb + 1 < nt; jb++) {        // nothing of D is left below the last diagonal block
-                if (trw && jb < 16) g_cholTrace[8 * jb + 4] = clock64() - tB;
-                if (trAny && lane == 0 && jb == 8) g_cholTrace[160 + wk] = clock64() - tB;      // every D-worker: arrives at B1(8)
-                named_bar_sync(1 + (jb & 1), NB);
-                // S: the rows of this warp's own X tiles (the chain solves the six rows of the next diagonal block)
-                const int rS = 6 * jb + 12;
-                const int nmtS = (nc - rS + 7) >> 3;
-                if (wk < nmtS) panel_tile_solve(A, Wall[jb], jb, rS + 8 * wk, nc, lane);
-                if (tb < nmtS) panel_tile_solve(A, Wall[jb], jb, rS + 8 * tb, nc, lane);
-                if (trw && jb < 16) g_cholTrace[8 * jb + 5] = clock64() - tB;
-                if (trAny && lane == 0 && jb == 8) g_cholTrace[144 + wk] = clock64() - tB;      // every D-worker: S(8) done
-                named_bar_sync(3 + (jb & 1), NB);
-                panel_worker_tiles(A, nc, nt, jb, wk, tb, lane, (trw && jb == 8) ? g_cholTrace + 168 : nullptr);
-                if (trw && jb == 8) g_cholTrace[171] = clock64();
-                if (wk == 0 && jb + 2 < nt) named_bar_arrive(5, 64);
-                if (trw && jb < 16) g_cholTrace[8 * jb + 7] = clock64() - tB;
-                if (trAny && lane == 0 && jb == 8) g_cholTrace[136 + wk] = clock64() - tB;      // every D-worker: X(8) done
+        } else if ((wid & 3) != 0 && wk < NWR) {
+            // block rows 1 .. 15 over NWR warps: the first 15 - NWR warps take an adjacent PAIR (rows 2w + 1, 2w + 2: the early rows,
+            // whose sums are short), the others one row; a pair runs as one instruction stream (panel_lag_acc2 / panel_tile_solve2)
+            const int nrw = nt - 1, npair = 15 - NWR;
+            const int ra = wk < npair ? 2 * wk + 1 : 2 * npair + (wk - npair) + 1;
+            const int rb = (wk < npair && ra + 1 <= nrw) ? ra + 1 : 0;
+            if (ra <= nrw) {
+                const int r0a = 6 * ra, r0b = 6 * rb, rlast = rb ? rb : ra;
+                if (ra == 1) {
+                    if (lane == 0) st_release_cta(&preReady[1], 1);
+                    if (trAny && lane == 0) g_cholTrace[8 + 4] = clock64() - tB;
+                }
+                for (int t = 0; t + 1 < rlast; t++) {
+                    const bool actA = t + 1 < ra;            // row a still has columns to solve (row b: always, inside the loop)
+                    const bool two = actA && rb != 0;
+                    const int r0x = actA ? r0a : r0b;        // the single job when only one row is active
+                    // the long part of the next target, off the chain's path: column block t + 1 by the columns [0, 6 t) --
+                    // final in block row t + 1 once rowProg[t + 1] >= t
+                    if (t > 0) {
+                        wait_counter(&rowProg[t + 1], t, true);
+                        panel_lag_acc2(A, 0, 6 * t, LagJob{t + 1, 6 * (t + 1), r0x}, LagJob{t + 1, 6 * (t + 1), r0b}, two, 6, R, lane);
+                    }
+                    wait_counter(&pubW, t + 1, true);
+                    panel_tile_solve2(A, Wall[t], t, r0x, r0b, two, R, lane, 6);
+                    if (lane == 0) {
+                        if (actA) st_release_cta(&rowProg[ra], t + 1);
+                        if (rb) st_release_cta(&rowProg[rb], t + 1);
+                    }
+                    // rank 6: D_r -= X[r, t] X[r, t]^T (own rows on both sides)
+                    panel_lag_acc2(A, 6 * t, 6 * t + 6, LagJob{actA ? ra : rb, r0x, r0x}, LagJob{rb, r0b, r0b}, two, 6, R, lane);
+                    wait_counter(&pubL, t + 1, true);
+                    // rank 6: C[r, t+1] -= X[r, t] L[t+1, t]^T
+                    panel_lag_acc2(A, 6 * t, 6 * t + 6, LagJob{t + 1, 6 * (t + 1), r0x}, LagJob{t + 1, 6 * (t + 1), r0b}, two, 6, R, lane);
+                    if (t + 2 == ra || t + 2 == rb) {
+                        const int rdone = t + 2;
+                        if (lane == 0) st_release_cta(&preReady[rdone], 1);
+                        if (trAny && lane == 0 && rdone < 16) g_cholTrace[8 * rdone + 4] = clock64() - tB;
+                    }
+                }
             }
+            if (trAny && lane == 0) g_cholTrace[136 + wk] = clock64() - tB;
         } else if ((wid & 3) != 0) {
-            const int sw = wk - NWD;                     // slab warp 0..3: tiles sw and sw + 4 of the rows from nc
-            const int nTs = (nS + 7) >> 3;
+            const int sw = wk - NWR;                     // slab warp: tiles sw, sw + NWS, sw + 2 NWS, ... of the rows from nc, in pairs
             if (sw < nTs) {
-                const bool two = sw + NWS < nTs;
-                const int ra0 = nc + 8 * sw, rb0 = nc + 8 * (two ? sw + NWS : sw);
                 for (int cb = 0; cb < nt; cb++) {
-                    while (ld_acquire_cta(&pubStep) < cb + 1) __nanosleep(64);
-                    __syncwarp();
-                    panel_slab_tiles(A, Wall[cb], cb, ra0, rb0, two, R, lane);
+                    wait_counter(&pubW, cb + 1, true);
+                    for (int tp = sw; tp < nTs; tp += 2 * NWS) {
+                        const bool two = tp + NWS < nTs;
+                        panel_slab_tiles(A, Wall[cb], cb, nc + 8 * tp, nc + 8 * (two ? tp + NWS : tp), two, R, lane);
+                    }
                 }
                 if (trAny && lane == 0) g_cholTrace[128 + sw] = clock64() - tB;      // slab warp done
             }

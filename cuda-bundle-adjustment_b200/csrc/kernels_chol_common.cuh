@@ -9,8 +9,8 @@ namespace cugo_b200 {
 
 constexpr int CHOL_MAXW = 16;               // block columns per supernode (panel width <= 96)
 constexpr double CHOL_PIVOT_TOL = 1e-14;    // reference zero-pivot tolerance, src/cholesky.hpp:79-92
-constexpr int CHOL_RB = 10;                 // block rows of L21 per panel slab (60 rows + rhs row)
-constexpr int PANEL_LD = 164;               // smem leading dimension: >= 6 MAXW + 6 RB + 1, == 4 (mod 16)
+constexpr int CHOL_RB = 16;                 // most block rows of L21 per panel slab (96 rows + rhs row); per level: Solver::planPanelSlabs
+constexpr int PANEL_LD = 196;               // smem leading dimension: >= 6 MAXW + 6 RB + 1, == 4 (mod 16)
 constexpr int CHOL_TB = 8;                  // block rows per update tile (48 rows)
 constexpr int UPD_LD = 52;                  // == 4 (mod 16): conflict-free DMMA fragment loads
 constexpr int UPD_CLD = 50;

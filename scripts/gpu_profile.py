@@ -54,12 +54,11 @@ if DIAG:
     trAll = s.debug_counters(176).reshape(-1)
     tr8 = trAll[:128].reshape(16, 8)
     print("traced CTA: R = %d rows, nt = %d block columns; slab warps done at" % (trAll[126], trAll[127]), trAll[128:132].tolist(),
-          "\n   D-workers at step 8: arrive at B1", trAll[160:168].tolist(), " S done", trAll[144:152].tolist(), " X done", trAll[136:144].tolist(),
-          "\n   D-worker 0, X(8): U part %d, L part %d, stores %d cycles" % (trAll[169] - trAll[168], trAll[170] - trAll[169], trAll[171] - trAll[170]))
-    print("decoupled panel loop, level 2, CTA 0, per step, cycles since the loop start: chain (arrive B1, -, rows solved = arrive B2, "
-          "next factor done) | D-worker 0 (arrives at B1, own S done, -, X done)")
-    for jb in range(16):
-        print("   step %2d" % jb, tr8[jb, :4].tolist(), tr8[jb, 4:].tolist())
+          " row warps done at", trAll[136:144].tolist())
+    print("data-flow panel loop, one level, CTA 0, per block row r, cycles since the loop start: chain (pubW = r, preReady[r] seen, pubL = r, "
+          "D_r factored) | the row warp's preReady[r] = 1")
+    for jb in range(1, 16):
+        print("   r %2d" % jb, tr8[jb, :4].tolist(), tr8[jb, 4])
 for rep in range(5):
     s.set_estimates(prob.poses, prob.landmarks)
     chi, lam, tr = s.optimize(10)
