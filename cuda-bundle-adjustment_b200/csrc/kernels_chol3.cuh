@@ -9,7 +9,7 @@
 
 namespace cugo_b200 {
 
-constexpr int PANEL3_TPB = 512;
+constexpr int PANEL3_TPB = 768;
 constexpr int BWD_MAXG = 8;            // CTAs that may share one supernode in the backward solve
 constexpr int PANEL3_NW = PANEL3_TPB / 32;
 
@@ -160,27 +160,45 @@ __device__ __forceinline__ void panel_factor_diag(double* A, double* invAll, int
     }
 }
 
+// C-fragment pair (x0, x1) = X[g][2q], X[g][2q+1] of an 8x6 block -> its A-fragment pair X[g][q], X[g][4+q] (the latter zero for
+// q >= 2), which is also the B-fragment of X^T.  Four 64-bit shuffles inside the quad of row g.
+__device__ __forceinline__ void frag_c_to_a(double x0, double x1, int lane, double& a0, double& a1) {
+    const int g4 = lane & ~3, q = lane & 3;
+    const double v0 = __shfl_sync(0xffffffffu, x0, g4 + (q >> 1)), v1 = __shfl_sync(0xffffffffu, x1, g4 + (q >> 1));
+    const double w0 = __shfl_sync(0xffffffffu, x0, g4 + 2), w1 = __shfl_sync(0xffffffffu, x1, g4 + 2);
+    a0 = (q & 1) ? v1 : v0;
+    a1 = q >= 2 ? 0.0 : (q ? w1 : w0);
+}
+
 // The chain's factor of the data-flow loop: Cholesky of D_jb AND W = L_D^-1 in one pass (row k of W needs row k of L and
 // the rows of W above it, so it fills the bubbles of the next pivot's rsqrt), W published through `pub` (value jb + 1)
 // BEFORE L_D and the reciprocal diagonal are stored -- nothing inside the loop reads those two.
 // Lane `lane` carries column min(lane, 5)... every lane runs the same instruction stream: column k = lane of W is
 // w_i = ([i == k] - sum_{p<i} l_ip w_p) / l_ii, exact zeros above the diagonal; lanes 0..5 store.
-__device__ __forceinline__ void panel_chain_factor(double* A, double* invAll, int* badFlag, int jb, int lane, double* Wsm, int* pub) {
+// 1 / sqrt(x) for the chain: the hardware approximation (about 20 bits) and ONE third-order step
+// y (1 + e/2 + 3/8 e^2), e = 1 - x y^2 -- error e^3 ~ 2^-60 before rounding; no special cases (x is a pivot > 1e-14, or the
+// factorisation has failed anyway).  55 dependent cycles against 74 for rsqrt().
+__device__ __forceinline__ double chain_rsqrt(double x) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double e = fma(-x * y, y, 1.0);
+    const double p = fma(e, 0.375, 0.5);
+    return fma(y * e, p, y);
+}
+__device__ __forceinline__ void panel_chain_core(double (&Ld)[21], double* A, double* invAll, int* badFlag, int jb, int lane, double* Wsm, int* pub) {
     const int j0 = 6 * jb;
-    double Ld[21], invd[6], w[6];
-#pragma unroll
-    for (int i = 0; i < 6; i++)
-#pragma unroll
-        for (int k = 0; k <= i; k++) Ld[tri(i, k)] = A[(j0 + k) * PANEL_LD + j0 + i];
+    double invd[6], w[6];
     bool bad = false;
 #pragma unroll
     for (int k = 0; k < 6; k++) {
-        double x = Ld[tri(k, k)];
-        if (!(x > CHOL_PIVOT_TOL)) { bad = true; x = 1.0; }
+        // a pivot <= tol fails the factorisation (the trial is rejected: st->fail); the test is kept OFF the dependent chain --
+        // what follows a bad pivot is never used, it only has to terminate
+        const double x = Ld[tri(k, k)];
+        bad = bad || !(x > CHOL_PIVOT_TOL);
         double sv = (lane == k) ? 1.0 : 0.0;            // row k of W: independent of this pivot's rsqrt up to the last product
 #pragma unroll
         for (int p2 = 0; p2 < k; p2++) sv -= Ld[tri(k, p2)] * w[p2];
-        const double inv = rsqrt(x);
+        const double inv = chain_rsqrt(x);
         invd[k] = inv;
         w[k] = sv * inv;
         Ld[tri(k, k)] = x * inv;
@@ -206,6 +224,52 @@ __device__ __forceinline__ void panel_chain_factor(double* A, double* invAll, in
         for (int k = 0; k < 6; k++) invAll[6 * jb + k] = invd[k];
         if (bad) *badFlag = 1;
     }
+}
+__device__ __forceinline__ void panel_chain_factor(double* A, double* invAll, int* badFlag, int jb, int lane, double* Wsm, int* pub) {
+    const int j0 = 6 * jb;
+    double Ld[21];
+#pragma unroll
+    for (int i = 0; i < 6; i++)
+#pragma unroll
+        for (int k = 0; k <= i; k++) Ld[tri(i, k)] = A[(j0 + k) * PANEL_LD + j0 + i];
+    panel_chain_core(Ld, A, invAll, badFlag, jb, lane, Wsm, pub);
+}
+// One step of the chain for block row r >= 1 (see the loop in k_chol_panel3): X[r, r-1] = C W_(r-1)^T on the tensor pipe,
+// published; D_r -= X X^T in fragment registers, handed to every lane by shuffles (entry (i, k) sits in lane 4 i + k / 2);
+// factor + W_r (panel_chain_core).
+__device__ __forceinline__ void panel_chain_step(double* A, double* invAll, int* badFlag, int r, int R, int lane, double (*Wall)[36],
+                                                 int* pubW, int* pubL) {
+    const int g = lane >> 2, q = lane & 3, cl = 2 * q, r0 = 6 * r, j0 = r0 - 6, row = r0 + g;
+    const int clc = cl < 6 ? cl : 0, n6 = g < 6 ? g : 0;
+    const double c0 = A[(j0 + clc) * PANEL_LD + row], c1 = A[(j0 + clc + 1) * PANEL_LD + row];     // C[r, r-1]
+    double d0 = A[(r0 + clc) * PANEL_LD + row], d1 = A[(r0 + clc + 1) * PANEL_LD + row];           // D_r so far
+    double wb0 = Wall[r - 1][n6 * 6 + q], wb1 = Wall[r - 1][n6 * 6 + 4 + (q & 1)];
+    if (q >= 2) wb1 = 0.0;
+    if (g >= 6) { wb0 = 0.0; wb1 = 0.0; }
+    double ca0, ca1;
+    frag_c_to_a(c0, c1, lane, ca0, ca1);
+    double x0 = 0.0, x1 = 0.0;
+    dmma884(x0, x1, ca0, wb0);
+    dmma884(x0, x1, ca1, wb1);
+    if (cl < 6 && g < 6) {
+        A[(j0 + cl) * PANEL_LD + row] = x0;
+        A[(j0 + cl + 1) * PANEL_LD + row] = x1;
+    }
+    __syncwarp();
+    if (lane == 0) st_release_cta(pubL, r);
+    double xa0, xa1;
+    frag_c_to_a(x0, x1, lane, xa0, xa1);
+    dmma884(d0, d1, -xa0, xa0);
+    dmma884(d0, d1, -xa1, xa1);
+    double Ld[21];
+#pragma unroll
+    for (int i = 0; i < 6; i++)
+#pragma unroll
+        for (int k = 0; k <= i; k++) {
+            const double v = __shfl_sync(0xffffffffu, (k & 1) ? d1 : d0, 4 * i + (k >> 1));
+            Ld[tri(i, k)] = v;
+        }
+    panel_chain_core(Ld, A, invAll, badFlag, r, lane, Wall[r], pubW);
 }
 
 // S-phase of one 8-row tile on the tensor pipe: X = A_blk W^T for rows [r0, r0 + 8) of block column jb (W = L_D(jb)^-1 from
@@ -328,18 +392,46 @@ __device__ __forceinline__ void panel_worker_tiles(double* A, int R, int nt, int
     }
 }
 
+// two tile solves in one instruction stream (rows r0a.. and, if `two`, r0b..), see panel_tile_solve
+__device__ __forceinline__ void panel_tile_solve2(double* A, const double* Wsm, int jb, int r0a, int r0b, bool two, int R, int lane, int nrows) {
+    const int j0 = 6 * jb, g = lane >> 2, q = lane & 3;
+    const int ra = r0a + g, rb = (two ? r0b : r0a) + g;
+    double a0 = A[(j0 + q) * PANEL_LD + ra], a1 = A[(j0 + 4 + (q & 1)) * PANEL_LD + ra];
+    double p0 = A[(j0 + q) * PANEL_LD + rb], p1 = A[(j0 + 4 + (q & 1)) * PANEL_LD + rb];
+    const int n = g < 6 ? g : 0;
+    double b0 = Wsm[n * 6 + q], b1 = Wsm[n * 6 + 4 + (q & 1)];
+    if (q >= 2) { a1 = 0.0; p1 = 0.0; b1 = 0.0; }
+    if (g >= 6) { b0 = 0.0; b1 = 0.0; }
+    double x0 = 0.0, x1 = 0.0, y0 = 0.0, y1 = 0.0;
+    dmma884(x0, x1, a0, b0);
+    dmma884(y0, y1, p0, b0);
+    dmma884(x0, x1, a1, b1);
+    dmma884(y0, y1, p1, b1);
+    if (q < 3 && g < nrows) {
+        if (ra < R) {
+            A[(j0 + 2 * q) * PANEL_LD + ra] = x0;
+            A[(j0 + 2 * q + 1) * PANEL_LD + ra] = x1;
+        }
+        if (two && rb < R) {
+            A[(j0 + 2 * q) * PANEL_LD + rb] = y0;
+            A[(j0 + 2 * q + 1) * PANEL_LD + rb] = y1;
+        }
+    }
+    __syncwarp();
+}
+
 // Rows below the diagonal part (the slab rows and the rhs row) are nobody's operand inside the panel: X = S L11^-T can lag
 // behind the factorisation of D.  A slab warp owns one or two fixed 8-row tiles and runs its own left-looking loop over the
 // block columns, tied to the chain only by the published step counter: for block column cb
 //   C = A[tile, cb] - sum_{k < 6 cb} X[tile, k] L[6 cb .., k]^T        (FP64 DMMA, K = 6 cb, two accumulators per tile)
 //   X[tile, cb] = C W_cb^T                                            (panel_tile_solve, through the panel itself)
 // Reads: its own rows, and rows [6 cb, 6 cb + 8) of the finished columns -- final once the chain has factored D_cb.
-__device__ __forceinline__ void panel_slab_tiles(double* A, const double* Wcb, int cb, int ra0, int rb0, bool two, int R, int lane) {
+__device__ __forceinline__ void panel_slab_tiles(double* A, const double* Wcb, int cb, int ra0, int rb0, bool two, int R, int lane, int phase = 3) {
     const int g = lane >> 2, q = lane & 3, cl = 2 * q;
     const bool st = cl < 6;
     const int c0 = 6 * cb, ra = ra0 + g, rb = rb0 + g;
     const int cu = st ? c0 + cl : c0;
-    if (cb > 0) {
+    if (cb > 0 && (phase & 1)) {
         const double ta0 = A[cu * PANEL_LD + ra], ta1 = A[(cu + 1) * PANEL_LD + ra];
         const double tb0 = A[cu * PANEL_LD + rb], tb1 = A[(cu + 1) * PANEL_LD + rb];
         double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0, e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
@@ -398,9 +490,7 @@ __device__ __forceinline__ void panel_slab_tiles(double* A, const double* Wcb, i
         }
         __syncwarp();
     }
-    panel_tile_solve(A, Wcb, cb, ra0, R, lane);
-    if (two) panel_tile_solve(A, Wcb, cb, rb0, R, lane);
-    __syncwarp();
+    if (phase & 2) panel_tile_solve2(A, Wcb, cb, ra0, rb0, two, R, lane, 8);
 }
 
 // Left-looking accumulate of one 8-row group into column block cb by the first K finished columns:
@@ -516,34 +606,6 @@ __device__ __forceinline__ void panel_lag_acc2(double* A, int K0, int K1, LagJob
     }
     __syncwarp();
 }
-// two tile solves in one instruction stream (rows r0a.. and, if `two`, r0b..), see panel_tile_solve
-__device__ __forceinline__ void panel_tile_solve2(double* A, const double* Wsm, int jb, int r0a, int r0b, bool two, int R, int lane, int nrows) {
-    const int j0 = 6 * jb, g = lane >> 2, q = lane & 3;
-    const int ra = r0a + g, rb = (two ? r0b : r0a) + g;
-    double a0 = A[(j0 + q) * PANEL_LD + ra], a1 = A[(j0 + 4 + (q & 1)) * PANEL_LD + ra];
-    double p0 = A[(j0 + q) * PANEL_LD + rb], p1 = A[(j0 + 4 + (q & 1)) * PANEL_LD + rb];
-    const int n = g < 6 ? g : 0;
-    double b0 = Wsm[n * 6 + q], b1 = Wsm[n * 6 + 4 + (q & 1)];
-    if (q >= 2) { a1 = 0.0; p1 = 0.0; b1 = 0.0; }
-    if (g >= 6) { b0 = 0.0; b1 = 0.0; }
-    double x0 = 0.0, x1 = 0.0, y0 = 0.0, y1 = 0.0;
-    dmma884(x0, x1, a0, b0);
-    dmma884(y0, y1, p0, b0);
-    dmma884(x0, x1, a1, b1);
-    dmma884(y0, y1, p1, b1);
-    if (q < 3 && g < nrows) {
-        if (ra < R) {
-            A[(j0 + 2 * q) * PANEL_LD + ra] = x0;
-            A[(j0 + 2 * q + 1) * PANEL_LD + ra] = x1;
-        }
-        if (two && rb < R) {
-            A[(j0 + 2 * q) * PANEL_LD + rb] = y0;
-            A[(j0 + 2 * q + 1) * PANEL_LD + rb] = y1;
-        }
-    }
-    __syncwarp();
-}
-
 // spin until a published counter reaches `need` (every lane acquires)
 __device__ __forceinline__ void wait_counter(const int* p, int need, bool nap) {
     int v;
@@ -553,6 +615,90 @@ __device__ __forceinline__ void wait_counter(const int* p, int need, bool nap) {
         if (nap) __nanosleep(40);
     }
     __syncwarp();
+}
+
+// One block row r (rows 6r .. 6r+5; 8 are computed) of the diagonal part, all its column blocks t = 0 .. r-2, by one warp.
+// The running target C[r, t] and the diagonal block D_r live in REGISTERS (C-fragment layout) from stage to stage; shared
+// memory sees only the solved X[r, t] (which other warps read) and, at the end, C[r, r-1] and D_r for the chain.  Per stage:
+//   cn  = A[r, t+1] - sum_{k < 6t} X[r, k] L[t+1, k]^T        long sum, before the chain is needed (rowProg[t+1] >= t)
+//   X   = C W_t^T                                           after pubW > t; stored; A-fragment of X by shuffles
+//   D  -= X X^T ;  cn -= X L[t+1, t]^T  (after pubL > t) ;  C = cn
+__device__ __forceinline__ void panel_row_run(double* A, const double (*Wall)[36], int r, int R, int lane, const int* pubW,
+                                              const int* pubL, int* rowProg, int* preReady) {
+    const int g = lane >> 2, q = lane & 3, cl = 2 * q, r0 = 6 * r, row = r0 + g;
+    const bool st = cl < 6 && g < 6 && row < R;
+    const int clc = cl < 6 ? cl : 0;
+    double c0 = A[clc * PANEL_LD + row], c1 = A[(clc + 1) * PANEL_LD + row];                       // C[r, 0]
+    double d0 = A[(r0 + clc) * PANEL_LD + row], d1 = A[(r0 + clc + 1) * PANEL_LD + row];           // D_r
+    const int n6 = g < 6 ? g : 0;
+    for (int t = 0; t + 1 < r; t++) {
+        const int j0 = 6 * t, j1 = j0 + 6;
+        // ---- next target and its long sum
+        double n0 = A[(j1 + clc) * PANEL_LD + row], n1 = A[(j1 + clc + 1) * PANEL_LD + row];
+        if (t > 0) {
+            wait_counter(rowProg + t + 1, t, true);
+            double s00 = 0.0, s01 = 0.0, s10 = 0.0, s11 = 0.0;
+            const double* Bp = A + j1 + g + q * PANEL_LD;
+            const double* Ap = A + row + q * PANEL_LD;
+            const int nfull = j0 >> 3, rem = j0 & 7;
+#pragma unroll 4
+            for (int it = 0; it < nfull; it++) {
+                const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
+                const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
+                dmma884(s00, s01, a0, b0);
+                dmma884(s10, s11, a1, b1);
+                Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD;
+            }
+            if (rem) {
+                const bool va = q < rem, vb = q + 4 < rem;
+                const int o1 = vb ? 4 * PANEL_LD : 0;
+                double b0 = Bp[0], b1 = Bp[o1], a0 = Ap[0], a1 = Ap[o1];
+                if (!va) { b0 = 0.0; a0 = 0.0; }
+                if (!vb) { b1 = 0.0; a1 = 0.0; }
+                dmma884(s00, s01, a0, b0);
+                dmma884(s10, s11, a1, b1);
+            }
+            n0 -= s00 + s10; n1 -= s01 + s11;
+        }
+        // ---- solve: X = C W_t^T
+        double ca0, ca1;
+        frag_c_to_a(c0, c1, lane, ca0, ca1);
+        wait_counter(pubW, t + 1, true);
+        double wb0 = Wall[t][n6 * 6 + q], wb1 = Wall[t][n6 * 6 + 4 + (q & 1)];
+        if (q >= 2) wb1 = 0.0;
+        if (g >= 6) { wb0 = 0.0; wb1 = 0.0; }
+        double x0 = 0.0, x1 = 0.0;
+        dmma884(x0, x1, ca0, wb0);
+        dmma884(x0, x1, ca1, wb1);
+        if (st) {
+            A[(j0 + cl) * PANEL_LD + row] = x0;
+            A[(j0 + cl + 1) * PANEL_LD + row] = x1;
+        }
+        __syncwarp();
+        if (lane == 0) st_release_cta(rowProg + r, t + 1);
+        double xa0, xa1;
+        frag_c_to_a(x0, x1, lane, xa0, xa1);
+        // ---- D_r -= X X^T
+        dmma884(d0, d1, -xa0, xa0);
+        dmma884(d0, d1, -xa1, xa1);
+        // ---- cn -= X L[t+1, t]^T
+        wait_counter(pubL, t + 1, true);
+        double lb0 = A[(j0 + q) * PANEL_LD + j1 + g], lb1 = A[(j0 + 4 + (q & 1)) * PANEL_LD + j1 + g];
+        if (q >= 2) lb1 = 0.0;
+        dmma884(n0, n1, -xa0, lb0);
+        dmma884(n0, n1, -xa1, lb1);
+        c0 = n0; c1 = n1;
+    }
+    if (st) {
+        if (r >= 2) {
+            A[(r0 - 6 + cl) * PANEL_LD + row] = c0;            // C[r, r-1] for the chain
+            A[(r0 - 6 + cl + 1) * PANEL_LD + row] = c1;
+        }
+        A[(r0 + cl) * PANEL_LD + row] = d0;
+        A[(r0 + cl + 1) * PANEL_LD + row] = d1;
+    }
+    __syncwarp();
+    if (lane == 0) st_release_cta(preReady + r, 1);
 }
 
 // S-phase work for one panel row r below the diagonal block jb: x L_D^T = a
@@ -812,12 +958,12 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
         //               D_r -= sum_m X[r, m] X[r, m]^T likewise in a long and a rank-6 part; then preReady[r] = 1.
         //   slab warp column block cb: wait pubW > cb, C = A[tile, cb] - sum_{m < cb} X[tile, m] L[cb, m]^T, X = C W_cb^T.
         // W is kept for every block column because row and slab warps may lag several steps.
-        // Warps: 0 = chain; 4, 8, 12 share its scheduler and sit the loop out (work there was measured to slow the chain by
-        // half).  Of the other twelve, NWS take the slab tiles (pairs of tiles, stride NWS; a CTA of the upper levels has one
-        // to three: planPanelSlabs), NWR = 12 - NWS the block rows 1 .. 15 of the diagonal part: rows 1-4 (short sums) one
-        // after the other on row warp 0, then as many adjacent pairs as it takes, the late rows (long sums) a warp each.
+        // Warps (24): 0 = chain; 4, 8, .., 20 share its scheduler and sit the loop out (work there was measured to slow the chain
+        // by half).  Of the other eighteen, fifteen take one block row of the diagonal part each (rows 1 .. 15), three the slab
+        // tiles (a tile each, or pairs with stride NWS when a CTA has more: planPanelSlabs).
+        static_assert(PANEL3_NW == 24, "warp roles of the data-flow loop");
         const int nTs = (nS + 7) >> 3;
-        const int NWS = nTs <= 3 ? 1 : (nTs <= 6 ? 2 : 4), NWR = 12 - NWS;
+        const int NWS = nTs > 6 ? 6 : 3, NWR = 18 - NWS;     // tall slabs (leaf levels): six slab warps, rows 13-15 double up
         const bool dbgT = CHOL_DIAG(c) && blockIdx.x == 0 && tid == 0 && lev < 64;
         const long long tLoop0 = dbgT ? clock64() : 0;
         // diagnostics (make DIAG=1): clocks of one level (CUGO_B200_DEBUG = 1 + 256 (level + 1); default level 2), CTA 0, per step r,
@@ -835,64 +981,29 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
                 if (trc && r < 16) g_cholTrace[8 * r] = clock64() - tB;
                 wait_counter(&preReady[r], 1, false);
                 if (trc && r < 16) g_cholTrace[8 * r + 1] = clock64() - tB;
-                panel_tile_solve(A, Wall[r - 1], r - 1, 6 * r, R, lane, 6);
-                __syncwarp();
-                if (lane == 0) st_release_cta(&pubL, r);
-                if (trc && r < 16) g_cholTrace[8 * r + 2] = clock64() - tB;
-                panel_diag_update(A, r - 1, lane);
-                __syncwarp();
-                panel_chain_factor(A, invAll, &badFlag, r, lane, Wall[r], &pubW);
+                panel_chain_step(A, invAll, &badFlag, r, R, lane, Wall, &pubW, &pubL);
                 if (trc && r < 16) g_cholTrace[8 * r + 3] = clock64() - tB;
             }
         } else if ((wid & 3) != 0 && wk < NWR) {
-            // block rows 1 .. 15 over NWR warps: the first 15 - NWR warps take an adjacent PAIR (rows 2w + 1, 2w + 2: the early rows,
-            // whose sums are short), the others one row; a pair runs as one instruction stream (panel_lag_acc2 / panel_tile_solve2)
-            const int nrw = nt - 1, npair = 15 - NWR;
-            const int ra = wk < npair ? 2 * wk + 1 : 2 * npair + (wk - npair) + 1;
-            const int rb = (wk < npair && ra + 1 <= nrw) ? ra + 1 : 0;
-            if (ra <= nrw) {
-                const int r0a = 6 * ra, r0b = 6 * rb, rlast = rb ? rb : ra;
-                if (ra == 1) {
-                    if (lane == 0) st_release_cta(&preReady[1], 1);
-                    if (trAny && lane == 0) g_cholTrace[8 + 4] = clock64() - tB;
-                }
-                for (int t = 0; t + 1 < rlast; t++) {
-                    const bool actA = t + 1 < ra;            // row a still has columns to solve (row b: always, inside the loop)
-                    const bool two = actA && rb != 0;
-                    const int r0x = actA ? r0a : r0b;        // the single job when only one row is active
-                    // the long part of the next target, off the chain's path: column block t + 1 by the columns [0, 6 t) --
-                    // final in block row t + 1 once rowProg[t + 1] >= t
-                    if (t > 0) {
-                        wait_counter(&rowProg[t + 1], t, true);
-                        panel_lag_acc2(A, 0, 6 * t, LagJob{t + 1, 6 * (t + 1), r0x}, LagJob{t + 1, 6 * (t + 1), r0b}, two, 6, R, lane);
-                    }
-                    wait_counter(&pubW, t + 1, true);
-                    panel_tile_solve2(A, Wall[t], t, r0x, r0b, two, R, lane, 6);
-                    if (lane == 0) {
-                        if (actA) st_release_cta(&rowProg[ra], t + 1);
-                        if (rb) st_release_cta(&rowProg[rb], t + 1);
-                    }
-                    // rank 6: D_r -= X[r, t] X[r, t]^T (own rows on both sides)
-                    panel_lag_acc2(A, 6 * t, 6 * t + 6, LagJob{actA ? ra : rb, r0x, r0x}, LagJob{rb, r0b, r0b}, two, 6, R, lane);
-                    wait_counter(&pubL, t + 1, true);
-                    // rank 6: C[r, t+1] -= X[r, t] L[t+1, t]^T
-                    panel_lag_acc2(A, 6 * t, 6 * t + 6, LagJob{t + 1, 6 * (t + 1), r0x}, LagJob{t + 1, 6 * (t + 1), r0b}, two, 6, R, lane);
-                    if (t + 2 == ra || t + 2 == rb) {
-                        const int rdone = t + 2;
-                        if (lane == 0) st_release_cta(&preReady[rdone], 1);
-                        if (trAny && lane == 0 && rdone < 16) g_cholTrace[8 * rdone + 4] = clock64() - tB;
-                    }
-                }
+            for (int r = wk + 1; r < nt; r += NWR) {
+                panel_row_run(A, Wall, r, R, lane, &pubW, &pubL, rowProg, preReady);
+                if (trAny && lane == 0 && r < 16) g_cholTrace[8 * r + 4] = clock64() - tB;
             }
             if (trAny && lane == 0) g_cholTrace[136 + wk] = clock64() - tB;
         } else if ((wid & 3) != 0) {
             const int sw = wk - NWR;                     // slab warp: tiles sw, sw + NWS, sw + 2 NWS, ... of the rows from nc, in pairs
             if (sw < nTs) {
                 for (int cb = 0; cb < nt; cb++) {
+                    // the long sum needs block row cb of L only (final at pubL = cb, a whole factor before W_cb)
+                    wait_counter(&pubL, cb, true);
+                    for (int tp = sw; tp < nTs; tp += 2 * NWS) {
+                        const bool two = tp + NWS < nTs;
+                        panel_slab_tiles(A, Wall[cb], cb, nc + 8 * tp, nc + 8 * (two ? tp + NWS : tp), two, R, lane, 1);
+                    }
                     wait_counter(&pubW, cb + 1, true);
                     for (int tp = sw; tp < nTs; tp += 2 * NWS) {
                         const bool two = tp + NWS < nTs;
-                        panel_slab_tiles(A, Wall[cb], cb, nc + 8 * tp, nc + 8 * (two ? tp + NWS : tp), two, R, lane);
+                        panel_slab_tiles(A, Wall[cb], cb, nc + 8 * tp, nc + 8 * (two ? tp + NWS : tp), two, R, lane, 2);
                     }
                 }
                 if (trAny && lane == 0) g_cholTrace[128 + sw] = clock64() - tB;      // slab warp done

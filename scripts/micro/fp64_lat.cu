@@ -61,6 +61,22 @@ __global__ void __launch_bounds__(1024) dmma_full(double* out, int iters, double
     for (int j = 0; j < 8; j++) s += c[j][0] + c[j][1];
     out[(blockIdx.x * blockDim.x + threadIdx.x) & 0xffff] = s;
 }
+// accuracy of the chain's reciprocal square root (kernels_chol3.cuh: chain_rsqrt) against rsqrt()
+__global__ void rsq_acc(double* out) {
+    double worst = 0.0, worst0 = 0.0;
+    for (int i = threadIdx.x; i < (1 << 20); i += blockDim.x) {
+        const double x = exp2(-46.0 + 110.0 * i / (1 << 20)) * (1.0 + 0.37 * (i % 97) / 97.0);
+        double y;
+        asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+        const double ref = rsqrt(x);
+        worst0 = fmax(worst0, fabs(y - ref) / ref);
+        const double e = fma(-x * y, y, 1.0);
+        const double p = fma(e, 0.375, 0.5);
+        y = fma(y * e, p, y);
+        worst = fmax(worst, fabs(y - ref) / ref);
+    }
+    out[threadIdx.x] = worst; out[256 + threadIdx.x] = worst0;
+}
 __global__ void ldslat(double* out, long long* cyc, int stride) {
     __shared__ int idx[1024];
     for (int i = threadIdx.x; i < 1024; i += blockDim.x) idx[i] = (i + stride) & 1023;
@@ -105,6 +121,12 @@ int main() {
             const double flop = 2.0 * 256 * 8.0 * iters * (nt / 32) * sms;
             printf("whole-GPU dmma %4d thr/SM x %d SMs: %.2f TFLOP/s (%.3f ms, CUDA events)\n", nt, sms, flop / (ms * 1e-3) / 1e12, ms);
         }
+    }
+    {
+        rsq_acc<<<1, 256>>>(out);
+        static double h2[512]; cudaMemcpy(h2, out, sizeof(h2), cudaMemcpyDeviceToHost);
+        double w = 0, w0 = 0; for (int i = 0; i < 256; i++) { if (h2[i] > w) w = h2[i]; if (h2[256 + i] > w0) w0 = h2[256 + i]; }
+        printf("rsqrt.approx.ftz.f64: max relative error %.3e; after one third-order step %.3e (against rsqrt(), x in [2^-46, 2^64])\n", w0, w);
     }
     printf("%s\n", cudaGetErrorString(cudaGetLastError()));
     return 0;
