@@ -701,6 +701,101 @@ __device__ __forceinline__ void panel_row_run(double* A, const double (*Wall)[36
     if (lane == 0) st_release_cta(preReady + r, 1);
 }
 
+// NT 8-row slab tiles (rows rt[i] .. rt[i] + 7, below the diagonal part) through ALL block columns t = 0 .. nt-1 by one warp, in one
+// instruction stream; the structure of panel_row_run without a diagonal block: the running targets stay in registers, shared
+// memory sees the solved X only.  The long sum of the next target needs block row t + 1 of L up to column 6 t (rowProg), the solve
+// W_t (pubW), the rank-6 rest L[t+1, t] (pubL) -- so a slab tile finishes one solve after the chain.
+template <int NT>
+__device__ __forceinline__ void panel_slab_run(double* A, const double (*Wall)[36], const int (&rt)[NT], int nt, int R, int lane,
+                                               const int* pubW, const int* pubL, const int* rowProg) {
+    const int g = lane >> 2, q = lane & 3, cl = 2 * q;
+    const int clc = cl < 6 ? cl : 0, n6 = g < 6 ? g : 0;
+    int row[NT];
+    bool st[NT];
+    double c0[NT], c1[NT];
+#pragma unroll
+    for (int i = 0; i < NT; i++) {
+        row[i] = min(rt[i] + g, PANEL_LD - 1);           // rows past R are computed and dropped; keep their loads inside the panel
+        st[i] = cl < 6 && rt[i] + g < R;
+        c0[i] = A[clc * PANEL_LD + row[i]]; c1[i] = A[(clc + 1) * PANEL_LD + row[i]];
+    }
+    for (int t = 0; t < nt; t++) {
+        const int j0 = 6 * t, j1 = j0 + 6;
+        const bool more = t + 1 < nt;
+        double n0[NT], n1[NT];
+        if (more) {
+#pragma unroll
+            for (int i = 0; i < NT; i++) { n0[i] = A[(j1 + clc) * PANEL_LD + row[i]]; n1[i] = A[(j1 + clc + 1) * PANEL_LD + row[i]]; }
+            if (t > 0) {
+                wait_counter(rowProg + t + 1, t, true);
+                double s0[NT], s1[NT], u0[NT], u1[NT];
+#pragma unroll
+                for (int i = 0; i < NT; i++) { s0[i] = s1[i] = u0[i] = u1[i] = 0.0; }
+                const double* Bp = A + j1 + g + q * PANEL_LD;
+                const int qo = q * PANEL_LD;
+                const int nfull = j0 >> 3, rem = j0 & 7;
+#pragma unroll 2
+                for (int it = 0; it < nfull; it++) {
+                    const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
+                    double a0[NT], a1[NT];
+#pragma unroll
+                    for (int i = 0; i < NT; i++) { a0[i] = A[qo + (8 * it) * PANEL_LD + row[i]]; a1[i] = A[qo + (8 * it + 4) * PANEL_LD + row[i]]; }
+#pragma unroll
+                    for (int i = 0; i < NT; i++) { dmma884(s0[i], s1[i], a0[i], b0); dmma884(u0[i], u1[i], a1[i], b1); }
+                    Bp += 8 * PANEL_LD;
+                }
+                if (rem) {
+                    const bool va = q < rem, vb = q + 4 < rem;
+                    const int o1 = vb ? 4 * PANEL_LD : 0;
+                    double b0 = Bp[0], b1 = Bp[o1];
+                    if (!va) b0 = 0.0;
+                    if (!vb) b1 = 0.0;
+#pragma unroll
+                    for (int i = 0; i < NT; i++) {
+                        double a0 = A[qo + (8 * nfull) * PANEL_LD + row[i]], a1 = A[qo + (8 * nfull) * PANEL_LD + o1 + row[i]];
+                        if (!va) a0 = 0.0;
+                        if (!vb) a1 = 0.0;
+                        dmma884(s0[i], s1[i], a0, b0);
+                        dmma884(u0[i], u1[i], a1, b1);
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < NT; i++) { n0[i] -= s0[i] + u0[i]; n1[i] -= s1[i] + u1[i]; }
+            }
+        }
+        // ---- solve
+        double ca0[NT], ca1[NT];
+#pragma unroll
+        for (int i = 0; i < NT; i++) frag_c_to_a(c0[i], c1[i], lane, ca0[i], ca1[i]);
+        wait_counter(pubW, t + 1, true);
+        double wb0 = Wall[t][n6 * 6 + q], wb1 = Wall[t][n6 * 6 + 4 + (q & 1)];
+        if (q >= 2) wb1 = 0.0;
+        if (g >= 6) { wb0 = 0.0; wb1 = 0.0; }
+        double x0[NT], x1[NT];
+#pragma unroll
+        for (int i = 0; i < NT; i++) { x0[i] = 0.0; x1[i] = 0.0; dmma884(x0[i], x1[i], ca0[i], wb0); }
+#pragma unroll
+        for (int i = 0; i < NT; i++) dmma884(x0[i], x1[i], ca1[i], wb1);
+#pragma unroll
+        for (int i = 0; i < NT; i++)
+            if (st[i]) { A[(j0 + cl) * PANEL_LD + row[i]] = x0[i]; A[(j0 + cl + 1) * PANEL_LD + row[i]] = x1[i]; }
+        __syncwarp();
+        if (!more) break;
+        double xa0[NT], xa1[NT];
+#pragma unroll
+        for (int i = 0; i < NT; i++) frag_c_to_a(x0[i], x1[i], lane, xa0[i], xa1[i]);
+        wait_counter(pubL, t + 1, true);
+        double lb0 = A[(j0 + q) * PANEL_LD + j1 + g], lb1 = A[(j0 + 4 + (q & 1)) * PANEL_LD + j1 + g];
+        if (q >= 2) lb1 = 0.0;
+#pragma unroll
+        for (int i = 0; i < NT; i++) {
+            dmma884(n0[i], n1[i], -xa0[i], lb0);
+            dmma884(n0[i], n1[i], -xa1[i], lb1);
+            c0[i] = n0[i]; c1[i] = n1[i];
+        }
+    }
+}
+
 // S-phase work for one panel row r below the diagonal block jb: x L_D^T = a
 __device__ __forceinline__ void panel_row_solve(double* A, const double* invAll, int jb, int r) {
     const int j0 = 6 * jb;
@@ -993,17 +1088,24 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
         } else if ((wid & 3) != 0) {
             const int sw = wk - NWR;                     // slab warp: tiles sw, sw + NWS, sw + 2 NWS, ... of the rows from nc, in pairs
             if (sw < nTs) {
-                for (int cb = 0; cb < nt; cb++) {
-                    // the long sum needs block row cb of L only (final at pubL = cb, a whole factor before W_cb)
-                    wait_counter(&pubL, cb, true);
-                    for (int tp = sw; tp < nTs; tp += 2 * NWS) {
-                        const bool two = tp + NWS < nTs;
-                        panel_slab_tiles(A, Wall[cb], cb, nc + 8 * tp, nc + 8 * (two ? tp + NWS : tp), two, R, lane, 1);
-                    }
-                    wait_counter(&pubW, cb + 1, true);
-                    for (int tp = sw; tp < nTs; tp += 2 * NWS) {
-                        const bool two = tp + NWS < nTs;
-                        panel_slab_tiles(A, Wall[cb], cb, nc + 8 * tp, nc + 8 * (two ? tp + NWS : tp), two, R, lane, 2);
+                if (nTs <= NWS) {
+                    // a tile per slab warp (the upper levels): running target in registers, one solve behind the chain
+                    const int rt1[1] = {nc + 8 * sw};
+                    panel_slab_run<1>(A, Wall, rt1, nt, R, lane, &pubW, &pubL, rowProg);
+                } else {
+                    // tall slabs (leaf levels): pairs of tiles through shared memory, left-looking per block column (measured
+                    // faster than two or three register-resident tiles per warp, which fall behind the chain)
+                    for (int cb = 0; cb < nt; cb++) {
+                        wait_counter(&pubL, cb, true);           // the long sum needs block row cb of L only
+                        for (int tp = sw; tp < nTs; tp += 2 * NWS) {
+                            const bool two = tp + NWS < nTs;
+                            panel_slab_tiles(A, Wall[cb], cb, nc + 8 * tp, nc + 8 * (two ? tp + NWS : tp), two, R, lane, 1);
+                        }
+                        wait_counter(&pubW, cb + 1, true);
+                        for (int tp = sw; tp < nTs; tp += 2 * NWS) {
+                            const bool two = tp + NWS < nTs;
+                            panel_slab_tiles(A, Wall[cb], cb, nc + 8 * tp, nc + 8 * (two ? tp + NWS : tp), two, R, lane, 2);
+                        }
                     }
                 }
                 if (trAny && lane == 0) g_cholTrace[128 + sw] = clock64() - tB;      // slab warp done
