@@ -228,7 +228,9 @@ struct Solver {
     DBuf<int> zr_levelPtr, zr_levelSn, zr_trsmPtr, zr_updPtr, zr_colOwn;
     void planDistFactor();
     void planPanelSlabs();
-    DBuf<int> zs_trsmPtr, zs_rbLev;    // panel-slab task table / slab height per level when chosen per level (planPanelSlabs)
+    DBuf<int> zs_trsmPtr, zs_rbLev, zs_updPtr;
+    std::vector<int> h_tbLev;        // update-tile height per level: CHOL_TB, or UPD_TBS where the level has few tiles
+    int updSmall = 1;               // option "upd_small" = 0: 48x48 update tiles on every level    // panel-slab task table / slab height per level when chosen per level (planPanelSlabs)
     int nblkG = 0;
     void commInit(int n, int r, const char* id);
     void allReduceSum(double* buf, size_t n) {
@@ -808,6 +810,8 @@ void Solver::buildStructure() {
     CK(cudaFuncSetAttribute(k_chol_panel3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_LD * ncMax * 8));
     CK(cudaFuncSetAttribute(k_chol_update3, cudaFuncAttributeMaxDynamicSharedMemorySize,
                             (2 * ncMax * UPD_LD + 2 * 6 * CHOL_TB * UPD_CLD) * 8));
+    CK(cudaFuncSetAttribute(k_chol_update_small, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            (2 * ncMax * UPD_LD + (UPD3_TPB / 32) * 6 * UPD_TBS * UPD_SCLD) * 8));
     CK(cudaStreamSynchronize(stream));
     systemBuilt = false; solved = false;
     lap("buffers");
@@ -959,15 +963,20 @@ void Solver::planPanelSlabs() {
     static const int cand[] = {2, 3, 4, 5, 6, 8, 10, 12, 14, 16};
     int a = 0;
     for (int l = 0; l < nlev; l++) {
-        int rb = panelRB > 0 ? panelRB : 10;        // no single wave even with the tallest slab: the round-1 height
+        int rb = panelRB > 0 ? panelRB : 10;
         if (panelRB == 0) {
+            // cost of the level ~ waves of CTAs (one CTA per SM: the panel takes most of its shared memory) x time of a CTA:
+            // the chain of diagonal blocks (fixed) against the slab rows its slab warps carry (grows with the slab height)
+            double best = 1e300;
             for (int cnd : cand) {
                 int ctas = 0;
                 for (int q = h_levelPtr[l]; q < h_levelPtr[l + 1]; q++) {
                     const int rt = rp[lsn[q] + 1] - rp[lsn[q]];
                     ctas += std::max(1, (rt + cnd - 1) / cnd);
                 }
-                if (ctas <= cap) { rb = cnd; break; }
+                const int waves = (ctas + sms - 1) / sms;
+                const double cost = waves * std::max(27.0, 12.0 + 2.2 * cnd) + (ctas > cap ? 0.5 : 0.0);
+                if (cost < best - 1e-9) { best = cost; rb = cnd; }
             }
         }
         rbLev[l] = rb;
@@ -978,6 +987,32 @@ void Solver::planPanelSlabs() {
         }
     }
     tr[nq] = a;
+    // update tiles: 24x24 instead of 48x48 on the levels where that still fits the GPU in one go (two CTAs per SM)
+    std::vector<int> up(nq + 1, 0);
+    h_tbLev.assign(nlev + 1, CHOL_TB);
+    int b = 0;
+    for (int l = 0; l < nlev; l++) {
+        auto tiles = [&](int tb) {
+            int t = 0;
+            for (int q = h_levelPtr[l]; q < h_levelPtr[l + 1]; q++) {
+                const int rt = rp[lsn[q] + 1] - rp[lsn[q]];
+                if (rt > 0) { const int n2 = (rt + tb) / tb; t += n2 * (n2 + 1) / 2; }
+            }
+            return t;
+        };
+        const int tb = (updSmall && tiles(UPD_TBS) <= 2 * sms) ? UPD_TBS : CHOL_TB;
+        h_tbLev[l] = tb;
+        for (int q = h_levelPtr[l]; q < h_levelPtr[l + 1]; q++) {
+            const int rt = rp[lsn[q] + 1] - rp[lsn[q]];
+            up[q] = b;
+            if (rt > 0) { const int n2 = (rt + tb) / tb; b += n2 * (n2 + 1) / 2; }
+        }
+    }
+    up[nq] = b;
+    zs_updPtr.alloc(nq + 1);
+    CK(cudaMemcpyAsync(zs_updPtr.p, up.data(), sizeof(int) * (nq + 1), cudaMemcpyHostToDevice, stream));
+    h_updPtr = up;
+    c.updPtr = zs_updPtr;
     zs_trsmPtr.alloc(nq + 1); zs_rbLev.alloc(nlev + 1);
     CK(cudaMemcpyAsync(zs_trsmPtr.p, tr.data(), sizeof(int) * (nq + 1), cudaMemcpyHostToDevice, stream));
     CK(cudaMemcpyAsync(zs_rbLev.p, rbLev.data(), sizeof(int) * (nlev + 1), cudaMemcpyHostToDevice, stream));
@@ -1123,7 +1158,11 @@ void Solver::enqueueSolve() {
         const int nUpd = h_updPtr[q1] - h_updPtr[q0];
         if (nUpd > 0) {
             const int kpad = (ncLev + 15) & ~15;
-            launch(k_chol_update3, nUpd, UPD3_TPB, (size_t)std::max(2 * kpad * UPD_LD, 2 * 6 * CHOL_TB * UPD_CLD) * 8, d, c, lev, kpad);
+            if (h_tbLev[lev] == UPD_TBS)
+                launch(k_chol_update_small, nUpd, UPD3_TPB,
+                       (size_t)std::max(2 * kpad * UPD_LD, (UPD3_TPB / 32) * 6 * UPD_TBS * UPD_SCLD) * 8, d, c, lev, kpad);
+            else
+                launch(k_chol_update3, nUpd, UPD3_TPB, (size_t)std::max(2 * kpad * UPD_LD, 2 * 6 * CHOL_TB * UPD_CLD) * 8, d, c, lev, kpad);
             mark("chol_update");
         }
     }
@@ -2059,13 +2098,14 @@ int cugo_b200_set_option(cugo_b200_solver* s, const char* name, int value) {
         if (!name) throw cugo_b200::ArgError("set_option: null name");
         const std::string n(name);
         if (n == "dist_factor") { S.distMode = value; S.structDirty = true; return; }
+        if (n == "upd_small") { S.updSmall = value; S.structDirty = true; return; }
         if (n == "panel_rb") {
             if (value < 0 || value > cugo_b200::CHOL_RB) throw cugo_b200::ArgError("set_option: panel_rb must be in [0, 16] (0: chosen per tree level)");
             S.panelRB = value; S.structDirty = true; return;
         }
         bool* f = n == "pdl" ? &S.pdl : n == "fuse_build" ? &S.fuseBuild : n == "panel_dc" ? &S.panelDC : n == "zinv" ? &S.zinvOn
                 : n == "bwd_split" ? &S.bwdSplit : n == "parallel_symbolic" ? &S.symParallel : nullptr;
-        if (!f) throw cugo_b200::ArgError("set_option: unknown option '" + n + "' (pdl, fuse_build, panel_dc, zinv, bwd_split, parallel_symbolic, dist_factor, panel_rb)");
+        if (!f) throw cugo_b200::ArgError("set_option: unknown option '" + n + "' (pdl, fuse_build, panel_dc, zinv, bwd_split, parallel_symbolic, dist_factor, panel_rb, upd_small)");
         *f = value != 0;
         S.structDirty = true;           // the options shape the structure and the trial graph
     });

@@ -1489,6 +1489,119 @@ __global__ void __launch_bounds__(UPD3_TPB) k_chol_update3(Dev d, Chol c, int le
     CHOL_GT(3);
 }
 
+// The same update for the UPPER tree levels, where a supernode has a few dozen tiles and most SMs idle: 24x24 tiles (four
+// times as many CTAs), K dealt to the 8 warps by 4-column steps (warp w: steps w, w + 8, ...), the eight partial tiles summed in
+// warp order -- deterministic.  Which levels use it: Solver::planPanelSlabs (tile height per level, Chol::tbLev).
+constexpr int UPD_TBS = 4;                  // block rows per small update tile (24 rows)
+constexpr int UPD_SCLD = 26;
+__global__ void __launch_bounds__(UPD3_TPB) k_chol_update_small(Dev d, Chol c, int lev, int kpadMax) {
+    extern __shared__ double sm[];
+    __shared__ ChildRef chs[CHOL_MAXCH];
+    __shared__ int invS[CHOL_MAXCH * 2 * UPD_TBS];
+    const LMState* st = d.st;
+    const int q0 = c.levelPtr[lev], q1 = c.levelPtr[lev + 1];
+    int q, tile;
+    find_task(c.updPtr, q0, q1, c.updPtr[q0] + blockIdx.x, &q, &tile);
+    const SnInfo n = sn_info(c, c.levelSn[q]);
+    int ti = (int)((sqrtf(8.0f * tile + 1.0f) - 1.0f) * 0.5f);
+    while ((ti + 1) * (ti + 2) / 2 <= tile) ti++;
+    while (ti * (ti + 1) / 2 > tile) ti--;
+    const int tj = tile - ti * (ti + 1) / 2;
+    constexpr int TS = 6 * UPD_TBS;
+    const int i0 = ti * TS, j0 = tj * TS;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int nc = n.nc, kp = (nc + 3) & ~3;
+    double* As = sm;
+    double* Bs = (ti == tj) ? sm : sm + kpadMax * UPD_LD;
+    double* Cs = sm;                                      // 8 partial tiles of 24 x UPD_SCLD over the operand stage
+    const double* __restrict__ Pn = c.L + c.Lptr[n.t];
+    const int ch0 = c.childPtr[n.t], nch = c.childPtr[n.t + 1] - ch0;
+    if (tid < nch && tid < CHOL_MAXCH) chs[tid] = load_child(c, ch0 + tid);
+    const int nchS = min(nch, CHOL_MAXCH);
+    if (nch > 0) {
+        __syncthreads();
+        for (int i = tid; i < nchS * 2 * UPD_TBS; i += UPD3_TPB) {
+            const int k = i % (2 * UPD_TBS);
+            const int fb = n.nt + (k < UPD_TBS ? UPD_TBS * ti + k : UPD_TBS * tj + (k - UPD_TBS));
+            invS[i] = fb < n.fb ? __ldg(chs[i / (2 * UPD_TBS)].inv + fb) : -1;
+        }
+    }
+    pdl_wait(); pdl_trigger();
+    if (st->done) return;
+    CHOL_GT(2);
+    for (int i = tid; i < kp * TS; i += UPD3_TPB) {
+        const int r = i % TS, k = i / TS;
+        const bool kin = k < nc;
+        cp_async8(As + k * UPD_LD + r, Pn + (size_t)(kin ? k : 0) * n.m + nc + i0 + r, kin && i0 + r < n.u);
+        if (ti != tj)
+            cp_async8(Bs + k * UPD_LD + r, Pn + (size_t)(kin ? k : 0) * n.m + nc + j0 + r, kin && j0 + r < n.u);
+    }
+    cp_async_wait_all();
+    __syncthreads();
+    const int fr8 = lane >> 2, fk = lane & 3;
+    double acc[3][3][2];
+#pragma unroll
+    for (int x = 0; x < 3; x++)
+#pragma unroll
+        for (int y = 0; y < 3; y++) acc[x][y][0] = acc[x][y][1] = 0.0;
+    for (int s4 = wid; s4 < (kp >> 2); s4 += UPD3_TPB / 32) {
+        double a[3], b[3];
+#pragma unroll
+        for (int x = 0; x < 3; x++) {
+            a[x] = As[(4 * s4 + fk) * UPD_LD + 8 * x + fr8];
+            b[x] = Bs[(4 * s4 + fk) * UPD_LD + 8 * x + fr8];
+        }
+#pragma unroll
+        for (int x = 0; x < 3; x++)
+#pragma unroll
+            for (int y = 0; y < 3; y++) dmma884(acc[x][y][0], acc[x][y][1], a[x], b[y]);
+    }
+    __syncthreads();            // every warp has read its operands: the stage becomes the partial tiles
+    {
+        double* Cd = Cs + wid * (TS * UPD_SCLD);
+#pragma unroll
+        for (int x = 0; x < 3; x++)
+#pragma unroll
+            for (int y = 0; y < 3; y++)
+#pragma unroll
+                for (int e = 0; e < 2; e++) Cd[(8 * y + 2 * fk + e) * UPD_SCLD + 8 * x + fr8] = acc[x][y][e];
+    }
+    __syncthreads();
+    // epilogue: add the children's blocks, store the lower triangle of U_t; one (block, column) unit per thread
+    double* __restrict__ Ut = c.U + c.Uptr[n.t];
+    const int rt = n.rt;
+    constexpr int NU = UPD_TBS * UPD_TBS * 6;
+    if (tid < NU) {
+        const int c6 = tid % 6, item = tid / 6, br = item % UPD_TBS, bc = item / UPD_TBS;
+        const int gbr = UPD_TBS * ti + br, gbc = UPD_TBS * tj + bc;
+        if (!(gbr > rt || gbc > gbr || gbc >= rt)) {
+            PullUnit u0, u1;
+            u0.kr = (gbr == rt) ? -1 : br;
+            u0.kc = UPD_TBS + bc;
+            u0.c6 = c6;
+            u0.rmin = (gbr == gbc) ? c6 : 0;
+            u1 = u0;
+            const int o = (6 * bc + c6) * UPD_SCLD + 6 * br;
+            double* dst = Ut + (size_t)(6 * gbc + c6) * n.u + 6 * gbr;
+            double v0[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, v1[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+            pull_pair(chs, invS, 2 * UPD_TBS, nchS, u0, u1, false, v0, v1);
+            if (nch > CHOL_MAXCH)
+                pull_unit(c, chs, ch0, nch, u0.kr < 0 ? -1 : n.nt + UPD_TBS * ti + u0.kr, n.nt + UPD_TBS * tj + bc, c6, u0.rmin, v0, CHOL_MAXCH);
+            const int nrr = u0.kr >= 0 ? 6 : 1;
+#pragma unroll
+            for (int rr = 0; rr < 6; rr++) {
+                if (rr < nrr && rr >= u0.rmin) {
+                    double sv = 0.0;
+#pragma unroll
+                    for (int w8 = 0; w8 < UPD3_TPB / 32; w8++) sv += Cs[w8 * (TS * UPD_SCLD) + o + rr];
+                    dst[rr] = v0[rr] - sv;
+                }
+            }
+        }
+    }
+    CHOL_GT(3);
+}
+
 // ---------------------------------------------------------------------------
 // ---------------------------------------------------------------------------
 // Z = L11^-1 of every supernode of a level -> c.Zinv (block lower triangle, nc x nc column-major per supernode at
