@@ -230,6 +230,7 @@ struct Solver {
     void planPanelSlabs();
     DBuf<int> zs_trsmPtr, zs_rbLev, zs_updPtr;
     std::vector<int> h_tbLev;        // update-tile height per level: CHOL_TB, or UPD_TBS where the level has few tiles
+    bool schurMma = false;          // option "schur_mma" = 1: the Schur products as DMMAs (measured slower: 0.184 vs 0.165 ms)
     int updSmall = 1;               // option "upd_small" = 0: 48x48 update tiles on every level    // panel-slab task table / slab height per level when chosen per level (planPanelSlabs)
     int nblkG = 0;
     void commInit(int n, int r, const char* id);
@@ -631,8 +632,10 @@ void Solver::buildStructure() {
             k_blk_pass<<<divUp(nmulAll, TB), TB, 0, stream>>>(prodRank, head, blkOf, nmulAll, schurCap, schurPasses, blkPass);
         }
         if (getenv("CUGO_B200_DEBUG")) fprintf(stderr, "[cugo_b200] max pose degree %d, schur stage %d blocks, %d row units\n", maxPoseDeg, schurCap, nRowUnits);
-        CK(cudaFuncSetAttribute(k_schur_rows<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)srow_smem_bytes(schurCap)));
-        CK(cudaFuncSetAttribute(k_schur_rows<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)srow_smem_bytes(schurCap)));
+        CK(cudaFuncSetAttribute(k_schur_rows<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)srow_smem_bytes(schurCap)));
+        CK(cudaFuncSetAttribute(k_schur_rows<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)srow_smem_bytes(schurCap)));
+        CK(cudaFuncSetAttribute(k_schur_rows<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)srow_smem_bytes(schurCap)));
+        CK(cudaFuncSetAttribute(k_schur_rows<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)srow_smem_bytes(schurCap)));
     }
 
     // ---- several ranks: the factorisation works on the union of the ranks' block patterns
@@ -1122,8 +1125,13 @@ void Solver::enqueueBuild() {
 void Solver::enqueueSolve() {
     launch(k_schur_inv<256>, divUp(d.nL, 256), 256, 0, d); mark("schur_inv");
     const int2* bp = schurPasses > 1 ? blkPass.p : nullptr;
-    if (f32) launch(k_schur_rows<float>, nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), d, schurCap, c.dbg, schurUnit, schurPasses, bp);
-    else launch(k_schur_rows<double>, nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), d, schurCap, c.dbg, schurUnit, schurPasses, bp);
+    if (schurMma) {
+        if (f32) launch(k_schur_rows<float, true>, nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), d, schurCap, c.dbg, schurUnit, schurPasses, bp);
+        else launch(k_schur_rows<double, true>, nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), d, schurCap, c.dbg, schurUnit, schurPasses, bp);
+    } else {
+        if (f32) launch(k_schur_rows<float, false>, nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), d, schurCap, c.dbg, schurUnit, schurPasses, bp);
+        else launch(k_schur_rows<double, false>, nRowUnits, SROW_TPB, srow_smem_bytes(schurCap), d, schurCap, c.dbg, schurUnit, schurPasses, bp);
+    }
     mark("schur_rows");
     // the one exchange step of a trial: partial reduced camera systems [Hsc | bsc] summed over the ranks
     if (nranks > 1)
@@ -2104,8 +2112,8 @@ int cugo_b200_set_option(cugo_b200_solver* s, const char* name, int value) {
             S.panelRB = value; S.structDirty = true; return;
         }
         bool* f = n == "pdl" ? &S.pdl : n == "fuse_build" ? &S.fuseBuild : n == "panel_dc" ? &S.panelDC : n == "zinv" ? &S.zinvOn
-                : n == "bwd_split" ? &S.bwdSplit : n == "parallel_symbolic" ? &S.symParallel : nullptr;
-        if (!f) throw cugo_b200::ArgError("set_option: unknown option '" + n + "' (pdl, fuse_build, panel_dc, zinv, bwd_split, parallel_symbolic, dist_factor, panel_rb, upd_small)");
+                : n == "schur_mma" ? &S.schurMma : n == "bwd_split" ? &S.bwdSplit : n == "parallel_symbolic" ? &S.symParallel : nullptr;
+        if (!f) throw cugo_b200::ArgError("set_option: unknown option '" + n + "' (pdl, fuse_build, panel_dc, zinv, bwd_split, parallel_symbolic, dist_factor, panel_rb, upd_small, schur_mma)");
         *f = value != 0;
         S.structDirty = true;           // the options shape the structure and the trial graph
     });

@@ -154,7 +154,8 @@ constexpr int SROW_NW = SROW_TPB / 32;
 constexpr int SROW_RING = 2 * 16 * 18;         // doubles per warp: two stages of 16 Hpl blocks
 constexpr int SROW_SIDE_LD = 14;               // doubles per edge of the phase-1 side stage: invHll 9, bl 3, pad
 constexpr int SROW_REGION = (SROW_NW * SROW_RING > SROW_TPB * SROW_SIDE_LD) ? SROW_NW * SROW_RING : SROW_TPB * SROW_SIDE_LD;
-constexpr int SROW_MAX_CAP = 480;              // Hpl blocks of the T stage: two CTAs per SM
+constexpr int SROW_MAX_CAP = 464;              // Hpl blocks of the T stage: two CTAs per SM (with the 2 KB of block descriptors)
+constexpr int SROW_NDESC = 256;                // Hsc blocks of a unit whose (first product, count) are staged in shared memory
 constexpr int SROW_UNIT = 2048;                // least products per work unit (engine: max(this, products / 1200))
 constexpr int SROW_BIG = 256;                  // blocks with more products are shared by all warps
 
@@ -293,10 +294,62 @@ __device__ __forceinline__ void srow_segment(const Dev& d, const double* T, doub
     }
 }
 
+// The same sum on the FP64 tensor pipe (round 2): the 16 products of a round are ONE product of a 6 x 48 by a 48 x 6 matrix --
+// [T_i(e_0) | T_i(e_1) | ...] [B_j(e_0) | B_j(e_1) | ...]^T, K index 3 p + k for product p, landmark dimension k -- i.e. twelve
+// DMMA m8n8k4 steps with both operands read straight from shared memory (T stage, copy ring) instead of 16 x 54 FMAs behind ~450
+// instructions of operand shuffling.  The accumulator fragment IS the block: lane (g, q) ends with elements (g, 2q), (g, 2q + 1),
+// so there is no reduction tree either.  out[] follows srow_elem_mma.
+__device__ __forceinline__ int srow_elem_mma(int lane, int j) {
+    const int g = lane >> 2, q = lane & 3;
+    return (g < 6 && q < 3) ? (2 * q + j) * 6 + g : -1;
+}
+template <typename HT>
+__device__ __forceinline__ void srow_segment_mma(const Dev& d, const double* T, double* ring, int c0, int cap, int pa, int pb,
+                                                 int lane, double out[2]) {
+    const int g = lane >> 2, q = lane & 3, g6 = g < 6 ? g : 0;
+    double acc0 = 0.0, acc1 = 0.0, acd0 = 0.0, acd1 = 0.0;      // two accumulator chains (even / odd steps)
+    const int nr = (pb - pa + 15) >> 4;
+    if (nr > 0) {
+        int sjn[5], rkc, rkn;
+        srow_meta(d, pa, pb, 0, lane, sjn, rkc);
+        srow_issue<HT>(d, ring, lane, sjn);
+        srow_meta(d, pa, pb, 1, lane, sjn, rkn);
+        for (int r = 0; r < nr; r++) {
+            srow_issue<HT>(d, ring + ((r + 1) & 1) * (16 * 18), lane, sjn);      // round r + 1 (nothing past the end)
+            int rk2;
+            srow_meta(d, pa, pb, r + 2, lane, sjn, rk2);
+            cp_async_wait_group<1>();                                         // round r has landed
+            __syncwarp();
+            // T offset of this lane pair's product (lanes 2p, 2p + 1 hold product p), -1 if it is not in the stage
+            const int e = rkc - c0;
+            const int toff = (e >= 0 && e < cap) ? 18 * e : -1;
+            const HT* B = reinterpret_cast<const HT*>(ring + (r & 1) * (16 * 18));
+            const int np = min(16, pb - pa - 16 * r);
+            const int nst = (3 * np + 3) >> 2;
+#pragma unroll 4
+            for (int s4 = 0; s4 < nst; s4++) {
+                const int kap = 4 * s4 + q, p = kap / 3, k = kap - 3 * p;
+                const int to = __shfl_sync(0xffffffffu, toff, 2 * p);
+                const bool ok = to >= 0 && p < np;
+                double a = T[(ok ? to : 0) + 6 * k + g6];
+                double b = (double)B[p * 18 + 6 * k + g6];
+                if (!ok) { a = 0.0; b = 0.0; }
+                if (g >= 6) { a = 0.0; b = 0.0; }
+                if (s4 & 1) dmma884(acd0, acd1, a, b);
+                else dmma884(acc0, acc1, a, b);
+            }
+            __syncwarp();                     // the stage is overwritten by the copies of round r + 2
+            rkc = rkn; rkn = rk2;
+        }
+    }
+    out[0] = acc0 + acd0;
+    out[1] = acc1 + acd1;
+}
+
 // blkPass (several passes only): per (block, pass) the range of the block's products whose row rank lies in
 // the pass's stage -- products of a block are ordered by landmark, as are the slots of a pose, so the range
 // is tight; the per-product rank test stays as the guarantee.
-template <typename HT>
+template <typename HT, bool MMA>
 __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hpl blocks the stage holds */, int dbg,
                                                             int unitProd, int npass, const int2* __restrict__ blkPass) {
     extern __shared__ __align__(16) double T[];     // [cap][18], block e at T + 18 e, column-major 6x3
@@ -304,6 +357,8 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
     __shared__ double part[2][SROW_NW][36];
     __shared__ double red[SROW_NW][6];
     __shared__ int nextBlk;
+    __shared__ int2 bdesc[SROW_NDESC];      // (first product, products) of the unit's blocks in this pass: one parallel load instead of a
+                                            // dependent global round trip per block and warp
     pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
 #ifndef CUGO_B200_DIAG
     dbg = 0;                         // the cycle counters exist in diagnostic builds only (make DIAG=1)
@@ -333,10 +388,11 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
         }
     }
     if (ub0 >= ub1 && u > 0) return;                // a block larger than the unit size swallowed this unit
-    const int e0 = srow_elem(lane, 0), e1 = srow_elem(lane, 1);
+    const int e0 = MMA ? srow_elem_mma(lane, 0) : srow_elem(lane, 0), e1 = MMA ? srow_elem_mma(lane, 1) : srow_elem(lane, 1);
     double* const ring = region + wid * SROW_RING;
     double tb[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     int par = 0;
+    long long dbgRounds = 0, dbgBlocks = 0;      // diagnostics: rounds / blocks handled by this warp
     for (int c0 = 0; c0 == 0 || c0 < deg; c0 += cap) {     // one pass unless deg > cap (loop-closure poses)
         const bool first = (c0 == 0);
         // ---- phase 1: T_e = Hpl_e invHll for the pose's blocks [c0, c0 + cap)
@@ -402,18 +458,29 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
             __syncthreads();        // the side stage is reused; T is complete after the last wave
         }
         if (tid == 0) nextBlk = ub0;
-        __syncthreads();
-        // ---- phase 2a: the large blocks, all warps on each
         const int ps = c0 / cap;
+        for (int k = tid; k < min(ub1 - ub0, SROW_NDESC); k += SROW_TPB) {
+            const int b = ub0 + k;
+            int2 dsc;
+            if (blkPass) { const int2 rg = blkPass[(size_t)b * npass + ps]; dsc = make_int2(rg.x, max(rg.y - rg.x, 0)); }
+            else { const int pb0 = d.prodPtr[b]; dsc = make_int2(pb0, d.prodPtr[b + 1] - pb0); }
+            bdesc[k] = dsc;
+        }
+        __syncthreads();
+        if (dbg && tid == 0 && blockIdx.x < 2048 && c0 == 0) g_schurDbg[2048 + blockIdx.x] = clock64() - tStart;   // phase 1 of the first pass
+        // ---- phase 2a: the large blocks, all warps on each
         for (int b = ub0; b < ub1; b++) {
             int bBeg, n;
-            if (blkPass) { const int2 rg = blkPass[(size_t)b * npass + ps]; bBeg = rg.x; n = max(rg.y - rg.x, 0); }
+            if (b - ub0 < SROW_NDESC) { const int2 dsc = bdesc[b - ub0]; bBeg = dsc.x; n = dsc.y; }
+            else if (blkPass) { const int2 rg = blkPass[(size_t)b * npass + ps]; bBeg = rg.x; n = max(rg.y - rg.x, 0); }
             else { bBeg = d.prodPtr[b]; n = d.prodPtr[b + 1] - bBeg; }
             if (n <= SROW_BIG) continue;
             const int qw = ((n + SROW_NW - 1) / SROW_NW + 15) & ~15;
             const int pa = bBeg + wid * qw;
+            dbgBlocks += 1000; dbgRounds += (max(min(pa + qw, bBeg + n) - pa, 0) + 15) >> 4;
             double o[2];
-            srow_segment<HT>(d, T, ring, c0, cap, pa, min(pa + qw, bBeg + n), lane, o);
+            if (MMA) srow_segment_mma<HT>(d, T, ring, c0, cap, pa, min(pa + qw, bBeg + n), lane, o);
+            else srow_segment<HT>(d, T, ring, c0, cap, pa, min(pa + qw, bBeg + n), lane, o);
             if (e0 >= 0) part[par][wid][e0] = o[0];
             if (e1 >= 0) part[par][wid][e1] = o[1];
             __syncthreads();
@@ -432,11 +499,14 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
             b = __shfl_sync(0xffffffffu, b, 0);
             if (b >= ub1) break;
             int bBeg, n;
-            if (blkPass) { const int2 rg = blkPass[(size_t)b * npass + ps]; bBeg = rg.x; n = max(rg.y - rg.x, 0); }
+            if (b - ub0 < SROW_NDESC) { const int2 dsc = bdesc[b - ub0]; bBeg = dsc.x; n = dsc.y; }
+            else if (blkPass) { const int2 rg = blkPass[(size_t)b * npass + ps]; bBeg = rg.x; n = max(rg.y - rg.x, 0); }
             else { bBeg = d.prodPtr[b]; n = d.prodPtr[b + 1] - bBeg; }
             if (n > SROW_BIG || (n == 0 && !first)) continue;
+            dbgBlocks++; dbgRounds += (n + 15) >> 4;
             double o[2];
-            srow_segment<HT>(d, T, ring, c0, cap, bBeg, bBeg + n, lane, o);
+            if (MMA) srow_segment_mma<HT>(d, T, ring, c0, cap, bBeg, bBeg + n, lane, o);
+            else srow_segment<HT>(d, T, ring, c0, cap, bBeg, bBeg + n, lane, o);
             if (e0 >= 0) srow_store(d, st, i, b, e0, o[0], first);
             if (e1 >= 0) srow_store(d, st, i, b, e1, o[1], first);
         }
@@ -455,7 +525,7 @@ __global__ void __launch_bounds__(SROW_TPB, 2) k_schur_rows(Dev d, int cap /* Hp
             d.bscPart[(size_t)i * 6 + tid] = d.b[(size_t)i * 6 + tid] - s;
         }
     }
-    if (dbg && tid == 0 && blockIdx.x < 8192) g_schurDbg[blockIdx.x] = clock64() - tStart;
+    if (dbg && tid == 0 && blockIdx.x < 2048) { g_schurDbg[blockIdx.x] = clock64() - tStart; g_schurDbg[4096 + blockIdx.x] = dbgRounds; g_schurDbg[6144 + blockIdx.x] = dbgBlocks; }
 }
 
 // work units of k_schur_rows: rows in launch order (heavy first), each cut into srow_units(products) units

@@ -41,7 +41,12 @@ if os.environ.get("CUGO_B200_DEBUG"):
     if not DIAG:
         print("(phase clocks need a diagnostic build of the library: make -C cuda-bundle-adjustment_b200 clean all DIAG=1)")
 if DIAG:
-    cyc = np.array(a[:s.sizes()["P"]], dtype=np.int64)
+    nun = min(2048, int(np.count_nonzero(np.array(a[:2048], dtype=np.int64))))
+    ph1 = np.array(a[2048:2048 + nun], dtype=np.int64)
+    rnd = np.array(a[4096:4096 + nun], dtype=np.int64); blk = np.array(a[6144:6144 + nun], dtype=np.int64)
+    print("schur warp 0 of every unit: rounds mean %.1f max %d; blocks (1000 per shared big block) mean %.1f max %d" % (rnd.mean(), rnd.max(), blk.mean(), blk.max()))
+    print("schur units: %d; phase 1 (T stage) cycles per unit  mean %.0f  median %.0f  max %.0f" % (nun, ph1.mean(), np.median(ph1), ph1.max()))
+    cyc = np.array(a[:nun], dtype=np.int64)
     print("schur rows: cycles per row  mean %.0f  median %.0f  p99 %.0f  max %.0f  (sum/148/2 = %.0f)" % (
         cyc.mean(), np.median(cyc), np.percentile(cyc, 99), cyc.max(), cyc.sum() / 296))
     print("  top rows", np.argsort(cyc)[-8:].tolist(), np.sort(cyc)[-8:].tolist())
