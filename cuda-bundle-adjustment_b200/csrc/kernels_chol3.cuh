@@ -1,9 +1,10 @@
 // kernels_chol3.cuh -- numeric multifrontal Cholesky of the reduced camera system and its solves
 // (replaces cusolverSpDcsrcholFactor / csrcholSolve, src/cholesky.hpp:109-156): k_chol_panel3 (one CTA per
-// (supernode, slab of <= CHOL_RB block rows of L21): [D; S] assembled and factored in shared memory, a decoupled chain warp
-// factors the 6x6 diagonal blocks while 12 worker warps run the DMMA updates with look-ahead), k_chol_update3 (48x48
-// tiles of the update matrices), k_chol_zinv (inverse of L11 on a side branch) and k_chol_bwd3 (backward solves).
-// DESIGN.md section 4 has the data flow and the measurements behind each choice.
+// (supernode, slab of block rows of L21): [D; S] assembled and factored in shared memory by a data-flow loop -- a chain warp for
+// the 6x6 diagonal blocks, a warp per block row of the diagonal part, slab warps behind published counters, FP64 DMMA
+// throughout), k_chol_update3 / k_chol_update_small (48x48 / 24x24 tiles of the update matrices), k_chol_zinv (inverse of L11
+// on a side branch) and k_chol_bwd3 (backward solves).  DESIGN.md section 4 has the data flow and the measurements behind
+// each choice.
 #pragma once
 #include "kernels_chol_common.cuh"
 
@@ -292,105 +293,6 @@ __device__ __forceinline__ void panel_tile_solve(double* A, const double* Wsm, i
     }
 }
 
-// X-phase work of one worker warp (see k_chol_panel3): 8-row tiles ta (and tb, if < nmt) of the rows from j2;
-//   U: block column jb -> block column jb+1 (rank 6), L: finished columns [0, j1) -> block column jb+2.
-__device__ __forceinline__ void panel_worker_tiles(double* A, int R, int nt, int jb, int ta, int tb, int lane, long long* trc = nullptr) {
-    if (trc) trc[0] = clock64();
-    const int j0 = 6 * jb, j1 = j0 + 6, j2 = j1 + 6;
-    const int fr8 = lane >> 2, fk = lane & 3;
-    const int nmt = (R - j2 + 7) >> 3;
-    if (ta < nmt) {
-        const bool two = tb < nmt, la = jb + 2 < nt;
-        const int cl = 2 * fk;
-        const bool st = cl < 6;                 // lanes whose two output columns exist
-        const int ra = j2 + 8 * ta + fr8, rb = j2 + 8 * (two ? tb : ta) + fr8;
-        const int cu = st ? j1 + cl : j1, cv = (st && la) ? j2 + cl : j1;      // valid columns for every lane
-        // ---- U operands (columns j0 + fk and j0 + 4 + fk <= j1 + 1 exist) and targets
-        double bu0 = A[(j0 + fk) * PANEL_LD + j1 + fr8], bu1 = A[(j0 + 4 + fk) * PANEL_LD + j1 + fr8];
-        double au0 = A[(j0 + fk) * PANEL_LD + ra], au1 = A[(j0 + 4 + fk) * PANEL_LD + ra];
-        double qu0 = A[(j0 + fk) * PANEL_LD + rb], qu1 = A[(j0 + 4 + fk) * PANEL_LD + rb];
-        if (fk >= 2) { bu1 = 0.0; au1 = 0.0; qu1 = 0.0; }
-        const double tu0 = A[cu * PANEL_LD + ra], tu1 = A[(cu + 1) * PANEL_LD + ra];
-        const double tv0 = A[cu * PANEL_LD + rb], tv1 = A[(cu + 1) * PANEL_LD + rb];
-        const double tc0 = A[cv * PANEL_LD + ra], tc1 = A[(cv + 1) * PANEL_LD + ra];
-        const double te0 = A[cv * PANEL_LD + rb], te1 = A[(cv + 1) * PANEL_LD + rb];
-        double u0 = 0.0, u1 = 0.0, v0 = 0.0, v1 = 0.0;
-        dmma884(u0, u1, au0, bu0);
-        dmma884(u0, u1, au1, bu1);
-        if (two) {
-            dmma884(v0, v1, qu0, bu0);
-            dmma884(v0, v1, qu1, bu1);
-        }
-        // ---- L: lane (fr8, fk) reads row (tile base + fr8) of column k0 + fk [+ 4]; pointers advance by
-        // eight columns per iteration, the partial last group is handled after the loop
-        double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0, e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
-        if (trc) trc[1] = clock64() + (long long)(u0 == 12345.678);
-        if (la) {
-            const double* Bp = A + j2 + fr8 + fk * PANEL_LD;
-            const double* Ap = A + ra + fk * PANEL_LD;
-            const double* Aq = A + rb + fk * PANEL_LD;
-            const int nfull = j1 >> 3, rem = j1 & 7;
-            const bool va = fk < rem, vb = fk + 4 < rem;
-            if (two) {
-#pragma unroll 2
-                for (int it = 0; it < nfull; it++) {
-                    const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
-                    const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
-                    const double q0 = Aq[0], q1 = Aq[4 * PANEL_LD];
-                    dmma884(c00, c01, a0, b0);
-                    dmma884(c10, c11, a1, b1);
-                    dmma884(e00, e01, q0, b0);
-                    dmma884(e10, e11, q1, b1);
-                    Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD; Aq += 8 * PANEL_LD;
-                }
-                if (rem) {                  // columns up to j1 + 7 < nc exist: load, then select
-                    double b0 = Bp[0], b1 = Bp[4 * PANEL_LD], a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
-                    double q0 = Aq[0], q1 = Aq[4 * PANEL_LD];
-                    if (!va) { b0 = 0.0; a0 = 0.0; q0 = 0.0; }
-                    if (!vb) { b1 = 0.0; a1 = 0.0; q1 = 0.0; }
-                    dmma884(c00, c01, a0, b0);
-                    dmma884(c10, c11, a1, b1);
-                    dmma884(e00, e01, q0, b0);
-                    dmma884(e10, e11, q1, b1);
-                }
-            } else {
-#pragma unroll 4
-                for (int it = 0; it < nfull; it++) {
-                    const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
-                    const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
-                    dmma884(c00, c01, a0, b0);
-                    dmma884(c10, c11, a1, b1);
-                    Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD;
-                }
-                if (rem) {
-                    double b0 = Bp[0], b1 = Bp[4 * PANEL_LD], a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
-                    if (!va) { b0 = 0.0; a0 = 0.0; }
-                    if (!vb) { b1 = 0.0; a1 = 0.0; }
-                    dmma884(c00, c01, a0, b0);
-                    dmma884(c10, c11, a1, b1);
-                }
-            }
-        }
-        // ---- stores
-        if (trc) trc[2] = clock64() + (long long)(c00 + c10 == 12345.678);
-        if (st && ra < R) {
-            A[(j1 + cl) * PANEL_LD + ra] = tu0 - u0;
-            A[(j1 + cl + 1) * PANEL_LD + ra] = tu1 - u1;
-            if (la) {
-                A[(j2 + cl) * PANEL_LD + ra] = tc0 - (c00 + c10);
-                A[(j2 + cl + 1) * PANEL_LD + ra] = tc1 - (c01 + c11);
-            }
-        }
-        if (two && st && rb < R) {
-            A[(j1 + cl) * PANEL_LD + rb] = tv0 - v0;
-            A[(j1 + cl + 1) * PANEL_LD + rb] = tv1 - v1;
-            if (la) {
-                A[(j2 + cl) * PANEL_LD + rb] = te0 - (e00 + e10);
-                A[(j2 + cl + 1) * PANEL_LD + rb] = te1 - (e01 + e11);
-            }
-        }
-    }
-}
 
 // two tile solves in one instruction stream (rows r0a.. and, if `two`, r0b..), see panel_tile_solve
 __device__ __forceinline__ void panel_tile_solve2(double* A, const double* Wsm, int jb, int r0a, int r0b, bool two, int R, int lane, int nrows) {
@@ -493,119 +395,6 @@ __device__ __forceinline__ void panel_slab_tiles(double* A, const double* Wcb, i
     if (phase & 2) panel_tile_solve2(A, Wcb, cb, ra0, rb0, two, R, lane, 8);
 }
 
-// Left-looking accumulate of one 8-row group into column block cb by the first K finished columns:
-//   A[r0 + g, 6 cb + n] -= sum_{K0 <= k < K1} A[r0 + g, k] A[6 cb + n, k]        (g < 8 rows, n < 6 columns)
-// stores limited to the first `nrows` rows (a 6-row block row computes 8 and keeps 6).  K0, K1 are multiples of 6.
-__device__ __forceinline__ void panel_lag_acc(double* A, int cb, int K0, int K1, int r0, int nrows, int R, int lane) {
-    const int K = K1 - K0;
-    if (K <= 0) return;
-    const int g = lane >> 2, q = lane & 3, cl = 2 * q;
-    const bool st = cl < 6;
-    const int c0 = 6 * cb, ra = r0 + g;
-    const int cu = st ? c0 + cl : c0;
-    const double t0 = A[cu * PANEL_LD + ra], t1 = A[(cu + 1) * PANEL_LD + ra];
-    double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0;
-    const double* Bp = A + c0 + g + (K0 + q) * PANEL_LD;
-    const double* Ap = A + ra + (K0 + q) * PANEL_LD;
-    const int nfull = K >> 3, rem = K & 7;
-#pragma unroll 4
-    for (int it = 0; it < nfull; it++) {
-        const double b0 = Bp[0], b1 = Bp[4 * PANEL_LD];
-        const double a0 = Ap[0], a1 = Ap[4 * PANEL_LD];
-        dmma884(c00, c01, a0, b0);
-        dmma884(c10, c11, a1, b1);
-        Bp += 8 * PANEL_LD; Ap += 8 * PANEL_LD;
-    }
-    if (rem) {
-        const bool va = q < rem, vb = q + 4 < rem;
-        const int o1 = vb ? 4 * PANEL_LD : 0;
-        double b0 = Bp[0], b1 = Bp[o1], a0 = Ap[0], a1 = Ap[o1];
-        if (!va) { b0 = 0.0; a0 = 0.0; }
-        if (!vb) { b1 = 0.0; a1 = 0.0; }
-        dmma884(c00, c01, a0, b0);
-        dmma884(c10, c11, a1, b1);
-    }
-    if (st && g < nrows && ra < R) {
-        A[(c0 + cl) * PANEL_LD + ra] = t0 - (c00 + c10);
-        A[(c0 + cl + 1) * PANEL_LD + ra] = t1 - (c01 + c11);
-    }
-    __syncwarp();
-}
-// Two left-looking accumulates in one instruction stream (the pair of block rows a row warp owns): job x in {a, b} does
-//   A[r0x + g, 6 cbx + n] -= sum_{K0 <= k < K1} A[r0x + g, k] A[brx + n, k]
-// with its own target column block cbx and operand rows brx; job b only if `two`.  Four independent accumulator chains,
-// all operand loads of a round ahead of its DMMAs.
-struct LagJob { int cb, br, r0; };
-__device__ __forceinline__ void panel_lag_acc2(double* A, int K0, int K1, LagJob ja, LagJob jb, bool two, int nrows, int R, int lane) {
-    const int K = K1 - K0;
-    if (K <= 0) return;
-    if (!two) jb = ja;
-    const int g = lane >> 2, q = lane & 3, cl = 2 * q;
-    const bool st = cl < 6;
-    const int ra = ja.r0 + g, rb = jb.r0 + g;
-    const int cua = 6 * ja.cb + (st ? cl : 0), cub = 6 * jb.cb + (st ? cl : 0);
-    const double ta0 = A[cua * PANEL_LD + ra], ta1 = A[(cua + 1) * PANEL_LD + ra];
-    const double tb0 = A[cub * PANEL_LD + rb], tb1 = A[(cub + 1) * PANEL_LD + rb];
-    double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0, e00 = 0.0, e01 = 0.0, e10 = 0.0, e11 = 0.0;
-    const double* Bpa = A + ja.br + g + (K0 + q) * PANEL_LD;
-    const double* Bpb = A + jb.br + g + (K0 + q) * PANEL_LD;
-    const double* Apa = A + ra + (K0 + q) * PANEL_LD;
-    const double* Apb = A + rb + (K0 + q) * PANEL_LD;
-    const int nfull = K >> 3, rem = K & 7;
-    if (two) {
-#pragma unroll 2
-        for (int it = 0; it < nfull; it++) {
-            const double b0 = Bpa[0], b1 = Bpa[4 * PANEL_LD], d0 = Bpb[0], d1 = Bpb[4 * PANEL_LD];
-            const double a0 = Apa[0], a1 = Apa[4 * PANEL_LD], q0 = Apb[0], q1 = Apb[4 * PANEL_LD];
-            dmma884(c00, c01, a0, b0);
-            dmma884(e00, e01, q0, d0);
-            dmma884(c10, c11, a1, b1);
-            dmma884(e10, e11, q1, d1);
-            Bpa += 8 * PANEL_LD; Bpb += 8 * PANEL_LD; Apa += 8 * PANEL_LD; Apb += 8 * PANEL_LD;
-        }
-        if (rem) {
-            const bool va = q < rem, vb = q + 4 < rem;
-            const int o1 = vb ? 4 * PANEL_LD : 0;
-            double b0 = Bpa[0], b1 = Bpa[o1], d0 = Bpb[0], d1 = Bpb[o1];
-            double a0 = Apa[0], a1 = Apa[o1], q0 = Apb[0], q1 = Apb[o1];
-            if (!va) { b0 = 0.0; a0 = 0.0; d0 = 0.0; q0 = 0.0; }
-            if (!vb) { b1 = 0.0; a1 = 0.0; d1 = 0.0; q1 = 0.0; }
-            dmma884(c00, c01, a0, b0);
-            dmma884(e00, e01, q0, d0);
-            dmma884(c10, c11, a1, b1);
-            dmma884(e10, e11, q1, d1);
-        }
-    } else {
-#pragma unroll 4
-        for (int it = 0; it < nfull; it++) {
-            const double b0 = Bpa[0], b1 = Bpa[4 * PANEL_LD];
-            const double a0 = Apa[0], a1 = Apa[4 * PANEL_LD];
-            dmma884(c00, c01, a0, b0);
-            dmma884(c10, c11, a1, b1);
-            Bpa += 8 * PANEL_LD; Apa += 8 * PANEL_LD;
-        }
-        if (rem) {
-            const bool va = q < rem, vb = q + 4 < rem;
-            const int o1 = vb ? 4 * PANEL_LD : 0;
-            double b0 = Bpa[0], b1 = Bpa[o1], a0 = Apa[0], a1 = Apa[o1];
-            if (!va) { b0 = 0.0; a0 = 0.0; }
-            if (!vb) { b1 = 0.0; a1 = 0.0; }
-            dmma884(c00, c01, a0, b0);
-            dmma884(c10, c11, a1, b1);
-        }
-    }
-    if (st && g < nrows) {
-        if (ra < R) {
-            A[cua * PANEL_LD + ra] = ta0 - (c00 + c10);
-            A[(cua + 1) * PANEL_LD + ra] = ta1 - (c01 + c11);
-        }
-        if (two && rb < R) {
-            A[cub * PANEL_LD + rb] = tb0 - (e00 + e10);
-            A[(cub + 1) * PANEL_LD + rb] = tb1 - (e01 + e11);
-        }
-    }
-    __syncwarp();
-}
 // spin until a published counter reaches `need` (every lane acquires)
 __device__ __forceinline__ void wait_counter(const int* p, int need, bool nap) {
     int v;
@@ -796,49 +585,6 @@ __device__ __forceinline__ void panel_slab_run(double* A, const double (*Wall)[3
     }
 }
 
-// S-phase work for one panel row r below the diagonal block jb: x L_D^T = a
-__device__ __forceinline__ void panel_row_solve(double* A, const double* invAll, int jb, int r) {
-    const int j0 = 6 * jb;
-    double x[6], Lc[5][6], iv[6];
-#pragma unroll
-    for (int k = 0; k < 6; k++) x[k] = A[(j0 + k) * PANEL_LD + r];
-#pragma unroll
-    for (int p = 0; p < 5; p++) {
-        const double2* lp = reinterpret_cast<const double2*>(A + (j0 + p) * PANEL_LD + j0);
-#pragma unroll
-        for (int h = 0; h < 3; h++) { const double2 v = lp[h]; Lc[p][2 * h] = v.x; Lc[p][2 * h + 1] = v.y; }
-    }
-    {
-        const double2* ip = reinterpret_cast<const double2*>(invAll + 6 * jb);
-#pragma unroll
-        for (int h = 0; h < 3; h++) { const double2 v = ip[h]; iv[2 * h] = v.x; iv[2 * h + 1] = v.y; }
-    }
-#pragma unroll
-    for (int k = 0; k < 6; k++) {
-        double sv = x[k];
-#pragma unroll
-        for (int p = 0; p < k; p++) sv -= x[p] * Lc[p][k];
-        x[k] = sv * iv[k];
-    }
-#pragma unroll
-    for (int k = 0; k < 6; k++) A[(j0 + k) * PANEL_LD + r] = x[k];
-}
-// D_(jb+1) -= L_(jb+1,jb) L_(jb+1,jb)^T, one entry per lane (lanes < 21)
-__device__ __forceinline__ void panel_diag_update(double* A, int jb, int lane) {
-    const int j0 = 6 * jb, j1 = j0 + 6;
-    if (lane < 21) {
-        int i = 0;
-#pragma unroll
-        for (int q = 1; q < 6; q++) i += (lane >= tri(q, 0)) ? 1 : 0;
-        const int k = lane - tri(i, 0);
-        double sv = 0.0;
-#pragma unroll
-        for (int p = 0; p < 6; p++) sv += A[(j0 + p) * PANEL_LD + j1 + i] * A[(j0 + p) * PANEL_LD + j1 + k];
-        A[(j1 + k) * PANEL_LD + j1 + i] -= sv;
-    }
-}
-__device__ __forceinline__ void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
-__device__ __forceinline__ void named_bar_arrive(int id, int nthreads) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
 
 // `early` (set by the host for lev > 0 under programmatic dependent launch): the predecessor kernel -- the
 // update or panel kernel of the level below -- signals its dependents only after its own pdl_wait(), so when this
