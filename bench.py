@@ -145,7 +145,7 @@ def run_ours(args, rank, world):
         g = synth.make_graph(args.workload)
         prob = pack.pack(g)
         s = solver.BlockSolver(dev, f32=args.f32)
-        s.initialize(prob)
+        s.initialize(prob, robust=args.robust, delta=args.delta)
         shard_prob = prob
     else:
         # weak scaling (default): the same poses, `world` times the landmarks and edges of the named shape;
@@ -384,7 +384,7 @@ def run_ours(args, rank, world):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle as orc
     if args.cpu_iters > 0:
-        o = orc.Oracle(prob, threads=1)
+        o = orc.Oracle(prob, robust=args.robust, delta=args.delta, threads=1)
         o.build_structure()
         t0 = time.perf_counter()
         cc, _, _ = o.optimize(args.cpu_iters)
@@ -400,7 +400,7 @@ def run_ours(args, rank, world):
     # ---- cold call: a NEW solver on the same host buffers: initialize + build_structure + optimize + read-back
     t0 = time.perf_counter()
     sc = solver.BlockSolver(dev, f32=args.f32)
-    sc.initialize(prob)
+    sc.initialize(prob, robust=args.robust, delta=args.delta)
     t1 = time.perf_counter()
     sc.build_structure()
     t2 = time.perf_counter()
@@ -443,7 +443,8 @@ def run_ours(args, rank, world):
         "dtype": "f64", "data": "synthetic (seeded generator cugo_b200/synth.py; reference inputs are absent)",
         "config": {"workload": "%s: %d poses / %d landmarks / %d edges (%d stereo), %d LM iterations, %s" % (
             args.workload, g.n_poses, g.n_landmarks, E, len(g.stereo_p), args.iters,
-            "FP64 arithmetic, FP32 Hpl storage (USE_FLOAT32 mode)" if args.f32 else "FP64"),
+            ("FP64 arithmetic, FP32 Hpl storage (USE_FLOAT32 mode)" if args.f32 else "FP64")
+            + ("" if args.robust == "none" else ", %s kernel (delta %g)" % (args.robust, args.delta))),
             "timing": "CUDA events on the solver stream around optimize(); L2 flushed (256 MB fill) between steps",
             "sizes": sizes},
         "e2e": {"value": e2e_value, "unit": "edges/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
@@ -515,7 +516,7 @@ def run_reference(args, rank, world):
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import oracle as orc
         prob = pack.pack(g)
-        o = orc.Oracle(prob, threads=1)
+        o = orc.Oracle(prob, robust=args.robust, delta=args.delta, threads=1)
         o.build_structure()
         t0 = time.perf_counter()
         cc, _, _ = o.optimize(args.cpu_iters)
@@ -552,6 +553,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=WORKLOAD)
     ap.add_argument("--f32", action="store_true", help="USE_FLOAT32 mode: single-precision Hpl storage (1 GPU)")
+    ap.add_argument("--robust", default="none", choices=["none", "huber", "cauchy", "tukey"], help="robust kernel of every edge set (1 GPU)")
+    ap.add_argument("--delta", type=float, default=1.0, help="robust kernel width")
     ap.add_argument("--dist-factor", type=int, default=1,
                     help="N > 1: factorisation distributed by assembly-tree subtree: 0 never, 1 when the factor flops make it pay "
                          "(default), 2 always")
