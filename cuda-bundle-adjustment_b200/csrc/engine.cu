@@ -21,6 +21,7 @@
 #include "kernels_chol3.cuh"
 #include "kernels_edge.cuh"
 #include "kernels_lm.cuh"
+#include "kernels_peer.cuh"
 #include "kernels_schur.cuh"
 #include "kernels_struct.cuh"
 #include "kernels_sym.cuh"
@@ -218,6 +219,19 @@ struct Solver {
     DBuf<unsigned long long> lkeys, gkeysAll, gkeysSorted, gkeys;
     DBuf<int> gHead, gIdx, gRowOf, gColInd, gRowPtr, hscSlot, d_cnt;
     DBuf<double> redA, redC, HscPartBuf;
+    // exchange over NVLink peer memory instead of NCCL (kernels_peer.cuh): one cudaMalloc'ed block per rank, opened by the
+    // others through CUDA IPC.  Option "peer_reduce" = 0 keeps ncclAllReduce (also the fallback when IPC is not available).
+    int peerMode = 1;
+    bool peerOn = false;
+    PeerCtx peer{};
+    char* peerLocal = nullptr;
+    size_t peerNred = 0;
+    void peerSetup(size_t nred);
+    void peerRelease();
+    void smallReduce(double* buf, int n) {
+        if (peerOn && n <= PEER_SMALL_MAX) k_peer_small<<<1, PEER_TPB, 0, stream>>>(peer, buf, n, d.st, 0);
+        else allReduceSum(buf, (size_t)n);
+    }
     // factorisation distributed by assembly-tree subtree (several ranks): supernodes on tree levels
     // >= distLc are factorised by every rank, the subtrees below are dealt to the ranks
     int distMode = 1;              // option "dist_factor": 0 never, 1 when the factor flops make it pay, 2 always
@@ -303,6 +317,7 @@ struct Solver {
         if (h_scalars) cudaFreeHost(h_scalars);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
+        peerRelease();
         if (comm && g_nccl.CommDestroy) g_nccl.CommDestroy(comm);
         if (evFork) cudaEventDestroy(evFork);
         if (evJoin) cudaEventDestroy(evJoin);
@@ -780,6 +795,11 @@ void Solver::buildStructure() {
         HscPartBuf.alloc(nred);
         CK(cudaMemsetAsync(HscPartBuf.p, 0, nred * sizeof(double), stream));
         d.HscPart = HscPartBuf.p; d.bscPart = HscPartBuf.p + (size_t)nblkG * 36;
+        peerSetup(nred);
+        if (peerOn) {           // partial and summed system live in the exchange block
+            d.HscPart = reinterpret_cast<double*>(peerLocal + peer.offPart); d.bscPart = d.HscPart + (size_t)nblkG * 36;
+            d.Hsc = reinterpret_cast<double*>(peerLocal + peer.offDst); d.bsc = d.Hsc + (size_t)nblkG * 36;
+        }
     }
     d.nranks = nranks; d.rank = rank; d.nblkG = nblkG; d.hscSlot = nranks > 1 ? hscSlot.p : nullptr;
     d.redA = nranks > 1 ? redA.p : nullptr; d.redC = nranks > 1 ? redC.p : nullptr;
@@ -949,6 +969,77 @@ void Solver::planDistFactor() {
     }
 }
 
+// Exchange block of this rank + the peers' blocks through CUDA IPC (collective: every rank calls it from build_structure).
+void Solver::peerSetup(size_t nred) {
+    peerRelease();
+    if (nranks < 2 || nranks > PEER_MAXR || !peerMode) return;
+    PeerCtx x{};
+    x.nranks = nranks; x.rank = rank;
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    x.offPart = 0;
+    x.offDst = up(nred * sizeof(double));
+    x.offSmall = x.offDst + up(nred * sizeof(double));
+    x.offFlag = x.offSmall + up((size_t)PEER_MAXR * PEER_SMALL_MAX * sizeof(double));
+    x.offEpoch = x.offFlag + up((size_t)3 * PEER_MAXR * PEER_CTAS * sizeof(int));
+    const size_t bytes = x.offEpoch + up((size_t)2 * PEER_CTAS * sizeof(int));
+    int ok = 1;
+    cudaIpcMemHandle_t mine{};
+    if (cudaMalloc(&peerLocal, bytes) != cudaSuccess) { peerLocal = nullptr; ok = 0; cudaGetLastError(); }
+    if (ok) {
+        CK(cudaMemsetAsync(peerLocal, 0, bytes, stream));
+        if (cudaIpcGetMemHandle(&mine, peerLocal) != cudaSuccess) { ok = 0; cudaGetLastError(); }
+    }
+    // handles of everybody (64 bytes each) + the flag that every rank got this far
+    DBuf<unsigned char> hbuf;
+    const size_t hsz = sizeof(cudaIpcMemHandle_t) + 8;
+    hbuf.alloc(hsz * (nranks + 1));
+    std::vector<unsigned char> host(hsz * (nranks + 1), 0);
+    memcpy(host.data() + hsz * nranks, &mine, sizeof(mine));
+    host[hsz * nranks + sizeof(mine)] = (unsigned char)ok;
+    CK(cudaMemcpyAsync(hbuf.p + hsz * nranks, host.data() + hsz * nranks, hsz, cudaMemcpyHostToDevice, stream));
+    NK(g_nccl.AllGather(hbuf.p + hsz * nranks, hbuf.p, hsz, ncclUint8, comm, stream));
+    CK(cudaMemcpyAsync(host.data(), hbuf.p, hsz * nranks, cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    for (int r = 0; r < nranks; r++) ok &= host[hsz * r + sizeof(mine)];
+    if (ok) {
+        for (int r = 0; r < nranks && ok; r++) {
+            if (r == rank) { x.base[r] = peerLocal; continue; }
+            cudaIpcMemHandle_t h;
+            memcpy(&h, host.data() + hsz * r, sizeof(h));
+            void* pp = nullptr;
+            if (cudaIpcOpenMemHandle(&pp, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = 0; cudaGetLastError(); break; }
+            x.base[r] = static_cast<char*>(pp);
+        }
+    }
+    // every rank must take the same path: agree once more
+    redC.alloc(4);
+    const double mineOk = ok ? 0.0 : 1.0;
+    CK(cudaMemcpyAsync(redC.p, &mineOk, sizeof(double), cudaMemcpyHostToDevice, stream));
+    allReduceSum(redC.p, 1);
+    double bad = 0.0;
+    CK(cudaMemcpyAsync(&bad, redC.p, sizeof(double), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    peer = x;
+    if (bad != 0.0) {
+        if (getenv("CUGO_B200_DEBUG")) fprintf(stderr, "[cugo_b200] peer memory not available on every rank: the exchange stays on NCCL\n");
+        peerRelease();
+        return;
+    }
+    peerOn = true;
+    peerNred = nred;
+    if (getenv("CUGO_B200_DEBUG") && rank == 0)
+        fprintf(stderr, "[cugo_b200] exchange over peer memory: %d ranks, %.1f MB per rank\n", nranks, bytes / 1048576.0);
+}
+void Solver::peerRelease() {
+    if (peerLocal || peerOn) {
+        cudaStreamSynchronize(stream);
+        for (int r = 0; r < peer.nranks; r++)
+            if (r != peer.rank && peer.base[r]) cudaIpcCloseMemHandle(peer.base[r]);
+        if (peerLocal) cudaFree(peerLocal);
+    }
+    peerLocal = nullptr; peerOn = false; peer = PeerCtx{};
+}
+
 // Slab height of the panel kernel per tree level.  A panel CTA factors the diagonal part of its supernode and one slab
 // of the rows below; the rows below are independent of each other, so on levels with few supernodes (the top of the
 // tree, where most SMs idle) short slabs spread them over more SMs, while the leaf levels keep tall slabs so that
@@ -1116,7 +1207,7 @@ void Solver::enqueueBuild() {
     }
     if (nranks > 1 && withA) {   // max diagonal of the *global* system for lambda0
         launch(k_pack_A<256>, std::min(divUp(6 * d.nP, 256), 148), 256, 0, d); mark("pack_A");
-        allReduceSum(d.redA, (size_t)6 * d.nP + nranks);
+        smallReduce(d.redA, 6 * d.nP + nranks);
     }
 }
 
@@ -1134,8 +1225,12 @@ void Solver::enqueueSolve() {
     }
     mark("schur_rows");
     // the one exchange step of a trial: partial reduced camera systems [Hsc | bsc] summed over the ranks
-    if (nranks > 1)
-        NK(g_nccl.AllReduce(d.HscPart, d.Hsc, (size_t)d.nblkG * 36 + (size_t)d.nP * 6, ncclFloat64, ncclSum, comm, stream));
+    if (nranks > 1) {
+        const size_t nred = (size_t)d.nblkG * 36 + (size_t)d.nP * 6;
+        if (peerOn) k_peer_allreduce<<<PEER_CTAS, PEER_TPB, 0, stream>>>(peer, nred, d.st);
+        else NK(g_nccl.AllReduce(d.HscPart, d.Hsc, nred, ncclFloat64, ncclSum, comm, stream));
+        mark("exchange");
+    }
     // levels [0, zTop] solve backward with the inverse of L11 (k_chol_zinv has the whole rest of the factorisation
     // to finish); the top three keep the blocked substitution
     const bool zOn = zinvOn && pdl && !profiling;
@@ -1210,7 +1305,7 @@ void Solver::enqueueSlot() {
     launch(k_errors<256>, d.errGrid, 256, 0, d, sp, 1, 1); mark("errors");
     if (nranks > 1) {
         launch(k_lm_sums<256>, 1, 256, 0, d); mark("lm_sums");
-        allReduceSum(d.redC, 3);
+        smallReduce(d.redC, 3);
     }
     launch(k_lm_decide<1024>, 1, 1024, 0, d); mark("lm_decide");
 }
@@ -1222,7 +1317,7 @@ int Solver::profileSlot(int cap, char* names, int nameLen, double* ms) {
     ensureStructure();
     use();
     k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
-    if (nranks > 1) { k_lm_sums<256><<<1, 256, 0, stream>>>(d); allReduceSum(d.redC, 3); }
+    if (nranks > 1) { k_lm_sums<256><<<1, 256, 0, stream>>>(d); smallReduce(d.redC, 3); }
     k_lm_begin<256><<<1, 256, 0, stream>>>(d, 1);
     const int saved = kernelsPerSlot;
     profiling = true;
@@ -1459,7 +1554,7 @@ int Solver::optimize(int niter, int cap, double* chi2, double* lambda, int* tria
     CK(cudaEventRecord(ev0, stream));
     long launched = 0;
     k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
-    if (nranks > 1) { k_lm_sums<256><<<1, 256, 0, stream>>>(d); allReduceSum(d.redC, 3); launched++; }
+    if (nranks > 1) { k_lm_sums<256><<<1, 256, 0, stream>>>(d); smallReduce(d.redC, 3); launched++; }
     k_lm_begin<256><<<1, 256, 0, stream>>>(d, niter);
     launched += 2;
     int slots = 0;
@@ -1818,7 +1913,7 @@ long Solver::getValues(int which, double* out, long cap) {
     case CUGO_B200_B: src = b; n = 6L * nP + 3L * nL; break;
     case CUGO_B200_X: src = x; n = 6L * nP + 3L * nL; break;
     case CUGO_B200_BSC: src = d.bsc; n = 6L * nP; break;
-    case CUGO_B200_HSC: src = Hsc; n = 36L * d.nblkG; break;
+    case CUGO_B200_HSC: src = d.Hsc; n = 36L * d.nblkG; break;
     case CUGO_B200_INVHLL: src = invHll; n = 9L * nL; break;
     case CUGO_B200_CHI_PER_EDGE: {
         n = E;
@@ -2106,6 +2201,7 @@ int cugo_b200_set_option(cugo_b200_solver* s, const char* name, int value) {
         if (!name) throw cugo_b200::ArgError("set_option: null name");
         const std::string n(name);
         if (n == "dist_factor") { S.distMode = value; S.structDirty = true; return; }
+        if (n == "peer_reduce") { S.peerMode = value; S.structDirty = true; return; }
         if (n == "upd_small") { S.updSmall = value; S.structDirty = true; return; }
         if (n == "panel_rb") {
             if (value < 0 || value > cugo_b200::CHOL_RB) throw cugo_b200::ArgError("set_option: panel_rb must be in [0, 16] (0: chosen per tree level)");
@@ -2113,7 +2209,7 @@ int cugo_b200_set_option(cugo_b200_solver* s, const char* name, int value) {
         }
         bool* f = n == "pdl" ? &S.pdl : n == "fuse_build" ? &S.fuseBuild : n == "panel_dc" ? &S.panelDC : n == "zinv" ? &S.zinvOn
                 : n == "schur_mma" ? &S.schurMma : n == "bwd_split" ? &S.bwdSplit : n == "parallel_symbolic" ? &S.symParallel : nullptr;
-        if (!f) throw cugo_b200::ArgError("set_option: unknown option '" + n + "' (pdl, fuse_build, panel_dc, zinv, bwd_split, parallel_symbolic, dist_factor, panel_rb, upd_small, schur_mma)");
+        if (!f) throw cugo_b200::ArgError("set_option: unknown option '" + n + "' (pdl, fuse_build, panel_dc, zinv, bwd_split, parallel_symbolic, dist_factor, panel_rb, upd_small, schur_mma, peer_reduce)");
         *f = value != 0;
         S.structDirty = true;           // the options shape the structure and the trial graph
     });

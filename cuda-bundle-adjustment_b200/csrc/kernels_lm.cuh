@@ -59,22 +59,8 @@ __global__ void __launch_bounds__(TPB) k_lm_prepare(Dev d) {
     if (threadIdx.x == 0) { st->fail = 0; st->slots++; }
 }
 
-// end of a trial: gain ratio, accept / reject, damping update, termination.
-template <int TPB>
-__global__ void __launch_bounds__(TPB) k_lm_decide(Dev d) {
-    __shared__ double sh[TPB / 32];
-    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
-    LMState* st = d.st;
-    if (st->done) return;
-    double Fhat = sum_array<TPB>(d.chiPartial, d.errGrid, sh);
-    const double lam = st->lambda;
-    double s = 0.0;
-    for (int i = threadIdx.x; i < 6 * d.nP; i += TPB) s += d.x[i] * (lam * d.x[i] + d.b[i]);
-    for (int i = threadIdx.x; i < d.nChunks; i += TPB) s += d.scalePartial[i];
-    double scaleRaw = block_sum<TPB>(s, sh);
-    if (threadIdx.x != 0) return;
-    bool fail = st->fail != 0;
-    if (d.nranks > 1) { Fhat = d.redC[0]; scaleRaw = d.redC[1]; fail = d.redC[2] > 0.0; }   // k_lm_sums + all-reduce ran before
+// the decision itself (one thread): gain ratio, accept / reject, damping update, termination
+__device__ __forceinline__ void lm_decide_tail(const Dev& d, LMState* st, double Fhat, double scaleRaw, bool fail, double lam) {
     const int maxq = 10;
     const double F = st->F;
     const double scale = scaleRaw + 1e-3;
@@ -116,6 +102,25 @@ __global__ void __launch_bounds__(TPB) k_lm_decide(Dev d) {
             if (st->iter >= st->niter) st->done = 1;
         }
     }
+}
+
+// end of a trial: gain ratio, accept / reject, damping update, termination.
+template <int TPB>
+__global__ void __launch_bounds__(TPB) k_lm_decide(Dev d) {
+    __shared__ double sh[TPB / 32];
+    pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
+    LMState* st = d.st;
+    if (st->done) return;
+    double Fhat = sum_array<TPB>(d.chiPartial, d.errGrid, sh);
+    const double lam = st->lambda;
+    double s = 0.0;
+    for (int i = threadIdx.x; i < 6 * d.nP; i += TPB) s += d.x[i] * (lam * d.x[i] + d.b[i]);
+    for (int i = threadIdx.x; i < d.nChunks; i += TPB) s += d.scalePartial[i];
+    double scaleRaw = block_sum<TPB>(s, sh);
+    if (threadIdx.x != 0) return;
+    bool fail = st->fail != 0;
+    if (d.nranks > 1) { Fhat = d.redC[0]; scaleRaw = d.redC[1]; fail = d.redC[2] > 0.0; }   // k_lm_sums + all-reduce ran before
+    lm_decide_tail(d, st, Fhat, scaleRaw, fail, lam);
 }
 
 // ---- multi-GPU: local partial sums that are all-reduced before the LM kernels read them ------------
