@@ -1303,6 +1303,10 @@ void Solver::enqueueSlot() {
     enqueueSolve();
     launch(k_update_poses<128>, divUp(d.nP, 128), 128, 0, d); mark("update_poses");
     launch(k_errors<256>, d.errGrid, 256, 0, d, sp, 1, 1); mark("errors");
+    if (nranks > 1 && peerOn) {
+        launch(k_lm_decide_peer<1024>, 1, 1024, 0, d, peer); mark("lm_decide");       // sums, exchange and decision in one kernel
+        return;
+    }
     if (nranks > 1) {
         launch(k_lm_sums<256>, 1, 256, 0, d); mark("lm_sums");
         smallReduce(d.redC, 3);

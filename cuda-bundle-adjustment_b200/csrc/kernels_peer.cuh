@@ -7,6 +7,7 @@
 // Memory: every rank cudaMalloc's one exchange block and opens the others' through CUDA IPC (Solver::peerSetup).
 #pragma once
 #include "engine.h"
+#include "kernels_lm.cuh"
 
 namespace cugo_b200 {
 
@@ -117,6 +118,45 @@ __global__ void __launch_bounds__(PEER_TPB) k_peer_small(PeerCtx x, double* buf,
     // writes, so close this one with a second barrier
     peer_barrier(x, 2, 1, ep);
     if (threadIdx.x == 0) *epoch = ep;
+}
+
+// End of a sharded trial in ONE kernel: the rank's chi2 / gain denominator / pivot flag (k_lm_sums), their sum over the ranks
+// through peer memory (one-shot, rank order: every rank decides on identical numbers) and the decision (lm_decide_tail) --
+// instead of k_lm_sums, a reduction kernel and k_lm_decide.  One CTA.  Slots: the tail of the one-shot region.
+template <int TPB>
+__global__ void __launch_bounds__(TPB) k_lm_decide_peer(Dev d, PeerCtx x) {
+    __shared__ double sh[TPB / 32];
+    __shared__ double mine[3], tot[3];
+    pdl_trigger(); pdl_wait();
+    LMState* st = d.st;
+    if (st->done) return;                   // identical on every rank
+    const double chi = sum_array<TPB>(d.chiPartial, d.errGrid, sh);          // (block sums: valid on thread 0 only)
+    const double lamTrue = st->lambda, lam = d.rank == 0 ? lamTrue : 0.0;
+    double s = 0.0;
+    for (int i = threadIdx.x; i < 6 * d.nP; i += TPB) s += d.x[i] * (lam * d.x[i] + d.b[i]);
+    for (int i = threadIdx.x; i < d.nChunks; i += TPB) s += d.scalePartial[i];
+    s = block_sum<TPB>(s, sh);
+    if (threadIdx.x == 0) { mine[0] = chi; mine[1] = s; mine[2] = st->fail ? 1.0 : 0.0; }
+    __syncthreads();
+    const int N = x.nranks;
+    int* epoch = reinterpret_cast<int*>(x.base[x.rank] + x.offEpoch) + PEER_CTAS + 1;
+    const int ep = *epoch + 1;
+    constexpr int SLOT = PEER_SMALL_MAX - 4;
+    if (threadIdx.x < N) {
+        double* slot = reinterpret_cast<double*>(x.base[threadIdx.x] + x.offSmall) + (size_t)x.rank * PEER_SMALL_MAX + SLOT;
+        slot[0] = mine[0]; slot[1] = mine[1]; slot[2] = mine[2];
+    }
+    peer_barrier(x, 2, 2, ep);
+    if (threadIdx.x < 3) {
+        const double* slots = reinterpret_cast<const double*>(x.base[x.rank] + x.offSmall) + SLOT + threadIdx.x;
+        double v = 0.0;
+        for (int p = 0; p < N; p++) v += __ldcg(slots + (size_t)p * PEER_SMALL_MAX);
+        tot[threadIdx.x] = v;
+    }
+    peer_barrier(x, 2, 3, ep);              // everybody has read the slots before anybody writes the next trial's
+    if (threadIdx.x != 0) return;
+    *epoch = ep;
+    lm_decide_tail(d, st, tot[0], tot[1], tot[2] > 0.0, lamTrue);
 }
 
 }  // namespace cugo_b200
