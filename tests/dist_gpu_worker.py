@@ -18,6 +18,7 @@ def main():
     robust = sys.argv[4] if len(sys.argv) > 4 else "none"
     delta = float(sys.argv[5]) if len(sys.argv) > 5 else 1.0
     dist_factor = int(sys.argv[6]) if len(sys.argv) > 6 else 1     # 2: force the subtree-distributed factorisation
+    peer_reduce = int(sys.argv[7]) if len(sys.argv) > 7 else 1     # 0: exchange step through ncclAllReduce instead of peer memory
     dev = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl")
@@ -25,6 +26,7 @@ def main():
         prob = pack.pack(synth.make_graph(name))
         s = cdist.DistBlockSolver(prob, dev, robust=robust, delta=delta)
         s.s.set_option("dist_factor", dist_factor)
+        s.s.set_option("peer_reduce", peer_reduce)
         chi, lam, tr = s.optimize(niter)
         chi2, _, _ = (None, None, None)
         poses, lms = s.estimates()

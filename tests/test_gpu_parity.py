@@ -305,15 +305,16 @@ def test_cpp_facade_matches_binding(graphs, tmp_path, name, rk, delta):
     np.testing.assert_array_equal(raw[7 * g.n_poses:].reshape(-1, 3), X)
 
 
-@pytest.mark.parametrize("name,robust,delta,dist_factor", [("small", "none", 1.0, 1), ("kitti07", "none", 1.0, 1),
-                                                          ("small", "huber", 2.4477, 1), ("loop", "none", 1.0, 2),
-                                                          ("kitti07", "none", 1.0, 2), ("kitti00", "none", 1.0, 2)])
-def test_two_gpus_match_one(graphs, gpu, tmp_path, name, robust, delta, dist_factor):
-    """Landmarks sharded over 2 GPUs (one process each, NCCL all-reduce of [Hsc | bsc] inside the trial
-    graph): chi2 per iteration within 1e-9 relative of the 1-GPU run, trial counts equal, estimates equal
-    to 1e-9, and the 2-GPU run is bit-reproducible.  dist_factor = 2 also forces the factorisation distributed by
-    assembly-tree subtree (owners factor their subtrees, the top is replicated, update matrices of the subtree roots
-    broadcast, pieces of x summed)."""
+@pytest.mark.parametrize("name,robust,delta,dist_factor,peer_reduce",
+                         [("small", "none", 1.0, 1, 1), ("kitti07", "none", 1.0, 1, 1), ("small", "huber", 2.4477, 1, 1),
+                          ("loop", "none", 1.0, 2, 1), ("kitti07", "none", 1.0, 2, 1), ("kitti00", "none", 1.0, 2, 1),
+                          ("kitti07", "none", 1.0, 1, 0)])
+def test_two_gpus_match_one(graphs, gpu, tmp_path, name, robust, delta, dist_factor, peer_reduce):
+    """Landmarks sharded over 2 GPUs (one process each; the partial systems [Hsc | bsc] summed inside the trial graph by the
+    peer-memory kernels of kernels_peer.cuh, or by ncclAllReduce with peer_reduce = 0): chi2 per iteration within 1e-9
+    relative of the 1-GPU run, trial counts equal, estimates equal to 1e-9, and the 2-GPU run is bit-reproducible.
+    dist_factor = 2 also forces the factorisation distributed by assembly-tree subtree (owners factor their subtrees, the
+    top is replicated, update matrices of the subtree roots broadcast, pieces of x summed)."""
     import os
     import subprocess
     import sys
@@ -323,8 +324,9 @@ def test_two_gpus_match_one(graphs, gpu, tmp_path, name, robust, delta, dist_fac
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     out = str(tmp_path / "two.npz")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
-           "--master-port", "29731", os.path.join(root, "tests", "dist_gpu_worker.py"), name, "8", out, robust, repr(delta), str(dist_factor)]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+           "--master-port", "29731", os.path.join(root, "tests", "dist_gpu_worker.py"), name, "8", out, robust, repr(delta), str(dist_factor),
+           str(peer_reduce)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr[-3000:]
     two = np.load(out)
     g, prob = graphs(name)
