@@ -211,7 +211,7 @@ struct Solver {
     bool symParallel = true;       // option "parallel_symbolic" = 0: the single-thread run of symbolic.h (the twin) on the device
     void symbolicParallel(const int* gRowOfP, const int* gRowPtrP, const int* gColIndP, int P);
     DBuf<double> cL, cU, cX, cW, cZ, cPart;
-    DBuf<int> cCnt;
+    DBuf<int> cCnt, cFlag;
     DBuf<int> z_levMaxNt;
     // multi-GPU
     int nranks = 1, rank = 0;
@@ -763,6 +763,8 @@ void Solver::buildStructure() {
     cZ.alloc((size_t)P * 6 * 6 * CHOL_MAXW);
     cPart.alloc((size_t)nsn * BWD_MAXG * 6 * CHOL_MAXW); cCnt.alloc(nsn);
     CK(cudaMemsetAsync(cCnt.p, 0, sizeof(int) * nsn, stream));
+    cFlag.alloc(nsn + 1);
+    CK(cudaMemsetAsync(cFlag.p, 0, sizeof(int) * (nsn + 1), stream));
 
     // ---- system buffers
     Hpp.alloc((size_t)nP * 36); Hll.alloc((size_t)nL * 9);
@@ -813,6 +815,7 @@ void Solver::buildStructure() {
     c.childIdx = z_childIdx; c.invPtr = z_invPtr; c.inv = z_inv; c.snBlkPtr = z_snBlkPtr; c.asmBlk = z_asmBlk;
     c.asmRow = z_asmRow; c.asmCol = z_asmCol;
     c.L = cL; c.U = cU; c.xperm = cX; c.Winv = cW; c.Zinv = cZ; c.bwdPart = cPart; c.bwdCnt = cCnt;
+    c.xFlag = cFlag; c.colToSn = y_colToSn;
     { const char* e = getenv("CUGO_B200_DEBUG"); c.dbg = e ? atoi(e) : 0; }   // diagnostic builds (make DIAG=1): 1 phase stamps, 3 also a worker warp's view
 
     // dynamic shared memory opt-in for the factorisation kernels

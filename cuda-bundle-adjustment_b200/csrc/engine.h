@@ -151,6 +151,8 @@ struct Chol {
     double* xperm;         // [6P] solution in permuted order
     double* bwdPart;       // [nsn x 8 x 6 MAXW] partial L21^T x_R vectors of the CTAs sharing a supernode (k_chol_bwd3)
     int* bwdCnt;           // [nsn] arrival counters of those CTAs (zero between trials)
+    int* xFlag;            // [nsn + 1] backward solve: epoch at which x of supernode t was stored; [nsn] = the current epoch
+    const int* colToSn;    // [P] supernode of every (permuted) block column
     const int* rbLev;      // [nlev] block rows of L21 per panel CTA on every tree level (<= CHOL_RB; Solver::planPanelSlabs)
     int dbg;               // 1: kernels record phase timestamps (diagnostics)
 };

@@ -1063,6 +1063,7 @@ __global__ void __launch_bounds__(PANEL3_TPB) k_chol_panel3(Dev d, Chol c, int l
             for (int r = cc + lane; r < nc; r += 32) dst[r] = src[r];
         for (int lr = lane; lr < nS; lr += 32) dst[6 * rb0 + lr] = src[nc + lr];
     }
+    if (lev == c.nlev - 1 && blockIdx.x == 0 && tid == 0) c.xFlag[c.nsn] += 1;     // a new solve: epoch of the backward flags
     CHOL_STAMP(5);
     CHOL_GT(1);
 }
@@ -1475,12 +1476,16 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int e
         }
         for (int i = tid; i < 21 * nt; i += TPB) cp_async8(Wsm + i, c.Winv + (size_t)n.s * 21 + i, true);
     }
-    if (early) pdl_wait();
-    pdl_trigger();
-    if (st->done) { cp_async_wait_all(); return; }
+    // Under programmatic dependent launch (`early`) the levels below become resident one after the other right away (signal on
+    // entry) and do NOT wait for the level above as a whole: the rows of x_R come from the ancestors of this supernode, the
+    // far ones were solved levels ago.  Every supernode publishes "x_t stored" (c.xFlag[t] = the solve's epoch, set by the top
+    // panel kernel); the product below takes its rows in chunks from the far end and waits per row for the flag of the
+    // ancestor that owns it -- so only the parent's rows are left when the parent finishes.  (Safe before pdl_wait: the
+    // factorisation completed before the first backward kernel signalled; x is ordered by the flags.)
+    if (early) pdl_trigger();
+    if (st->done) { cp_async_wait_all(); if (early) pdl_wait(); else pdl_trigger(); return; }
+    const int epoch = __ldcg(c.xFlag + c.nsn);
     CHOL_GT(4);
-    for (int i = rLo + tid; i < rHi; i += TPB) xR[i] = c.xperm[(size_t)__ldg(Rt + i / 6) * 6 + i % 6];
-    __syncthreads();                    // xR visible; L11 / W are only needed after the product
     CHOL_STAMP(17);
     CHOL_GT(7);
     constexpr int NW = TPB / 32;
@@ -1490,7 +1495,17 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int e
         double acc[CPW];
 #pragma unroll
         for (int j = 0; j < CPW; j++) acc[j] = 0.0;
-        for (int r0 = rLo; r0 < rHi; r0 += 128) {
+        const int nch = (rHi - rLo + 127) >> 7;
+        for (int ch = nch - 1; ch >= 0; ch--) {
+            const int r0 = rLo + 128 * ch;
+            if (tid < 128 && r0 + tid < rHi) {          // this chunk of x_R, each row once its owner has published
+                const int r = r0 + tid, col = __ldg(Rt + r / 6);
+                const int* fl = c.xFlag + __ldg(c.colToSn + col);
+                int fv;
+                do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(fv) : "l"(fl) : "memory"); } while (fv != epoch);
+                xR[r] = __ldcg(c.xperm + (size_t)col * 6 + r % 6);
+            }
+            __syncthreads();
             double v[4][CPW], xv[4];
             // unconditional loads (rows / columns beyond the block are clamped and their products vanish): guarded
             // loads compile to branches and would serialise the 4 x CPW loads a lane keeps in flight
@@ -1511,6 +1526,8 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int e
 #pragma unroll
                 for (int j = 0; j < CPW; j++) acc[j] += v[u][j] * xv[u];
         }
+        if (early) pdl_wait();          // before the first global write: kernels still complete in launch order
+        else pdl_trigger();
 #pragma unroll
         for (int j = 0; j < CPW; j++) {
             const int cc = wid + NW * j;
@@ -1591,6 +1608,9 @@ __global__ void __launch_bounds__(TPB) k_chol_bwd3(Dev d, Chol c, int lev, int e
         c.xperm[(size_t)(n.s + i / 6) * 6 + i % 6] = v;
         d.x[(size_t)c.perm[n.s + i / 6] * 6 + i % 6] = v;
     }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(c.xFlag + n.t), "r"(epoch) : "memory");   // x_t is out
     CHOL_GT(5);
 }
 
