@@ -148,8 +148,8 @@ struct HostSet {
 struct Solver {
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaStream_t side = nullptr;   // low-priority branch of the trial graph: k_chol_zinv beside the factorisation
-    cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    cudaStream_t side = nullptr, side2 = nullptr;   // low-priority branches of the trial graph: k_chol_zinv beside the factorisation
+    cudaEvent_t evFork = nullptr, evJoin = nullptr, evJoin2 = nullptr;   // (two branches, levels alternate: one chain of 13 x 32 us ended after the forward pass)
     int panelRB = 0;               // option "panel_rb": block rows of L21 per panel CTA; 0 = per tree level (planPanelSlabs), else 1..CHOL_RB
     bool bwdSplit = true;          // option "bwd_split" = 0: one CTA per supernode in the backward solve
     bool zinvOn = true;            // option "zinv" = 0: backward solves by blocked substitution on every level
@@ -321,7 +321,9 @@ struct Solver {
         if (comm && g_nccl.CommDestroy) g_nccl.CommDestroy(comm);
         if (evFork) cudaEventDestroy(evFork);
         if (evJoin) cudaEventDestroy(evJoin);
+        if (evJoin2) cudaEventDestroy(evJoin2);
         if (side) cudaStreamDestroy(side);
+        if (side2) cudaStreamDestroy(side2);
         if (stream) cudaStreamDestroy(stream);
     }
 
@@ -829,6 +831,8 @@ void Solver::buildStructure() {
         int lo = 0, hi = 0;
         CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));     // lo = lowest priority
         CK(cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, lo));
+        CK(cudaStreamCreateWithPriority(&side2, cudaStreamNonBlocking, lo));
+        CK(cudaEventCreateWithFlags(&evJoin2, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&evFork, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&evJoin, cudaEventDisableTiming));
     }
@@ -1238,7 +1242,8 @@ void Solver::enqueueSolve() {
     // to finish); the top three keep the blocked substitution
     const bool zOn = zinvOn && pdl && !profiling;
     const int zTop = c.nlev - 4;
-    bool forked = false;             // the side branch carries at least one k_chol_zinv
+    bool forked = false;             // the side branches carry at least one k_chol_zinv
+    int nz = 0;
     for (int lev = 0; lev < c.nlev; lev++) {
         const int q0 = h_levelPtr[lev], q1 = h_levelPtr[lev + 1];
         const int ncLev = 6 * h_levMaxNt[lev];
@@ -1254,11 +1259,13 @@ void Solver::enqueueSolve() {
                (size_t)PANEL_LD * ncLev * 8, d, c, lev, (pdl && !profiling && lev > 0 && lev != distLc) ? 1 : 0);
         mark("chol_panel");
         if (zOn && lev <= zTop) {      // L11^-1 of the level on the low-priority branch, beside the rest of the factorisation
+            cudaStream_t sd = (nz & 1) ? side2 : side;
             CK(cudaEventRecord(evFork, stream));
-            CK(cudaStreamWaitEvent(side, evFork, 0));
+            CK(cudaStreamWaitEvent(sd, evFork, 0));
             const size_t zb = (2 * (size_t)ncLev * (ncLev + 1) + 21 * CHOL_MAXW + 36 * 8) * 8;
-            k_chol_zinv<256><<<q1 - q0, 256, zb, side>>>(d, c, lev);
+            k_chol_zinv<256><<<q1 - q0, 256, zb, sd>>>(d, c, lev);
             kernelsPerSlot++;
+            nz++;
             forked = true;
         }
         const int nUpd = h_updPtr[q1] - h_updPtr[q0];
@@ -1278,6 +1285,10 @@ void Solver::enqueueSolve() {
         if (zOn && forked && lev == zTop) {
             CK(cudaEventRecord(evJoin, side));
             CK(cudaStreamWaitEvent(stream, evJoin, 0));
+            if (nz > 1) {
+                CK(cudaEventRecord(evJoin2, side2));
+                CK(cudaStreamWaitEvent(stream, evJoin2, 0));
+            }
         }
         // few supernodes on a level: several CTAs share the L21^T x_R product of each
         const int nsnLev = h_levelPtr[lev + 1] - h_levelPtr[lev];
