@@ -1101,7 +1101,7 @@ void Solver::planPanelSlabs() {
             }
             return t;
         };
-        const int tb = (updSmall && tiles(UPD_TBS) <= 2 * sms) ? UPD_TBS : CHOL_TB;
+        const int tb = (updSmall && tiles(UPD_TBS) <= (updSmall + 1) * sms) ? UPD_TBS : CHOL_TB;     // option value k: levels with up to (k + 1) x SMs small tiles
         h_tbLev[l] = tb;
         for (int q = h_levelPtr[l]; q < h_levelPtr[l + 1]; q++) {
             const int rt = rp[lsn[q] + 1] - rp[lsn[q]];
