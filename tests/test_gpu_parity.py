@@ -226,6 +226,16 @@ def test_engine_switches_agree(graphs, gpu, name):
         np.testing.assert_allclose(chi, chi_ref, rtol=CHI2_RTOL, err_msg=str(off))
         np.testing.assert_array_equal(tr, tr_ref)
         s2.close()
+    # round 2: slab height of the panel kernel (0 = per tree level, the default), update-tile height, Schur products as DMMAs
+    for opts in [{"panel_rb": 1}, {"panel_rb": 3}, {"panel_rb": 10}, {"panel_rb": 16}, {"upd_small": 0}, {"upd_small": 15},
+                 {"schur_mma": 1}, {"panel_rb": 2, "panel_dc": 0, "upd_small": 15, "schur_mma": 1}]:
+        s2, _ = gpu(prob)
+        for k, v in opts.items():
+            s2.set_option(k, v)
+        chi, _, tr = s2.optimize(6)
+        np.testing.assert_allclose(chi, chi_ref, rtol=CHI2_RTOL, err_msg=str(opts))
+        np.testing.assert_array_equal(tr, tr_ref)
+        s2.close()
 
 
 F32_CHI2_RTOL = 1e-4      # north_star: chi2 per iteration within 1e-4 relative under USE_FLOAT32
