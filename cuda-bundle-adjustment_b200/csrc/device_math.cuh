@@ -10,6 +10,10 @@
 namespace cugo_b200 {
 
 enum { RK_NONE = 0, RK_CAUCHY = 1, RK_TUKEY = 2, RK_HUBER = 3 };
+// edge kinds (the `dim` code of an edge set).  2 / 3 are the reference's MonoEdgeSet / StereoEdgeSet (their measurement
+// dimension); 4 is its DepthEdgeSet (include/ba_types.h:171-234: three rows, the third the inverse depth); 5 / 6 its
+// pose-only ICP sets PlaneEdgeSet / LineEdgeSet (include/icp_types.h:19-107, one row; kernels_poseonly.cuh).
+enum { EDGE_MONO = 2, EDGE_STEREO = 3, EDGE_DEPTH = 4, EDGE_PLANE = 5, EDGE_LINE = 6 };
 
 // Robust kernels rho(x), rho'(x), x = omega |e|^2.
 // None/Tukey/Cauchy: src/cuda/cuda_block_solver.cu:972-1027.  Huber (absent from the
@@ -54,6 +58,9 @@ __device__ __forceinline__ void world_to_camera(const double q[4], const double 
 
 // residual e = proj(Xc) - meas, mono (dim 2) or stereo (dim 3):
 // cuda_block_solver.cu:409-424, 1100-1105.  cam = fx fy cx cy bf.
+// Depth (dim code 4): proj = (u, v, 1/Z), camProjectDepth :426-432.  The reference's depth kernel takes meas - proj and
+// pairs it with the stereo Jacobian (:2341-2343, include/ba_types.h:217), which makes every step an ascent direction
+// (SURVEY.md 9.12); here the residual keeps the sign of the other edges and has its own third Jacobian row.
 __device__ __forceinline__ void residual(int dim, const double Xc[3], const double cam[5],
                                          double mu, double mv, double mr, double e[3]) {
     const double invZ = 1.0 / Xc[2];
@@ -61,7 +68,7 @@ __device__ __forceinline__ void residual(int dim, const double Xc[3], const doub
     const double pv = cam[1] * invZ * Xc[1] + cam[3];
     e[0] = pu - mu;
     e[1] = pv - mv;
-    e[2] = (dim == 3) ? (pu - cam[4] * invZ) - mr : 0.0;
+    e[2] = (dim == 3) ? (pu - cam[4] * invZ) - mr : (dim == EDGE_DEPTH ? invZ - mr : 0.0);
 }
 
 // rotation matrix of q: cuda_block_solver.cu:449-478.  R[r][c].
@@ -78,7 +85,7 @@ __device__ __forceinline__ void quat_to_R(const double q[4], double R[3][3]) {
 
 // Pose Jacobian JP[r][c] (dim x 6), J = -d proj / d x, g2o linearizeOplus sign
 // convention: mono cuda_block_solver.cu:515-527, stereo :558-577.  Row 2 is zero
-// for mono edges so callers can run fixed-trip loops.
+// for mono edges so callers can run fixed-trip loops.  Depth edges: rows 0-1 as stereo, row 2 of 1/Z.
 __device__ __forceinline__ void jacobian_pose(int dim, const double Xc[3], const double cam[5],
                                               double JP[3][6]) {
     const double X = Xc[0], Y = Xc[1], Z = Xc[2];
@@ -101,9 +108,14 @@ __device__ __forceinline__ void jacobian_pose(int dim, const double Xc[3], const
         JP[1][0] = (1 + Y * Y * invZZ) * fv; JP[1][1] = -X * Y * invZZ * fv;
         JP[1][2] = -X * invZ * fv;           JP[1][3] = 0;
         JP[1][4] = -1 * invZ * fv;           JP[1][5] = Y * invZZ * fv;
-        JP[2][0] = JP[0][0] - bf * Y * invZZ; JP[2][1] = JP[0][1] + bf * X * invZZ;
-        JP[2][2] = JP[0][2];                  JP[2][3] = JP[0][3];
-        JP[2][4] = 0;                         JP[2][5] = JP[0][5] - bf * invZZ;
+        if (dim == 3) {
+            JP[2][0] = JP[0][0] - bf * Y * invZZ; JP[2][1] = JP[0][1] + bf * X * invZZ;
+            JP[2][2] = JP[0][2];                  JP[2][3] = JP[0][3];
+            JP[2][4] = 0;                         JP[2][5] = JP[0][5] - bf * invZZ;
+        } else {    // depth: -d(1/Z)/d(delta) = (1/Z^2) dZ/d(delta), dZ/d(delta) = (Y, -X, 0, 0, 0, 1)
+            JP[2][0] = Y * invZZ; JP[2][1] = -X * invZZ; JP[2][2] = 0;
+            JP[2][3] = 0;         JP[2][4] = 0;          JP[2][5] = invZZ;
+        }
     }
 }
 
@@ -130,7 +142,7 @@ __device__ __forceinline__ void jacobian_landmark(int dim, const double Xc[3], c
         for (int c = 0; c < 3; c++) {
             JL[0][c] = -fu * R[0][c] * invZ + fu * X * R[2][c] * invZZ;
             JL[1][c] = -fv * R[1][c] * invZ + fv * Y * R[2][c] * invZZ;
-            JL[2][c] = JL[0][c] - bf * R[2][c] * invZZ;
+            JL[2][c] = (dim == 3) ? JL[0][c] - bf * R[2][c] * invZZ : R[2][c] * invZZ;   // depth: -d(1/Z)/dXw
         }
     }
 }

@@ -22,6 +22,7 @@
 #include "kernels_edge.cuh"
 #include "kernels_lm.cuh"
 #include "kernels_peer.cuh"
+#include "kernels_poseonly.cuh"
 #include "kernels_schur.cuh"
 #include "kernels_struct.cuh"
 #include "kernels_sym.cuh"
@@ -136,13 +137,25 @@ struct DBuf {
 };
 
 struct HostSet {
-    int dim = 0, n = 0, nomega = 0, ncam = 0, rk = 0;
+    int dim = 0, n = 0, nomega = 0, ncam = 0, rk = 0;   // dim: the edge kind (device_math.cuh: 2 mono, 3 stereo, 4 depth)
+    int cols() const { return dim == 2 ? 2 : 3; }       // measurement columns
     double delta = 1.0;
     std::vector<int> iP, iL, out;
     std::vector<double> meas, omega, cam;
     bool stale = false;      // measurements / informations were last updated on the device only (refreshHostSets)
     double outThr = 0.0;     // EdgeSet::setOutlierThreshold (0 = no gating)
     int outCount = 0;        // EdgeSet::getOutlierCount: edges of the set flagged so far
+};
+
+// one PlaneEdgeSet / LineEdgeSet of the reference (include/icp_types.h): pose-only edges, kept apart from the BA sets
+// (own id range, cugo_b200.h: CUGO_B200_ICP_SET_BASE) because they never enter the landmark-major structure
+constexpr int ICP_SET_BASE = 1024;
+struct IcpHostSet {
+    int kind = EDGE_PLANE, n = 0, nomega = 1, rk = 0;
+    double delta = 1.0;
+    int cols() const { return kind == EDGE_PLANE ? 7 : 10; }
+    std::vector<int> iP;
+    std::vector<double> meas, omega;
 };
 
 struct Solver {
@@ -159,6 +172,26 @@ struct Solver {
     bool haveVertices = false;
     std::vector<HostSet> sets;
     bool structDirty = true, systemBuilt = false, solved = false;
+    // SURVEY.md 8(f) row 4 (kernels_poseonly.cuh): ICP edge sets, and graphs without free landmarks
+    std::vector<IcpHostSet> icpSets;
+    bool poseOnly = false;         // nL == 0: no Schur complement, Hpp is block diagonal
+    long nIcp = 0;
+    IcpDev ic{};
+    DBuf<int> i_rIP, i_src, i_iP, i_posePtr, i_sliceCnt, i_slicePtr, i_keyOut;
+    DBuf<int2> i_units;
+    DBuf<uint8_t> i_rset, i_set;
+    DBuf<double> i_rw, i_w, i_rpay, i_pay, i_part;
+    int nHpl_ = 0, nChunks_ = 0;   // sizes set by buildEdgeOrders()
+    int addIcpEdgeSet(int kind, int n, const int* iP, const double* meas, const double* omega, int nomega, int rk, double delta);
+    void refreshIcpParams();
+    void buildEdgeOrders();
+    void buildSchurStructure(int TB, int gE, int gE1, int nHpl, int nChunks, bool perEdgeCam, bool anyOut);
+    bool lapOn = false;
+    std::chrono::steady_clock::time_point lapPrev;
+    void lap(const char* what);
+    void buildIcp();
+    void finishPoseOnly();
+    void enqueueErrors(int which, int guarded, bool viaLaunch);
     // device state
     Dev d{};
     Chol c{};
@@ -404,7 +437,8 @@ void Solver::setEstimates(const double* poses7, const double* lms) {
 int Solver::addEdgeSet(int dim, int n, const int* iP, const int* iL, const double* meas, const double* omega,
                        int nomega, const double* cam, int ncam, int rk, double delta) {
     if (!haveVertices) throw StateError("add_edge_set before set_vertices");
-    if ((dim != 2 && dim != 3) || n < 0) throw ArgError("add_edge_set: dim must be 2 or 3, n >= 0");
+    if ((dim != EDGE_MONO && dim != EDGE_STEREO && dim != EDGE_DEPTH) || n < 0)
+        throw ArgError("add_edge_set: dim must be 2 (mono), 3 (stereo) or 4 (depth), n >= 0");
     if (n > 0 && (!iP || !iL || !meas || !omega || !cam)) throw ArgError("add_edge_set: null pointer");
     if ((nomega != 1 && nomega != n) || (ncam != 1 && ncam != n)) throw ArgError("add_edge_set: nomega/ncam must be 1 or n");
     if (rk < 0 || rk > 3) throw ArgError("add_edge_set: unknown robust kernel");
@@ -416,7 +450,7 @@ int Solver::addEdgeSet(int dim, int n, const int* iP, const int* iL, const doubl
     HostSet s;
     s.dim = dim; s.n = n; s.nomega = nomega; s.ncam = ncam; s.rk = rk; s.delta = delta;
     s.iP.assign(iP, iP + n); s.iL.assign(iL, iL + n);
-    s.meas.assign(meas, meas + (size_t)n * dim);
+    s.meas.assign(meas, meas + (size_t)n * s.cols());
     if (n > 0) {
         s.omega.assign(omega, omega + nomega);
         s.cam.assign(cam, cam + (size_t)ncam * 5);
@@ -466,41 +500,59 @@ static int readInt(Solver& S, const int* dptr) {
     return v;
 }
 
+void Solver::lap(const char* what) {
+    if (!lapOn) return;
+    cudaStreamSynchronize(stream);
+    const auto t = std::chrono::steady_clock::now();
+    fprintf(stderr, "[cugo_b200] build_structure: %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t - lapPrev).count());
+    lapPrev = t;
+}
+
 void Solver::buildStructure() {
     if (!haveVertices) throw StateError("build_structure before set_vertices");
     use();
-    const bool dbgT = getenv("CUGO_B200_DEBUG") != nullptr;
-    auto tNow = [&]() { cudaStreamSynchronize(stream); return std::chrono::steady_clock::now(); };
-    auto tPrev = std::chrono::steady_clock::now();
-    auto lap = [&](const char* what) {
-        if (!dbgT) return;
-        const auto t = tNow();
-        fprintf(stderr, "[cugo_b200] build_structure: %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t - tPrev).count());
-        tPrev = t;
-    };
+    lapOn = getenv("CUGO_B200_DEBUG") != nullptr;
+    lapPrev = std::chrono::steady_clock::now();
     refreshHostSets();
     syncOutliersToHost();
-    if (nL_all == 0 || nL == 0) throw UnsupportedError("graph has no free landmarks: pose-only problems use the reference's dense LU path, outside this engine");
     if (nP == 0) throw UnsupportedError("graph has no free poses");
-    E = 0;
+    E = 0; nIcp = 0;
     bool perEdgeCam = false, anyOut = false;
     for (auto& s : sets) {
         E += s.n;
         if (s.ncam > 1) perEdgeCam = true;
         if (!s.out.empty() || s.outThr > 0) anyOut = true;
     }
-    if (E == 0) throw StateError("build_structure: no edges");
-    if (E > 0x7fffffff / 18) throw UnsupportedError("edge count exceeds 32-bit block indexing");
+    for (auto& s : icpSets) nIcp += s.n;
+    // no free landmarks: the reference's doSchur_ == false path (src/block_solver.cpp:80,226-234) -- kernels_poseonly.cuh
+    poseOnly = (nL == 0);
+    if (E == 0 && nIcp == 0) throw StateError("build_structure: no edges");
+    if (!poseOnly && E == 0) throw StateError("build_structure: free landmarks but no edge observes them");
+    if ((poseOnly || nIcp > 0) && nranks > 1)
+        throw UnsupportedError("pose-only graphs and ICP edge sets run on one GPU (nothing to shard: they have no landmarks)");
+    if (E > 0x7fffffff / 18 || nIcp > 0x7fffffff / ICP_COLS) throw UnsupportedError("edge count exceeds 32-bit block indexing");
     perEdgeCam_ = perEdgeCam; anyOut_ = anyOut;
     refreshSetParams();
     dropGraphs();
+    nHpl_ = 0; nChunks_ = 0; nPoseUnits = 0;
+    if (E > 0) buildEdgeOrders();
+    if (nIcp > 0) buildIcp();
+    if (poseOnly) { finishPoseOnly(); return; }
+    const int TB = 256;
+    const int gE = divUp(E, TB), gE1 = divUp(E + 1, TB);
+    const int nHpl = nHpl_, nChunks = nChunks_;
+    buildSchurStructure(TB, gE, gE1, nHpl, nChunks, perEdgeCam, anyOut);
+}
 
+// raw edge arrays -> device, landmark-major order + Hpl CSC + CTA chunks, pose-major copy + slices (E > 0)
+void Solver::buildEdgeOrders() {
+    const bool perEdgeCam = perEdgeCam_, anyOut = anyOut_;
     // ---- raw edge arrays (input order) -> device.  The sets' arrays go up as the caller gave them (indices straight
     // into place, interleaved measurements through a staging buffer) and are split into the SoA arrays on the device.
     {
         r_iP.alloc(E); r_iL.alloc(E); r_m0.alloc(E); r_m1.alloc(E); r_m2.alloc(E); r_w.alloc(E); r_set.alloc(E);
         size_t nMeas = 0, nOm = 0, nCamRows = sets.size();
-        for (auto& s : sets) { nMeas += (size_t)s.n * s.dim; nOm += s.nomega; if (s.ncam > 1) nCamRows += s.n; }
+        for (auto& s : sets) { nMeas += (size_t)s.n * s.cols(); nOm += s.nomega; if (s.ncam > 1) nCamRows += s.n; }
         u_meas.alloc(std::max<size_t>(nMeas, 1)); u_w.alloc(std::max<size_t>(nOm, 1));
         if (perEdgeCam) { r_cam.alloc(E); cams.alloc(nCamRows * 5); }
         if (anyOut) { r_out.alloc(E); CK(cudaMemsetAsync(r_out.p, 0, E, stream)); }
@@ -512,9 +564,9 @@ void Solver::buildStructure() {
             const int g = divUp(s.n, 256);
             CK(cudaMemcpyAsync(r_iP.p + o, s.iP.data(), (size_t)s.n * sizeof(int), cudaMemcpyHostToDevice, stream));
             CK(cudaMemcpyAsync(r_iL.p + o, s.iL.data(), (size_t)s.n * sizeof(int), cudaMemcpyHostToDevice, stream));
-            CK(cudaMemcpyAsync(u_meas.p + om, s.meas.data(), (size_t)s.n * s.dim * sizeof(double), cudaMemcpyHostToDevice, stream));
+            CK(cudaMemcpyAsync(u_meas.p + om, s.meas.data(), (size_t)s.n * s.cols() * sizeof(double), cudaMemcpyHostToDevice, stream));
             CK(cudaMemcpyAsync(u_w.p + oo, s.omega.data(), (size_t)s.nomega * sizeof(double), cudaMemcpyHostToDevice, stream));
-            k_scatter_meas<<<g, 256, 0, stream>>>(u_meas.p + om, u_w.p + oo, s.n, s.dim, s.nomega, r_m0.p + o, r_m1.p + o,
+            k_scatter_meas<<<g, 256, 0, stream>>>(u_meas.p + om, u_w.p + oo, s.n, s.cols(), s.nomega, r_m0.p + o, r_m1.p + o,
                                                   r_m2.p + o, r_w.p + o);
             CK(cudaMemsetAsync(r_set.p + o, (int)si, s.n, stream));
             if (perEdgeCam) {
@@ -531,7 +583,7 @@ void Solver::buildStructure() {
                 CK(cudaMemcpyAsync(ivalA.p, s.out.data(), (size_t)s.n * sizeof(int), cudaMemcpyHostToDevice, stream));
                 k_int_to_flag<<<g, 256, 0, stream>>>(ivalA.p, s.n, r_out.p + o);
             }
-            o += s.n; om += (size_t)s.n * s.dim; oo += s.nomega;
+            o += s.n; om += (size_t)s.n * s.cols(); oo += s.nomega;
         }
     }
     lap("raw edge arrays -> device");
@@ -590,6 +642,12 @@ void Solver::buildStructure() {
     CK(cudaMemsetAsync(poseTicket.p, 0, sizeof(int) * std::max(nP, 1), stream));
 
     lap("pose-major order, slices");
+    nHpl_ = nHpl; nChunks_ = nChunks;
+}
+
+// Hsc pattern, product lists, symbolic analysis, system buffers, trial graph (graphs with free landmarks)
+void Solver::buildSchurStructure(const int TB, const int gE, const int gE1, const int nHpl, const int nChunks,
+                                 const bool perEdgeCam, const bool anyOut) {
     // ---- Hsc block pattern + product lists
     prodCnt.alloc(nL + 1); prodOff.alloc(nL + 1);
     k_prod_counts<<<divUp(nL + 1, TB), TB, 0, stream>>>(colPtr, nL, prodCnt);
@@ -775,7 +833,7 @@ void Solver::buildStructure() {
     invHll.alloc((size_t)nL * 9);
     Hsc.alloc((size_t)nblkG * 36 + (size_t)nP * 6);     // [Hsc | bsc] contiguous: one all-reduce with several ranks
     const int errGrid = std::min(divUp(E, 256), 148 * 8);
-    chiPartial.alloc(errGrid); scalePartial.alloc(nChunks); maxDiagL.alloc(nChunks); maxDiagP.alloc(nP);
+    chiPartial.alloc((size_t)errGrid + (nIcp > 0 ? ic.grid : 0)); scalePartial.alloc(nChunks); maxDiagL.alloc(nChunks); maxDiagP.alloc(nP);
     scalars.alloc(8);
     CK(cudaMemsetAsync(x.p, 0, ((size_t)nP * 6 + (size_t)nL * 3) * sizeof(double), stream));
 
@@ -808,7 +866,7 @@ void Solver::buildStructure() {
     d.nranks = nranks; d.rank = rank; d.nblkG = nblkG; d.hscSlot = nranks > 1 ? hscSlot.p : nullptr;
     d.redA = nranks > 1 ? redA.p : nullptr; d.redC = nranks > 1 ? redC.p : nullptr;
     d.chiPartial = chiPartial; d.scalePartial = scalePartial; d.maxDiagL = maxDiagL; d.maxDiagP = maxDiagP;
-    d.chiEdge = nullptr; d.errGrid = errGrid;
+    d.chiEdge = nullptr; d.errGrid = errGrid; d.nChi = errGrid + (nIcp > 0 ? ic.grid : 0);
     d.pose[0] = pose0; d.pose[1] = pose1; d.lm[0] = lm0; d.lm[1] = lm1; d.st = state;
 
     c.P = P; c.nsn = nsn; c.nlev = counts.nlev;
@@ -849,6 +907,121 @@ void Solver::buildStructure() {
     captureSlot();
     structDirty = false;            // only once the trial graph exists
     lap("graph capture");
+}
+
+// ---------------------------------------------------------------------------
+// ICP edge sets and graphs without free landmarks (kernels_poseonly.cuh)
+// ---------------------------------------------------------------------------
+int Solver::addIcpEdgeSet(int kind, int n, const int* iP, const double* meas, const double* omega, int nomega, int rk,
+                          double delta) {
+    if (!haveVertices) throw StateError("add_icp_edge_set before set_vertices");
+    if ((kind != EDGE_PLANE && kind != EDGE_LINE) || n < 0) throw ArgError("add_icp_edge_set: kind must be plane or line, n >= 0");
+    if (n > 0 && (!iP || !meas || !omega)) throw ArgError("add_icp_edge_set: null pointer");
+    if (nomega != 1 && nomega != n) throw ArgError("add_icp_edge_set: nomega must be 1 or n");
+    if (rk < 0 || rk > 3) throw ArgError("add_icp_edge_set: unknown robust kernel");
+    if ((int)icpSets.size() >= MAX_ICP_SETS) throw ArgError("add_icp_edge_set: too many ICP edge sets");
+    IcpHostSet s;
+    s.kind = kind; s.n = n; s.nomega = n > 0 ? nomega : 1; s.rk = rk; s.delta = delta;
+    for (int i = 0; i < n; i++) {
+        if (iP[i] < 0 || iP[i] >= nP_all) throw ArgError("add_icp_edge_set: pose index out of range");
+        if (iP[i] >= nP) throw ArgError("add_icp_edge_set: edge on a fixed pose is not active");
+        if (kind == EDGE_LINE && !(meas[(size_t)i * 10 + 6] > 0)) throw ArgError("add_icp_edge_set: line length must be > 0");
+    }
+    s.iP.assign(iP, iP + n);
+    s.meas.assign(meas, meas + (size_t)n * s.cols());
+    if (n > 0) s.omega.assign(omega, omega + nomega); else s.omega.assign(1, 1.0);
+    icpSets.push_back(std::move(s));
+    structDirty = true;
+    return ICP_SET_BASE + (int)icpSets.size() - 1;
+}
+
+void Solver::refreshIcpParams() {
+    for (size_t i = 0; i < icpSets.size(); i++) {
+        ic.kind[i] = icpSets[i].kind; ic.rkType[i] = icpSets[i].rk; ic.rkDelta[i] = icpSets[i].delta;
+    }
+}
+
+// the sets' arrays go up as given, are split into the column-major payload and sorted by pose on the device
+void Solver::buildIcp() {
+    const size_t nI = (size_t)nIcp;
+    const int TB = 256, gI = divUp(nIcp, TB);
+    i_rIP.alloc(nI); i_rset.alloc(nI); i_rw.alloc(nI); i_rpay.alloc(nI * ICP_COLS);
+    size_t off = 0;
+    for (size_t si = 0; si < icpSets.size(); si++) {
+        const IcpHostSet& s = icpSets[si];
+        if (s.n == 0) continue;
+        u_meas.alloc((size_t)s.n * s.cols()); u_w.alloc(s.nomega);
+        CK(cudaMemcpyAsync(i_rIP.p + off, s.iP.data(), (size_t)s.n * sizeof(int), cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(u_meas.p, s.meas.data(), (size_t)s.n * s.cols() * sizeof(double), cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(u_w.p, s.omega.data(), (size_t)s.nomega * sizeof(double), cudaMemcpyHostToDevice, stream));
+        k_icp_scatter<<<divUp(s.n, TB), TB, 0, stream>>>(u_meas, u_w, s.n, s.cols(), s.nomega, nI, off, i_rpay, i_rw);
+        CK(cudaMemsetAsync(i_rset.p + off, (int)si, s.n, stream));
+        off += s.n;
+    }
+    i_src.alloc(nI); i_iP.alloc(nI); i_keyOut.alloc(nI);
+    k_fill_index<<<gI, TB, 0, stream>>>(i_iP.p, (int)nI, 0, 1);          // (i_iP: the identity, values of the sort)
+    sortPairs(*this, i_rIP.p, i_keyOut.p, i_iP.p, i_src.p, (int)nI, bitsFor((unsigned long long)nP_all));
+    i_set.alloc(nI); i_w.alloc(nI); i_pay.alloc(nI * ICP_COLS);
+    k_icp_gather<<<gI, TB, 0, stream>>>(i_src, nI, i_rset, i_rw, i_rpay, i_set, i_w, i_pay);
+    i_posePtr.alloc(nP_all + 1);
+    k_lower_bounds<<<divUp(nP_all + 1, TB), TB, 0, stream>>>(i_keyOut, (int)nI, nP_all, i_posePtr);
+    i_sliceCnt.alloc(nP + 1); i_slicePtr.alloc(nP + 1);
+    k_icp_slice_count<<<divUp(nP + 1, TB), TB, 0, stream>>>(i_posePtr, nP, i_sliceCnt);
+    exclusiveScan(*this, i_sliceCnt.p, i_slicePtr.p, nP + 1);
+    const int nUnits = readInt(*this, i_slicePtr.p + nP);
+    i_units.alloc(std::max(nUnits, 1)); i_part.alloc((size_t)std::max(nUnits, 1) * 27);
+    k_pose_units_fill<<<divUp(std::max(nP, 1), TB), TB, 0, stream>>>(i_slicePtr, nP, i_units);
+    ic.nI = (int)nI; ic.nUnits = nUnits; ic.grid = std::max(1, std::min(divUp(nIcp, 256), 148 * 8));
+    ic.iP = i_keyOut; ic.set = i_set; ic.w = i_w; ic.pay = i_pay; ic.posePtr = i_posePtr; ic.slicePtr = i_slicePtr;
+    ic.units = i_units; ic.part = i_part;
+    refreshIcpParams();
+    lap("ICP edges: pose order, slices");
+}
+
+// graph without free landmarks: no Hpl, no Schur complement, no symbolic analysis -- Hpp is block diagonal
+void Solver::finishPoseOnly() {
+    Hpp.alloc((size_t)nP * 36); b.alloc((size_t)nP * 6); x.alloc((size_t)nP * 6); maxDiagP.alloc(nP); scalars.alloc(8);
+    const int errGrid = std::max(1, std::min(divUp(E, 256), 148 * 8));
+    chiPartial.alloc((size_t)errGrid + (nIcp > 0 ? ic.grid : 0));
+    CK(cudaMemsetAsync(x.p, 0, (size_t)nP * 6 * sizeof(double), stream));
+    Dev nd{};
+    nd.nP_all = nP_all; nd.nP = nP; nd.nL_all = nL_all; nd.nL = 0; nd.E = (int)E;
+    if (E > 0) {
+        nd.s_iP = s_iP; nd.s_iL = s_iL; nd.s_uv = s_uv; nd.s_r = s_r; nd.s_w = s_w; nd.s_set = s_set;
+        nd.s_cam = perEdgeCam_ ? s_cam.p : nullptr; nd.s_out = anyOut_ ? s_out.p : nullptr; nd.s_gid = s_gid;
+        nd.s_hplPre = s_hplPre; nd.lmEdgePtr = lmEdgePtr; nd.chunkLm = chunkLm;
+        nd.posePtr = posePtr; nd.p_iL = p_iL; nd.p_uv = p_uv; nd.p_r = p_r; nd.p_w = p_w; nd.p_set = p_set;
+        nd.p_cam = perEdgeCam_ ? p_cam.p : nullptr; nd.p_out = anyOut_ ? p_out.p : nullptr;
+        nd.cams = perEdgeCam_ ? cams.p : nullptr;
+        nd.nPoseUnits = nPoseUnits; nd.poseSlicePtr = poseSlicePtr; nd.poseUnits = poseUnits; nd.posePart = posePart;
+        nd.poseTicket = poseTicket;
+    }
+    nd.Hpp = Hpp; nd.b = b; nd.x = x; nd.chiPartial = chiPartial; nd.maxDiagP = maxDiagP;
+    nd.errGrid = errGrid; nd.nChi = errGrid + (nIcp > 0 ? ic.grid : 0);
+    nd.pose[0] = pose0; nd.pose[1] = pose1; nd.lm[0] = lm0; nd.lm[1] = lm1; nd.st = state;
+    nd.nranks = 1; nd.rank = 0;
+    d = nd;
+    c = Chol{};
+    counts = SymCounts{};
+    memset(factStats, 0, sizeof(factStats));
+    nmulRef = 0; nnzSymm = 0; nblkG = 0;
+    if (!h_state) CK(cudaMallocHost(&h_state, sizeof(LMState)));
+    CK(cudaStreamSynchronize(stream));
+    systemBuilt = false; solved = false;
+    structDirty = true;
+    captureSlot();
+    structDirty = false;
+    lap("pose-only: buffers, graph capture");
+}
+
+void Solver::enqueueErrors(int which, int guarded, bool viaLaunch) {
+    if (viaLaunch) {
+        launch(k_errors<256>, d.errGrid, 256, 0, d, sp, which, guarded); mark("errors");
+        if (nIcp > 0) { launch(k_icp_errors<256>, ic.grid, 256, 0, d, ic, which, guarded); mark("icp_errors"); }
+    } else {
+        k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, which, guarded);
+        if (nIcp > 0) k_icp_errors<256><<<ic.grid, 256, 0, stream>>>(d, ic, which, guarded);
+    }
 }
 
 // ---------------------------------------------------------------------------
@@ -1202,7 +1375,9 @@ void Solver::symbolicParallel(const int* gRowOfP, const int* gRowPtrP, const int
 // ---------------------------------------------------------------------------
 void Solver::enqueueBuild() {
     static_assert(LM_CHUNK == 128, "k_build runs both passes with 128 threads");
-    if (fuseBuild && !profiling) {
+    if (poseOnly) {       // no free landmarks: the pose-major pass alone
+        if (E > 0) { launch(k_build_pose<128>, d.nPoseUnits, 128, 0, d, sp); mark("build_pose"); }
+    } else if (fuseBuild && !profiling) {
         if (f32) launch(k_build<LM_CHUNK, float>, d.nPoseUnits + d.nChunks, LM_CHUNK, 0, d, sp);
         else launch(k_build<LM_CHUNK, double>, d.nPoseUnits + d.nChunks, LM_CHUNK, 0, d, sp);
         mark("build");
@@ -1211,6 +1386,10 @@ void Solver::enqueueBuild() {
         else launch(k_build_lm<LM_CHUNK, double>, d.nChunks, LM_CHUNK, 0, d, sp);
         mark("build_lm");
         launch(k_build_pose<128>, d.nPoseUnits, 128, 0, d, sp); mark("build_pose");
+    }
+    if (nIcp > 0) {       // ICP edges add to Hpp / bp / the max diagonal of their poses
+        launch(k_icp_build<256>, ic.nUnits, 256, 0, d, ic); mark("icp_build");
+        launch(k_icp_add<128>, divUp(d.nP, 4), 128, 0, d, ic, E == 0 ? 1 : 0); mark("icp_add");
     }
     if (nranks > 1 && withA) {   // max diagonal of the *global* system for lambda0
         launch(k_pack_A<256>, std::min(divUp(6 * d.nP, 256), 148), 256, 0, d); mark("pack_A");
@@ -1221,6 +1400,10 @@ void Solver::enqueueBuild() {
 // Schur complement -> multifrontal Cholesky (levels up) -> backward solve (levels
 // down) -> back-substitution (+ landmark part of the update)
 void Solver::enqueueSolve() {
+    if (poseOnly) {       // block-diagonal system: one 6x6 solve per pose (reference: dense LU of the whole 6P x 6P matrix)
+        launch(k_po_solve<128>, divUp(d.nP, 128), 128, 0, d); mark("pose_solve");
+        return;
+    }
     launch(k_schur_inv<256>, divUp(d.nL, 256), 256, 0, d); mark("schur_inv");
     const int2* bp = schurPasses > 1 ? blkPass.p : nullptr;
     if (schurMma) {
@@ -1316,7 +1499,7 @@ void Solver::enqueueSlot() {
     launch(k_lm_prepare<1024>, 1, 1024, 0, d); mark("lm_prepare");
     enqueueSolve();
     launch(k_update_poses<128>, divUp(d.nP, 128), 128, 0, d); mark("update_poses");
-    launch(k_errors<256>, d.errGrid, 256, 0, d, sp, 1, 1); mark("errors");
+    enqueueErrors(1, 1, true);
     if (nranks > 1 && peerOn) {
         launch(k_lm_decide_peer<1024>, 1, 1024, 0, d, peer); mark("lm_decide");       // sums, exchange and decision in one kernel
         return;
@@ -1334,7 +1517,7 @@ void Solver::enqueueSlot() {
 int Solver::profileSlot(int cap, char* names, int nameLen, double* ms) {
     ensureStructure();
     use();
-    k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
+    enqueueErrors(0, 0, false);
     if (nranks > 1) { k_lm_sums<256><<<1, 256, 0, stream>>>(d); smallReduce(d.redC, 3); }
     k_lm_begin<256><<<1, 256, 0, stream>>>(d, 1);
     const int saved = kernelsPerSlot;
@@ -1387,10 +1570,10 @@ void Solver::refreshHostSets() {
     for (HostSet& hs : sets) {
         if (hs.stale && hs.n > 0 && off + hs.n <= (size_t)r_m0.cap) {
             use();
-            u_meas.alloc((size_t)hs.n * hs.dim); u_w.alloc(hs.n);
+            u_meas.alloc((size_t)hs.n * hs.cols()); u_w.alloc(hs.n);
             k_gather_meas<<<divUp(hs.n, 256), 256, 0, stream>>>(r_m0.p + off, r_m1.p + off, r_m2.p + off, r_w.p + off, hs.n,
-                                                               hs.dim, u_meas, u_w);
-            hs.meas.resize((size_t)hs.n * hs.dim); hs.omega.resize(hs.n); hs.nomega = hs.n;
+                                                               hs.cols(), u_meas, u_w);
+            hs.meas.resize((size_t)hs.n * hs.cols()); hs.omega.resize(hs.n); hs.nomega = hs.n;
             CK(cudaMemcpyAsync(hs.meas.data(), u_meas.p, hs.meas.size() * sizeof(double), cudaMemcpyDeviceToHost, stream));
             CK(cudaMemcpyAsync(hs.omega.data(), u_w.p, hs.omega.size() * sizeof(double), cudaMemcpyDeviceToHost, stream));
             CK(cudaStreamSynchronize(stream));
@@ -1407,7 +1590,7 @@ void Solver::updateMeasurements(int setId, const double* meas, const double* ome
     if (!meas || !omega || (nomega != 1 && nomega != hs.n)) throw ArgError("update_measurements: bad arguments");
     if (structDirty) {            // no device arrays yet: keep the host copy, the next build_structure uploads it
         refreshHostSets();
-        hs.meas.assign(meas, meas + (size_t)hs.n * hs.dim);
+        hs.meas.assign(meas, meas + (size_t)hs.n * hs.cols());
         hs.omega.assign(omega, omega + nomega);
         hs.nomega = nomega;
         return;
@@ -1418,10 +1601,10 @@ void Solver::updateMeasurements(int setId, const double* meas, const double* ome
     size_t off = 0;
     for (int i = 0; i < setId; i++) off += sets[i].n;
     const int n = hs.n;
-    u_meas.alloc((size_t)n * hs.dim); u_w.alloc(std::max(nomega, 1));
-    CK(cudaMemcpyAsync(u_meas.p, meas, (size_t)n * hs.dim * sizeof(double), cudaMemcpyHostToDevice, stream));
+    u_meas.alloc((size_t)n * hs.cols()); u_w.alloc(std::max(nomega, 1));
+    CK(cudaMemcpyAsync(u_meas.p, meas, (size_t)n * hs.cols() * sizeof(double), cudaMemcpyHostToDevice, stream));
     CK(cudaMemcpyAsync(u_w.p, omega, (size_t)nomega * sizeof(double), cudaMemcpyHostToDevice, stream));
-    k_scatter_meas<<<divUp(n, 256), 256, 0, stream>>>(u_meas, u_w, n, hs.dim, nomega, r_m0.p + off, r_m1.p + off,
+    k_scatter_meas<<<divUp(n, 256), 256, 0, stream>>>(u_meas, u_w, n, hs.cols(), nomega, r_m0.p + off, r_m1.p + off,
                                                       r_m2.p + off, r_w.p + off);
     hs.stale = true;
     RawEdges raw{(int)E, r_iP, r_iL, r_m0, r_m1, r_m2, r_w, r_set, perEdgeCam_ ? r_cam.p : nullptr,
@@ -1504,8 +1687,8 @@ double Solver::computeErrors() {
     requireSingle("compute_errors");
     ensureStructure();
     use();
-    k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
-    k_reduce<256><<<1, 256, 0, stream>>>(d.chiPartial, d.errGrid, nullptr, 0, 0, scalars.p);
+    enqueueErrors(0, 0, false);
+    k_reduce<256><<<1, 256, 0, stream>>>(d.chiPartial, d.nChi, nullptr, 0, 0, scalars.p);
     return readScalar(*this, 0);
 }
 
@@ -1571,10 +1754,10 @@ int Solver::optimize(int niter, int cap, double* chi2, double* lambda, int* tria
     // any iteration count is accepted, as in the reference; statistics are kept for the first MAX_STATS iterations
     CK(cudaEventRecord(ev0, stream));
     long launched = 0;
-    k_errors<256><<<d.errGrid, 256, 0, stream>>>(d, sp, 0, 0);
+    enqueueErrors(0, 0, false);
     if (nranks > 1) { k_lm_sums<256><<<1, 256, 0, stream>>>(d); smallReduce(d.redC, 3); launched++; }
     k_lm_begin<256><<<1, 256, 0, stream>>>(d, niter);
-    launched += 2;
+    launched += 2 + (nIcp > 0 ? 1 : 0);
     int slots = 0;
     const int maxSlots = niter * 10 + 1;
     int batch = niter;
@@ -1638,7 +1821,7 @@ __global__ void __launch_bounds__(TPB) k_compute_outliers(Dev d, SetParams sp, O
         const double X[3] = {__ldg(lm + 3 * (size_t)iL), __ldg(lm + 3 * (size_t)iL + 1), __ldg(lm + 3 * (size_t)iL + 2)};
         load_cam(d, sp, d.s_cam, k, set, cam);
         const double2 uv = __ldg(d.s_uv + k);
-        const double mr = (dim == 3) ? __ldg(d.s_r + k) : 0.0;
+        const double mr = (dim != 2) ? __ldg(d.s_r + k) : 0.0;
         world_to_camera(q, t, X, Xc);
         residual(dim, Xc, cam, uv.x, uv.y, mr, e);
         const double chi = rk_rho(sp.rkType[set], sp.rkDelta[set], __ldg(d.s_w + k) * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]));
@@ -1846,6 +2029,10 @@ __global__ void k_mul_out(const unsigned long long* keys, const int* vals, int n
 long Solver::getStructure(int which, int* out, long cap) {
     ensureStructure();
     use();
+    if (poseOnly) {       // a graph without free landmarks has no Hpl / Hsc pattern and no elimination tree
+        if (which == CUGO_B200_HPL_COLPTR || which == CUGO_B200_HPL_ROWIND) return 0;
+        if (which != CUGO_B200_EDGE2HPL || E == 0) throw UnsupportedError("get_structure: pose-only graph (block-diagonal Hpp, no Schur structure)");
+    }
     auto copyOut = [&](const int* dptr, long n) {
         if (out && cap >= n && n > 0) {
             CK(cudaMemcpyAsync(out, dptr, n * sizeof(int), cudaMemcpyDeviceToHost, stream));
@@ -1930,8 +2117,8 @@ long Solver::getValues(int which, double* out, long cap) {
         break;
     case CUGO_B200_B: src = b; n = 6L * nP + 3L * nL; break;
     case CUGO_B200_X: src = x; n = 6L * nP + 3L * nL; break;
-    case CUGO_B200_BSC: src = d.bsc; n = 6L * nP; break;
-    case CUGO_B200_HSC: src = d.Hsc; n = 36L * d.nblkG; break;
+    case CUGO_B200_BSC: src = d.bsc; n = poseOnly ? 0 : 6L * nP; break;
+    case CUGO_B200_HSC: src = d.Hsc; n = poseOnly ? 0 : 36L * d.nblkG; break;
     case CUGO_B200_INVHLL: src = invHll; n = 9L * nL; break;
     case CUGO_B200_CHI_PER_EDGE: {
         n = E;
@@ -2035,7 +2222,7 @@ int cugo_b200_set_vertices(cugo_b200_solver* s, int nP_all, int nP_active, const
 }
 
 int cugo_b200_clear_edge_sets(cugo_b200_solver* s) {
-    return guarded(s, [&](Solver& S) { S.sets.clear(); S.structDirty = true; });
+    return guarded(s, [&](Solver& S) { S.sets.clear(); S.icpSets.clear(); S.structDirty = true; });
 }
 
 int cugo_b200_add_edge_set(cugo_b200_solver* s, int dim, int n, const int* iP, const int* iL,
@@ -2047,8 +2234,38 @@ int cugo_b200_add_edge_set(cugo_b200_solver* s, int dim, int n, const int* iP, c
     });
 }
 
+int cugo_b200_add_depth_edge_set(cugo_b200_solver* s, int n, const int* iP, const int* iL, const double* measurements,
+                                 const double* omegas, int nomega, const double* cameras5, int ncam, int robust_type,
+                                 double robust_delta, int* set_id) {
+    return guarded(s, [&](Solver& S) {
+        const int id = S.addEdgeSet(cugo_b200::EDGE_DEPTH, n, iP, iL, measurements, omegas, nomega, cameras5, ncam, robust_type, robust_delta);
+        if (set_id) *set_id = id;
+    });
+}
+int cugo_b200_add_plane_edge_set(cugo_b200_solver* s, int n, const int* iP, const double* matches7, const double* omegas,
+                                 int nomega, int robust_type, double robust_delta, int* set_id) {
+    return guarded(s, [&](Solver& S) {
+        const int id = S.addIcpEdgeSet(cugo_b200::EDGE_PLANE, n, iP, matches7, omegas, nomega, robust_type, robust_delta);
+        if (set_id) *set_id = id;
+    });
+}
+int cugo_b200_add_line_edge_set(cugo_b200_solver* s, int n, const int* iP, const double* matches10, const double* omegas,
+                                int nomega, int robust_type, double robust_delta, int* set_id) {
+    return guarded(s, [&](Solver& S) {
+        const int id = S.addIcpEdgeSet(cugo_b200::EDGE_LINE, n, iP, matches10, omegas, nomega, robust_type, robust_delta);
+        if (set_id) *set_id = id;
+    });
+}
+
 int cugo_b200_set_robust_kernel(cugo_b200_solver* s, int set_id, int robust_type, double robust_delta) {
     return guarded(s, [&](Solver& S) {
+        if (robust_type < 0 || robust_type > 3) throw cugo_b200::ArgError("set_robust_kernel: unknown kernel");
+        if (set_id >= cugo_b200::ICP_SET_BASE && set_id < cugo_b200::ICP_SET_BASE + (int)S.icpSets.size()) {
+            auto& is = S.icpSets[set_id - cugo_b200::ICP_SET_BASE];
+            is.rk = robust_type; is.delta = robust_delta;
+            if (!S.structDirty) { S.refreshIcpParams(); S.dropGraphs(); S.captureSlot(); }
+            return;
+        }
         if (set_id < 0 || set_id >= (int)S.sets.size()) throw cugo_b200::ArgError("set_robust_kernel: bad set id");
         if (robust_type < 0 || robust_type > 3) throw cugo_b200::ArgError("set_robust_kernel: unknown kernel");
         S.sets[set_id].rk = robust_type; S.sets[set_id].delta = robust_delta;

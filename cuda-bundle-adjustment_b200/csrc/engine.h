@@ -15,7 +15,7 @@ constexpr int POSE_STRIDE = 8;     // poses are padded 7 -> 8 doubles (16 B vect
 
 // per edge set parameters (reference: one EdgeSet object each, include/ba_types.h)
 struct SetParams {
-    int dim[MAX_SETS];        // 2 mono / 3 stereo
+    int dim[MAX_SETS];        // edge kind: 2 mono / 3 stereo / 4 depth (device_math.cuh)
     int rkType[MAX_SETS];
     double rkDelta[MAX_SETS];
     double cam[MAX_SETS][5];  // shared camera of the set (used when the set has no per-edge cameras)
@@ -107,12 +107,13 @@ struct Dev {
     double* HscPart;
     double* bscPart;
     // reductions
-    double* chiPartial;         // [errGrid]
+    double* chiPartial;         // [nChi]: one per CTA of k_errors, then one per CTA of k_icp_errors
     double* scalePartial;       // [nChunks]
     double* maxDiagL;           // [nChunks]
     double* maxDiagP;           // [nP]
     double* chiEdge;            // [E] per-edge rho(chi2) in global edge order, or nullptr
-    int errGrid;
+    int errGrid;                // CTAs of k_errors
+    int nChi;                   // entries of chiPartial the LM kernels sum (errGrid + the ICP kernel's CTAs)
     LMState* st;
     // multi-GPU (one process per GPU, landmarks sharded).  Every rank holds all poses
     // and the *global* Hsc pattern; bRowPtr/bColInd/bRowOf/prodPtr/nblk above describe the LOCAL blocks.
@@ -121,6 +122,29 @@ struct Dev {
     const int* hscSlot;         // [nblk] local block -> global block id, nullptr = identity
     double* redA;               // [6 nP + nranks] diag(Hpp) partials + one-hot landmark max-diagonal (all-reduced)
     double* redC;               // [2] chi2, gain denominator (all-reduced)
+};
+
+// Pose-only ("unary") ICP edges: the reference's PlaneEdgeSet / LineEdgeSet (include/icp_types.h:19-107).  They touch
+// Hpp and bp only, so they live beside the BA edge arrays: sorted by pose, payload column-major [10][nI] in the field
+// order of the reference's match structs (src/measurements.h:13-101) --
+//   plane: normal[3], originDistance, pointP[3];   line: a[3], b[3], length, pointP[3].
+constexpr int MAX_ICP_SETS = 8;
+constexpr int ICP_COLS = 10;
+constexpr int ICP_SLICE = 2048;    // edges per CTA of k_icp_build
+struct IcpDev {
+    int nI;                     // edges of all ICP sets
+    int nUnits, grid;           // CTAs of k_icp_build / k_icp_errors
+    const int* iP;              // [nI] pose of the edge (sorted)
+    const uint8_t* set;         // [nI] ICP set (index into kind / rk below)
+    const double* w;            // [nI] information
+    const double* pay;          // [ICP_COLS][nI]
+    const int* posePtr;         // [nP_all+1]
+    const int* slicePtr;        // [nP+1]
+    const int2* units;          // [nUnits] (pose, slice)
+    double* part;               // [nUnits][27] partial JtJ (21) and Jte (6) of every unit
+    int kind[MAX_ICP_SETS];     // EDGE_PLANE / EDGE_LINE
+    int rkType[MAX_ICP_SETS];
+    double rkDelta[MAX_ICP_SETS];
 };
 
 // multifrontal factorisation data (see symbolic.h)

@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(TPB) k_errors(Dev d, SetParams sp, int which, 
         const double X[3] = {__ldg(lm + 3 * (size_t)iL), __ldg(lm + 3 * (size_t)iL + 1), __ldg(lm + 3 * (size_t)iL + 2)};
         load_cam(d, sp, d.s_cam, k, set, cam);
         const double2 uv = __ldg(d.s_uv + k);
-        const double mr = (dim == 3) ? __ldg(d.s_r + k) : 0.0;
+        const double mr = (dim != 2) ? __ldg(d.s_r + k) : 0.0;
         world_to_camera(q, t, X, Xc);
         residual(dim, Xc, cam, uv.x, uv.y, mr, e);
         const double chi = rk_rho(sp.rkType[set], sp.rkDelta[set],
@@ -113,7 +113,7 @@ __device__ __forceinline__ void build_lm_cta(const Dev& d, const SetParams& sp, 
                                      __ldg(lm + 3 * (size_t)iL + 2)};
                 load_cam(d, sp, d.s_cam, k, set, cam);
                 const double2 uv = __ldg(d.s_uv + k);
-                const double mr = (dim == 3) ? __ldg(d.s_r + k) : 0.0;
+                const double mr = (dim != 2) ? __ldg(d.s_r + k) : 0.0;
                 world_to_camera(q, t, X, Xc);
                 residual(dim, Xc, cam, uv.x, uv.y, mr, e);
                 const double omega = __ldg(d.s_w + k);
@@ -231,7 +231,7 @@ __device__ __forceinline__ void build_pose_cta(const Dev& d, const SetParams& sp
         const double X[3] = {__ldg(lm + 3 * (size_t)iL), __ldg(lm + 3 * (size_t)iL + 1), __ldg(lm + 3 * (size_t)iL + 2)};
         load_cam(d, sp, d.p_cam, k, set, cam);
         const double2 uv = __ldg(d.p_uv + k);
-        const double mr = (dim == 3) ? __ldg(d.p_r + k) : 0.0;
+        const double mr = (dim != 2) ? __ldg(d.p_r + k) : 0.0;
         world_to_camera(q, t, X, Xc);
         residual(dim, Xc, cam, uv.x, uv.y, mr, e);
         const double omega = __ldg(d.p_w + k);

@@ -22,7 +22,7 @@ __device__ __forceinline__ double sum_array(const double* a, int n, double* sh) 
 template <int TPB>
 __global__ void __launch_bounds__(TPB) k_lm_begin(Dev d, int niter) {
     __shared__ double sh[TPB / 32];
-    double F = sum_array<TPB>(d.chiPartial, d.errGrid, sh);
+    double F = sum_array<TPB>(d.chiPartial, d.nChi, sh);
     if (threadIdx.x == 0) {
         LMState* st = d.st;
         if (d.nranks > 1) F = d.redC[0];
@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(TPB) k_lm_decide(Dev d) {
     pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
     LMState* st = d.st;
     if (st->done) return;
-    double Fhat = sum_array<TPB>(d.chiPartial, d.errGrid, sh);
+    double Fhat = sum_array<TPB>(d.chiPartial, d.nChi, sh);
     const double lam = st->lambda;
     double s = 0.0;
     for (int i = threadIdx.x; i < 6 * d.nP; i += TPB) s += d.x[i] * (lam * d.x[i] + d.b[i]);
@@ -149,7 +149,7 @@ template <int TPB>
 __global__ void __launch_bounds__(TPB) k_lm_sums(Dev d) {
     __shared__ double sh[TPB / 32];
     pdl_trigger(); pdl_wait();   // engine.h: nothing mutable is touched before the predecessor has completed
-    const double chi = sum_array<TPB>(d.chiPartial, d.errGrid, sh);
+    const double chi = sum_array<TPB>(d.chiPartial, d.nChi, sh);
     const double lam = d.rank == 0 ? d.st->lambda : 0.0;
     double s = 0.0;
     for (int i = threadIdx.x; i < 6 * d.nP; i += TPB) s += d.x[i] * (lam * d.x[i] + d.b[i]);

@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(TPB) k_lm_decide_peer(Dev d, PeerCtx x) {
     pdl_trigger(); pdl_wait();
     LMState* st = d.st;
     if (st->done) return;                   // identical on every rank
-    const double chi = sum_array<TPB>(d.chiPartial, d.errGrid, sh);          // (block sums: valid on thread 0 only)
+    const double chi = sum_array<TPB>(d.chiPartial, d.nChi, sh);          // (block sums: valid on thread 0 only)
     const double lamTrue = st->lambda, lam = d.rank == 0 ? lamTrue : 0.0;
     double s = 0.0;
     for (int i = threadIdx.x; i < 6 * d.nP; i += TPB) s += d.x[i] * (lam * d.x[i] + d.b[i]);

@@ -25,6 +25,9 @@ class EdgeSetArrays:
     omega: np.ndarray        # [n] or [1] float64
     cam: np.ndarray          # [n,5] or [1,5] float64
     src: np.ndarray          # [n] position of the edge in the graph's edge list
+    # "" = by dim; "depth" = DepthEdgeSet (dim 3: u, v, 1/z); "plane" / "line" = the pose-only ICP sets (dim 1; iL and cam
+    # empty; meas [n,7] normal, originDistance, pointP / [n,10] a, b, length, pointP -- src/measurements.h:13-101)
+    kind: str = ""
 
     @property
     def n(self):

@@ -107,30 +107,41 @@ class BlockSolver:
         self._ck(self.lib.cugo_b200_set_vertices(self.h, poses.shape[0], prob.nP_act, _p(poses, C.c_double),
                                                  lms.shape[0], prob.nL_act, _p(lms, C.c_double)))
         self._ck(self.lib.cugo_b200_clear_edge_sets(self.h))
+        self.set_ids = []
         for i, s in enumerate(prob.sets):
             rk = robust[i] if isinstance(robust, (list, tuple)) else robust
             dl = delta[i] if isinstance(delta, (list, tuple)) else delta
+            rkc = RK[rk] if isinstance(rk, str) else int(rk)
             sid = C.c_int()
-            iP, iL, meas, om, cam = _i32(s.iP), _i32(s.iL), _f64(s.meas), _f64(s.omega), _f64(s.cam)
-            self._ck(self.lib.cugo_b200_add_edge_set(
-                self.h, s.dim, s.n, _p(iP, C.c_int), _p(iL, C.c_int), _p(meas, C.c_double),
-                _p(om, C.c_double), int(om.shape[0]), _p(cam, C.c_double), int(cam.shape[0]),
-                RK[rk] if isinstance(rk, str) else int(rk), C.c_double(dl), C.byref(sid)))
+            kind = getattr(s, "kind", "")
+            iP, meas, om = _i32(s.iP), _f64(s.meas), _f64(s.omega)
+            if kind in ("plane", "line"):      # PlaneEdgeSet / LineEdgeSet (include/icp_types.h:19-107)
+                fn = self.lib.cugo_b200_add_plane_edge_set if kind == "plane" else self.lib.cugo_b200_add_line_edge_set
+                self._ck(fn(self.h, s.n, _p(iP, C.c_int), _p(meas, C.c_double), _p(om, C.c_double), int(om.shape[0]),
+                            rkc, C.c_double(dl), C.byref(sid)))
+            else:
+                iL, cam = _i32(s.iL), _f64(s.cam)
+                dim = 4 if kind == "depth" else s.dim      # DepthEdgeSet (include/ba_types.h:171-234)
+                self._ck(self.lib.cugo_b200_add_edge_set(
+                    self.h, dim, s.n, _p(iP, C.c_int), _p(iL, C.c_int), _p(meas, C.c_double),
+                    _p(om, C.c_double), int(om.shape[0]), _p(cam, C.c_double), int(cam.shape[0]),
+                    rkc, C.c_double(dl), C.byref(sid)))
+            self.set_ids.append(sid.value)
 
     def set_estimates(self, poses, lms):
         poses, lms = _f64(poses), _f64(lms)
         self._ck(self.lib.cugo_b200_set_estimates(self.h, _p(poses, C.c_double), _p(lms, C.c_double)))
 
     def set_robust_kernel(self, set_idx, robust, delta):
-        self._ck(self.lib.cugo_b200_set_robust_kernel(self.h, set_idx, RK[robust], C.c_double(delta)))
+        self._ck(self.lib.cugo_b200_set_robust_kernel(self.h, self.set_ids[set_idx], RK[robust], C.c_double(delta)))
 
     def set_outliers(self, set_idx, mask):
         m = _i32(mask)
-        self._ck(self.lib.cugo_b200_set_outliers(self.h, set_idx, _p(m, C.c_int)))
+        self._ck(self.lib.cugo_b200_set_outliers(self.h, self.set_ids[set_idx], _p(m, C.c_int)))
 
     # -- outlier gating (EdgeSet::setOutlierThreshold / updateEdges / getOutlierCount) -------------------
     def set_outlier_threshold(self, set_idx, thr):
-        self._ck(self.lib.cugo_b200_set_outlier_threshold(self.h, int(set_idx), C.c_double(thr)))
+        self._ck(self.lib.cugo_b200_set_outlier_threshold(self.h, self.set_ids[set_idx], C.c_double(thr)))
 
     def update_edges(self):
         self._ck(self.lib.cugo_b200_update_edges(self.h))
@@ -139,7 +150,7 @@ class BlockSolver:
         """(mask [n] int32 in the set's edge order, outlier count)"""
         m = np.zeros(self.prob.sets[set_idx].n, np.int32)
         no, ni = C.c_int(), C.c_int()
-        self._ck(self.lib.cugo_b200_get_outliers(self.h, int(set_idx), _p(m, C.c_int), C.byref(no), C.byref(ni)))
+        self._ck(self.lib.cugo_b200_get_outliers(self.h, self.set_ids[set_idx], _p(m, C.c_int), C.byref(no), C.byref(ni)))
         return m, no.value
 
     # -- stage API ----------------------------------------------------------------
@@ -253,7 +264,7 @@ class BlockSolver:
 
     def update_measurements(self, set_idx, meas, omega):
         meas, omega = _f64(meas), _f64(omega)
-        self._ck(self.lib.cugo_b200_update_measurements(self.h, set_idx, _p(meas, C.c_double), _p(omega, C.c_double),
+        self._ck(self.lib.cugo_b200_update_measurements(self.h, self.set_ids[set_idx], _p(meas, C.c_double), _p(omega, C.c_double),
                                                         int(omega.shape[0])))
 
     # -- multi-GPU plumbing (see cugo_b200/dist.py) ---------------------------------------------------

@@ -298,3 +298,97 @@ def perturb_poses(g: Graph, rot: float, trans: float, seed: int) -> Graph:
                          w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2, w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2], 1)
     g.pose_t = g.pose_t + trans * rng.standard_normal(g.pose_t.shape)
     return g
+
+
+# ---------------------------------------------------------------------------
+# depth edges, pose-only ICP edges, graphs without free landmarks.  These helpers work on PACKED
+# problems (cugo_b200.pack.Problem): the reference JSON schema has no records for these edge kinds.
+# ---------------------------------------------------------------------------
+def stereo_to_depth(prob):
+    """Every stereo set (u, v, u_r) becomes a DepthEdgeSet (include/ba_types.h:171-234) with the measurement
+    (u, v, 1/z), 1/z = (u - u_r) / bf -- the same observations in the depth camera model."""
+    import copy
+    out = copy.copy(prob)
+    out.sets = []
+    for s in prob.sets:
+        if s.dim == 3 and getattr(s, "kind", "") == "":
+            m = s.meas.copy()
+            bf = s.cam[:, 4] if s.cam.shape[0] > 1 else s.cam[0, 4]
+            m[:, 2] = (s.meas[:, 0] - s.meas[:, 2]) / bf
+            # information of the inverse depth row is shared with the pixel rows (one omega per edge): scale it into pixels
+            s = dataclasses.replace(s, meas=np.ascontiguousarray(m), kind="depth")
+        out.sets.append(s)
+    return out
+
+
+def fix_all_landmarks(prob):
+    """The same problem with every landmark fixed: the reference's doSchur_ == false path (src/block_solver.cpp:80)
+    -- motion-only bundle adjustment."""
+    import copy
+    out = copy.copy(prob)
+    out.nL_act = 0
+    keep = []
+    for s in prob.sets:
+        if getattr(s, "kind", "") in ("plane", "line"):
+            keep.append(s)
+            continue
+        act = s.iP < prob.nP_act            # edges between a fixed pose and a (now) fixed landmark are inactive
+        idx = np.flatnonzero(act)
+        keep.append(dataclasses.replace(
+            s, iP=np.ascontiguousarray(s.iP[idx]), iL=np.ascontiguousarray(s.iL[idx]),
+            meas=np.ascontiguousarray(s.meas[idx]), src=np.ascontiguousarray(s.src[idx]),
+            omega=np.ascontiguousarray(s.omega[idx]) if s.omega.shape[0] > 1 else s.omega,
+            cam=np.ascontiguousarray(s.cam[idx]) if s.cam.shape[0] > 1 else s.cam))
+    out.sets = keep
+    return out
+
+
+def make_icp_problem(n_poses=6, n_planes=400, n_lines=300, seed=11, noise=0.01, rot=0.05, trans=0.2, n_fixed=0,
+                     true_poses=None):
+    """Pose-only ICP problem (reference include/icp_types.h): every pose T maps platform points into the world,
+    Pw = R(q) p + t.  Scene: random planes (unit normal n, offset d) and line segments (a, b); a match holds the point
+    p = T_true^-1 (world point on the plane / line) + noise.  Estimates start from T_true perturbed by rot / trans.
+    true_poses ([P,7], optional) replaces the random T_true.
+    Returns a packed Problem with a "plane" and a "line" edge set (either may be empty -> left out)."""
+    from .pack import Problem, EdgeSetArrays
+    rng = np.random.default_rng(seed)
+    P = n_poses
+    Rt = _rodrigues(0.6 * rng.standard_normal((P, 3)))
+    tt = 5.0 * rng.standard_normal((P, 3))
+    if true_poses is not None:
+        Rt, tt = quat_to_rot(np.asarray(true_poses)[:P, :4]), np.asarray(true_poses)[:P, 4:].copy()
+    nact = P - n_fixed
+    dR = _rodrigues(rot * rng.standard_normal((P, 3)))
+    R0 = dR @ Rt
+    t0 = tt + trans * rng.standard_normal((P, 3))
+    R0[nact:], t0[nact:] = Rt[nact:], tt[nact:]          # fixed poses sit at the truth
+    poses = np.concatenate([rot_to_quat(R0), t0], 1)
+    sets = []
+
+    def to_platform(ip, Xw):
+        return np.einsum("nji,nj->ni", Rt[ip], Xw - tt[ip]) + noise * rng.standard_normal(Xw.shape)
+
+    if n_planes > 0:
+        ip = rng.integers(0, nact, n_planes).astype(np.int32)
+        n = rng.standard_normal((n_planes, 3))
+        n /= np.linalg.norm(n, axis=1, keepdims=True)
+        dist = 3.0 * rng.standard_normal(n_planes)
+        X = 4.0 * rng.standard_normal((n_planes, 3))
+        X = X - ((X * n).sum(1) - dist)[:, None] * n      # onto the plane
+        m = np.concatenate([n, dist[:, None], to_platform(ip, X)], 1)
+        sets.append(EdgeSetArrays(dim=1, iP=ip, iL=np.zeros(0, np.int32), meas=np.ascontiguousarray(m),
+                                  omega=1.0 + rng.random(n_planes), cam=np.zeros((0, 5)),
+                                  src=np.arange(n_planes), kind="plane"))
+    if n_lines > 0:
+        ip = rng.integers(0, nact, n_lines).astype(np.int32)
+        a = 4.0 * rng.standard_normal((n_lines, 3))
+        b = a + rng.standard_normal((n_lines, 3)) + 0.5
+        X = a + rng.random((n_lines, 1)) * (b - a)
+        length = np.linalg.norm(a - b, axis=1)
+        # a point exactly on the line has no residual gradient (|c| = 0): keep the matches a little off it
+        X = X + 0.05 * rng.standard_normal((n_lines, 3))
+        m = np.concatenate([a, b, length[:, None], to_platform(ip, X)], 1)
+        sets.append(EdgeSetArrays(dim=1, iP=ip, iL=np.zeros(0, np.int32), meas=np.ascontiguousarray(m),
+                                  omega=np.array([2.0]), cam=np.zeros((0, 5)), src=np.arange(n_lines), kind="line"))
+    return Problem(poses=np.ascontiguousarray(poses), landmarks=np.zeros((0, 3)), nP_act=nact, nL_act=0,
+                   pose_ids=np.arange(P), lm_ids=np.zeros(0, np.int64), sets=sets)

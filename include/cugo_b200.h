@@ -35,7 +35,7 @@ enum {
     CUGO_B200_ENODEVICE = -2,   /* no usable CUDA device (there is no CPU path) */
     CUGO_B200_ECUDA = -3,       /* CUDA runtime error */
     CUGO_B200_ESTATE = -4,      /* call order violated (e.g. solve before build_system) */
-    CUGO_B200_EUNSUPPORTED = -5 /* outside the hot path (e.g. pose-only graph: reference DenseLinearSolver) */
+    CUGO_B200_EUNSUPPORTED = -5 /* outside what the engine covers (e.g. ICP edge sets on several GPUs) */
 };
 
 /* robust kernels: reference RobustKernelType {None, Cauchy, Tukey} (src/robust_kernel.h:12-17);
@@ -89,13 +89,36 @@ const char* cugo_b200_last_error(const cugo_b200_solver* s);
 int cugo_b200_set_vertices(cugo_b200_solver* s, int nP_all, int nP_active, const double* poses7,
                            int nL_all, int nL_active, const double* landmarks3);
 /* ... and edge sets (EdgeSet::init / mapDevice, src/optimisable_graph.hpp:474-601).  dim: 2 =
- * MonoEdgeSet, 3 = StereoEdgeSet (include/ba_types.h:34-169).  nomega / ncam are 1 or n.  Only
+ * MonoEdgeSet, 3 = StereoEdgeSet (include/ba_types.h:34-169), 4 = DepthEdgeSet (below: 3 measurement columns).  nomega / ncam are 1 or n.  Only
  * active edges (not both endpoints fixed) may be passed.  Returns the set id in *set_id. */
 int cugo_b200_clear_edge_sets(cugo_b200_solver* s);
 int cugo_b200_add_edge_set(cugo_b200_solver* s, int dim, int n, const int* iP, const int* iL,
                            const double* measurements, const double* omegas, int nomega,
                            const double* cameras5, int ncam, int robust_type, double robust_delta,
                            int* set_id);
+/* -- the reference's other edge types.
+ * DepthEdgeSet (include/ba_types.h:171-234): measurement (u, v, 1/z), three rows.  Same arguments as
+ * cugo_b200_add_edge_set (equivalent to dim = 4 there).  The reference pairs the residual meas - proj with the
+ * stereo Jacobian (src/cuda/cuda_block_solver.cu:2341-2343 with ba_types.h:217), which turns every step into an
+ * ascent direction; here the residual is proj - meas like the other edges and the third Jacobian row is that of 1/Z. */
+int cugo_b200_add_depth_edge_set(cugo_b200_solver* s, int n, const int* iP, const int* iL,
+                                 const double* measurements, const double* omegas, int nomega,
+                                 const double* cameras5, int ncam, int robust_type, double robust_delta,
+                                 int* set_id);
+/* PlaneEdgeSet / LineEdgeSet (include/icp_types.h:19-107): pose-only edges with one scalar residual, added to Hpp / bp of
+ * their pose.  matches7 / matches10 are the reference's match structs as they lie in memory (src/measurements.h:13-101):
+ *   plane: normal[3], originDistance, pointP[3]          e = normal . (T pointP) - originDistance
+ *   line : a[3], b[3], length (= |a - b| > 0), pointP[3] e = |(T pointP - a) x (T pointP - b)| / length
+ * with T pointP = R(q) pointP + t.  Edges on fixed poses are rejected (inactive).  The ids returned for these sets start
+ * at CUGO_B200_ICP_SET_BASE; they are accepted by cugo_b200_set_robust_kernel only (the reference's ICP kernels know
+ * no outlier mask).  One GPU.  A graph whose landmarks are all fixed (or that has none) is solved without the Schur
+ * complement: Hpp is block diagonal there (reference: DenseLinearSolver over the whole 6P x 6P matrix,
+ * src/block_solver.cpp:226-234,344-354, src/cholesky.hpp:314-516). */
+#define CUGO_B200_ICP_SET_BASE 1024
+int cugo_b200_add_plane_edge_set(cugo_b200_solver* s, int n, const int* iP, const double* matches7,
+                                 const double* omegas, int nomega, int robust_type, double robust_delta, int* set_id);
+int cugo_b200_add_line_edge_set(cugo_b200_solver* s, int n, const int* iP, const double* matches10,
+                                const double* omegas, int nomega, int robust_type, double robust_delta, int* set_id);
 /* EdgeSet::setRobustKernel (src/optimisable_graph.hpp:401-406); per set here, process-global there */
 int cugo_b200_set_robust_kernel(cugo_b200_solver* s, int set_id, int robust_type, double robust_delta);
 /* caller-supplied outlier mask of a set (reference d_outliers / BaseEdge::inactivate, src/optimisable_graph.h:341-408);

@@ -67,10 +67,22 @@ class Oracle:
         for i, s in enumerate(prob.sets):
             rk = robust[i] if isinstance(robust, (list, tuple)) else robust
             dl = delta[i] if isinstance(delta, (list, tuple)) else delta
-            rc = self.lib.bao_add_edge_set(
-                self.h, s.dim, s.n, _p(s.iP, C.c_int), _p(s.iL, C.c_int), _p(s.meas, C.c_double),
-                _p(s.omega, C.c_double), int(s.omega.shape[0]), _p(s.cam, C.c_double),
-                int(s.cam.shape[0]), RK[rk] if isinstance(rk, str) else int(rk), C.c_double(dl))
+            rkc = RK[rk] if isinstance(rk, str) else int(rk)
+            kind = getattr(s, "kind", "")
+            if kind in ("plane", "line"):
+                rc = self.lib.bao_add_icp_edge_set(
+                    self.h, 2 if kind == "plane" else 3, s.n, _p(s.iP, C.c_int), _p(s.meas, C.c_double),
+                    _p(s.omega, C.c_double), int(s.omega.shape[0]), rkc, C.c_double(dl))
+            elif kind == "depth":
+                rc = self.lib.bao_add_depth_edge_set(
+                    self.h, s.n, _p(s.iP, C.c_int), _p(s.iL, C.c_int), _p(s.meas, C.c_double),
+                    _p(s.omega, C.c_double), int(s.omega.shape[0]), _p(s.cam, C.c_double),
+                    int(s.cam.shape[0]), rkc, C.c_double(dl))
+            else:
+                rc = self.lib.bao_add_edge_set(
+                    self.h, s.dim, s.n, _p(s.iP, C.c_int), _p(s.iL, C.c_int), _p(s.meas, C.c_double),
+                    _p(s.omega, C.c_double), int(s.omega.shape[0]), _p(s.cam, C.c_double),
+                    int(s.cam.shape[0]), rkc, C.c_double(dl))
             assert rc == 0, rc
 
     def __del__(self):
