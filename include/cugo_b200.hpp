@@ -13,6 +13,7 @@
 //   src/optimisable_graph.h:161-330  (vertex sets)        BaseVertexSet, VertexSet<T>, PoseVertexSet, LandmarkVertexSet
 //   src/optimisable_graph.h:341-505  (edges)              BaseEdge, Edge<DIM>, MonoEdge, StereoEdge
 //   src/optimisable_graph.h:510-680  (edge sets)          BaseEdgeSet, EdgeSet<DIM>, MonoEdgeSet, StereoEdgeSet
+//   include/ba_types.h:171-234, include/icp_types.h       DepthEdgeSet; PlaneEdgeSet / LineEdgeSet (pose-only ICP edges)
 //   src/fixed_vector.h:29-474, src/camera.h               Vec<T,N>, Vec2d, Vec3d, QuatD, Se3D, Camera
 //   src/robust_kernel.h:12-17                             RobustKernelType (+ Huber)
 //
@@ -26,6 +27,7 @@
 
 #include <array>
 #include <chrono>
+#include <cmath>
 #include <cstddef>
 #include <cstdint>
 #include <cstdio>
@@ -310,6 +312,63 @@ private:
 };
 using MonoEdge = Edge<2>;      // g2o EdgeSE3ProjectXYZ
 using StereoEdge = Edge<3>;    // g2o EdgeStereoSE3ProjectXYZ
+using DepthEdge = Edge<3>;     // include/ba_types.h:258-264: measurement (u, v, 1/z)
+
+// ---- pose-only ICP edges (include/icp_types.h:110-125, src/measurements.h:13-101): one vertex, one scalar residual.
+// The match structs keep the reference's member order: they go to the engine as they lie in memory.
+struct PointToLineMatch {
+    Vec3d a, b;                 // two points of the line
+    double length = 0;          // |a - b|
+    Vec3d pointP;               // the matched point, platform coordinates
+    PointToLineMatch() {}
+    PointToLineMatch(const Vec3d& start, const Vec3d& finish, const Vec3d& p = Vec3d()) : a(start), b(finish), pointP(p) {
+        double s = 0;
+        for (int i = 0; i < 3; i++) s += (a[i] - b[i]) * (a[i] - b[i]);
+        length = std::sqrt(s);
+    }
+};
+struct PointToPlaneMatch {
+    Vec3d normal;               // unit normal
+    double originDistance = 0;  // signed distance of the plane from the origin
+    Vec3d pointP;
+    PointToPlaneMatch() {}
+    PointToPlaneMatch(const Vec3d& n, double offset, const Vec3d& p) : normal(n), originDistance(offset), pointP(p) {}
+};
+static_assert(sizeof(PointToLineMatch) == 10 * sizeof(double) && sizeof(PointToPlaneMatch) == 7 * sizeof(double),
+              "match structs are plain runs of doubles");
+
+template <typename M>
+class UnaryEdge : public BaseEdge {
+public:
+    using Measurement = M;
+    BaseVertex* getVertex(int i) override { return i == 0 ? v_ : nullptr; }
+    void setVertex(BaseVertex* v, int i) override {
+        if (i != 0) throw std::runtime_error("cugo: a pose-only edge has one vertex");
+        v_ = v; v->addEdge(this);
+    }
+    bool allVerticesFixed() const noexcept override { return v_->isFixed(); }
+    bool anyVerticesNotFixed() const noexcept override { return !v_->isFixed(); }
+    bool allVerticesNotFixed() const noexcept override { return !v_->isFixed(); }
+    const double* measurementData() const noexcept override { return reinterpret_cast<const double*>(&m_); }
+    int dim() const noexcept override { return 1; }
+    void setMeasurement(const Measurement& m) noexcept { m_ = m; }
+    const Measurement& getMeasurement() const noexcept { return m_; }
+    void setInformation(Information info) noexcept override { info_ = info; }
+    Information getInformation() noexcept override { return info_; }
+    void setCamera(const Camera&) noexcept override {}
+    Camera& getCamera() noexcept override { return cam_; }
+    void inactivate() noexcept override { active_ = false; }
+    void setActive() noexcept override { active_ = true; }
+    bool isActive() const noexcept override { return active_; }
+private:
+    BaseVertex* v_ = nullptr;
+    Measurement m_;
+    Information info_ = 1.0;
+    Camera cam_;
+    bool active_ = true;
+};
+using PlaneEdge = UnaryEdge<PointToPlaneMatch>;
+using LineEdge = UnaryEdge<PointToLineMatch>;
 
 // ---- edge sets (src/optimisable_graph.h:510-680) ------------------------------------------------------
 class BaseEdgeSet {
@@ -335,7 +394,7 @@ public:
     // flat arrays handed to cugo_b200_add_edge_set (the reference's EdgeSet::init,
     // src/optimisable_graph.hpp:474-572): active edges = flagged active and not both vertices fixed
     struct Packed {
-        int dim = 0, n = 0, nomega = 0, ncam = 0, rk = 0;
+        int dim = 0, n = 0, nomega = 0, ncam = 0, rk = 0;     // dim: the engine's edge kind (2 mono, 3 stereo, 4 depth, 5 plane, 6 line)
         double delta = 1.0;
         std::vector<int> iP, iL;
         std::vector<double> meas, omega, cam;
@@ -343,10 +402,12 @@ public:
     virtual void pack(const GraphOptimisationOptions& opt, Packed& out) = 0;
 };
 
-template <int DIM>
+// KIND: what the engine is told (cugo_b200.h): DIM for mono / stereo, 4 depth, 5 plane, 6 line (the last two pose-only)
+template <int DIM, int KIND = DIM>
 class EdgeSet : public BaseEdgeSet {
 public:
-    using EdgeType = Edge<DIM>;
+    static constexpr bool UNARY = KIND >= 5;
+    static constexpr int COLS = KIND == 5 ? 7 : (KIND == 6 ? 10 : DIM);     // doubles per measurement
     void addEdge(BaseEdge* e) override { if (index_.insert(e).second) edges_.push_back(e); }
     void removeEdge(BaseEdge* e) override {
         if (!index_.erase(e)) return;
@@ -377,7 +438,7 @@ public:
     }
     void pack(const GraphOptimisationOptions& opt, Packed& out) override {
         out = Packed();
-        out.dim = DIM; out.rk = (int)rk_; out.delta = delta_;
+        out.dim = KIND; out.rk = (int)rk_; out.delta = delta_;
         outCount_ = 0;
         // pass 1: which edges go to the engine (active flag set, not both vertices fixed), per chunk; pass 2: fill
         const size_t ne = edges_.size();
@@ -397,9 +458,11 @@ public:
         for (int c = 0; c < nth; c++) cnt[c + 1] += cnt[c];
         const size_t n = cnt[nth];
         packed_.resize(n);
-        out.iP.resize(n); out.iL.resize(n); out.meas.resize(n * DIM);
+        out.iP.resize(n); out.meas.resize(n * COLS);
+        if (!UNARY) out.iL.resize(n);
+        const bool perCam = opt.perEdgeCamera && !UNARY;
         if (opt.perEdgeInformation) out.omega.resize(n);
-        if (opt.perEdgeCamera) out.cam.resize(n * 5);
+        if (perCam) out.cam.resize(n * 5);
         detail::parallelChunks(ne, nth, [&](int c, size_t b, size_t e) {
             size_t o = cnt[c];
             for (size_t i = b; i < e; i++) {
@@ -407,11 +470,11 @@ public:
                 BaseEdge* ed = edges_[i];
                 packed_[o] = ed;
                 out.iP[o] = ed->getVertex(0)->getIndex();
-                out.iL[o] = ed->getVertex(1)->getIndex();
+                if (!UNARY) out.iL[o] = ed->getVertex(1)->getIndex();
                 const double* m = ed->measurementData();
-                for (int k = 0; k < DIM; k++) out.meas[o * DIM + k] = m[k];
+                for (int k = 0; k < COLS; k++) out.meas[o * COLS + k] = m[k];
                 if (opt.perEdgeInformation) out.omega[o] = ed->getInformation();
-                if (opt.perEdgeCamera) {
+                if (perCam) {
                     const Camera& cm = ed->getCamera();
                     double* v = &out.cam[o * 5];
                     v[0] = cm.fx; v[1] = cm.fy; v[2] = cm.cx; v[3] = cm.cy; v[4] = cm.bf;
@@ -422,9 +485,9 @@ public:
         out.n = (int)n;
         nActive_ = n;
         if (!opt.perEdgeInformation) out.omega.assign(1, info_);
-        if (!opt.perEdgeCamera) out.cam = {cam_.fx, cam_.fy, cam_.cx, cam_.cy, cam_.bf};
+        if (!perCam) out.cam = {cam_.fx, cam_.fy, cam_.cx, cam_.cy, cam_.bf};
         out.nomega = opt.perEdgeInformation ? out.n : 1;
-        out.ncam = opt.perEdgeCamera ? out.n : 1;
+        out.ncam = perCam ? out.n : 1;
         if (out.n == 0) { out.omega.assign(1, info_); out.cam.assign(5, 0.0); out.nomega = out.ncam = 1; }
     }
 private:
@@ -441,6 +504,9 @@ private:
 };
 using MonoEdgeSet = EdgeSet<2>;
 using StereoEdgeSet = EdgeSet<3>;
+using DepthEdgeSet = EdgeSet<3, 4>;     // include/ba_types.h:171-234
+using PlaneEdgeSet = EdgeSet<1, 5>;     // include/icp_types.h:64-107
+using LineEdgeSet = EdgeSet<1, 6>;      // include/icp_types.h:19-61
 
 using EdgeSetVec = std::vector<BaseEdgeSet*>;
 using VertexSetVec = std::vector<BaseVertexSet*>;
@@ -478,40 +544,56 @@ public:
     // (src/block_solver.cpp:161-170).
     void initialize(const EdgeSetVec& edgeSets, const VertexSetVec& vertexSets) {
         const auto t0 = now();
-        if (vertexSets.size() != 2 || vertexSets[0]->estimateDim() != 7 || vertexSets[1]->estimateDim() != 3)
+        // (a pose-only graph -- ICP edge sets alone -- may come with the pose vertex set only, include/icp_types.h:28)
+        if (vertexSets.empty() || vertexSets.size() > 2 || vertexSets[0]->estimateDim() != 7 ||
+            (vertexSets.size() == 2 && vertexSets[1]->estimateDim() != 3))
             throw std::runtime_error("cugo: add the pose vertex set first, then the landmark vertex set");
+        const bool haveL = vertexSets.size() == 2;
         for (auto* vs : vertexSets) vs->assignIndices();
         vertexSets[0]->packEstimates(poses_);
-        vertexSets[1]->packEstimates(landmarks_);
+        if (haveL) vertexSets[1]->packEstimates(landmarks_); else landmarks_.clear();
         std::vector<BaseEdgeSet::Packed> packed(edgeSets.size());
         nedges_ = 0;
         for (size_t i = 0; i < edgeSets.size(); i++) { edgeSets[i]->pack(options, packed[i]); nedges_ += packed[i].n; }
         const int nPa = (int)vertexSets[0]->size(), nP = vertexSets[0]->getActiveSize();
-        const int nLa = (int)vertexSets[1]->size(), nL = vertexSets[1]->getActiveSize();
+        const int nLa = haveL ? (int)vertexSets[1]->size() : 0, nL = haveL ? vertexSets[1]->getActiveSize() : 0;
         bool same = uploaded_ && nPa == nPa_ && nP == nP_ && nLa == nLa_ && nL == nL_ && packed.size() == last_.size();
-        for (size_t i = 0; same && i < packed.size(); i++)
+        for (size_t i = 0; same && i < packed.size(); i++) {
             same = packed[i].dim == last_[i].dim && packed[i].iP == last_[i].iP && packed[i].iL == last_[i].iL &&
                    packed[i].nomega == last_[i].nomega && packed[i].cam == last_[i].cam;
+            // the engine refreshes measurements in place for the BA sets only: changed ICP matches go up as a new graph
+            if (same && packed[i].dim >= 5) same = packed[i].meas == last_[i].meas && packed[i].omega == last_[i].omega;
+        }
         if (same) {
             ck(cugo_b200_set_estimates(h_, poses_.data(), landmarks_.data()));
             for (size_t i = 0; i < packed.size(); i++) {
                 if (packed[i].meas != last_[i].meas || packed[i].omega != last_[i].omega)
-                    ck(cugo_b200_update_measurements(h_, (int)i, packed[i].meas.data(), packed[i].omega.data(), packed[i].nomega));
+                    ck(cugo_b200_update_measurements(h_, ids_[i], packed[i].meas.data(), packed[i].omega.data(), packed[i].nomega));
                 if (packed[i].rk != last_[i].rk || packed[i].delta != last_[i].delta)
-                    ck(cugo_b200_set_robust_kernel(h_, (int)i, packed[i].rk, packed[i].delta));
+                    ck(cugo_b200_set_robust_kernel(h_, ids_[i], packed[i].rk, packed[i].delta));
             }
         } else {
             ck(cugo_b200_set_vertices(h_, nPa, nP, poses_.data(), nLa, nL, landmarks_.data()));
             ck(cugo_b200_clear_edge_sets(h_));
-            for (auto& p : packed) {
-                int id = -1;
-                ck(cugo_b200_add_edge_set(h_, p.dim, p.n, p.iP.data(), p.iL.data(), p.meas.data(), p.omega.data(), p.nomega,
-                                          p.cam.data(), p.ncam, p.rk, p.delta, &id));
+            ids_.assign(packed.size(), -1);
+            for (size_t i = 0; i < packed.size(); i++) {
+                auto& p = packed[i];
+                if (p.dim == 5)
+                    ck(cugo_b200_add_plane_edge_set(h_, p.n, p.iP.data(), p.meas.data(), p.omega.data(), p.nomega, p.rk, p.delta, &ids_[i]));
+                else if (p.dim == 6)
+                    ck(cugo_b200_add_line_edge_set(h_, p.n, p.iP.data(), p.meas.data(), p.omega.data(), p.nomega, p.rk, p.delta, &ids_[i]));
+                else
+                    ck(cugo_b200_add_edge_set(h_, p.dim, p.n, p.iP.data(), p.iL.data(), p.meas.data(), p.omega.data(), p.nomega,
+                                              p.cam.data(), p.ncam, p.rk, p.delta, &ids_[i]));
             }
             nPa_ = nPa; nP_ = nP; nLa_ = nLa; nL_ = nL;
         }
-        for (size_t i = 0; i < edgeSets.size(); i++)
-            ck(cugo_b200_set_outlier_threshold(h_, (int)i, edgeSets[i]->getOutlierThreshold()));
+        for (size_t i = 0; i < edgeSets.size(); i++) {
+            const bool icp = packed[i].dim >= 5;
+            if (icp && edgeSets[i]->getOutlierThreshold() > 0.0)
+                throw std::runtime_error("cugo: outlier gating is not available for the pose-only ICP edge sets");
+            if (!icp) ck(cugo_b200_set_outlier_threshold(h_, ids_[i], edgeSets[i]->getOutlierThreshold()));
+        }
         last_.swap(packed);
         uploaded_ = true;
         profItems_[PROF_ITEM_INITIALIZE] = ms(t0);
@@ -564,7 +646,7 @@ public:
             if (!(edgeSets[i]->getOutlierThreshold() > 0.0) || edgeSets[i]->nActiveEdges() == 0) continue;
             mask.assign(edgeSets[i]->nActiveEdges(), 0);
             int no = 0, ni = 0;
-            ck(cugo_b200_get_outliers(h_, (int)i, mask.data(), &no, &ni));
+            ck(cugo_b200_get_outliers(h_, ids_[i], mask.data(), &no, &ni));
             edgeSets[i]->applyOutlierMask(mask.data(), mask.size());
         }
     }
@@ -576,7 +658,7 @@ public:
         need();
         ck(cugo_b200_get_estimates(h_, poses_.data(), landmarks_.data()));
         vertexSets[0]->unpackEstimates(poses_.data());
-        vertexSets[1]->unpackEstimates(landmarks_.data());
+        if (vertexSets.size() > 1) vertexSets[1]->unpackEstimates(landmarks_.data());
     }
     // the reference's nine profile strings (src/block_solver.cpp:470-488); host wall-clock ms of the last call of each
     // stage (every staged call of the C ABI synchronises).  Items 4 and 5 are inside "1" / "6" here.
@@ -617,6 +699,7 @@ private:
     int nPa_ = 0, nP_ = 0, nLa_ = 0, nL_ = 0;
     std::vector<double> poses_, landmarks_;
     std::vector<BaseEdgeSet::Packed> last_;
+    std::vector<int> ids_;                  // engine id of every edge set (the ICP sets have their own range)
     double profItems_[PROF_ITEM_COUNT];
 };
 

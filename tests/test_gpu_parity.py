@@ -186,7 +186,7 @@ def test_error_conventions(graphs):
     s2 = solver.BlockSolver(0)
     s2.initialize(nol)
     with pytest.raises(solver.CugoError):
-        s2.build_structure()                    # pose-only graph: outside the hot path
+        s2.build_structure()                    # a graph without edges
 
 
 def test_full_size_properties(graphs, gpu):

@@ -262,3 +262,73 @@ def test_icp_argument_errors():
     with pytest.raises(solver.CugoError):                        # no Schur structure to read
         s.structure("hsc_rowptr")
     s.optimize(2)
+
+
+def _write_icp_file(prob, path):
+    """ICP1 file read by samples/sample_icp.cpp (poses by index = by id here)."""
+    import struct
+    plane = [s for s in prob.sets if s.kind == "plane"]
+    line = [s for s in prob.sets if s.kind == "line"]
+    with open(path, "wb") as f:
+        P = prob.poses.shape[0]
+        f.write(struct.pack("<4i", 0x31504349, P, plane[0].n if plane else 0, line[0].n if line else 0))
+        f.write(np.ascontiguousarray(prob.poses, np.float64).tobytes())
+        f.write((np.arange(P) >= prob.nP_act).astype(np.int32).tobytes())
+        for sets in (plane, line):
+            if not sets:
+                continue
+            s = sets[0]
+            om = s.omega if s.omega.shape[0] == s.n else np.full(s.n, s.omega[0])
+            f.write(np.ascontiguousarray(s.iP, np.int32).tobytes())
+            f.write(np.ascontiguousarray(s.meas, np.float64).tobytes())
+            f.write(np.ascontiguousarray(om, np.float64).tobytes())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("rk,delta", [(0, 1.0), (1, 0.5)])
+def test_cpp_facade_icp_sample_matches_binding(tmp_path, rk, delta):
+    """PlaneEdgeSet / LineEdgeSet / PoseVertexSet through include/cugo_b200.hpp (samples/sample_icp.cpp) drive the same
+    engine as the ctypes binding: identical chi2 per iteration and final poses."""
+    import json
+    import os
+    import subprocess
+    from cugo_b200 import solver, synth
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "cuda-bundle-adjustment_b200", "lib", "sample_icp")
+    prob = synth.make_icp_problem(n_poses=7, n_fixed=2, n_planes=900, n_lines=700, rot=0.2, trans=0.6, seed=3)
+    path, est = str(tmp_path / "p.icp"), str(tmp_path / "poses.bin")
+    _write_icp_file(prob, path)
+    r = subprocess.run([exe, path, "8", str(rk), repr(delta), est], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    out = json.loads(r.stdout)
+    s = solver.BlockSolver(0)
+    s.initialize(prob, robust={0: "none", 1: "cauchy"}[rk], delta=delta)
+    chi, _, _ = s.optimize(8)
+    assert out["chi2"] == [float(c) for c in chi]
+    np.testing.assert_array_equal(np.fromfile(est, np.float64).reshape(-1, 7), s.estimates()[0])
+
+
+@pytest.mark.gpu
+def test_outlier_gating_without_free_landmarks(graphs):
+    """Row f3 on the block-diagonal path: threshold -> mask on the device at the end of optimize(), same masks and chi2 as
+    the oracle's restatement of the reference flow."""
+    from cugo_b200 import synth
+    prob = synth.fix_all_landmarks(graphs("small", outlier_frac=0.05, seed=7002)[1])
+    s, o = _pair(prob)
+    for e in (s, o):
+        for i in range(len(prob.sets)):
+            e.set_outlier_threshold(i, 30.0)
+    chi_g, _, tr_g = s.optimize(4); chi_o, _, tr_o = o.optimize(4)
+    np.testing.assert_array_equal(tr_g, tr_o)
+    np.testing.assert_allclose(chi_g, chi_o, rtol=CHI2_RTOL)
+    total = 0
+    for i in range(len(prob.sets)):
+        mg, cg = s.outliers(i); mo, co = o.outliers(i)
+        np.testing.assert_array_equal(mg, mo)
+        assert cg == co
+        total += cg
+    assert total > 0
+    chi_g2, _, tr_g2 = s.optimize(4); chi_o2, _, tr_o2 = o.optimize(4)
+    np.testing.assert_array_equal(tr_g2, tr_o2)
+    np.testing.assert_allclose(chi_g2, chi_o2, rtol=CHI2_RTOL)
+    assert chi_g2[0] < chi_g[-1]
