@@ -1389,7 +1389,7 @@ void Solver::enqueueBuild() {
     }
     if (nIcp > 0) {       // ICP edges add to Hpp / bp / the max diagonal of their poses
         launch(k_icp_build<256>, ic.nUnits, 256, 0, d, ic); mark("icp_build");
-        launch(k_icp_add<128>, divUp(d.nP, 4), 128, 0, d, ic, E == 0 ? 1 : 0); mark("icp_add");
+        launch(k_icp_add<256>, d.nP, 256, 0, d, ic, E == 0 ? 1 : 0); mark("icp_add");
     }
     if (nranks > 1 && withA) {   // max diagonal of the *global* system for lambda0
         launch(k_pack_A<256>, std::min(divUp(6 * d.nP, 256), 148), 256, 0, d); mark("pack_A");

@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(TPB) k_icp_errors(Dev d, IcpDev ic, int which,
 
 // J^T w J (21 unique entries) and J^T w e (6) of one slice of a pose's ICP edges -> ic.part[unit]
 template <int TPB>
-__global__ void __launch_bounds__(TPB) k_icp_build(Dev d, IcpDev ic) {
+__global__ void __launch_bounds__(TPB, 2) k_icp_build(Dev d, IcpDev ic) {
     __shared__ double red[TPB / 32][27];
     pdl_trigger(); pdl_wait();
     const LMState* st = d.st;
@@ -118,19 +118,38 @@ __global__ void __launch_bounds__(TPB) k_icp_build(Dev d, IcpDev ic) {
     }
 }
 
-// Hpp / bp / max diagonal of every free pose += its ICP units, in unit order (one warp per pose).  init: the graph has no BA
-// edges, so nothing was written before -- set instead of add.
+// Hpp / bp / max diagonal of every free pose += its ICP units (one CTA per pose: a scan matched against a map puts
+// hundreds of units on ONE pose).  Warp g sums the units g, g + G, ... in that order, four loads in flight; warp 0 adds the
+// G partial sums in warp order -- a fixed order, so runs repeat bit for bit.  init: the graph has no BA edges, so nothing
+// was written before -- set instead of add.
 template <int TPB>
 __global__ void __launch_bounds__(TPB) k_icp_add(Dev d, IcpDev ic, int init) {
+    constexpr int G = TPB / 32;
+    __shared__ double sh[G][27];
     pdl_trigger(); pdl_wait();
     const LMState* st = d.st;
     if (st->done || !st->needBuild) return;
-    const int lane = threadIdx.x & 31;
-    const int p = blockIdx.x * (TPB / 32) + (threadIdx.x >> 5);
-    if (p >= d.nP) return;               // (the whole warp)
+    const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
+    const int p = blockIdx.x;
     double s = 0.0;
+    if (lane < 27) {
+        const int u1 = ic.slicePtr[p + 1];
+        int u = ic.slicePtr[p] + grp;
+        const double* __restrict__ part = ic.part + lane;
+        for (; u + 3 * G < u1; u += 4 * G) {
+            const double a0 = __ldcg(part + (size_t)u * 27), a1 = __ldcg(part + (size_t)(u + G) * 27);
+            const double a2 = __ldcg(part + (size_t)(u + 2 * G) * 27), a3 = __ldcg(part + (size_t)(u + 3 * G) * 27);
+            s += a0; s += a1; s += a2; s += a3;
+        }
+        for (; u < u1; u += G) s += __ldcg(part + (size_t)u * 27);
+        sh[grp][lane] = s;
+    }
+    __syncthreads();
+    if (grp != 0) return;
+    s = 0.0;
     if (lane < 27)
-        for (int u = ic.slicePtr[p]; u < ic.slicePtr[p + 1]; u++) s += ic.part[(size_t)u * 27 + lane];
+#pragma unroll
+        for (int g = 0; g < G; g++) s += sh[g][lane];
     double mx = 0.0;
 #pragma unroll
     for (int round = 0; round < 2; round++) {

@@ -38,7 +38,8 @@ SYMBOLS = (
     "cugo_b200_get_last_timing", "cugo_b200_stream", "cugo_b200_profile_trial", "cugo_b200_update_measurements",
     "cugo_b200_debug_counters", "cugo_b200_get_factor_stats", "cugo_b200_comm_unique_id", "cugo_b200_comm_init",
     "cugo_b200_chi2_noalloc", "cugo_b200_set_outlier_threshold", "cugo_b200_update_edges", "cugo_b200_get_outliers",
-    "cugo_b200_set_option",
+    "cugo_b200_set_option", "cugo_b200_add_depth_edge_set", "cugo_b200_add_plane_edge_set",
+    "cugo_b200_add_line_edge_set",
 )
 
 _lib = None
