@@ -9,7 +9,8 @@
 // (distance :352-370), Pw = R(q) pointP + t (se3MulVec :334-342).  The reference's ICP Jacobians are unfinished
 // (computeJacobians_Line multiplies by an uninitialised matrix, :2286-2288; computeJacobians_Plane interleaves the rotation and
 // translation columns, :2208-2227; the Line error kernel sums e instead of omega e^2, :2407-2409), so the Jacobians here are
-// derived from the residuals and pinned by finite differences (tests/test_poseonly.py), as SURVEY.md 8(f) asks.
+// derived from the residuals and pinned by finite differences, while the residuals themselves are pinned to the reference's
+// own output (tests/test_poseonly.py, goldens ref_f4_*), as SURVEY.md 8(f) asks ("fix ... rather than copy").
 // Like the BA edges: J = -de/d(delta) for T <- Exp(delta) T, delta = (omega, upsilon); b = J^T w e; H = J^T w J; H x = b.
 #pragma once
 #include "device_math.cuh"
@@ -88,6 +89,7 @@ __global__ void __launch_bounds__(TPB, 2) k_icp_build(Dev d, IcpDev ic) {
 #pragma unroll
     for (int i = 0; i < 27; i++) a[i] = 0.0;
     const int k0 = ic.posePtr[p] + un.y * ICP_SLICE, k1 = min(ic.posePtr[p + 1], k0 + ICP_SLICE);
+#pragma unroll 2
     for (int k = k0 + threadIdx.x; k < k1; k += TPB) {
         const int set = ic.set[k];
         double Pw[3], g[3];

@@ -47,3 +47,32 @@ def read_graph(path: str) -> Graph:
     return Graph(pose_q=pose[:, :4].copy(), pose_t=pose[:, 4:].copy(), pose_fixed=pf.astype(np.uint8),
                  lm_xyz=lm, lm_fixed=lf.astype(np.uint8), mono_p=mp, mono_l=ml, mono_meas=mm,
                  mono_info=mi, stereo_p=sp, stereo_l=sl, stereo_meas=sm, stereo_info=si, camera=cam)
+
+
+ICP_MAGIC = 0x31504349
+
+
+def write_icp(prob, path: str) -> None:
+    """ICP1 file of a packed pose-only problem (synth.make_icp_problem; pose ids = indices), read by
+    samples/sample_icp.cpp and the reference driver of the row-f4 goldens:
+
+      int32  magic 'ICP1', P, nPlane, nLine
+      f64    pose[P][7]; int32 fixed[P]
+      int32  plane_pose[nPlane]; f64 plane_match[nPlane][7] (normal, originDistance, pointP); f64 plane_info[nPlane]
+      int32  line_pose[nLine];   f64 line_match[nLine][10] (a, b, length, pointP);            f64 line_info[nLine]
+    """
+    plane = [s for s in prob.sets if getattr(s, "kind", "") == "plane"]
+    line = [s for s in prob.sets if getattr(s, "kind", "") == "line"]
+    with open(path, "wb") as f:
+        P = prob.poses.shape[0]
+        np.array([ICP_MAGIC, P, plane[0].n if plane else 0, line[0].n if line else 0], np.int32).tofile(f)
+        np.ascontiguousarray(prob.poses, np.float64).tofile(f)
+        (np.arange(P) >= prob.nP_act).astype(np.int32).tofile(f)
+        for sets in (plane, line):
+            if not sets:
+                continue
+            s = sets[0]
+            om = s.omega if s.omega.shape[0] == s.n else np.full(s.n, s.omega[0])
+            np.ascontiguousarray(s.iP, np.int32).tofile(f)
+            np.ascontiguousarray(s.meas, np.float64).tofile(f)
+            np.ascontiguousarray(om, np.float64).tofile(f)
