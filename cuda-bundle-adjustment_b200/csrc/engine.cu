@@ -6,7 +6,17 @@
 #include <cub/cub.cuh>
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+// NCCL is loaded with dlopen at run time (several ranks only); a single-GPU build does not need its headers: the
+// handful of types / enumerators used below are declared here when <nccl.h> is absent (values as in nccl.h 2.x).
+#if __has_include(<nccl.h>) && !defined(CUGO_B200_NO_NCCL_HEADER)
 #include <nccl.h>
+#else
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+typedef enum { ncclSuccess = 0 } ncclResult_t;
+typedef enum { ncclUint8 = 1, ncclInt32 = 2, ncclUint64 = 5, ncclFloat64 = 8 } ncclDataType_t;
+typedef enum { ncclSum = 0 } ncclRedOp_t;
+#endif
 
 #include <algorithm>
 #include <chrono>
