@@ -80,6 +80,9 @@ def shard_problem(prob: Problem, world: int, rank: int, mode: str = "strided") -
     local_of[lm_index] = np.arange(lm_index.shape[0])
     sets = []
     for s in prob.sets:
+        kind = getattr(s, "kind", "")
+        if kind in ("plane", "line"):
+            raise ValueError("shard_problem: pose-only ICP edge sets have no landmarks to shard by; they run on one GPU")
         keep = np.flatnonzero(local_of[s.iL] >= 0)
         per_edge_w = s.omega.shape[0] == s.n and s.n > 1
         per_edge_c = s.cam.shape[0] == s.n and s.n > 1
@@ -90,7 +93,7 @@ def shard_problem(prob: Problem, world: int, rank: int, mode: str = "strided") -
             meas=np.ascontiguousarray(s.meas[keep]),
             omega=np.ascontiguousarray(s.omega[keep] if per_edge_w else s.omega[:1]),
             cam=np.ascontiguousarray(s.cam[keep] if per_edge_c else s.cam[:1]),
-            src=s.src[keep]))
+            src=s.src[keep], kind=kind))
     local = Problem(poses=prob.poses, landmarks=np.ascontiguousarray(prob.landmarks[lm_index]),
                     nP_act=prob.nP_act, nL_act=int(own_free.shape[0]), pose_ids=prob.pose_ids,
                     lm_ids=prob.lm_ids[lm_index], sets=sets)

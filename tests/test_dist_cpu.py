@@ -77,3 +77,23 @@ def test_partial_reduced_systems_sum_to_the_full_one(graphs, tmp_path):
     Hfull = np.triu(Hsum) + np.triu(Hsum, 1).T
     xp = np.linalg.solve(Hfull, red["sum"][n:n + 6 * P])
     assert np.abs(xp - o.values("x")[:6 * P]).max() < 1e-8 * np.abs(xp).max()
+
+
+def test_shards_keep_the_edge_kind_and_refuse_pose_only_sets(graphs):
+    """Row f4 on several GPUs: a depth set stays a depth set on every shard (and the shards' chi2 add up to the whole graph's
+    in the oracle); pose-only ICP sets have no landmarks to shard by and are refused."""
+    import oracle
+    from cugo_b200 import dist as cdist, synth
+    prob = synth.stereo_to_depth(graphs("small")[1])
+    total = oracle.Oracle(prob)
+    total.build_structure()
+    parts = 0.0
+    for r in range(2):
+        sh = cdist.shard_problem(prob, 2, r)
+        assert [getattr(s, "kind", "") for s in sh.prob.sets] == [getattr(s, "kind", "") for s in prob.sets]
+        o = oracle.Oracle(sh.prob)
+        o.build_structure()
+        parts += o.compute_errors()
+    assert parts == pytest.approx(total.compute_errors(), rel=1e-12)
+    with pytest.raises(ValueError):
+        cdist.shard_problem(synth.make_icp_problem(), 2, 0)
