@@ -23,7 +23,10 @@ def main():
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl")
     try:
-        prob = pack.pack(synth.make_graph(name))
+        depth = name.endswith("+depth")          # row f4: the stereo set read as a DepthEdgeSet
+        prob = pack.pack(synth.make_graph(name.split("+")[0]))
+        if depth:
+            prob = synth.stereo_to_depth(prob)
         s = cdist.DistBlockSolver(prob, dev, robust=robust, delta=delta)
         s.s.set_option("dist_factor", dist_factor)
         s.s.set_option("peer_reduce", peer_reduce)

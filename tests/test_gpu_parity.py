@@ -318,7 +318,7 @@ def test_cpp_facade_matches_binding(graphs, tmp_path, name, rk, delta):
 @pytest.mark.parametrize("name,robust,delta,dist_factor,peer_reduce",
                          [("small", "none", 1.0, 1, 1), ("kitti07", "none", 1.0, 1, 1), ("small", "huber", 2.4477, 1, 1),
                           ("loop", "none", 1.0, 2, 1), ("kitti07", "none", 1.0, 2, 1), ("kitti00", "none", 1.0, 2, 1),
-                          ("kitti07", "none", 1.0, 1, 0)])
+                          ("kitti07", "none", 1.0, 1, 0), ("small+depth", "none", 1.0, 1, 1)])
 def test_two_gpus_match_one(graphs, gpu, tmp_path, name, robust, delta, dist_factor, peer_reduce):
     """Landmarks sharded over 2 GPUs (one process each; the partial systems [Hsc | bsc] summed inside the trial graph by the
     peer-memory kernels of kernels_peer.cuh, or by ncclAllReduce with peer_reduce = 0): chi2 per iteration within 1e-9
@@ -339,7 +339,10 @@ def test_two_gpus_match_one(graphs, gpu, tmp_path, name, robust, delta, dist_fac
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr[-3000:]
     two = np.load(out)
-    g, prob = graphs(name)
+    g, prob = graphs(name.split("+")[0])
+    if name.endswith("+depth"):
+        from cugo_b200 import synth
+        prob = synth.stereo_to_depth(prob)
     s, o = gpu(prob, robust=robust, delta=delta)
     chi, lam, tr = s.optimize(8)
     np.testing.assert_array_equal(two["trials"], tr)
