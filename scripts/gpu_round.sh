@@ -21,5 +21,6 @@ scripts/micro/fp64_lat > $OUT/fp64_microbench.log 2>&1
 bash scripts/ab_lib.sh kitti00 cuda-bundle-adjustment_b200/lib/libcugo_b200_base.so - > $OUT/panel_ab.log 2>&1
 python scripts/ab_opts.py kitti00 - panel_dc=0 panel_rb=10 upd_small=0 schur_mma=1 pdl=0 > $OUT/ab_options.log 2>&1
 python scripts/gpu_profile.py venice > $OUT/venice_per_kernel.log 2>&1
+python scripts/bench_poseonly.py > $OUT/poseonly_bench.log 2>&1      # row f4: ICP scan / window, motion-only KITTI-00 shape
 # gpurun brings back at most 64 MiB: the report itself stays on the box, its CSV exports travel
 rm -f $OUT/prof.ncu-rep; gzip -f $OUT/ncu_full_raw.csv
