@@ -409,7 +409,7 @@ void Solver::uploadPoses(const double* poses7) {
     for (int i = 0; i < nP_all; i++)
         for (int k = 0; k < 7; k++) p8[(size_t)i * POSE_STRIDE + k] = poses7[(size_t)i * 7 + k];
     CK(cudaMemcpyAsync(pose0.p, p8.data(), p8.size() * sizeof(double), cudaMemcpyHostToDevice, stream));
-    CK(cudaMemcpyAsync(pose1.p, p8.data(), p8.size() * sizeof(double), cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpyAsync(pose1.p, pose0.p, p8.size() * sizeof(double), cudaMemcpyDeviceToDevice, stream));
     CK(cudaStreamSynchronize(stream));
 }
 
@@ -430,9 +430,9 @@ void Solver::setEstimates(const double* poses7, const double* lms) {
     if (!haveVertices) throw StateError("set_estimates before set_vertices");
     use();
     uploadPoses(poses7);
-    if (nL_all > 0) {
+    if (nL_all > 0) {       // one trip over PCIe; the trial buffer is filled on the device
         CK(cudaMemcpyAsync(lm0.p, lms, (size_t)nL_all * 3 * sizeof(double), cudaMemcpyHostToDevice, stream));
-        CK(cudaMemcpyAsync(lm1.p, lms, (size_t)nL_all * 3 * sizeof(double), cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(lm1.p, lm0.p, (size_t)nL_all * 3 * sizeof(double), cudaMemcpyDeviceToDevice, stream));
     }
     state.alloc(1);
     // estimates live in buffer 0 again
