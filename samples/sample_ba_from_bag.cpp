@@ -5,7 +5,8 @@
 // checksum; optionally dumps the final estimates (poses by id [P][7], landmarks by id [L][3]).
 //
 //   g++ -std=c++17 -O2 -Iinclude samples/sample_ba_from_bag.cpp -Lcuda-bundle-adjustment_b200/lib -lcugo_b200
-//   usage: sample_ba_from_bag graph.bag niter [robust(0 none,1 cauchy,2 tukey,3 huber) delta] [estimates.bin] [warmup 0|1]
+//   usage: sample_ba_from_bag graph.bag niter [robust(0 none,1 cauchy,2 tukey,3 huber) delta] [estimates.bin] [warmup 0|1] [depth 0|1]
+//   depth 1: the stereo edges (u, v, u_r) go into a DepthEdgeSet as (u, v, (u - u_r) / bf) -- include/ba_types.h:171-234
 #include <cugo_b200.hpp>
 
 #include <chrono>
@@ -46,6 +47,7 @@ static int run(int argc, char** argv) {
     const double delta = argc > 4 ? atof(argv[4]) : 1.0;
     const char* dump = argc > 5 ? argv[5] : nullptr;
     const bool warmup = argc > 6 ? atoi(argv[6]) != 0 : false;
+    const bool depth = argc > 7 ? atoi(argv[7]) != 0 : false;
 
     cugo::GraphOptimisationOptions options;
     options.perEdgeInformation = true;
@@ -56,6 +58,7 @@ static int run(int argc, char** argv) {
     auto* landmarkVertexSet = new cugo::LandmarkVertexSet(true);
     auto* monoEdgeSet = new cugo::MonoEdgeSet();
     auto* stereoEdgeSet = new cugo::StereoEdgeSet();
+    auto* depthEdgeSet = new cugo::DepthEdgeSet();
 
     for (int i = 0; i < g.P; i++) {
         const cugo::QuatD q(&g.pose[(size_t)i * 7]);
@@ -79,19 +82,24 @@ static int run(int argc, char** argv) {
         e->setCamera(camera);
         monoEdgeSet->addEdge(e);
     }
+    depthEdgeSet->setCamera(camera);
     for (int i = 0; i < g.Es; i++) {
-        auto* e = new cugo::StereoEdge();
+        auto* e = new cugo::StereoEdge();       // (DepthEdge is the same 3-row edge type)
         e->setVertex(poseVertexSet->getVertex(g.sp[i]), 0);
         e->setVertex(landmarkVertexSet->getVertex(g.sl[i]), 1);
-        e->setMeasurement(cugo::Vec3d(&g.smeas[(size_t)i * 3]));
+        cugo::Vec3d m(&g.smeas[(size_t)i * 3]);
+        if (depth) m[2] = (m[0] - m[2]) / g.cam[4];
+        e->setMeasurement(m);
         e->setInformation(g.sinfo[i]);
         e->setCamera(camera);
-        stereoEdgeSet->addEdge(e);
+        if (depth) depthEdgeSet->addEdge(e); else stereoEdgeSet->addEdge(e);
     }
     optimizer->addEdgeSet<cugo::MonoEdgeSet>(monoEdgeSet);
-    optimizer->addEdgeSet<cugo::StereoEdgeSet>(stereoEdgeSet);
+    if (depth) optimizer->addEdgeSet<cugo::DepthEdgeSet>(depthEdgeSet);
+    else optimizer->addEdgeSet<cugo::StereoEdgeSet>(stereoEdgeSet);
     monoEdgeSet->setRobustKernel((cugo::RobustKernelType)rk, delta);
     stereoEdgeSet->setRobustKernel((cugo::RobustKernelType)rk, delta);
+    depthEdgeSet->setRobustKernel((cugo::RobustKernelType)rk, delta);
 
     if (warmup) {   // as the reference's sample: a one-iteration run whose result is written back
         optimizer->initialize();
@@ -127,9 +135,10 @@ static int run(int argc, char** argv) {
     // the optimiser owns nothing: the client frees vertices, edges and sets (include/cuda_graph_optimisation.h:129-130)
     for (auto* e : monoEdgeSet->get()) delete e;
     for (auto* e : stereoEdgeSet->get()) delete e;
+    for (auto* e : depthEdgeSet->get()) delete e;
     for (auto& kv : poseVertexSet->get()) delete kv.second;
     for (auto& kv : landmarkVertexSet->get()) delete kv.second;
-    delete monoEdgeSet; delete stereoEdgeSet; delete poseVertexSet; delete landmarkVertexSet;
+    delete monoEdgeSet; delete stereoEdgeSet; delete depthEdgeSet; delete poseVertexSet; delete landmarkVertexSet;
     return 0;
 }
 

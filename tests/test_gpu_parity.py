@@ -285,7 +285,7 @@ def test_engine_matches_reference_goldens(case):
     assert rep["final_rmse"] <= EST_ATOL, rep
 
 
-@pytest.mark.parametrize("name,rk,delta", [("small", 0, 1.0), ("kitti07", 0, 1.0), ("small", 3, 2.4477)])
+@pytest.mark.parametrize("name,rk,delta", [("small", 0, 1.0), ("kitti07", 0, 1.0), ("small", 3, 2.4477), ("small+depth", 0, 1.0)])
 def test_cpp_facade_matches_binding(graphs, tmp_path, name, rk, delta):
     """The reference-style C++ API (include/cugo_b200.hpp, samples/sample_ba_from_bag.cpp: vertex / edge
     objects, initialize(), optimize()) drives the same engine: chi2 trajectory and final estimates equal
@@ -296,10 +296,15 @@ def test_cpp_facade_matches_binding(graphs, tmp_path, name, rk, delta):
     from cugo_b200 import graphio, pack, solver
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     exe = os.path.join(root, "cuda-bundle-adjustment_b200", "lib", "sample_ba_from_bag")
-    g, prob = graphs(name)
+    depth = name.endswith("+depth")           # row f4: the stereo edges through the facade's DepthEdgeSet
+    g, prob = graphs(name.split("+")[0])
+    if depth:
+        from cugo_b200 import synth
+        prob = synth.stereo_to_depth(prob)
     bag, est = str(tmp_path / "g.bag"), str(tmp_path / "est.bin")
     graphio.write_graph(g, bag)
-    r = subprocess.run([exe, bag, "6", str(rk), repr(delta), est, "1"], capture_output=True, text=True, timeout=600)
+    r = subprocess.run([exe, bag, "6", str(rk), repr(delta), est, "1", "1" if depth else "0"], capture_output=True, text=True,
+                       timeout=600)
     assert r.returncode == 0, r.stderr
     out = json.loads(r.stdout)
     s = solver.BlockSolver(0)
