@@ -22,6 +22,7 @@ typedef enum { ncclSum = 0 } ncclRedOp_t;
 #include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <stdexcept>
 #include <string>
@@ -164,8 +165,10 @@ struct IcpHostSet {
     int kind = EDGE_PLANE, n = 0, nomega = 1, rk = 0;
     double delta = 1.0;
     int cols() const { return kind == EDGE_PLANE ? 7 : 10; }
-    std::vector<int> iP;
-    std::vector<double> meas, omega;
+    // The caller's arrays go straight to the device when the set is added (no host copy: an ICP caller re-matches and
+    // re-adds its sets before every solve, so this IS its hot path -- 1.5 M matches are 100 MB).
+    std::unique_ptr<DBuf<int>> iP;
+    std::unique_ptr<DBuf<double>> meas, omega;
 };
 
 struct Solver {
@@ -937,9 +940,15 @@ int Solver::addIcpEdgeSet(int kind, int n, const int* iP, const double* meas, co
         if (iP[i] >= nP) throw ArgError("add_icp_edge_set: edge on a fixed pose is not active");
         if (kind == EDGE_LINE && !(meas[(size_t)i * 10 + 6] > 0)) throw ArgError("add_icp_edge_set: line length must be > 0");
     }
-    s.iP.assign(iP, iP + n);
-    s.meas.assign(meas, meas + (size_t)n * s.cols());
-    if (n > 0) s.omega.assign(omega, omega + nomega); else s.omega.assign(1, 1.0);
+    if (n > 0) {
+        use();
+        s.iP.reset(new DBuf<int>); s.meas.reset(new DBuf<double>); s.omega.reset(new DBuf<double>);
+        s.iP->alloc(n); s.meas->alloc((size_t)n * s.cols()); s.omega->alloc(nomega);
+        CK(cudaMemcpyAsync(s.iP->p, iP, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(s.meas->p, meas, (size_t)n * s.cols() * sizeof(double), cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(s.omega->p, omega, (size_t)nomega * sizeof(double), cudaMemcpyHostToDevice, stream));
+        CK(cudaStreamSynchronize(stream));      // the caller's arrays are free again on return
+    }
     icpSets.push_back(std::move(s));
     structDirty = true;
     return ICP_SET_BASE + (int)icpSets.size() - 1;
@@ -951,7 +960,7 @@ void Solver::refreshIcpParams() {
     }
 }
 
-// the sets' arrays go up as given, are split into the column-major payload and sorted by pose on the device
+// the sets' arrays (on the device since add_*_edge_set) are split into the column-major payload and sorted by pose
 void Solver::buildIcp() {
     const size_t nI = (size_t)nIcp;
     const int TB = 256, gI = divUp(nIcp, TB);
@@ -960,11 +969,8 @@ void Solver::buildIcp() {
     for (size_t si = 0; si < icpSets.size(); si++) {
         const IcpHostSet& s = icpSets[si];
         if (s.n == 0) continue;
-        u_meas.alloc((size_t)s.n * s.cols()); u_w.alloc(s.nomega);
-        CK(cudaMemcpyAsync(i_rIP.p + off, s.iP.data(), (size_t)s.n * sizeof(int), cudaMemcpyHostToDevice, stream));
-        CK(cudaMemcpyAsync(u_meas.p, s.meas.data(), (size_t)s.n * s.cols() * sizeof(double), cudaMemcpyHostToDevice, stream));
-        CK(cudaMemcpyAsync(u_w.p, s.omega.data(), (size_t)s.nomega * sizeof(double), cudaMemcpyHostToDevice, stream));
-        k_icp_scatter<<<divUp(s.n, TB), TB, 0, stream>>>(u_meas, u_w, s.n, s.cols(), s.nomega, nI, off, i_rpay, i_rw);
+        CK(cudaMemcpyAsync(i_rIP.p + off, s.iP->p, (size_t)s.n * sizeof(int), cudaMemcpyDeviceToDevice, stream));
+        k_icp_scatter<<<divUp(s.n, TB), TB, 0, stream>>>(s.meas->p, s.omega->p, s.n, s.cols(), s.nomega, nI, off, i_rpay, i_rw);
         CK(cudaMemsetAsync(i_rset.p + off, (int)si, s.n, stream));
         off += s.n;
     }
