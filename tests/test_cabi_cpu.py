@@ -53,9 +53,18 @@ def test_cpp_facade_sample_builds_and_refuses_without_device(tmp_path):
                           stdout=subprocess.DEVNULL)
     exe = os.path.join(ROOT, "cuda-bundle-adjustment_b200", "lib", "sample_ba_from_bag")
     assert os.path.exists(exe)
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "cuda-bundle-adjustment_b200"), "lib/sample_icp"],
+                          stdout=subprocess.DEVNULL)
+    exe_icp = os.path.join(ROOT, "cuda-bundle-adjustment_b200", "lib", "sample_icp")
+    assert os.path.exists(exe_icp)
     if torch.cuda.is_available():
         pytest.skip("a GPU is present")
     bag = str(tmp_path / "tiny.bag")
     graphio.write_graph(synth.make_graph("tiny"), bag)
     r = subprocess.run([exe, bag, "3"], capture_output=True, text=True)
+    assert r.returncode == 4 and "no CUDA device" in r.stderr
+    # the pose-only sample (PlaneEdgeSet / LineEdgeSet, pose vertex set alone) likewise
+    icp = str(tmp_path / "p.icp")
+    graphio.write_icp(synth.make_icp_problem(n_poses=3, n_planes=40, n_lines=30), icp)
+    r = subprocess.run([exe_icp, icp, "3"], capture_output=True, text=True)
     assert r.returncode == 4 and "no CUDA device" in r.stderr
