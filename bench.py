@@ -403,20 +403,24 @@ def run_ours(args, rank, world):
     s.set_estimates(h_poses, h_lms)
     s.optimize(args.iters)
     torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    sc = solver.BlockSolver(dev, f32=args.f32)
-    sc.initialize(prob, robust=args.robust, delta=args.delta)
-    t1 = time.perf_counter()
-    sc.build_structure()
-    t2 = time.perf_counter()
-    sc.optimize(args.iters)
-    sc.estimates(out=(o_poses, o_lms))
-    t3 = time.perf_counter()
-    sc.close()
-    cold = {"ms_total": (t3 - t0) * 1e3, "ms_initialize": (t1 - t0) * 1e3, "ms_build_structure": (t2 - t1) * 1e3,
-            "ms_optimize_and_readback": (t3 - t2) * 1e3,
-            "what": "new solver, host buffers: set_vertices/add_edge_set + build_structure (sorts, symbolic analysis, graph "
-                    "capture) + optimize(%d) + get_estimates, wall clock" % args.iters}
+    def cold_call():
+        t0 = time.perf_counter()
+        sc = solver.BlockSolver(dev, f32=args.f32)
+        sc.initialize(prob, robust=args.robust, delta=args.delta)
+        t1 = time.perf_counter()
+        sc.build_structure()
+        t2 = time.perf_counter()
+        sc.optimize(args.iters)
+        sc.estimates(out=(o_poses, o_lms))
+        t3 = time.perf_counter()
+        sc.close()
+        return {"ms_total": (t3 - t0) * 1e3, "ms_initialize": (t1 - t0) * 1e3, "ms_build_structure": (t2 - t1) * 1e3,
+                "ms_optimize_and_readback": (t3 - t2) * 1e3}
+    cold = cold_call()
+    cold["what"] = ("new solver, host buffers: set_vertices/add_edge_set + build_structure (sorts, symbolic analysis, graph "
+                    "capture) + optimize(%d) + get_estimates, wall clock; 'again' = the next new solver of the process (host "
+                    "heap pages and the device memory pool warm: what a caller with a new graph per keyframe sees)" % args.iters)
+    cold["again"] = cold_call()
     # ---- the drop-in claim: initialize() + optimize() through the C++ facade (include/cugo_b200.hpp) from vertex / edge
     # OBJECTS, as the reference's sample times it (samples/sample_ba_from_file/main.cpp:185-190), after its warm-up run
     facade = None
